@@ -1,0 +1,362 @@
+/*
+ * theia_b200.h - C-ABI of the B200-native forward photon tracing path.
+ *
+ * This is the drop-in boundary. The reference (tkerscher/theia)
+ * has no FFI: its boundary is a source-level plugin API in which Python components own
+ * ctypes.Structure parameter blocks (layout(scalar), no padding) and raw 64 bit device
+ * addresses, and hephaistos dispatches one compute shader per tracer. Every entry point
+ * below replaces one such dispatch / driver call; the citation names the reference
+ * interface it replaces (paths relative to the reference root, sh/ = src/theia/shader/).
+ *
+ * Conventions
+ *  - plain C, plain pointers and sizes, no torch types.
+ *  - every function returns 0 on success, <0 on error; theia_last_error() returns a
+ *    thread-local message for the last failing call.
+ *  - "dev" pointers are CUDA device pointers (torch.Tensor.data_ptr()); "host" pointers
+ *    are ordinary host memory and are only read during the call.
+ *  - the caller owns all memory. The library never allocates device memory and never
+ *    keeps a pointer beyond the call, except inside acceleration structures it wrote into
+ *    a caller supplied buffer.
+ *  - work is enqueued on the caller supplied cudaStream_t (void*), no synchronisation.
+ *  - parameter blocks are byte-identical to the reference's ctypes.Structure mirrors.
+ */
+#ifndef THEIA_B200_H
+#define THEIA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define THEIA_ABI_VERSION 1
+
+/* ------------------------------------------------------------------ result codes */
+/* sh/result.glsl:10-28, src/theia/trace.py:308-343 */
+enum {
+    THEIA_RESULT_SUCCESS = 0,
+    THEIA_RESULT_RAY_CREATED = 1,
+    THEIA_RESULT_RAY_SCATTERED = 2,
+    THEIA_RESULT_RAY_HIT = 3,
+    THEIA_RESULT_RAY_DETECTED = 4,
+    THEIA_RESULT_VOLUME_HIT = 5,
+    THEIA_RESULT_RAY_LOST = -1,
+    THEIA_RESULT_RAY_DECAYED = -2,
+    THEIA_RESULT_RAY_ABSORBED = -3,
+    THEIA_RESULT_RAY_MISSED = -4,
+    THEIA_RESULT_MAX_ITER = -5,
+    THEIA_ERROR_MAX_VALUE = -10,
+    THEIA_ERROR_UNKNOWN = -10,
+    THEIA_ERROR_MEDIA_MISMATCH = -11,
+    THEIA_ERROR_TRACE_ABORT = -12,
+    THEIA_ERROR_RAY_BAD = -13
+};
+
+/* ------------------------------------------------------------------ parameter blocks
+ * All blocks use scalar layout: 4 byte alignment, no padding (sh/preamble.glsl:20-21). */
+#pragma pack(push, 4)
+
+/* src/theia/random.py:202-254, sh/random.philox.glsl:8-11 */
+typedef struct theia_philox_params {
+    uint32_t key[2];    /* 64 bit key, little endian words */
+    uint32_t offset[4]; /* 128 bit counter offset, little endian words */
+} theia_philox_params_t;
+
+/* sh/ray.propagate.glsl:18-26 */
+typedef struct theia_propagate_params {
+    float scatterCoefficient;
+    float lowerBBoxCorner[3];
+    float upperBBoxCorner[3];
+    float maxTime;
+    float maxDist;
+} theia_propagate_params_t;
+
+/* src/theia/trace.py:589-598, sh/tracer.volume.forward.glsl:18-23 */
+typedef struct theia_volume_trace_params {
+    uint64_t medium;
+    int32_t objectId;
+    theia_propagate_params_t propagation;
+} theia_volume_trace_params_t;
+
+/* src/theia/trace.py:1136-1145, sh/tracer.scene.forward.glsl:36-41 */
+typedef struct theia_scene_trace_params {
+    int32_t targetId;
+    uint64_t sourceMedium;
+    theia_propagate_params_t propagation;
+} theia_scene_trace_params_t;
+
+/* light sources -------------------------------------------------------------- */
+/* src/theia/light.py:1133-1139, sh/lightsource.spherical.glsl:7-14 */
+typedef struct theia_light_spherical {
+    float position[3];
+    float contribFwd;
+    float contribBwd;
+    float t_min;
+    float t_max;
+} theia_light_spherical_t;
+
+/* src/theia/light.py:934-944, sh/lightsource.cone.glsl:6-20 */
+typedef struct theia_light_cone {
+    float position[3];
+    float direction[3];
+    float cosOpeningAngle;
+    float contribFwd;
+    float contribBwd;
+    float t_min;
+    float t_max;
+    float polRef[3];
+    float stokes[4];
+} theia_light_cone_t;
+
+/* src/theia/light.py:1064-1072, sh/lightsource.pencil.glsl:4-16 */
+typedef struct theia_light_pencil {
+    float position[3];
+    float direction[3];
+    float budget;
+    float t_min;
+    float t_max;
+    float stokes[4];
+    float polRef[3];
+} theia_light_pencil_t;
+
+/* src/theia/light.py:1590-1600, sh/lightsource.particles.cascade.glsl:13-38 */
+typedef struct theia_light_cascade {
+    float startPosition[3];
+    float startTime;
+    float direction[3];
+    float effectiveLength;
+    float a_angular;
+    float b_angular;
+    float a_long;
+    float b_long;
+} theia_light_cascade_t;
+
+/* src/theia/light.py:1452-1461, sh/lightsource.particles.muon.glsl:13-26 */
+typedef struct theia_light_muon {
+    float startPosition[3];
+    float startTime;
+    float endPosition[3];
+    float endTime;
+    float energyScale;
+    float a_angular;
+    float b_angular;
+} theia_light_muon_t;
+
+/* wavelength sources ---------------------------------------------------------- */
+/* src/theia/light.py:272-273, sh/wavelengthsource.const.glsl:6-8 */
+typedef struct theia_wavelength_const {
+    float lambda;
+} theia_wavelength_const_t;
+
+/* src/theia/light.py:308-312, sh/wavelengthsource.uniform.glsl:6-10 */
+typedef struct theia_wavelength_uniform {
+    float lam_min;
+    float lam_max;
+    float contrib;
+} theia_wavelength_uniform_t;
+
+/* targets / guides ------------------------------------------------------------ */
+/* src/theia/target.py:105-112 and 169-176, sh/target.sphere.glsl:8-16,
+ * sh/target.sphere.inner.glsl:8-16 (last field: hemisphereProb resp. prob) */
+typedef struct theia_target_sphere {
+    float position[3];
+    float radius;
+    float invPos[3];
+    float invRad;
+    float prob;
+} theia_target_sphere_t;
+
+/* src/theia/target.py:497-502, sh/target_guide.sphere.glsl:7-10 */
+typedef struct theia_guide_sphere {
+    float position[3];
+    float radius;
+    float prob; /* unused by the device code, kept for layout parity */
+} theia_guide_sphere_t;
+
+/* src/theia/response.py:1264-1265, sh/response.histogram.glsl:11-14 */
+typedef struct theia_histogram_params {
+    float t0;
+    float binSize;
+} theia_histogram_params_t;
+
+/* src/theia/scene.py:628-635, sh/scene.types.glsl:16-20 */
+typedef struct theia_geometry {
+    uint64_t vertices; /* dev: float[nVerts][6] position, normal */
+    uint64_t indices;  /* dev: int32[nTris][3] */
+    uint64_t material; /* dev: theia Material (24 B) or 0 */
+} theia_geometry_t;
+
+#pragma pack(pop)
+
+/* ------------------------------------------------------------------ component kinds */
+enum { THEIA_LIGHT_SPHERICAL = 1, THEIA_LIGHT_CONE = 2, THEIA_LIGHT_PENCIL = 3,
+       THEIA_LIGHT_CASCADE = 4, THEIA_LIGHT_MUON = 5 };
+/* light flags (reference: preamble macros of the light source snippets) */
+enum { THEIA_LIGHT_FLAG_POLARIZED = 1,     /* LIGHTSOURCE_POLARIZED, light.py:1009-1011 */
+       THEIA_LIGHT_FLAG_FRANK_TAMM_IS = 2  /* FRANK_TAMM_IS, light.py:1517-1519 */ };
+enum { THEIA_WAVELENGTH_CONST = 1, THEIA_WAVELENGTH_UNIFORM = 2 };
+enum { THEIA_TARGET_NONE = 0, THEIA_TARGET_SPHERE = 1, THEIA_TARGET_INNER_SPHERE = 2 };
+enum { THEIA_GUIDE_NONE = 0, THEIA_GUIDE_SPHERE = 1 };
+enum { THEIA_RESPONSE_EMPTY = 0, THEIA_RESPONSE_RECORD = 1, THEIA_RESPONSE_HISTOGRAM = 2 };
+enum { THEIA_VALUE_UNIFORM = 1 };
+enum { THEIA_CALLBACK_EMPTY = 0, THEIA_CALLBACK_STAT = 1, THEIA_CALLBACK_TRACK = 2 };
+enum { THEIA_TRACER_VOLUME_FORWARD = 1, THEIA_TRACER_SCENE_FORWARD = 2 };
+
+/* A component = kind + flags + host pointer to its byte-identical parameter block. */
+typedef struct theia_component {
+    uint32_t kind;
+    uint32_t flags;
+    const void *params;   /* host */
+    uint32_t params_size; /* bytes, checked against the kind */
+    uint32_t _pad;
+} theia_component_t;
+
+/* Hit response (sh/response.*.glsl). */
+typedef struct theia_response {
+    uint32_t kind;       /* THEIA_RESPONSE_* */
+    uint32_t value_kind; /* THEIA_VALUE_* (histogram only) */
+    /* histogram: sh/response.histogram.glsl, src/theia/response.py:1200-1421 */
+    theia_histogram_params_t hist;
+    uint32_t n_bins;
+    uint32_t hist_capacity; /* number of partial histograms hist_partials can hold */
+    float *hist_partials;   /* dev: float[hist_capacity][n_bins]; partial i is written by CTA i */
+    /* record: sh/response.record.glsl, sh/response.queue.glsl:6-33 (SoA, count first) */
+    uint32_t *queue;        /* dev: uint32 count; then field-major float/int arrays */
+    uint32_t queue_capacity;
+    uint32_t queue_polarized;
+    /* B200 extension (test seam): if non-null, the path index and the event number that
+     * produced hit k are written to tag_path[k], tag_event[k]. */
+    uint32_t *tag_path;
+    uint32_t *tag_event;
+} theia_response_t;
+
+/* Trace event callback (sh/callback.*.glsl, src/theia/trace.py:77-305). */
+typedef struct theia_callback {
+    uint32_t kind;            /* THEIA_CALLBACK_* */
+    uint32_t track_polarized; /* TRACK_POLARIZED */
+    uint64_t *stats;          /* dev: 12 x uint64 in the order of trace.py:86-100 */
+    void *track_buffer;       /* dev: layout of sh/callback.track.glsl:6-25 */
+    uint32_t track_count;     /* TRACK_COUNT */
+    uint32_t track_length;    /* TRACK_LENGTH */
+} theia_callback_t;
+
+/* One launch of a forward tracer. Replaces Tracer.run(i) -> program.dispatchIndirect
+ * (src/theia/trace.py:762-770, 1327-1336, 478-481). */
+typedef struct theia_trace_launch {
+    uint32_t struct_size; /* sizeof(theia_trace_launch_t) */
+    uint32_t tracer;      /* THEIA_TRACER_* */
+    /* variant key = the reference's preamble macros (trace.py:666-673, 1225-1235) */
+    uint32_t polarized;               /* POLARIZATION */
+    uint32_t disable_mis;             /* DISABLE_MIS */
+    uint32_t disable_direct_lighting; /* DISABLE_DIRECT_LIGHTING */
+    uint32_t disable_transmission;    /* DISABLE_TRANSMISSION (scene) */
+    uint32_t disable_volume_border;   /* DISABLE_VOLUME_BORDER (scene) */
+    uint32_t hit_use_transmitted_dir; /* HIT_USE_TRANSMITTED_DIR (scene) */
+    uint32_t path_length;             /* PATH_LENGTH */
+    uint32_t block_size;              /* BLOCK_SIZE; only used to size partial histograms */
+    /* DispatchParams (trace.py:354-360) */
+    uint32_t batch_size;
+    /* B200 extension: global index of the first path of this launch. Path k of the launch
+     * uses RNG stream first_path + k, so one batch can be split over several GPUs. */
+    uint32_t first_path;
+    /* TraceParams: theia_volume_trace_params_t or theia_scene_trace_params_t (host) */
+    const void *trace_params;
+    uint32_t trace_params_size;
+    uint32_t _pad0;
+    theia_philox_params_t rng;
+    theia_component_t light;
+    theia_component_t wavelength;
+    theia_component_t target; /* volume tracer */
+    theia_component_t guide;  /* scene tracer, THEIA_GUIDE_NONE = no MIS */
+    theia_response_t response;
+    theia_callback_t callback;
+    const void *tlas; /* dev: acceleration structure written by theia_tlas_build (scene) */
+    void *stream;     /* cudaStream_t */
+} theia_trace_launch_t;
+
+/* ------------------------------------------------------------------ library */
+const char *theia_last_error(void);
+int theia_abi_version(void);
+/* Number of SMs etc. of the current device; used by the host to size buffers. */
+int theia_device_info(int *sm_count, int *cc_major, int *cc_minor);
+
+/* ------------------------------------------------------------------ RNG
+ * Replaces the RNGBufferSink dispatch (src/theia/random.py:44-199, sh/random.sink.glsl):
+ * out[s * samples + c] = random_s(baseStream + s, baseCount + c) for dim == 1,
+ * out[2*(s*samples+c) + {0,1}] = random2D_s(...) for dim == 2. */
+int theia_philox_fill(const theia_philox_params_t *params, uint32_t baseStream,
+                      uint32_t baseCount, uint32_t streams, uint32_t samples, uint32_t dim,
+                      float *out_dev, void *stream);
+/* Raw Philox4x32-10 block function (known-answer tests): out[4*i..] = philox(ctr[i], key[i]). */
+int theia_philox_raw(const uint32_t *ctr_dev, const uint32_t *key_dev, uint32_t n,
+                     uint32_t *out_dev, void *stream);
+
+/* ------------------------------------------------------------------ acceleration structures
+ * Replace hp.GeometryStore (BLAS build, src/theia/scene.py:550) and
+ * hp.AccelerationStructure (TLAS build, src/theia/scene.py:668). Vulkan style two step
+ * build: query sizes, caller allocates, library writes the structure into the buffer. */
+typedef struct theia_as_sizes {
+    uint64_t result_bytes;  /* buffer that will hold the finished structure */
+    uint64_t scratch_bytes; /* temporary build memory */
+} theia_as_sizes_t;
+
+int theia_blas_sizes(uint32_t n_triangles, theia_as_sizes_t *sizes);
+/* vertices_dev: float[nVerts][6], indices_dev: uint32[nTris][3] (scene.py:434-440).
+ * Both must stay valid while the BLAS is in use (hits fetch vertices from them). */
+int theia_blas_build(const float *vertices_dev, uint32_t n_vertices,
+                     const uint32_t *indices_dev, uint32_t n_triangles, void *result_dev,
+                     uint64_t result_bytes, void *scratch_dev, uint64_t scratch_bytes,
+                     void *stream);
+
+/* One TLAS instance (hp.GeometryInstance + Scene.GLSLGeometry, scene.py:595-604, 652-666). */
+typedef struct theia_instance_desc {
+    float obj_to_world[12]; /* 3x4 row major */
+    float world_to_obj[12]; /* 3x4 row major, inverse of the above */
+    const void *blas;       /* dev: result buffer of theia_blas_build */
+    theia_geometry_t geometry;
+    int32_t custom_index;   /* detectorId */
+    uint32_t _pad;
+} theia_instance_desc_t;
+
+int theia_tlas_sizes(uint32_t n_instances, theia_as_sizes_t *sizes);
+/* instances: HOST array. Instance order = instance id (scene.py:652-668). */
+int theia_tlas_build(const theia_instance_desc_t *instances, uint32_t n_instances,
+                     void *result_dev, uint64_t result_bytes, void *scratch_dev,
+                     uint64_t scratch_bytes, void *stream);
+
+/* Test seam for the ray query: closest hit of n rays against a TLAS.
+ * rays_dev: float[n][8] = origin xyz, tmax, direction xyz, unused.
+ * out_dev: int32[n][4] = instance id (-1 = miss), primitive id, custom index, 0;
+ * out_bary_dev: float[n][4] = t, u, v, 0. Also reports traversal statistics if
+ * stats_dev != NULL: uint64[4] = nodes visited, triangles tested, instances entered, rays. */
+int theia_tlas_query(const void *tlas_dev, const float *rays_dev, uint32_t n, int32_t *out_dev,
+                     float *out_bary_dev, uint64_t *stats_dev, void *stream);
+
+/* ------------------------------------------------------------------ tracers */
+/* Number of CTAs the launch will use = number of partial histograms it writes. */
+int theia_trace_grid_size(const theia_trace_launch_t *launch, uint32_t *n_blocks);
+/* Runs VolumeForwardTracer / SceneForwardTracer for one batch. */
+int theia_trace_forward(const theia_trace_launch_t *launch);
+
+/* ------------------------------------------------------------------ responses */
+/* Replaces the HistogramReducer dispatch (sh/estimator.reduce.glsl:17-35,
+ * src/theia/response.py:1188-1197): out[b] = norm * kahan_sum_h partial[h][b]; the partials
+ * are cleared afterwards when clear != 0 (hp.clearTensor(histIn)). */
+int theia_hist_reduce(float *partials_dev, uint32_t n_hist, uint32_t n_bins, float norm,
+                      float *out_dev, int clear, void *stream);
+/* Replaces the HitReplay dispatch (sh/response.replay.glsl:35-50): feeds the hits of a
+ * queue (same SoA layout as theia_response_t.queue) to a response. */
+int theia_hit_replay(const uint32_t *queue_dev, uint32_t capacity, uint32_t polarized,
+                     const theia_response_t *response, uint32_t block_size, void *stream);
+
+/* ------------------------------------------------------------------ device math test seam
+ * Evaluates the library's deterministic float math on the device (fn: 0 sin, 1 cos, 2 exp,
+ * 3 log, 4 pow(x,y)). Used by the parity tests only. */
+int theia_math_eval(uint32_t fn, const float *x_dev, const float *y_dev, uint32_t n,
+                    float *out_dev, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* THEIA_B200_H */

@@ -1,0 +1,152 @@
+"""
+ORACLE - TEST INFRASTRUCTURE ONLY.
+
+ctypes binding of the CPU oracle (oracle/oracle.cpp). Only ``tests/``,
+``__graft_entry__.smoke()`` and the CPU baseline / reference arm of ``bench.py`` may import
+this package; the product (``theia_b200``) never does.
+
+The oracle consumes the same C-ABI launch description as the CUDA library
+(include/theia_b200.h) with host pointers in place of device pointers. The parity harness
+therefore builds every object twice: once on the "cuda" device for the product and once
+under ``theia_b200._device.useDevice("cpu")`` for the oracle.
+"""
+
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from ctypes import POINTER, byref, c_float, c_int, c_int32, c_uint32, c_uint64, c_void_p
+
+import numpy as np
+
+from theia_b200 import _abi
+
+_DIR = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_DIR, "_build", "liboracle.so")
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    """Compiles the oracle with the Makefile next to this file."""
+    if force or not os.path.exists(_SO):
+        subprocess.run(["make", "-C", _DIR] + (["-B"] if force else []), check=True, capture_output=True)
+    return _SO
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        build()
+        l = ctypes.CDLL(_SO)
+        l.orc_scene_create.restype = c_void_p
+        l.orc_scene_create.argtypes = [POINTER(_abi.InstanceDesc), c_uint32, c_void_p, c_void_p, c_int]
+        l.orc_scene_destroy.argtypes = [c_void_p]
+        l.orc_trace_forward.argtypes = [POINTER(_abi.TraceLaunch), c_int, c_void_p]
+        l.orc_philox_fill.argtypes = [POINTER(_abi.PhiloxParams), c_uint32, c_uint32, c_uint32, c_uint32, c_uint32,
+                                      c_void_p]
+        l.orc_philox_raw.argtypes = [c_void_p, c_void_p, c_uint32, c_void_p]
+        l.orc_math_eval.argtypes = [c_uint32, c_void_p, c_void_p, c_uint32, c_void_p]
+        l.orc_tlas_query.argtypes = [c_void_p, c_void_p, c_uint32, c_void_p, c_void_p, c_void_p]
+        l.orc_hist_reduce.argtypes = [c_void_p, c_uint32, c_uint32, c_float, c_void_p, c_int]
+        l.orc_hit_replay.argtypes = [c_void_p, c_uint32, c_uint32, POINTER(_abi.Response), c_uint32]
+        _lib = l
+    return _lib
+
+
+def _ptr(a: np.ndarray) -> int:
+    return a.ctypes.data
+
+
+def philoxParams(key: int, offset: int) -> _abi.PhiloxParams:
+    p = _abi.PhiloxParams()
+    p.key[0], p.key[1] = key & 0xFFFFFFFF, (key >> 32) & 0xFFFFFFFF
+    for k in range(4):
+        p.offset[k] = (offset >> (32 * k)) & 0xFFFFFFFF
+    return p
+
+
+def philoxFill(key: int, offset: int, streams: int, samples: int, *, baseStream: int = 0, baseCount: int = 0,
+               dim: int = 1) -> np.ndarray:
+    out = np.zeros(streams * samples * dim, dtype=np.float32)
+    p = philoxParams(key, offset)
+    lib().orc_philox_fill(byref(p), baseStream, baseCount, streams, samples, dim, _ptr(out))
+    return out.reshape(streams, samples, dim) if dim > 1 else out.reshape(streams, samples)
+
+
+def philoxRaw(ctr: np.ndarray, key: np.ndarray) -> np.ndarray:
+    ctr = np.ascontiguousarray(ctr, dtype=np.uint32).reshape(-1, 4)
+    key = np.ascontiguousarray(key, dtype=np.uint32).reshape(-1, 2)
+    out = np.zeros_like(ctr)
+    lib().orc_philox_raw(_ptr(ctr), _ptr(key), len(ctr), _ptr(out))
+    return out
+
+
+MATH_FN = {"sin": 0, "cos": 1, "exp": 2, "log": 3, "pow": 4}
+
+
+def mathEval(fn: str, x: np.ndarray, y: np.ndarray | None = None) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    y = np.zeros_like(x) if y is None else np.ascontiguousarray(y, dtype=np.float32)
+    out = np.zeros_like(x)
+    lib().orc_math_eval(MATH_FN[fn], _ptr(x), _ptr(y), x.size, _ptr(out))
+    return out
+
+
+class OracleScene:
+    """Oracle side acceleration structure of a ``theia_b200.scene.Scene`` built on the cpu device."""
+
+    def __init__(self, scene, *, bruteForce: bool = False) -> None:
+        if scene._device != "cpu":
+            raise ValueError("the oracle needs a scene built under useDevice('cpu')")
+        self._scene = scene  # keeps host geometry alive
+        n = len(scene.instances)
+        self.handle = lib().orc_scene_create(scene._descs, n, _ptr(scene._vertexCounts), _ptr(scene._triangleCounts),
+                                             int(bruteForce))
+
+    def query(self, rays: np.ndarray, *, stats: bool = False):
+        """rays: float32[n, 8] = origin, tmax, direction, unused -> (ids int32[n,4], tuv float32[n,4])"""
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        n = len(rays)
+        ids = np.zeros((n, 4), dtype=np.int32)
+        tuv = np.zeros((n, 4), dtype=np.float32)
+        st = np.zeros(4, dtype=np.uint64)
+        lib().orc_tlas_query(self.handle, _ptr(rays), n, _ptr(ids), _ptr(tuv), _ptr(st) if stats else None)
+        return (ids, tuv, st) if stats else (ids, tuv)
+
+    def __del__(self) -> None:
+        try:
+            lib().orc_scene_destroy(self.handle)
+        except Exception:
+            pass
+
+
+def trace(tracer, i: int = 0, *, scene: OracleScene | None = None, threads: int = 0, update: bool = True):
+    """
+    Runs one batch of ``tracer`` (built on the cpu device) on the oracle, writing into the
+    tracer's own (host) response / callback buffers.
+    Returns counters: uint64[6] = segments, responses, nodes, triangles, instances, rays.
+    """
+    if tracer._device != "cpu":
+        raise ValueError("the oracle needs a tracer built under useDevice('cpu')")
+    if update:
+        for _, stage in tracer.collectStages():
+            stage.update(i)
+    L, keep = tracer._launch(i)
+    if L.tracer == _abi.TRACER_SCENE_FORWARD:
+        if scene is None:
+            scene = OracleScene(tracer.scene)
+        L.tlas = scene.handle
+    counters = np.zeros(6, dtype=np.uint64)
+    rc = lib().orc_trace_forward(byref(L), threads, _ptr(counters))
+    if rc != 0:
+        raise RuntimeError(f"oracle error {rc}")
+    return counters
+
+
+def histReduce(partials: np.ndarray, norm: float, *, clear: bool = False) -> np.ndarray:
+    partials = np.ascontiguousarray(partials, dtype=np.float32)
+    nHist, nBins = partials.shape
+    out = np.zeros(nBins, dtype=np.float32)
+    lib().orc_hist_reduce(_ptr(partials), nHist, nBins, norm, _ptr(out), int(clear))
+    return out

@@ -1,0 +1,114 @@
+"""ctypes mirrors of the C-ABI structures and enums of include/theia_b200.h."""
+
+from __future__ import annotations
+
+from ctypes import POINTER, Structure, c_float, c_int32, c_uint32, c_uint64, c_void_p
+
+ABI_VERSION = 1
+
+# component kinds
+LIGHT_SPHERICAL, LIGHT_CONE, LIGHT_PENCIL, LIGHT_CASCADE, LIGHT_MUON = 1, 2, 3, 4, 5
+LIGHT_FLAG_POLARIZED, LIGHT_FLAG_FRANK_TAMM_IS = 1, 2
+WAVELENGTH_CONST, WAVELENGTH_UNIFORM = 1, 2
+TARGET_NONE, TARGET_SPHERE, TARGET_INNER_SPHERE = 0, 1, 2
+GUIDE_NONE, GUIDE_SPHERE = 0, 1
+RESPONSE_EMPTY, RESPONSE_RECORD, RESPONSE_HISTOGRAM = 0, 1, 2
+VALUE_UNIFORM = 1
+CALLBACK_EMPTY, CALLBACK_STAT, CALLBACK_TRACK = 0, 1, 2
+TRACER_VOLUME_FORWARD, TRACER_SCENE_FORWARD = 1, 2
+
+
+class PhiloxParams(Structure):
+    _pack_ = 4
+    _fields_ = [("key", c_uint32 * 2), ("offset", c_uint32 * 4)]
+
+
+class HistogramParams(Structure):
+    _pack_ = 4
+    _fields_ = [("t0", c_float), ("binSize", c_float)]
+
+
+class Geometry(Structure):
+    _pack_ = 4
+    _fields_ = [("vertices", c_uint64), ("indices", c_uint64), ("material", c_uint64)]
+
+
+class Component(Structure):
+    _fields_ = [
+        ("kind", c_uint32),
+        ("flags", c_uint32),
+        ("params", c_void_p),
+        ("params_size", c_uint32),
+        ("_pad", c_uint32),
+    ]
+
+
+class Response(Structure):
+    _fields_ = [
+        ("kind", c_uint32),
+        ("value_kind", c_uint32),
+        ("hist", HistogramParams),
+        ("n_bins", c_uint32),
+        ("hist_capacity", c_uint32),
+        ("hist_partials", c_void_p),
+        ("queue", c_void_p),
+        ("queue_capacity", c_uint32),
+        ("queue_polarized", c_uint32),
+        ("tag_path", c_void_p),
+        ("tag_event", c_void_p),
+    ]
+
+
+class Callback(Structure):
+    _fields_ = [
+        ("kind", c_uint32),
+        ("track_polarized", c_uint32),
+        ("stats", c_void_p),
+        ("track_buffer", c_void_p),
+        ("track_count", c_uint32),
+        ("track_length", c_uint32),
+    ]
+
+
+class TraceLaunch(Structure):
+    _fields_ = [
+        ("struct_size", c_uint32),
+        ("tracer", c_uint32),
+        ("polarized", c_uint32),
+        ("disable_mis", c_uint32),
+        ("disable_direct_lighting", c_uint32),
+        ("disable_transmission", c_uint32),
+        ("disable_volume_border", c_uint32),
+        ("hit_use_transmitted_dir", c_uint32),
+        ("path_length", c_uint32),
+        ("block_size", c_uint32),
+        ("batch_size", c_uint32),
+        ("first_path", c_uint32),
+        ("trace_params", c_void_p),
+        ("trace_params_size", c_uint32),
+        ("_pad0", c_uint32),
+        ("rng", PhiloxParams),
+        ("light", Component),
+        ("wavelength", Component),
+        ("target", Component),
+        ("guide", Component),
+        ("response", Response),
+        ("callback", Callback),
+        ("tlas", c_void_p),
+        ("stream", c_void_p),
+    ]
+
+
+class ASSizes(Structure):
+    _fields_ = [("result_bytes", c_uint64), ("scratch_bytes", c_uint64)]
+
+
+class InstanceDesc(Structure):
+    _fields_ = [
+        ("obj_to_world", c_float * 12),
+        ("world_to_obj", c_float * 12),
+        ("blas", c_void_p),
+        ("geometry", Geometry),
+        ("custom_index", c_int32),
+        ("_pad", c_uint32),
+    ]
