@@ -273,6 +273,10 @@ typedef struct theia_trace_launch {
     theia_callback_t callback;
     const void *tlas; /* dev: acceleration structure written by theia_tlas_build (scene) */
     void *stream;     /* cudaStream_t */
+    /* B200 extension (measurement): if non-null, uint64[4] on the device that the launch adds
+     * to: path segments (trace() executions, the reference's EventStatisticCallback sum),
+     * responses (hits), shadow rays, paths started. */
+    uint64_t *work_counters;
 } theia_trace_launch_t;
 
 /* ------------------------------------------------------------------ library */

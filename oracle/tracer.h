@@ -22,6 +22,7 @@ struct Sink {
     uint64_t nResponse = 0;
     uint64_t nSegments = 0;  // trace() executions
     uint32_t curEvent = 0;
+    uint32_t seq = 0;  // running number of the path's hits inside the current event (test tags)
 
     explicit Sink(const theia_trace_launch_t* l) : L(l) {
         if (l->response.kind == THEIA_RESPONSE_HISTOGRAM) hist.assign(l->response.n_bins, 0.0f);
@@ -38,12 +39,14 @@ struct Sink {
             uint32_t bin = (uint32_t)ib;
             if (bin < r.n_bins) hist[bin] += value;
         } else if (r.kind == THEIA_RESPONSE_RECORD) {
-            hits.push_back(TaggedHit{item, idx, curEvent});
+            hits.push_back(TaggedHit{item, idx, curEvent | (seq << 16)});
+            seq++;
         }
     }
     // sh/callback.stat.glsl:21-62, sh/callback.track.glsl:28-98
     void onEvent(const Ray& ray, int code, uint32_t idx, uint32_t i, bool polarized) {
         curEvent = i;
+        seq = 0;
         if (i >= 1 && code != THEIA_RESULT_MAX_ITER) nSegments++;
         const theia_callback_t& cb = L->callback;
         if (cb.kind == THEIA_CALLBACK_STAT) {

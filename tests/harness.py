@@ -1,0 +1,259 @@
+"""
+Shared scenario builders and the parity harness of the test-suite.
+
+Every scenario is built twice from the same Python description: once on the "cuda" device
+(the product: CUDA kernels behind the C-ABI) and once under ``useDevice("cpu")`` for the CPU
+oracle (``oracle/``), which consumes the same launch description over host memory. The
+scenarios are the configurations of BASELINE.json / SURVEY.md section 8d at test sizes.
+"""
+
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import theia_b200.units as u  # noqa: E402
+from theia_b200 import _device, light, material, random, response, scene, target, trace  # noqa: E402
+from theia_b200.testing import WaterTestModel  # noqa: E402
+
+ASSETS = os.path.join(ROOT, "assets")
+
+
+class HomogenousModel(material.DispersionFreeMedium, material.HenyeyGreensteinPhaseFunction, material.MediumModel):
+    """examples/01_volume_tracing.ipynb cell 5 of the reference"""
+
+    ModelName = "homogenous"
+
+    def __init__(self, *, n=1.33, ng=1.33, mu_a=0.05, mu_s=0.02, g=0.2) -> None:
+        material.DispersionFreeMedium.__init__(self, n=n, ng=ng, mu_a=mu_a, mu_s=mu_s)
+        material.HenyeyGreensteinPhaseFunction.__init__(self, g)
+
+
+def makeResponse(kind: str, *, polarized: bool = False, nBins: int = 100, binSize: float = 5.0, t0: float = 0.0):
+    if kind == "record":
+        r = response.HitRecorder(polarized=polarized)
+        r.enableTags()
+        return r
+    if kind == "hist":
+        return response.HistogramHitResponse(response.UniformValueResponse(), nBins=nBins, binSize=binSize, t0=t0)
+    if kind == "empty":
+        return response.EmptyResponse()
+    raise ValueError(kind)
+
+
+def makeCallback(kind: str | None, capacity: int, length: int, polarized: bool = False):
+    if kind == "stat":
+        return trace.EventStatisticCallback()
+    if kind == "track":
+        return trace.TrackRecordCallback(capacity, length, polarized=polarized)
+    return None
+
+
+def makeLight(kind: str, *, polarized: bool = False, position=(1.0, 0.0, 0.0), direction=(-1.0, 0.0, 0.0)):
+    if kind == "spherical":
+        return light.SphericalLightSource(position=position, timeRange=(0.0, 10.0), budget=1e5)
+    if kind == "cone":
+        return light.ConeLightSource(position=position, direction=direction, timeRange=(0.0, 10.0), cosOpeningAngle=0.8,
+                                     budget=1e5, polarizationReference=(0.0, 1.0, 0.0), stokes=(1.0, 0.9, 0.1, -0.3),
+                                     polarized=polarized)
+    if kind == "pencil":
+        return light.PencilLightSource(position=position, direction=direction, timeRange=(0.0, 1.0), budget=1e3,
+                                       stokes=(1.0, 1.0, 0.0, 0.0), polarizationRef=(0.0, 1.0, 0.0))
+    if kind == "cascade":
+        return light.ParticleCascadeLightSource(position, 2.0, direction, effectiveLength=5300.0, a_angular=0.54,
+                                                b_angular=3.3, a_long=4.6, b_long=0.58)
+    if kind == "muon":
+        end = tuple(position[k] + 30.0 * direction[k] for k in range(3))
+        return light.MuonTrackLightSource(position, 1.0, end, 1.0 + 30.0 / 0.299792458, muonEnergy=1e3)
+    raise ValueError(kind)
+
+
+def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None, mis: bool = True, direct: bool = True,
+                   polarized: bool = False, lightKind: str = "spherical", targetKind: str = "sphere",
+                   wavelength: str = "const", water: bool = False, nScattering: int = 10, key: int = 42,
+                   scatterCoefficient: float = 0.05, nBins: int = 100, binSize: float = 5.0, maxTime: float = 1000.0):
+    """Config C1 (examples/01 of the reference) and its flag variations (tests/test_trace.py:90-212)."""
+    model = WaterTestModel() if water else HomogenousModel()
+    med = model.createMedium()
+    store = material.MaterialStore([], media=[med])
+    if targetKind == "sphere":
+        tgt = target.SphereTarget(position=(-1.0, 0.0, 0.0), radius=0.5)
+        src = makeLight(lightKind, polarized=polarized)
+    else:
+        tgt = target.InnerSphereTarget(position=(0.0, 0.0, 0.0), radius=8.0)
+        src = makeLight(lightKind, polarized=polarized, position=(0.5, 0.2, -0.1), direction=(0.0, 0.6, 0.8))
+    wl = light.ConstWavelengthSource(500.0) if wavelength == "const" else light.UniformWavelengthSource(
+        lambdaRange=(400.0, 700.0))
+    r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize)
+    rng = random.PhiloxRNG(key=key)
+    cb = makeCallback(callback, N, nScattering + 2, polarized)
+    tr = trace.VolumeForwardTracer(N, src, tgt, wl, r, rng, medium=store.media[med.name], nScattering=nScattering,
+                                   scatterCoefficient=scatterCoefficient, callback=cb, polarized=polarized,
+                                   disableDirectLighting=not direct, disableTargetSampling=not mis, maxTime=maxTime)
+    rng.autoAdvance = tr.nRNGSamples
+    return {"tracer": tr, "response": r, "callback": cb, "rng": rng, "store": store}
+
+
+def _sceneCommon(N, instances, store, medium, src, wl, resp, callback, polarized, maxPathLength, targetId, guide, key,
+                 nBins, binSize, **kw):
+    sc = scene.Scene(instances, store, medium=medium)
+    r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize)
+    rng = random.PhiloxRNG(key=key)
+    cb = makeCallback(callback, N, maxPathLength + 1, polarized)
+    tr = trace.SceneForwardTracer(N, src, wl, r, rng, sc, maxPathLength=maxPathLength, targetId=targetId,
+                                  targetGuide=guide, callback=cb, polarized=polarized, **kw)
+    rng.autoAdvance = tr.nRNGSamples
+    return {"tracer": tr, "response": r, "callback": cb, "rng": rng, "store": store, "scene": sc}
+
+
+def sceneC2(N: int, *, resp: str = "record", callback: str | None = None, polarized: bool = True,
+            lightKind: str = "pencil", key: int = 0xC0FFEE, nBins: int = 100, binSize: float = 2.0, **kw):
+    """Config C2: pencil / cone beam into a glass sphere and a detector cube, polarized."""
+    water = WaterTestModel().createMedium()
+    glass = material.BK7Model().createMedium()
+    mats = [material.Material("glassSphere", glass, water, flags="TR"),
+            material.Material("detector", None, water, flags="BD")]
+    store = material.MaterialStore(mats, media=[water, glass])
+    meshes = scene.MeshStore({"sphere": os.path.join(ASSETS, "sphere.stl"), "cube": os.path.join(ASSETS, "cube.ply")})
+    inst = [
+        meshes.createInstance("sphere", "glassSphere", scene.Transform.TRS(scale=0.8, translate=(3.0, 0.0, 0.0))),
+        meshes.createInstance("cube", "detector", scene.Transform.TRS(scale=0.5, translate=(6.0, 0.0, 0.0)),
+                              detectorId=1),
+    ]
+    if lightKind == "pencil":
+        src = light.PencilLightSource(position=(0.0, 0.05, 0.02), direction=(1.0, 0.0, 0.0), timeRange=(0.0, 1.0),
+                                      stokes=(1.0, 1.0, 0.0, 0.0), polarizationRef=(0.0, 1.0, 0.0), budget=1e3)
+    else:
+        src = light.ConeLightSource(position=(0.0, 0.0, 0.0), direction=(1.0, 0.0, 0.0), cosOpeningAngle=0.95,
+                                    timeRange=(0.0, 1.0), budget=1e3, polarized=polarized,
+                                    stokes=(1.0, 0.8, 0.2, 0.1))
+    wl = light.UniformWavelengthSource(lambdaRange=(400.0, 700.0))
+    return _sceneCommon(N, inst, store, store.media["water"], src, wl, resp, callback, polarized, 10, 1, None, key,
+                        nBins, binSize, **kw)
+
+
+def sceneC3(N: int, *, resp: str = "record", callback: str | None = None, polarized: bool = False, guide: bool = True,
+            key: int = 0xC01DC0FFEE, nBins: int = 200, binSize: float = 1.0, **kw):
+    """Config C3: suzanne detector inside a glass torus, scattering medium, target guide."""
+    med = HomogenousModel(mu_a=0.05, mu_s=0.05, g=0.9).createMedium()
+    glass = material.BK7Model().createMedium()
+    mats = [material.Material("det", None, med, flags="BD"), material.Material("glass", glass, med, flags="TR")]
+    store = material.MaterialStore(mats, media=[med, glass])
+    meshes = scene.MeshStore({"suzanne": os.path.join(ASSETS, "suzanne.stl"),
+                              "torus": os.path.join(ASSETS, "torus.stl")})
+    inst = [
+        meshes.createInstance("suzanne", "det", scene.Transform.TRS(scale=1.0), detectorId=1),
+        meshes.createInstance("torus", "glass", scene.Transform.TRS(scale=2.0, rotate=(1.0, 0.0, 0.0, 90.0))),
+    ]
+    src = light.SphericalLightSource(position=(0.0, -6.0, 0.0), timeRange=(0.0, 5.0), budget=1e5)
+    wl = light.ConstWavelengthSource(450.0)
+    g = target.SphereTargetGuide(position=(0.0, 0.0, 0.0), radius=1.5) if guide else None
+    return _sceneCommon(N, inst, store, store.media[med.name], src, wl, resp, callback, polarized, 10, 1, g, key,
+                        nBins, binSize, **kw)
+
+
+def sceneC5(N: int, *, resp: str = "hist", callback: str | None = None, polarized: bool = False,
+            lattice=(10, 10, 50), pitch=(60.0, 60.0, 10.0), lightKind: str = "cascade", key: int = 0x5EED,
+            nBins: int = 500, binSize: float = 10.0, maxPathLength: int = 10, **kw):
+    """Config C5: lattice of spherical optical modules (one shared BLAS) in sea water."""
+    water = WaterTestModel().createMedium()
+    glass = material.BK7Model().createMedium()
+    mats = [material.Material("module", glass, water, flags=("DB", "B"))]
+    store = material.MaterialStore(mats, media=[water, glass])
+    meshes = scene.MeshStore({"sphere": os.path.join(ASSETS, "sphere.stl")})
+    nx, ny, nz = lattice
+    inst = []
+    i = 0
+    for ix in range(nx):
+        for iy in range(ny):
+            for iz in range(nz):
+                pos = ((ix - 0.5 * (nx - 1)) * pitch[0], (iy - 0.5 * (ny - 1)) * pitch[1],
+                       (iz - 0.5 * (nz - 1)) * pitch[2])
+                inst.append(meshes.createInstance("sphere", "module",
+                                                  scene.Transform.TRS(scale=0.2159, translate=pos), detectorId=i))
+                i += 1
+    if lightKind == "cascade":
+        src = light.ParticleCascadeLightSource((3.0, 2.0, 1.0), 0.0, (0.0, 0.0, 1.0), effectiveLength=5300.0,
+                                               a_angular=0.54, b_angular=3.3, a_long=4.6, b_long=0.58)
+    else:
+        src = makeLight(lightKind, position=(3.0, 2.0, -100.0), direction=(0.0, 0.0, 1.0))
+    wl = light.UniformWavelengthSource(lambdaRange=(300.0, 600.0))
+    return _sceneCommon(N, inst, store, store.media["water"], src, wl, resp, callback, polarized, maxPathLength, -1,
+                        None, key, nBins, binSize, **kw)
+
+
+# ---------------------------------------------------------------------------------------------
+def runGpu(cfg, i: int = 0, *, sync: bool = True):
+    """Updates and runs all stages of the tracer once on the GPU (like pl.runPipeline)."""
+    import torch
+    from theia_b200 import pipeline as pl
+    pl.runPipeline(cfg["tracer"].collectStages(), i)
+    if sync:
+        torch.cuda.synchronize()
+
+
+def runOracle(cfg, i: int = 0, *, threads: int = 0, oracleScene=None):
+    """Runs the same batch on the CPU oracle; results land in the response's host buffers."""
+    import oracle
+    tr = cfg["tracer"]
+    counters = oracle.trace(tr, i, scene=oracleScene, threads=threads)
+    r = cfg["response"]
+    if isinstance(r, response.HistogramHitResponse):
+        red = r._reducer
+        p = red._block("Params", i)
+        parts = red.histIn.numpy().reshape(-1, r.nBins)
+        out = oracle.histReduce(parts, p.normalization, clear=True)
+        red.histIn.zero_()
+        red._buffer[i].numpy()[:] = out
+    else:
+        for _, stage in tr.collectStages():
+            if stage is tr:
+                continue
+            for cmd in stage.run(i):
+                cmd()
+    return counters
+
+
+FIELDS = ["position", "direction", "normal", "wavelength", "time", "contrib", "objectId"]
+POL_FIELDS = ["stokes", "polarizationRef"]
+
+
+def sortedHits(cfg, i: int = 0):
+    """Hits of the last batch sorted by (path, event tag): dict of arrays."""
+    r = cfg["response"]
+    v = r.queue.view(i)
+    n = min(v.count, r.capacity)
+    path, tag = r.tags()
+    path, tag = path[:n].astype(np.int64), tag[:n].astype(np.int64)
+    order = np.lexsort((tag, path))
+    out = {"path": path[order], "tag": tag[order], "count": v.count}
+    names = FIELDS + (POL_FIELDS if r.polarized else [])
+    for f in names:
+        out[f] = np.array(v[f][:n])[order]
+    return out
+
+
+def compareHits(a, b, *, rtol: float = 0.0, atol: float = 0.0):
+    """Returns (n_common_paths_mismatching, max relative error) between two sortedHits dicts."""
+    assert a["count"] == b["count"], f"hit counts differ: {a['count']} vs {b['count']}"
+    assert np.array_equal(a["path"], b["path"]) and np.array_equal(a["tag"], b["tag"]), "hit (path, event) tags differ"
+    assert np.array_equal(a["objectId"], b["objectId"])
+    worst = 0.0
+    for f in a:
+        if f in ("path", "tag", "count", "objectId"):
+            continue
+        x, y = a[f].astype(np.float64), b[f].astype(np.float64)
+        if rtol == 0.0 and atol == 0.0:
+            same = (x == y) | (np.isnan(x) & np.isnan(y))
+            assert same.all(), f"field {f}: {np.count_nonzero(~same)} of {same.size} values differ bitwise"
+        else:
+            err = np.abs(x - y) / (atol + rtol * np.maximum(np.abs(x), np.abs(y)))
+            worst = max(worst, float(err.max(initial=0.0)))
+            assert (err <= 1.0).all(), f"field {f}: max error ratio {err.max()}"
+    return worst

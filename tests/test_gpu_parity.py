@@ -1,0 +1,233 @@
+"""
+GPU parity tests: the CUDA path (through the C-ABI) against the CPU oracle on the same
+seeded inputs. Integer / index results must match bit-exact; with the arithmetic contract of
+DESIGN.md (same operation order, deterministic transcendental functions) the float results
+match bit-exact too, which is far inside the 1e-5 relative tolerance north_star states.
+"""
+
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import harness as H
+from theia_b200 import _device, _lib
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-5  # tolerance stated by BASELINE.json north_star (float fields of a hit)
+
+
+def both(builder, N, **kw):
+    with _device.useDevice("cuda"):
+        g = builder(N, **kw)
+    with _device.useDevice("cpu"):
+        c = builder(N, **kw)
+    return g, c
+
+
+# ------------------------------------------------------------------ Philox / math
+def test_philox_known_answers(cuda, orc):
+    ctr = np.array([[0, 0, 0, 0], [0xFFFFFFFF] * 4, [0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344]], np.uint32)
+    key = np.array([[0, 0], [0xFFFFFFFF] * 2, [0xA4093822, 0x299F31D0]], np.uint32)
+    want = np.array([[0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8], [0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD],
+                     [0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1]], np.uint32)
+    c = torch.from_numpy(ctr.view(np.int32)).cuda()
+    k = torch.from_numpy(key.view(np.int32)).cuda()
+    out = torch.zeros(3, 4, dtype=torch.int32, device="cuda")
+    _lib.check(_lib.load().theia_philox_raw(c.data_ptr(), k.data_ptr(), 3, out.data_ptr(), 0))
+    got = out.cpu().numpy().view(np.uint32)
+    assert np.array_equal(got, want)
+    assert np.array_equal(orc.philoxRaw(ctr, key), want)
+
+
+@pytest.mark.parametrize("key,offset", [(0xC0FFEE, 0), (42, (1 << 128) - 5), ((1 << 64) - 1, (1 << 32) - 2)])
+def test_philox_stream_bit_exact(cuda, orc, key, offset):
+    from theia_b200.random import PhiloxRNG, RNGBufferSink
+    streams, samples = 4096, 256
+    with _device.useDevice("cuda"):
+        rng = PhiloxRNG(key=key, offset=offset)
+        sink = RNGBufferSink(rng, streams, samples)
+        from theia_b200 import pipeline as pl
+        pl.runPipeline([rng, sink])
+        torch.cuda.synchronize()
+        got = sink.tensor.cpu().numpy().reshape(streams, samples)
+    want = orc.philoxFill(key, offset, streams, samples)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert got.min() >= 0.0 and got.max() < 1.0
+
+
+def test_philox_uniformity(cuda):
+    # the reference's own pin (tests/test_random.py:67-81): 20 bins, max deviation < 0.5 %
+    lib = _lib.load()
+    from theia_b200 import _abi
+    p = _abi.PhiloxParams()
+    p.key[0] = 0xC0FFEE
+    streams, samples = 4096, 8192
+    out = torch.zeros(streams * samples, dtype=torch.float32, device="cuda")
+    _lib.check(lib.theia_philox_fill(ctypes.byref(p), 0, 0, streams, samples, 1, out.data_ptr(), 0))
+    hist = torch.histc(out, bins=20, min=0.0, max=1.0).cpu().numpy() / out.numel()
+    assert np.abs(hist * 20 - 1.0).max() < 5e-3
+
+
+@pytest.mark.parametrize("fn", ["sin", "cos", "exp", "log", "pow"])
+def test_device_math_bit_exact(cuda, orc, fn):
+    rng = np.random.default_rng(7)
+    n = 1 << 18
+    if fn in ("sin", "cos"):
+        x = rng.uniform(-20.0, 20.0, n)
+    elif fn == "exp":
+        x = rng.uniform(-110.0, 90.0, n)
+    elif fn == "log":
+        x = np.exp(rng.uniform(-100.0, 80.0, n))
+    else:
+        x = np.exp(rng.uniform(-20.0, 5.0, n))
+    x = x.astype(np.float32)
+    y = rng.uniform(-4.0, 4.0, n).astype(np.float32)
+    xd, yd = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    out = torch.zeros(n, dtype=torch.float32, device="cuda")
+    import oracle
+    _lib.check(_lib.load().theia_math_eval(oracle.MATH_FN[fn], xd.data_ptr(), yd.data_ptr(), n, out.data_ptr(), 0))
+    got = out.cpu().numpy()
+    want = orc.mathEval(fn, x, y)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    ref = {"sin": np.sin, "cos": np.cos, "exp": np.exp, "log": np.log}.get(fn)
+    exact = ref(x.astype(np.float64)) if ref else np.power(x.astype(np.float64), y.astype(np.float64))
+    ok = np.isfinite(exact) & (np.abs(exact) > 1e-30) & (np.abs(exact) < 1e30)
+    rel = np.abs(got[ok] - exact[ok]) / np.maximum(np.abs(exact[ok]), 1e-6 if fn in ("sin", "cos") else 0.0)
+    assert rel.max() < 4e-7  # a few ulp, inside what GLSL guarantees for its built-ins
+
+
+# ------------------------------------------------------------------ ray query
+def _randomRays(rng, n, lo, hi, tmax):
+    o = rng.uniform(lo, hi, (n, 3))
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, :3] = o
+    rays[:, 3] = tmax
+    rays[:, 4:7] = d
+    return rays
+
+
+@pytest.mark.parametrize("builder,kw,box", [
+    (H.sceneC2, {}, (-2.0, 8.0)),
+    (H.sceneC3, {}, (-4.0, 4.0)),
+    (H.sceneC5, {"lattice": (6, 6, 6), "resp": "record"}, (-200.0, 200.0)),
+])
+def test_ray_query_matches_brute_force(cuda, orc, builder, kw, box):
+    g, c = both(builder, 256, **kw)
+    rng = np.random.default_rng(3)
+    n = 200000
+    rays = _randomRays(rng, n, box[0], box[1], 1000.0)
+    # axis aligned and grazing rays
+    rays[:1000, 4:7] = np.eye(3, dtype=np.float32)[rng.integers(0, 3, 1000)] * rng.choice([-1.0, 1.0], (1000, 1))
+    brute = orc.OracleScene(c["scene"], bruteForce=True)
+    ids_w, tuv_w = brute.query(rays)
+    rd = torch.from_numpy(rays).cuda()
+    ids = torch.zeros(n, 4, dtype=torch.int32, device="cuda")
+    tuv = torch.zeros(n, 4, dtype=torch.float32, device="cuda")
+    st = torch.zeros(4, dtype=torch.int64, device="cuda")
+    _lib.check(_lib.load().theia_tlas_query(g["scene"].tlas.data_ptr(), rd.data_ptr(), n, ids.data_ptr(), tuv.data_ptr(),
+                                            st.data_ptr(), 0))
+    torch.cuda.synchronize()
+    ids_g, tuv_g = ids.cpu().numpy(), tuv.cpu().numpy()
+    assert np.count_nonzero(ids_w[:, 0] >= 0) > n // 100
+    assert np.array_equal(ids_g, ids_w), f"{np.count_nonzero((ids_g != ids_w).any(1))} rays hit a different triangle"
+    assert np.array_equal(tuv_g.view(np.uint32), tuv_w.view(np.uint32))
+    stats = st.cpu().numpy()
+    assert stats[3] == n and stats[0] > 0
+
+
+# ------------------------------------------------------------------ tracers, per path parity
+VOLUME_CASES = [
+    dict(),
+    dict(mis=False),
+    dict(mis=False, direct=False),
+    dict(direct=False),
+    dict(polarized=True, water=True),
+    dict(polarized=True, water=True, lightKind="cone", mis=False),
+    dict(lightKind="pencil", polarized=True, water=True),
+    dict(lightKind="cascade", water=True, wavelength="uniform"),
+    dict(lightKind="muon", water=True, wavelength="uniform"),
+    dict(targetKind="inner", mis=True),
+    dict(targetKind="inner", mis=False, polarized=True, water=True),
+]
+
+
+@pytest.mark.parametrize("kw", VOLUME_CASES, ids=lambda k: ",".join(f"{a}={b}" for a, b in k.items()) or "C1")
+def test_volume_tracer_hits_bit_exact(cuda, orc, kw):
+    N = 1 << 14
+    g, c = both(H.volumeScenario, N, resp="record", **kw)
+    H.runGpu(g)
+    H.runOracle(c)
+    a, b = H.sortedHits(g), H.sortedHits(c)
+    assert b["count"] > N // 8
+    H.compareHits(a, b)
+
+
+SCENE_CASES = [
+    (H.sceneC2, dict()),
+    (H.sceneC2, dict(lightKind="cone")),
+    (H.sceneC2, dict(polarized=False, lightKind="cone", useRefractedHitDir=True)),
+    (H.sceneC2, dict(lightKind="cone", disableTransmission=True)),
+    (H.sceneC3, dict()),
+    (H.sceneC3, dict(guide=False)),
+    (H.sceneC3, dict(polarized=True, disableDirectLighting=True)),
+    (H.sceneC5, dict(resp="record", lattice=(6, 6, 6), pitch=(4.0, 4.0, 4.0))),
+]
+
+
+@pytest.mark.parametrize("builder,kw", SCENE_CASES, ids=lambda v: getattr(v, "__name__", None) or ",".join(
+    f"{a}={b}" for a, b in v.items()) or "default")
+def test_scene_tracer_hits_bit_exact(cuda, orc, builder, kw):
+    N = 1 << 14
+    kw = dict(kw)
+    kw.setdefault("resp", "record")
+    g, c = both(builder, N, **kw)
+    H.runGpu(g)
+    H.runOracle(c)
+    a, b = H.sortedHits(g), H.sortedHits(c)
+    assert b["count"] > 100
+    H.compareHits(a, b)
+
+
+@pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict()), (H.volumeScenario, dict(mis=False)),
+                                        (H.sceneC2, dict(lightKind="cone")), (H.sceneC3, dict())])
+def test_event_statistics_match(cuda, orc, builder, kw):
+    N = 1 << 14
+    g, c = both(builder, N, resp="empty", callback="stat", **kw)
+    H.runGpu(g)
+    H.runOracle(c)
+    got, want = g["callback"]._read(), c["callback"]._read()
+    assert np.array_equal(got, want), f"{got} != {want}"
+    assert got[0] == N
+
+
+@pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict(polarized=True, water=True)), (H.sceneC2, dict())])
+def test_track_record_matches(cuda, orc, builder, kw):
+    N = 2048
+    g, c = both(builder, N, resp="empty", callback="track", **kw)
+    H.runGpu(g)
+    H.runOracle(c)
+    tg, lg, cg = g["callback"].result(0)
+    tc, lc, cc = c["callback"].result(0)
+    assert np.array_equal(lg, lc) and np.array_equal(cg, cc)
+    for k in range(N):
+        n = min(int(lg[k]) + 1, tg.shape[1])
+        assert np.array_equal(tg[k, :n].view(np.uint32), tc[k, :n].view(np.uint32)), f"track {k}"
+
+
+@pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict()), (H.sceneC3, dict()),
+                                        (H.sceneC2, dict(lightKind="cone", polarized=False))])
+def test_histogram_matches_oracle(cuda, orc, builder, kw):
+    N = 1 << 16
+    g, c = both(builder, N, resp="hist", **kw)
+    H.runGpu(g)
+    H.runOracle(c)
+    got, want = g["response"].result(0).astype(np.float64), c["response"].result(0).astype(np.float64)
+    assert want.sum() > 0
+    # same hits, different float summation order (the reference compares with rtol 1e-4:
+    # tests/test_response.py:92-99)
+    assert np.allclose(got, want, rtol=1e-4, atol=1e-7 * want.max())

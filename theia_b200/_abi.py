@@ -96,6 +96,7 @@ class TraceLaunch(Structure):
         ("callback", Callback),
         ("tlas", c_void_p),
         ("stream", c_void_p),
+        ("work_counters", c_void_p),
     ]
 
 

@@ -1,0 +1,355 @@
+// C-ABI entry points of libtheia_b200.so (include/theia_b200.h): error reporting, launch
+// validation and translation into the device launch block, plus the small kernels behind
+// the RNG sink, the histogram reducer, the hit replay and the ray query test seam.
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include "trace_scene.cuh"
+#include "trace_volume.cuh"
+
+namespace theia {
+
+static thread_local char g_error[512] = "";
+
+void setError(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+static int cudaFail(cudaError_t e, const char* what) {
+    setError("%s: %s", what, cudaGetErrorString(e));
+    return -2;
+}
+#define CUDA_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) return cudaFail(e_, #expr); } while (0)
+
+static uint32_t blocksFor(uint64_t n, uint32_t bs) { return (uint32_t)((n + bs - 1) / bs); }
+
+// ------------------------------------------------------------------ small kernels
+// sh/random.sink.glsl:17-39
+__global__ void philoxFillKernel(theia_philox_params_t p, uint32_t baseStream, uint32_t baseCount, uint32_t streams,
+                                 uint32_t samples, uint32_t dim, float* out) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (uint64_t)streams * samples) return;
+    uint32_t s = (uint32_t)(i / samples), c = (uint32_t)(i % samples);
+    PhiloxKey key = philoxStreamKey(p, baseStream + s);
+    if (dim == 1) {
+        out[i] = random_s(p, key, baseCount + c);
+    } else {
+        out[2 * i] = random_s(p, key, baseCount + c);
+        out[2 * i + 1] = random_s(p, key, baseCount + c + 1);
+    }
+}
+__global__ void philoxRawKernel(const uint32_t* ctr, const uint32_t* key, uint32_t n, uint32_t* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t r[4];
+    philox4x32_10(ctr[4 * i], ctr[4 * i + 1], ctr[4 * i + 2], ctr[4 * i + 3], key[2 * i], key[2 * i + 1], r);
+    out[4 * i] = r[0]; out[4 * i + 1] = r[1]; out[4 * i + 2] = r[2]; out[4 * i + 3] = r[3];
+}
+__global__ void mathEvalKernel(uint32_t fn, const float* x, const float* y, uint32_t n, float* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float s, c;
+    switch (fn) {
+    case 0: dm_sincos(x[i], &s, &c); out[i] = s; break;
+    case 1: dm_sincos(x[i], &s, &c); out[i] = c; break;
+    case 2: out[i] = dm_exp(x[i]); break;
+    case 3: out[i] = dm_log(x[i]); break;
+    default: out[i] = dm_pow(x[i], y[i]); break;
+    }
+}
+// sh/estimator.reduce.glsl:17-35: per bin Kahan sum over the partial histograms (precise)
+__global__ void histReduceKernel(float* partials, uint32_t nHist, uint32_t nBins, float norm, float* out, int clear) {
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nBins) return;
+    float result = 0.0f, c = 0.0f;
+    for (uint32_t n = 0; n < nHist; ++n) {
+        float* p = partials + (size_t)n * nBins + b;
+        float y = __fsub_rn(*p, c);
+        float t = __fadd_rn(result, y);
+        c = __fsub_rn(__fsub_rn(t, result), y);
+        result = t;
+        if (clear) *p = 0.0f;
+    }
+    out[b] = result * norm;
+}
+// sh/response.replay.glsl:35-50
+__global__ void __launch_bounds__(128) hitReplayKernel(const uint32_t* queue, uint32_t capacity, uint32_t polarized,
+                                                       ResponseDev r) {
+    extern __shared__ float sharedHist[];
+    if (r.kind == THEIA_RESPONSE_HISTOGRAM && r.hist_shared)
+        for (uint32_t b = threadIdx.x; b < r.n_bins; b += blockDim.x) sharedHist[b] = 0.0f;
+    __syncthreads();
+    float* hist = nullptr;
+    if (r.kind == THEIA_RESPONSE_HISTOGRAM)
+        hist = r.hist_shared ? sharedHist : r.hist_partials + (size_t)(blockIdx.x % r.hist_capacity) * r.n_bins;
+    uint32_t count = min(queue[0], capacity);
+    uint32_t nResp = 0;
+    // grid-stride over warps so that all 32 lanes reach commitHit together
+    for (uint32_t base = blockIdx.x * blockDim.x; base < capacity; base += gridDim.x * blockDim.x) {
+        uint32_t k = base + threadIdx.x;
+        bool has = k < count;
+        HitItem item;
+        item.contrib = 0.0f; item.time = 0.0f;
+        if (has) item = loadHit(queue, capacity, polarized != 0, k);
+        commitHit(r, hist, has, item, k, 0u, nResp);
+    }
+    __syncthreads();
+    if (r.kind == THEIA_RESPONSE_HISTOGRAM && r.hist_shared) {
+        const bool exclusive = gridDim.x <= r.hist_capacity;
+        float* dst = r.hist_partials + (size_t)(blockIdx.x % r.hist_capacity) * r.n_bins;
+        for (uint32_t b = threadIdx.x; b < r.n_bins; b += blockDim.x) {
+            float v = sharedHist[b];
+            if (exclusive) dst[b] += v;
+            else if (v != 0.0f) atomicAdd(dst + b, v);
+        }
+    }
+}
+// ray query test seam
+__global__ void __launch_bounds__(128) tlasQueryKernel(const void* tlas, const float* rays, uint32_t n, int32_t* out,
+                                                       float* outBary, unsigned long long* stats) {
+    __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
+    WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
+    const uint32_t nTop = stageTopNodes(tlas, sharedTop);
+    __syncthreads();
+    const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* r = rays + 8 * (size_t)i;
+    TraversalStats st = {0, 0, 0};
+    RayHit h = closestHit<true>(sc, v3(r), v3(r + 4), r[3], &st);
+    out[4 * i + 0] = h.valid ? h.instance : -1;
+    out[4 * i + 1] = h.valid ? h.prim : -1;
+    out[4 * i + 2] = h.valid ? sc.instances[h.slot].customIndex : -1;
+    out[4 * i + 3] = 0;
+    outBary[4 * i + 0] = h.valid ? h.t : 0.0f;
+    outBary[4 * i + 1] = h.valid ? h.u : 0.0f;
+    outBary[4 * i + 2] = h.valid ? h.v : 0.0f;
+    outBary[4 * i + 3] = 0.0f;
+    if (stats) {
+        atomicAdd(stats + 0, (unsigned long long)st.nodes);
+        atomicAdd(stats + 1, (unsigned long long)st.tris);
+        atomicAdd(stats + 2, (unsigned long long)st.instances);
+        atomicAdd(stats + 3, 1ull);
+    }
+}
+
+// ------------------------------------------------------------------ launch translation
+#define HIST_SHARED_MAX_BINS 8192u
+
+static int fillResponse(const theia_response_t& r, ResponseDev& d) {
+    memset(&d, 0, sizeof(d));
+    d.kind = r.kind;
+    if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
+        if (r.value_kind != THEIA_VALUE_UNIFORM) { setError("histogram response: unsupported value response %u", r.value_kind); return -1; }
+        if (!r.hist_partials || r.hist_capacity == 0 || r.n_bins == 0) { setError("histogram response: missing partial histogram buffer"); return -1; }
+        d.t0 = r.hist.t0; d.binSize = r.hist.binSize; d.n_bins = r.n_bins; d.hist_capacity = r.hist_capacity;
+        d.hist_partials = r.hist_partials;
+        d.hist_shared = r.n_bins <= HIST_SHARED_MAX_BINS ? 1u : 0u;
+    } else if (r.kind == THEIA_RESPONSE_RECORD) {
+        if (!r.queue || r.queue_capacity == 0) { setError("record response: missing queue"); return -1; }
+        d.queue = r.queue; d.queue_capacity = r.queue_capacity; d.queue_polarized = r.queue_polarized;
+        d.tag_path = r.tag_path; d.tag_event = r.tag_event;
+    } else if (r.kind != THEIA_RESPONSE_EMPTY) {
+        setError("unknown response kind %u", r.kind);
+        return -1;
+    }
+    return 0;
+}
+
+template <typename T>
+static int copyBlock(const theia_component_t& c, T& dst, const char* what) {
+    if (!c.params || c.params_size != sizeof(T)) {
+        setError("%s: parameter block has %u bytes, expected %zu", what, c.params_size, sizeof(T));
+        return -1;
+    }
+    memcpy(&dst, c.params, sizeof(T));
+    return 0;
+}
+
+static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
+    if (!L || L->struct_size != sizeof(theia_trace_launch_t)) { setError("launch: struct_size mismatch (ABI version?)"); return -1; }
+    memset(&D, 0, sizeof(D));
+    D.disable_mis = L->disable_mis; D.disable_direct_lighting = L->disable_direct_lighting;
+    D.disable_transmission = L->disable_transmission; D.disable_volume_border = L->disable_volume_border;
+    D.hit_use_transmitted_dir = L->hit_use_transmitted_dir; D.path_length = L->path_length;
+    D.batch_size = L->batch_size; D.first_path = L->first_path;
+    D.rng = L->rng;
+    if (L->tracer == THEIA_TRACER_VOLUME_FORWARD) {
+        if (!L->trace_params || L->trace_params_size != sizeof(theia_volume_trace_params_t)) { setError("volume tracer: bad TraceParams block"); return -1; }
+        theia_volume_trace_params_t p;
+        memcpy(&p, L->trace_params, sizeof(p));
+        D.medium = p.medium; D.objectId = p.objectId; D.propagation = p.propagation;
+        D.target.kind = L->target.kind;
+        if (L->target.kind != THEIA_TARGET_SPHERE && L->target.kind != THEIA_TARGET_INNER_SPHERE) { setError("volume tracer: unsupported target kind %u", L->target.kind); return -1; }
+        if (copyBlock(L->target, D.target.p, "target")) return -1;
+    } else if (L->tracer == THEIA_TRACER_SCENE_FORWARD) {
+        if (!L->trace_params || L->trace_params_size != sizeof(theia_scene_trace_params_t)) { setError("scene tracer: bad TraceParams block"); return -1; }
+        theia_scene_trace_params_t p;
+        memcpy(&p, L->trace_params, sizeof(p));
+        D.medium = p.sourceMedium; D.objectId = p.targetId; D.propagation = p.propagation;
+        if (!L->tlas) { setError("scene tracer: no acceleration structure"); return -1; }
+        if (L->path_length == 0) { setError("scene tracer: path_length must be at least 1"); return -1; }
+        D.tlas = L->tlas;
+        D.guide.kind = L->guide.kind;
+        if (L->guide.kind == THEIA_GUIDE_SPHERE) { if (copyBlock(L->guide, D.guide.p, "target guide")) return -1; }
+        else if (L->guide.kind != THEIA_GUIDE_NONE) { setError("scene tracer: unsupported guide kind %u", L->guide.kind); return -1; }
+    } else {
+        setError("unknown tracer kind %u", L->tracer);
+        return -1;
+    }
+    D.light.kind = L->light.kind; D.light.flags = L->light.flags;
+    switch (L->light.kind) {
+    case THEIA_LIGHT_SPHERICAL: if (copyBlock(L->light, D.light.p.spherical, "spherical light")) return -1; break;
+    case THEIA_LIGHT_CONE: if (copyBlock(L->light, D.light.p.cone, "cone light")) return -1; break;
+    case THEIA_LIGHT_PENCIL: if (copyBlock(L->light, D.light.p.pencil, "pencil light")) return -1; break;
+    case THEIA_LIGHT_CASCADE: if (copyBlock(L->light, D.light.p.cascade, "cascade light")) return -1; break;
+    case THEIA_LIGHT_MUON: if (copyBlock(L->light, D.light.p.muon, "muon light")) return -1; break;
+    default: setError("unsupported light source kind %u", L->light.kind); return -1;
+    }
+    D.wavelength.kind = L->wavelength.kind;
+    switch (L->wavelength.kind) {
+    case THEIA_WAVELENGTH_CONST: if (copyBlock(L->wavelength, D.wavelength.p.constant, "const wavelength")) return -1; break;
+    case THEIA_WAVELENGTH_UNIFORM: if (copyBlock(L->wavelength, D.wavelength.p.uniform, "uniform wavelength")) return -1; break;
+    default: setError("unsupported wavelength source kind %u", L->wavelength.kind); return -1;
+    }
+    if (fillResponse(L->response, D.response)) return -1;
+    D.callback.kind = L->callback.kind; D.callback.track_polarized = L->callback.track_polarized;
+    D.callback.stats = (unsigned long long*)L->callback.stats; D.callback.track_buffer = L->callback.track_buffer;
+    D.callback.track_count = L->callback.track_count; D.callback.track_length = L->callback.track_length;
+    if (L->callback.kind == THEIA_CALLBACK_STAT && !L->callback.stats) { setError("statistic callback without buffer"); return -1; }
+    if (L->callback.kind == THEIA_CALLBACK_TRACK && !L->callback.track_buffer) { setError("track callback without buffer"); return -1; }
+    D.work_counters = (unsigned long long*)L->work_counters;
+    return 0;
+}
+
+#define TRACE_THREADS 128u
+
+struct KernelPlan { const void* fn; size_t smem; uint32_t grid; };
+
+static int plan(const theia_trace_launch_t* L, const DeviceLaunch& D, KernelPlan& K) {
+    const bool pol = L->polarized != 0;
+    size_t smem = (D.response.kind == THEIA_RESPONSE_HISTOGRAM && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
+    if (L->tracer == THEIA_TRACER_VOLUME_FORWARD) {
+        K.fn = pol ? (const void*)volumeForwardKernel<true> : (const void*)volumeForwardKernel<false>;
+    } else {
+        K.fn = pol ? (const void*)sceneForwardKernel<true> : (const void*)sceneForwardKernel<false>;
+        smem += sizeof(WideNode) * THEIA_TOP_NODES;
+    }
+    K.smem = smem;
+    int dev = 0, sms = 0, perSm = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (smem > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(K.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, K.fn, (int)TRACE_THREADS, smem));
+    if (perSm < 1) { setError("tracer kernel does not fit on an SM"); return -1; }
+    // persistent grid: a whole number of resident CTAs per SM, never more CTAs than warps of work
+    uint32_t full = (uint32_t)sms * (uint32_t)perSm;
+    uint32_t need = blocksFor(D.batch_size, TRACE_THREADS);
+    K.grid = need < full ? (need > 0 ? need : 1u) : full;
+    return 0;
+}
+
+}  // namespace theia
+
+using namespace theia;
+
+extern "C" {
+
+const char* theia_last_error(void) { return g_error; }
+int theia_abi_version(void) { return THEIA_ABI_VERSION; }
+
+int theia_device_info(int* sm_count, int* cc_major, int* cc_minor) {
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (sm_count) CUDA_TRY(cudaDeviceGetAttribute(sm_count, cudaDevAttrMultiProcessorCount, dev));
+    if (cc_major) CUDA_TRY(cudaDeviceGetAttribute(cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (cc_minor) CUDA_TRY(cudaDeviceGetAttribute(cc_minor, cudaDevAttrComputeCapabilityMinor, dev));
+    return 0;
+}
+
+int theia_philox_fill(const theia_philox_params_t* params, uint32_t baseStream, uint32_t baseCount, uint32_t streams,
+                      uint32_t samples, uint32_t dim, float* out_dev, void* stream) {
+    if (!params || !out_dev || (dim != 1 && dim != 2)) { setError("theia_philox_fill: bad argument"); return -1; }
+    uint64_t n = (uint64_t)streams * samples;
+    if (n == 0) return 0;
+    philoxFillKernel<<<blocksFor(n, 256), 256, 0, (cudaStream_t)stream>>>(*params, baseStream, baseCount, streams, samples, dim, out_dev);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int theia_philox_raw(const uint32_t* ctr_dev, const uint32_t* key_dev, uint32_t n, uint32_t* out_dev, void* stream) {
+    if (!ctr_dev || !key_dev || !out_dev) { setError("theia_philox_raw: null argument"); return -1; }
+    if (n == 0) return 0;
+    philoxRawKernel<<<blocksFor(n, 256), 256, 0, (cudaStream_t)stream>>>(ctr_dev, key_dev, n, out_dev);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int theia_math_eval(uint32_t fn, const float* x_dev, const float* y_dev, uint32_t n, float* out_dev, void* stream) {
+    if (fn > 4 || !x_dev || !out_dev || (fn == 4 && !y_dev)) { setError("theia_math_eval: bad argument"); return -1; }
+    if (n == 0) return 0;
+    mathEvalKernel<<<blocksFor(n, 256), 256, 0, (cudaStream_t)stream>>>(fn, x_dev, y_dev, n, out_dev);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int theia_hist_reduce(float* partials_dev, uint32_t n_hist, uint32_t n_bins, float norm, float* out_dev, int clear,
+                      void* stream) {
+    if (!partials_dev || !out_dev) { setError("theia_hist_reduce: null argument"); return -1; }
+    if (n_bins == 0) return 0;
+    histReduceKernel<<<blocksFor(n_bins, 128), 128, 0, (cudaStream_t)stream>>>(partials_dev, n_hist, n_bins, norm, out_dev, clear);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int theia_hit_replay(const uint32_t* queue_dev, uint32_t capacity, uint32_t polarized, const theia_response_t* response,
+                     uint32_t block_size, void* stream) {
+    (void)block_size;
+    if (!queue_dev || !response) { setError("theia_hit_replay: null argument"); return -1; }
+    ResponseDev r;
+    if (fillResponse(*response, r)) return -1;
+    if (capacity == 0) return 0;
+    size_t smem = (r.kind == THEIA_RESPONSE_HISTOGRAM && r.hist_shared) ? (size_t)r.n_bins * 4 : 0;
+    uint32_t grid = blocksFor(capacity, 128);
+    if (r.kind == THEIA_RESPONSE_HISTOGRAM && grid > r.hist_capacity) grid = r.hist_capacity;
+    if (grid > 148 * 8) grid = 148 * 8;
+    hitReplayKernel<<<grid, 128, smem, (cudaStream_t)stream>>>(queue_dev, capacity, polarized, r);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, int32_t* out_dev, float* out_bary_dev,
+                     uint64_t* stats_dev, void* stream) {
+    if (!tlas_dev || !rays_dev || !out_dev || !out_bary_dev) { setError("theia_tlas_query: null argument"); return -1; }
+    if (n == 0) return 0;
+    tlasQueryKernel<<<blocksFor(n, 128), 128, 0, (cudaStream_t)stream>>>(tlas_dev, rays_dev, n, out_dev, out_bary_dev,
+                                                                         (unsigned long long*)stats_dev);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int theia_trace_grid_size(const theia_trace_launch_t* launch, uint32_t* n_blocks) {
+    DeviceLaunch D;
+    KernelPlan K;
+    if (!n_blocks) { setError("theia_trace_grid_size: null argument"); return -1; }
+    if (translate(launch, D)) return -1;
+    if (plan(launch, D, K)) return -1;
+    *n_blocks = K.grid;
+    return 0;
+}
+
+int theia_trace_forward(const theia_trace_launch_t* launch) {
+    DeviceLaunch D;
+    KernelPlan K;
+    if (translate(launch, D)) return -1;
+    if (D.batch_size == 0) return 0;
+    if (plan(launch, D, K)) return -1;
+    void* args[] = {&D};
+    CUDA_TRY(cudaLaunchKernel(K.fn, dim3(K.grid), dim3(TRACE_THREADS), args, K.smem, (cudaStream_t)launch->stream));
+    return 0;
+}
+
+}  // extern "C"

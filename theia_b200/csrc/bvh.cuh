@@ -1,0 +1,220 @@
+// Acceleration structure format and software ray query.
+//
+// The reference traces rays with GL_EXT_ray_query against a Vulkan TLAS built by the driver
+// (sh/scene.traverse.glsl:310-323, src/theia/scene.py:550, 668); B200 has no RT cores, so
+// the structure and its traversal are part of this library:
+//   * two levels: one BLAS per mesh (object space), one TLAS over instances (world space);
+//   * 8-wide nodes of 80 bytes with child boxes quantised to 8 bit per axis on a
+//     power-of-two grid anchored at the node's lower corner, read with five 128 bit loads;
+//     children are stored sorted along the node's widest axis so that slots can be visited
+//     near-to-far by scanning the hit mask upwards or downwards;
+//   * leaf triangles are stored pre-gathered (3 x 16 bytes, primitive id in the padding).
+// Ray query semantics (Vulkan): closest opaque triangle with t in (0, tmax), no culling,
+// barycentrics (u, v) weighting v1 and v2. Triangle test: watertight test of Woop, Benthin
+// and Wald (JCGT 2013) in object space with the unnormalised direction (t is the world
+// parameter), double precision fallback for zero edge functions; ties in t go to the lower
+// (instance, primitive). The result is therefore independent of the tree, and the box tests
+// only have to be conservative: quantised boxes are rounded outwards and every slab
+// interval is widened by a few ulp of its operands.
+#pragma once
+#include "detmath.cuh"
+
+namespace theia {
+
+struct alignas(16) WideNode {  // 80 bytes
+    float px, py, pz;          // origin of the quantisation grid (lower corner)
+    uint8_t ex, ey, ez;        // biased float exponent of the grid step per axis
+    uint8_t imask;             // bit i set: child i is an inner node
+    uint32_t childBase;        // index of the first inner child (inner children are contiguous, slot order)
+    uint32_t primBase;         // index of the first primitive of the leaf children (contiguous, slot order)
+    uint8_t meta[8];           // 0: empty; inner: 1 + rank among inner children; leaf: count | offset << 3
+    uint8_t qlox[8], qloy[8], qloz[8];
+    uint8_t qhix[8], qhiy[8], qhiz[8];
+};
+static_assert(sizeof(WideNode) == 80, "WideNode layout");
+
+struct alignas(16) TriRec {  // 48 bytes
+    float v0x, v0y, v0z;
+    uint32_t prim;
+    float v1x, v1y, v1z;
+    uint32_t pad1;
+    float v2x, v2y, v2z;
+    uint32_t pad2;
+};
+static_assert(sizeof(TriRec) == 48, "TriRec layout");
+
+#define THEIA_BLAS_MAGIC 0x534C4254u  // "TBLS"
+#define THEIA_TLAS_MAGIC 0x534C5454u  // "TTLS"
+#define THEIA_LEAF_MAX 4
+#define THEIA_STACK_SIZE 128  // traversal stack entries per ray
+
+struct alignas(16) BlasHeader {  // 64 bytes, followed by nodes then triangles
+    uint32_t magic, nNodes, nTris, orderAxis;
+    uint64_t nodesOffset, trisOffset;
+    float lo[3], hi[3];  // object space bounds
+    uint32_t pad[2];
+};
+static_assert(sizeof(BlasHeader) == 64, "BlasHeader layout");
+
+struct alignas(16) InstanceRec {  // 144 bytes
+    float w2o[12];                // 3x4 row major world -> object
+    const WideNode* blasNodes;
+    const TriRec* blasTris;
+    float o2w[12];                // 3x4 row major object -> world
+    uint64_t vertices, indices, material;  // Scene.GLSLGeometry (scene.py:628-635)
+    int32_t customIndex;
+    uint32_t pad;  // instance id (the records are stored in leaf order)
+};
+static_assert(sizeof(InstanceRec) == 144, "InstanceRec layout");
+
+struct alignas(16) TlasHeader {  // 64 bytes, followed by nodes then instance records
+    uint32_t magic, nNodes, nInstances, pad0;
+    uint64_t nodesOffset, instancesOffset;
+    float lo[3], hi[3];
+    uint32_t pad[2];
+};
+static_assert(sizeof(TlasHeader) == 64, "TlasHeader layout");
+
+struct RayHit {
+    bool valid;
+    int32_t instance, prim;  // instance id (TLAS build order), primitive id inside the mesh
+    int32_t slot;            // position of the instance record inside the TLAS (leaf order)
+    float t, u, v;
+};
+struct TraversalStats { uint32_t nodes, tris, instances; };
+
+// Node fetch: five 128 bit loads through the read-only path.
+struct NodeRegs { uint4 a, b, c, d, e; };
+TDEV NodeRegs loadNode(const WideNode* n) {
+    const uint4* p = reinterpret_cast<const uint4*>(n);
+    NodeRegs r;
+    r.a = __ldg(p); r.b = __ldg(p + 1); r.c = __ldg(p + 2); r.d = __ldg(p + 3); r.e = __ldg(p + 4);
+    return r;
+}
+TDEV NodeRegs loadNodeShared(const WideNode* n) {
+    const uint4* p = reinterpret_cast<const uint4*>(n);
+    NodeRegs r;
+    r.a = p[0]; r.b = p[1]; r.c = p[2]; r.d = p[3]; r.e = p[4];
+    return r;
+}
+
+TDEV float safeInv(float d) {
+    float inv = 1.0f / d;
+    if (!(abs_(inv) <= 1e30f)) inv = copysignf(1e30f, d);
+    return inv;
+}
+TDEV uint32_t byteOf(uint32_t w, int i) { return (w >> (8 * i)) & 0xFFu; }
+
+// Ray in the space of the structure being traversed.
+struct SlabRay {
+    float ox, oy, oz;
+    float ix, iy, iz;  // safe inverse direction
+};
+
+// Tests the eight quantised child boxes of a node against [0, lim]; returns the hit mask and
+// the entry distances. Each axis interval is widened by ~5 ulp of its operands.
+TDEV uint32_t testChildren(const NodeRegs& n, const SlabRay& r, float lim, float tmin[8]) {
+    const float EPS = 6e-7f;
+    float px = u2f(n.a.x), py = u2f(n.a.y), pz = u2f(n.a.z);
+    float sx = u2f(byteOf(n.a.w, 0) << 23), sy = u2f(byteOf(n.a.w, 1) << 23), sz = u2f(byteOf(n.a.w, 2) << 23);
+    float ax = sx * r.ix, ay = sy * r.iy, az = sz * r.iz;
+    float bx = (px - r.ox) * r.ix, by = (py - r.oy) * r.iy, bz = (pz - r.oz) * r.iz;
+    float ex = EPS * fmaf(256.0f, fabsf(ax), fabsf(bx));
+    float ey = EPS * fmaf(256.0f, fabsf(ay), fabsf(by));
+    float ez = EPS * fmaf(256.0f, fabsf(az), fabsf(bz));
+    float bxl = bx - ex, bxh = bx + ex, byl = by - ey, byh = by + ey, bzl = bz - ez, bzh = bz + ez;
+    // per axis: words holding the near / far plane bytes of children 0-3 and 4-7
+    // layout: b = {childBase, primBase, meta0-3, meta4-7}, c = {qlox, qlox, qloy, qloy},
+    //         d = {qloz, qloz, qhix, qhix}, e = {qhiy, qhiy, qhiz, qhiz}
+    const bool nx = r.ix < 0.0f, ny = r.iy < 0.0f, nz = r.iz < 0.0f;
+    uint32_t xn0 = nx ? n.d.z : n.c.x, xn1 = nx ? n.d.w : n.c.y, xf0 = nx ? n.c.x : n.d.z, xf1 = nx ? n.c.y : n.d.w;
+    uint32_t yn0 = ny ? n.e.x : n.c.z, yn1 = ny ? n.e.y : n.c.w, yf0 = ny ? n.c.z : n.e.x, yf1 = ny ? n.c.w : n.e.y;
+    uint32_t zn0 = nz ? n.e.z : n.d.x, zn1 = nz ? n.e.w : n.d.y, zf0 = nz ? n.d.x : n.e.z, zf1 = nz ? n.d.y : n.e.w;
+    uint32_t mask = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int j = i & 3;
+        uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, j);
+        float tnx = fmaf((float)byteOf(i < 4 ? xn0 : xn1, j), ax, bxl);
+        float tfx = fmaf((float)byteOf(i < 4 ? xf0 : xf1, j), ax, bxh);
+        float tny = fmaf((float)byteOf(i < 4 ? yn0 : yn1, j), ay, byl);
+        float tfy = fmaf((float)byteOf(i < 4 ? yf0 : yf1, j), ay, byh);
+        float tnz = fmaf((float)byteOf(i < 4 ? zn0 : zn1, j), az, bzl);
+        float tfz = fmaf((float)byteOf(i < 4 ? zf0 : zf1, j), az, bzh);
+        float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+        float tf = fminf(fminf(tfx, tfy), fminf(tfz, lim));
+        tmin[i] = tn;
+        if (meta != 0 && tn <= tf) mask |= 1u << i;
+    }
+    return mask;
+}
+
+// Per (ray, instance) setup of the watertight test
+struct WoopRay {
+    float o[3], d[3];
+    int kx, ky, kz;
+    float Sx, Sy, Sz;
+};
+TDEV float pick(const float v[3], int k) { return k == 0 ? v[0] : (k == 1 ? v[1] : v[2]); }
+TDEV void woopSetup(WoopRay& r) {
+    float ax = abs_(r.d[0]), ay = abs_(r.d[1]), az = abs_(r.d[2]);
+    int kz = 0;
+    float m = ax;
+    if (ay > m) { kz = 1; m = ay; }
+    if (az > m) { kz = 2; m = az; }
+    int kx = kz + 1; if (kx == 3) kx = 0;
+    int ky = kx + 1; if (ky == 3) ky = 0;
+    if (pick(r.d, kz) < 0.0f) { int t = kx; kx = ky; ky = t; }
+    r.kx = kx; r.ky = ky; r.kz = kz;
+    r.Sz = 1.0f / pick(r.d, kz);
+    r.Sx = pick(r.d, kx) * r.Sz;
+    r.Sy = pick(r.d, ky) * r.Sz;
+}
+TDEV bool woopIntersect(const WoopRay& r, const float v0[3], const float v1[3], const float v2[3], float tmax,
+                        float* t_out, float* u_out, float* v_out) {
+    float A[3] = {v0[0] - r.o[0], v0[1] - r.o[1], v0[2] - r.o[2]};
+    float B[3] = {v1[0] - r.o[0], v1[1] - r.o[1], v1[2] - r.o[2]};
+    float C[3] = {v2[0] - r.o[0], v2[1] - r.o[1], v2[2] - r.o[2]};
+    float Akz = pick(A, r.kz), Bkz = pick(B, r.kz), Ckz = pick(C, r.kz);
+    float Ax = fmaf(-r.Sx, Akz, pick(A, r.kx)), Ay = fmaf(-r.Sy, Akz, pick(A, r.ky));
+    float Bx = fmaf(-r.Sx, Bkz, pick(B, r.kx)), By = fmaf(-r.Sy, Bkz, pick(B, r.ky));
+    float Cx = fmaf(-r.Sx, Ckz, pick(C, r.kx)), Cy = fmaf(-r.Sy, Ckz, pick(C, r.ky));
+    float U = Cx * By - Cy * Bx;
+    float V = Ax * Cy - Ay * Cx;
+    float W = Bx * Ay - By * Ax;
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {
+        double CxBy = (double)Cx * (double)By, CyBx = (double)Cy * (double)Bx;
+        U = (float)(CxBy - CyBx);
+        double AxCy = (double)Ax * (double)Cy, AyCx = (double)Ay * (double)Cx;
+        V = (float)(AxCy - AyCx);
+        double BxAy = (double)Bx * (double)Ay, ByAx = (double)By * (double)Ax;
+        W = (float)(BxAy - ByAx);
+    }
+    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
+    float det = U + V + W;
+    if (det == 0.0f) return false;
+    float Az = r.Sz * Akz, Bz = r.Sz * Bkz, Cz = r.Sz * Ckz;
+    float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
+    if (det < 0.0f) {
+        if (!(T < 0.0f) || !(T > tmax * det)) return false;
+    } else {
+        if (!(T > 0.0f) || !(T < tmax * det)) return false;
+    }
+    float rcp = 1.0f / det;
+    *t_out = T * rcp;
+    *u_out = V * rcp;
+    *v_out = W * rcp;
+    return true;
+}
+
+TDEV void transformPoint(const float m[12], const float p[3], float out[3]) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+        out[i] = fmaf(m[4 * i + 2], p[2], fmaf(m[4 * i + 1], p[1], fmaf(m[4 * i + 0], p[0], m[4 * i + 3])));
+}
+TDEV void transformVector(const float m[12], const float p[3], float out[3]) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) out[i] = fmaf(m[4 * i + 2], p[2], fmaf(m[4 * i + 1], p[1], m[4 * i + 0] * p[0]));
+}
+
+}  // namespace theia

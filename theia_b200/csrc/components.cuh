@@ -1,0 +1,277 @@
+// Component snippets of the reference as device functions: wavelength sources, light
+// sources (forward sampling), volume-tracer targets and scene-tracer target guides
+// (sh/wavelengthsource.*.glsl, sh/lightsource.*.glsl, sh/random.gamma.glsl, sh/target.*.glsl,
+// sh/target_guide.*.glsl). The byte-identical parameter blocks of include/theia_b200.h are
+// copied into the kernel's constant parameter space by the launcher.
+#pragma once
+#include "physics.cuh"
+
+namespace theia {
+
+union LightBlock {
+    theia_light_spherical_t spherical;
+    theia_light_cone_t cone;
+    theia_light_pencil_t pencil;
+    theia_light_cascade_t cascade;
+    theia_light_muon_t muon;
+};
+union WavelengthBlock {
+    theia_wavelength_const_t constant;
+    theia_wavelength_uniform_t uniform;
+};
+struct LightSel { uint32_t kind, flags; LightBlock p; };
+struct WavelengthSel { uint32_t kind; WavelengthBlock p; };
+struct TargetSel { uint32_t kind; theia_target_sphere_t p; };
+struct GuideSel { uint32_t kind; theia_guide_sphere_t p; };
+
+// ------------------------------------------------------------------ wavelength sources
+// sh/wavelengthsource.const.glsl:10-12, sh/wavelengthsource.uniform.glsl:12-16
+TDEV WavelengthSample sampleWavelength(const WavelengthSel& c, Rng& rng) {
+    if (c.kind == THEIA_WAVELENGTH_CONST) return {c.p.constant.lambda, 1.0f};
+    float u = rng.next();
+    float lam = mix_(c.p.uniform.lam_min, c.p.uniform.lam_max, u);
+    return {lam, c.p.uniform.contrib};
+}
+
+// ------------------------------------------------------------------ sh/random.gamma.glsl:9-29
+// Cheng's GA rejection sampler: data dependent number of draws (1 + 2k).
+static __device__ __noinline__ float sampleGamma(float alpha, Rng& rng) {
+    float scale = 1.0f;
+    if (alpha < 1.0f) {
+        scale = dm_pow(rng.next(), 1.0f / alpha);
+        alpha += 1.0f;
+    }
+    float a = sqrtf(2.0f * alpha - 1.0f);
+    float b = alpha - dm_log(4.0f);
+    float c = alpha + 1.0f / alpha;
+    for (int it = 0; it < 1000000; ++it) {
+        vec2 u = rng.next2();
+        float V = a * dm_log(u.x / (1.0f - u.x));
+        float X = alpha * dm_exp(V);
+        if (b + c * V - X >= dm_log(u.x * u.x * u.y)) return scale * X;
+    }
+    return T_NAN;
+}
+
+// ------------------------------------------------------------------ sh/lightsource.particles.common.glsl
+// :52-61
+TDEV float frank_tamm(float lambda, float n) {
+    lambda *= 1e-3f;
+    float sin2_theta = 1.0f - 1.0f / (n * n);
+    float result = T_TWO_PI * 7.2973525693f / (lambda * lambda) * sin2_theta;
+    return max_(result, 0.0f);
+}
+// :68-97
+static __device__ __noinline__ float particle_sampleEmissionAngle(float n, float a, float b, float u) {
+    float cos_chev = 1.0f / n;
+    float int_lower = 1.0f - dm_exp(-b * dm_pow(1.0f - cos_chev, a));
+    float int_upper = 1.0f - dm_exp(-b * dm_pow(1.0f + cos_chev, a));
+    u = u * (int_upper + int_lower) - int_lower;
+    float x = dm_pow(-dm_log(1.0f - abs_(u)) / b, 1.0f / a);
+    return cos_chev - sign_(u) * x;
+}
+
+// ------------------------------------------------------------------ light sources (forward)
+template <bool POL>
+TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants medium, Rng& rng) {
+    switch (c.kind) {
+    case THEIA_LIGHT_SPHERICAL: {  // sh/lightsource.spherical.glsl:16-34
+        const theia_light_spherical_t& p = c.p.spherical;
+        vec3 rayDir = sampleUnitSphere(rng.next2());
+        float v = rng.next();
+        float startTime = mix_(p.t_min, p.t_max, v);
+        return createSourceRay<POL>(v3(p.position), rayDir, startTime, p.contribFwd);
+    }
+    case THEIA_LIGHT_CONE: {  // sh/lightsource.cone.glsl:22-72
+        const theia_light_cone_t& p = c.p.cone;
+        vec2 u = rng.next2();
+        float phi = T_TWO_PI * u.x;
+        float cos_theta = (1.0f - u.y) + p.cosOpeningAngle * u.y;
+        float sin_theta = sqrtf(max_(1.0f - cos_theta * cos_theta, 0.0f));
+        float sp, cp;
+        dm_sincos(phi, &sp, &cp);
+        vec3 localDir = {sin_theta * cp, sin_theta * sp, cos_theta};
+        mat3 trafo = createLocalCOSY(normalize(v3(p.direction)));
+        vec3 rayDir = trafo * localDir;
+        float v = rng.next();
+        float startTime = mix_(p.t_min, p.t_max, v);
+        if (c.flags & THEIA_LIGHT_FLAG_POLARIZED) {
+            vec3 polRef = v3(p.polRef);
+            polRef = polRef - dot(polRef, rayDir) * rayDir;
+            polRef = normalize(polRef);
+            return createSourceRay(v3(p.position), rayDir, v4(p.stokes), polRef, startTime, p.contribFwd);
+        }
+        return createSourceRay<POL>(v3(p.position), rayDir, startTime, p.contribFwd);
+    }
+    case THEIA_LIGHT_PENCIL: {  // sh/lightsource.pencil.glsl:18-35
+        const theia_light_pencil_t& p = c.p.pencil;
+        float u = rng.next();
+        float startTime = mix_(p.t_min, p.t_max, u);
+        return createSourceRay(v3(p.position), v3(p.direction), v4(p.stokes), v3(p.polRef), startTime, p.budget);
+    }
+    case THEIA_LIGHT_CASCADE: {  // sh/lightsource.particles.cascade.glsl:40-69
+        const theia_light_cascade_t& p = c.p.cascade;
+        float z = sampleGamma(p.a_long, rng) * p.b_long;
+        vec3 dir = v3(p.direction);
+        vec3 rayPos = fma3(z, dir, v3(p.startPosition));
+        float time = fmaf(z, T_INV_SPEED_OF_LIGHT, p.startTime);
+        vec2 u = rng.next2();
+        float phi = T_TWO_PI * u.x;
+        float cos_theta = particle_sampleEmissionAngle(medium.n, p.a_angular, p.b_angular, u.y);
+        vec3 rayDir = createLocalCOSY(dir) * sphericalToCartessian(phi, cos_theta);
+        float contrib = p.effectiveLength;
+        if (!(c.flags & THEIA_LIGHT_FLAG_FRANK_TAMM_IS)) contrib *= frank_tamm(wavelength, medium.n);
+        return createSourceRay<POL>(rayPos, rayDir, time, contrib);
+    }
+    case THEIA_LIGHT_MUON: {  // sh/lightsource.particles.muon.glsl:28-59
+        const theia_light_muon_t& p = c.p.muon;
+        float u = rng.next();
+        vec3 s = v3(p.startPosition), e = v3(p.endPosition);
+        vec3 position = {mix_(s.x, e.x, u), mix_(s.y, e.y, u), mix_(s.z, e.z, u)};
+        float startTime = mix_(p.startTime, p.endTime, u);
+        float contrib = distance(s, e);
+        contrib *= p.energyScale;
+        vec2 v = rng.next2();
+        float phi = T_TWO_PI * v.x;
+        float cos_theta = particle_sampleEmissionAngle(medium.n, p.a_angular, p.b_angular, v.y);
+        vec3 trackDir = normalize(e - s);
+        vec3 rayDir = createLocalCOSY(trackDir) * sphericalToCartessian(phi, cos_theta);
+        if (!(c.flags & THEIA_LIGHT_FLAG_FRANK_TAMM_IS)) contrib *= frank_tamm(wavelength, medium.n);
+        return createSourceRay<POL>(position, rayDir, startTime, contrib);
+    }
+    }
+    SourceRay bad;  // sh/lightsource.common.glsl:28-37
+    bad.position = v3(T_NAN); bad.direction = v3(T_NAN);
+    bad.stokes = {1.0f, 0.0f, 0.0f, 0.0f}; bad.polRef = v3(0.0f);
+    bad.startTime = T_NAN; bad.contrib = T_NAN;
+    return bad;
+}
+
+// sh/tracer.volume.forward.glsl:223-229, sh/tracer.scene.forward.glsl:50-56
+template <bool POL>
+TDEV Ray sampleRay(const WavelengthSel& wl, const LightSel& light, uint64_t medium, Rng& rng) {
+    WavelengthSample photon = sampleWavelength(wl, rng);
+    MediumConstants constants = lookUpMedium(medium, photon.wavelength);
+    SourceRay lightRay = sampleLight<POL>(light, photon.wavelength, constants, rng);
+    return createRay(lightRay, medium, constants, photon);
+}
+
+// ------------------------------------------------------------------ sh/target.common.glsl
+// The sphere targets only ever produce worldToObj = mat3(invRad): carried as a scalar.
+struct TargetSample {
+    vec3 position, normal;
+    float dist;
+    vec3 objPosition, objNormal;
+    float prob;
+    bool valid;
+    float invRad;
+};
+TDEV TargetSample createTargetSampleMiss() {  // :77-91
+    TargetSample t;
+    t.position = v3(0.0f); t.normal = v3(0.0f); t.objPosition = v3(0.0f); t.objNormal = v3(0.0f);
+    t.dist = T_INF; t.prob = 0.0f; t.valid = false; t.invRad = 1.0f;
+    return t;
+}
+
+// sh/target.sphere.glsl:18-43, sh/target.sphere.inner.glsl:18-36
+TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
+    const theia_target_sphere_t& p = c.p;
+    vec3 center = v3(p.position);
+    TargetSample t;
+    t.invRad = p.invRad;
+    if (c.kind == THEIA_TARGET_SPHERE) {
+        vec3 dir = normalize(observer - center);
+        float d = distance(observer, center);
+        float cosOpening = p.radius / d;
+        vec3 normal = createLocalCOSY(dir) * sampleDirectionCone(cosOpening, rng.next2());
+        vec3 pos = normal * p.radius + center;
+        float prob = p.prob / (1.0f - cosOpening);
+        bool valid = !isinf_(prob);
+        if (!valid) prob = 0.0f;
+        t.position = pos; t.normal = normal; t.dist = distance(pos, observer);
+        t.objPosition = normal; t.objNormal = normal; t.prob = prob; t.valid = valid;
+    } else {
+        vec3 normal = sampleUnitSphere(rng.next2());
+        vec3 pos = p.radius * normal + center;
+        t.position = pos; t.normal = -normal; t.dist = distance(observer, pos);
+        t.objPosition = normal; t.objNormal = -normal; t.prob = p.prob; t.valid = true;
+    }
+    return t;
+}
+// sh/target.sphere.glsl:45-78, sh/target.sphere.inner.glsl:38-56
+TDEV TargetSample intersectTarget(const TargetSel& c, vec3 observer, vec3 direction) {
+    const theia_target_sphere_t& p = c.p;
+    vec3 center = v3(p.position);
+    vec2 ts = intersectSphere(center, p.radius, observer, direction);
+    TargetSample r;
+    r.invRad = p.invRad;
+    if (c.kind == THEIA_TARGET_SPHERE) {
+        float t = ts.x;
+        bool hit = (t > 0.0f) && !isinf_(t);
+        if (!hit) return createTargetSampleMiss();
+        vec3 pos = fma3(t, direction, observer);
+        vec3 nrm = normalize(pos - center);
+        float d = distance(observer, center);
+        float cosOpening = p.radius / d;
+        float prob = p.prob / (1.0f - cosOpening);
+        bool valid = !isinf_(prob);
+        if (!valid) prob = 0.0f;
+        r.position = pos; r.normal = nrm; r.dist = t; r.objPosition = nrm; r.objNormal = nrm;
+        r.prob = prob; r.valid = valid;
+        return r;
+    }
+    float t = ts.y;
+    bool hit = (t > 0.0f) && !isinf_(t);
+    vec3 pos = fma3(t, direction, observer);
+    vec3 nrm = normalize(center - pos);
+    r.position = pos; r.normal = nrm; r.dist = t; r.objPosition = -nrm; r.objNormal = nrm;
+    r.prob = p.prob; r.valid = hit;
+    return r;
+}
+// sh/target.sphere.glsl:80-83, sh/target.sphere.inner.glsl:58-60
+TDEV bool isOccludedByTarget(const TargetSel& c, vec3 position) {
+    float d = distance(position, v3(c.p.position));
+    return c.kind == THEIA_TARGET_SPHERE ? d <= c.p.radius : d >= c.p.radius;
+}
+
+// ------------------------------------------------------------------ sh/target_guide.sphere.glsl
+struct TargetGuideSample { vec3 dir; float dist, prob; };
+
+TDEV void guideCone(const theia_guide_sphere_t& p, vec3 observer, float* d, vec3* viewDir, float* cosMin,
+                    float* prob) {
+    vec3 center = v3(p.position);
+    *d = distance(center, observer);
+    *viewDir = normalize(center - observer);
+    float sinMax = p.radius / *d;
+    float sin2Max = sinMax * sinMax;
+    float cm = 1.0f - sqrtf(max_(1.0f - sin2Max, 0.0f));
+    if (sin2Max < 0.00068523f) cm = 0.5f * sin2Max;
+    *cosMin = cm;
+    float pr = 1.0f / (T_TWO_PI * cm);
+    pr *= (*d > p.radius) ? 1.0f : 0.0f;
+    *prob = pr;
+}
+// :15-51
+TDEV TargetGuideSample sampleTargetGuide(const GuideSel& c, vec3 observer, Rng& rng) {
+    float d, cosMin, prob;
+    vec3 viewDir;
+    guideCone(c.p, observer, &d, &viewDir, &cosMin, &prob);
+    float cosTheta = 1.0f - cosMin * rng.next();
+    float sinTheta = sqrtf(max_(1.0f - cosTheta * cosTheta, 0.0f));
+    float phi = T_TWO_PI * rng.next();
+    float sp, cp;
+    dm_sincos(phi, &sp, &cp);
+    vec3 dir = createLocalCOSY(viewDir) * vec3{sinTheta * sp, sinTheta * cp, cosTheta};
+    return {dir, d + c.p.radius, prob};
+}
+// :53-81
+TDEV TargetGuideSample evalTargetGuide(const GuideSel& c, vec3 observer, vec3 direction) {
+    float d, cosMin, prob;
+    vec3 viewDir;
+    guideCone(c.p, observer, &d, &viewDir, &cosMin, &prob);
+    float cosDir = dot(viewDir, direction);
+    prob *= (cosMin >= 1.0f - cosDir) ? 1.0f : 0.0f;
+    return {direction, d + c.p.radius, prob};
+}
+
+}  // namespace theia
