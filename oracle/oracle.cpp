@@ -186,6 +186,9 @@ int orc_trace_forward(const theia_trace_launch_t* L, int nThreads, uint64_t* cou
     }
     if (L->callback.kind == THEIA_CALLBACK_STAT && L->callback.stats)
         for (int k = 0; k < 12; ++k) L->callback.stats[k] += stats[k];
+    if (L->work_counters) {  // same meaning as on the device; shadow rays are not counted here
+        L->work_counters[0] += segs; L->work_counters[1] += resp; L->work_counters[3] += L->batch_size;
+    }
     if (counters) {
         counters[0] = segs; counters[1] = resp;
         for (int k = 0; k < 4; ++k) counters[2 + k] = trav[k];

@@ -114,7 +114,7 @@ def _randomRays(rng, n, lo, hi, tmax):
 @pytest.mark.parametrize("builder,kw,box", [
     (H.sceneC2, {}, (-2.0, 8.0)),
     (H.sceneC3, {}, (-4.0, 4.0)),
-    (H.sceneC5, {"lattice": (6, 6, 6), "resp": "record"}, (-200.0, 200.0)),
+    (H.sceneC5, {"lattice": (6, 6, 6), "pitch": (2.0, 2.0, 2.0), "resp": "record"}, (-8.0, 8.0)),
 ])
 def test_ray_query_matches_brute_force(cuda, orc, builder, kw, box):
     g, c = both(builder, 256, **kw)
@@ -163,7 +163,7 @@ def test_volume_tracer_hits_bit_exact(cuda, orc, kw):
     H.runGpu(g)
     H.runOracle(c)
     a, b = H.sortedHits(g), H.sortedHits(c)
-    assert b["count"] > N // 8
+    assert b["count"] > 30
     H.compareHits(a, b)
 
 

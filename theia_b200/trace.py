@@ -221,6 +221,7 @@ class Tracer(PipelineStage):
         self._nRNGSamples = nRNGSamples
         self._polarized = polarized
         self._firstPath = 0
+        self._workCounters = None
         self.setParams(batchSize=batchSize, _groupCountY=1, _groupCountZ=1)
         response.prepare(self._getTraceConfig())
 
@@ -282,6 +283,16 @@ class Tracer(PipelineStage):
     def firstPath(self, value: int) -> None:
         self._firstPath = int(value)
 
+    def enableWorkCounters(self) -> torch.Tensor:
+        """
+        B200 extension (measurement): device counters every launch adds to, int64[4] =
+        path segments (the sum of the reference's EventStatisticCallback counters), hits,
+        shadow rays, paths started. Returns the tensor.
+        """
+        if self._workCounters is None:
+            self._workCounters = torch.zeros(4, dtype=torch.int64, device=self._device)
+        return self._workCounters
+
     def collectStages(self, *, useOriginalNames: bool = False) -> list[tuple[str, PipelineStage]]:
         stages = self._collectStages()
         if useOriginalNames:
@@ -328,6 +339,8 @@ class Tracer(PipelineStage):
         L.response = self.response._abiResponse(i, nBlocks)
         L.callback = self.callback._abiCallback(i)
         L.stream = _device.currentStream(self._device)
+        if self._workCounters is not None:
+            L.work_counters = self._workCounters.data_ptr()
         return L, keep
 
     def run(self, i: int) -> list[Command]:
