@@ -277,6 +277,12 @@ typedef struct theia_trace_launch {
      * to: path segments (trace() executions, the reference's EventStatisticCallback sum),
      * responses (hits), shadow rays, paths started. */
     uint64_t *work_counters;
+    /* B200 extension: device scratch memory for the wavefront form of the scene tracer
+     * (path state, ray / result buffers, queues; size from theia_trace_workspace_size).
+     * NULL selects the single-launch form (every path stays in the registers of one thread),
+     * which is meant for small batches. Contents need not be preserved between launches. */
+    void *workspace;
+    uint64_t workspace_bytes;
 } theia_trace_launch_t;
 
 /* ------------------------------------------------------------------ library */
@@ -340,6 +346,9 @@ int theia_tlas_query(const void *tlas_dev, const float *rays_dev, uint32_t n, in
 /* ------------------------------------------------------------------ tracers */
 /* Number of CTAs the launch will use = number of partial histograms it writes. */
 int theia_trace_grid_size(const theia_trace_launch_t *launch, uint32_t *n_blocks);
+/* Bytes of theia_trace_launch_t.workspace the launch needs to run in wavefront form
+ * (0 for the volume tracer, which has no wavefront form). */
+int theia_trace_workspace_size(const theia_trace_launch_t *launch, uint64_t *bytes);
 /* Runs VolumeForwardTracer / SceneForwardTracer for one batch. */
 int theia_trace_forward(const theia_trace_launch_t *launch);
 

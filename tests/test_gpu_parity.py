@@ -179,12 +179,14 @@ SCENE_CASES = [
 ]
 
 
+@pytest.mark.parametrize("mode", ["single", "wavefront"])
 @pytest.mark.parametrize("builder,kw", SCENE_CASES, ids=lambda v: getattr(v, "__name__", None) or ",".join(
     f"{a}={b}" for a, b in v.items()) or "default")
-def test_scene_tracer_hits_bit_exact(cuda, orc, builder, kw):
+def test_scene_tracer_hits_bit_exact(cuda, orc, builder, kw, mode):
     N = 1 << 14
     kw = dict(kw)
     kw.setdefault("resp", "record")
+    kw["mode"] = mode
     g, c = both(builder, N, **kw)
     H.runGpu(g)
     H.runOracle(c)
@@ -194,7 +196,9 @@ def test_scene_tracer_hits_bit_exact(cuda, orc, builder, kw):
 
 
 @pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict()), (H.volumeScenario, dict(mis=False)),
-                                        (H.sceneC2, dict(lightKind="cone")), (H.sceneC3, dict())])
+                                        (H.sceneC2, dict(lightKind="cone")), (H.sceneC3, dict()),
+                                        (H.sceneC2, dict(lightKind="cone", mode="wavefront")),
+                                        (H.sceneC3, dict(mode="wavefront"))])
 def test_event_statistics_match(cuda, orc, builder, kw):
     N = 1 << 14
     g, c = both(builder, N, resp="empty", callback="stat", **kw)
@@ -205,7 +209,8 @@ def test_event_statistics_match(cuda, orc, builder, kw):
     assert got[0] == N
 
 
-@pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict(polarized=True, water=True)), (H.sceneC2, dict())])
+@pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict(polarized=True, water=True)), (H.sceneC2, dict()),
+                                        (H.sceneC2, dict(mode="wavefront")), (H.sceneC3, dict(mode="wavefront"))])
 def test_track_record_matches(cuda, orc, builder, kw):
     N = 2048
     g, c = both(builder, N, resp="empty", callback="track", **kw)
@@ -219,7 +224,8 @@ def test_track_record_matches(cuda, orc, builder, kw):
         assert np.array_equal(tg[k, :n].view(np.uint32), tc[k, :n].view(np.uint32)), f"track {k}"
 
 
-@pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict()), (H.sceneC3, dict()),
+@pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict()), (H.sceneC3, dict(mode="single")),
+                                        (H.sceneC3, dict(mode="wavefront")),
                                         (H.sceneC2, dict(lightKind="cone", polarized=False))])
 def test_histogram_matches_oracle(cuda, orc, builder, kw):
     N = 1 << 16

@@ -97,6 +97,8 @@ class TraceLaunch(Structure):
         ("tlas", c_void_p),
         ("stream", c_void_p),
         ("work_counters", c_void_p),
+        ("workspace", c_void_p),
+        ("workspace_bytes", c_uint64),
     ]
 
 

@@ -31,6 +31,7 @@ SYMBOLS = {
                                  c_void_p]),
     "theia_tlas_query": (c_int, [c_void_p, c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p]),
     "theia_trace_grid_size": (c_int, [POINTER(_abi.TraceLaunch), POINTER(c_uint32)]),
+    "theia_trace_workspace_size": (c_int, [POINTER(_abi.TraceLaunch), POINTER(c_uint64)]),
     "theia_trace_forward": (c_int, [POINTER(_abi.TraceLaunch)]),
     "theia_hist_reduce": (c_int, [c_void_p, c_uint32, c_uint32, c_float, c_void_p, c_int, c_void_p]),
     "theia_hit_replay": (c_int, [c_void_p, c_uint32, c_uint32, POINTER(_abi.Response), c_uint32, c_void_p]),

@@ -5,8 +5,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
-#include "trace_scene.cuh"
 #include "trace_volume.cuh"
+#include "wavefront.cuh"
 
 namespace theia {
 
@@ -252,6 +252,82 @@ static int plan(const theia_trace_launch_t* L, const DeviceLaunch& D, KernelPlan
     return 0;
 }
 
+// zeroes the wavefront counters selected by mask
+__global__ void wfResetKernel(uint32_t* counters, uint32_t mask) {
+    if (threadIdx.x < WF_NCOUNTERS && ((mask >> threadIdx.x) & 1u)) counters[threadIdx.x] = 0u;
+}
+
+static int persistentGrid(const void* fn, size_t smem, uint32_t* grid) {
+    int dev = 0, sms = 0, perSm = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fn, (int)TRACE_THREADS, smem));
+    if (perSm < 1) { setError("wavefront kernel does not fit on an SM"); return -1; }
+    *grid = (uint32_t)sms * (uint32_t)perSm;
+    return 0;
+}
+
+static size_t workspaceBytes(const theia_trace_launch_t* L) {
+    if (L->tracer != THEIA_TRACER_SCENE_FORWARD) return 0;
+    return layoutWorkspace(nullptr, L->batch_size, L->polarized != 0, L->guide.kind != THEIA_GUIDE_NONE, nullptr);
+}
+
+// Scene tracer, wavefront form: generate, then per segment trace + shade (+ shadow trace +
+// shadow shade with a target guide). All launches are asynchronous on the caller's stream.
+static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D) {
+    const bool pol = L->polarized != 0, guide = D.guide.kind != THEIA_GUIDE_NONE;
+    cudaStream_t st = (cudaStream_t)L->stream;
+    if (((uintptr_t)L->workspace & 255u) != 0) { setError("workspace must be 256 byte aligned"); return -1; }
+    Workspace ws;
+    size_t need = layoutWorkspace(L->workspace, D.batch_size, pol, guide, &ws);
+    if (L->workspace_bytes < need) {
+        setError("workspace too small: %llu bytes given, %llu needed", (unsigned long long)L->workspace_bytes,
+                 (unsigned long long)need);
+        return -1;
+    }
+    const size_t histSmem = (D.response.kind == THEIA_RESPONSE_HISTOGRAM && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
+    const void* genFn = pol ? (const void*)wfGenerateKernel<true> : (const void*)wfGenerateKernel<false>;
+    const void* shadeFn = pol ? (const void*)wfShadeKernel<true> : (const void*)wfShadeKernel<false>;
+    const void* shadowFn = pol ? (const void*)wfShadeShadowKernel<true> : (const void*)wfShadeShadowKernel<false>;
+    uint32_t gGen, gShade, gShadow, gTrace;
+    if (persistentGrid(genFn, 0, &gGen) || persistentGrid(shadeFn, histSmem, &gShade) ||
+        persistentGrid(shadowFn, histSmem, &gShadow) || persistentGrid((const void*)wfTraceKernel, 0, &gTrace))
+        return -1;
+    // partial histograms: one row per CTA of the shading grids
+    uint32_t need128 = blocksFor(D.batch_size, TRACE_THREADS);
+    if (gGen > need128) gGen = need128;
+    if (gShade > need128) gShade = need128;
+    if (gShadow > need128) gShadow = need128;
+    if (gTrace > need128) gTrace = need128;
+    wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 0xFFu);
+    {
+        void* args[] = {(void*)&D, (void*)&ws};
+        CUDA_TRY(cudaLaunchKernel(genFn, dim3(gGen), dim3(TRACE_THREADS), args, 0, st));
+    }
+    uint32_t cur = 0;
+    for (uint32_t it = 1; it <= D.path_length; ++it) {
+        const uint32_t nextBit = cur ? (1u << WF_CNT_QUEUE0) : (1u << WF_CNT_QUEUE1);
+        wfResetKernel<<<1, 32, 0, st>>>(ws.counters, nextBit | (1u << WF_CNT_SHADOW) | (1u << WF_CNT_CURSOR));
+        wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.ray, ws.result, ws.queue[cur],
+                                                        ws.counters + (cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0),
+                                                        ws.counters + WF_CNT_CURSOR, 1u);
+        {
+            void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
+            CUDA_TRY(cudaLaunchKernel(shadeFn, dim3(gShade), dim3(TRACE_THREADS), args, histSmem, st));
+        }
+        if (guide && it < D.path_length) {
+            wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 1u << WF_CNT_CURSOR);
+            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.shadowRay, ws.shadowResult, ws.shadowQueue,
+                                                            ws.counters + WF_CNT_SHADOW, ws.counters + WF_CNT_CURSOR, 2u);
+            void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
+            CUDA_TRY(cudaLaunchKernel(shadowFn, dim3(gShadow), dim3(TRACE_THREADS), args, histSmem, st));
+        }
+        cur ^= 1u;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
 }  // namespace theia
 
 using namespace theia;
@@ -341,11 +417,21 @@ int theia_trace_grid_size(const theia_trace_launch_t* launch, uint32_t* n_blocks
     return 0;
 }
 
+int theia_trace_workspace_size(const theia_trace_launch_t* launch, uint64_t* bytes) {
+    if (!launch || !bytes || launch->struct_size != sizeof(theia_trace_launch_t)) {
+        setError("theia_trace_workspace_size: bad argument");
+        return -1;
+    }
+    *bytes = workspaceBytes(launch);
+    return 0;
+}
+
 int theia_trace_forward(const theia_trace_launch_t* launch) {
     DeviceLaunch D;
     KernelPlan K;
     if (translate(launch, D)) return -1;
     if (D.batch_size == 0) return 0;
+    if (launch->tracer == THEIA_TRACER_SCENE_FORWARD && launch->workspace) return launchWavefront(launch, D);
     if (plan(launch, D, K)) return -1;
     void* args[] = {&D};
     CUDA_TRY(cudaLaunchKernel(K.fn, dim3(K.grid), dim3(TRACE_THREADS), args, K.smem, (cudaStream_t)launch->stream));

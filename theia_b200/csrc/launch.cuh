@@ -208,7 +208,7 @@ TDEV void sinkInit(const DeviceLaunch& P, SinkShared* sh, float* hist) {
     for (uint32_t i = threadIdx.x; i < 16; i += blockDim.x) {
         if (i < 12) sh->stats[i] = 0; else sh->work[i - 12] = 0;
     }
-    if (P.response.kind == THEIA_RESPONSE_HISTOGRAM && P.response.hist_shared)
+    if (hist && P.response.kind == THEIA_RESPONSE_HISTOGRAM && P.response.hist_shared)
         for (uint32_t b = threadIdx.x; b < P.response.n_bins; b += blockDim.x) hist[b] = 0.0f;
     __syncthreads();
 }
@@ -229,7 +229,7 @@ TDEV void sinkFinish(const DeviceLaunch& P, SinkShared* sh, const float* hist, u
         }
     }
     __syncthreads();
-    if (P.response.kind == THEIA_RESPONSE_HISTOGRAM && P.response.hist_shared) {
+    if (hist && P.response.kind == THEIA_RESPONSE_HISTOGRAM && P.response.hist_shared) {
         // sh/response.histogram.glsl:35-45: one partial histogram per work group
         const bool exclusive = gridDim.x <= P.response.hist_capacity;
         float* dst = P.response.hist_partials + (size_t)(blockIdx.x % P.response.hist_capacity) * P.response.n_bins;

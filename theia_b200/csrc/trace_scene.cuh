@@ -57,7 +57,7 @@ TDEV bool traceShadowRay(const DeviceLaunch& P, const SceneView& sc, Ray ray, ve
 }
 
 template <bool POL>
-__global__ void __launch_bounds__(128) sceneForwardKernel(const __grid_constant__ DeviceLaunch P) {
+__global__ void __launch_bounds__(128, 4) sceneForwardKernel(const __grid_constant__ DeviceLaunch P) {
     extern __shared__ float4 sharedRaw[];
     __shared__ SinkShared sh;
     // dynamic shared memory: [top TLAS nodes][histogram]

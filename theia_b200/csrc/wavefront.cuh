@@ -1,0 +1,544 @@
+// Wavefront form of the SceneForwardTracer (sh/tracer.scene.forward.glsl +
+// sh/scene.traverse.glsl of the reference).
+//
+// The path state lives in HBM as structure-of-arrays (one slot per path of the batch, slot =
+// path number) and each path segment is split into kernels joined by queues of live slots:
+//
+//   generate : sample wavelength + light, create the ray, prepare the first ray query
+//   per segment:
+//     trace  : ray queries only (BVH traversal + triangle tests). Persistent warps; a lane
+//              that finishes its ray immediately fetches the next one (warp-aggregated
+//              counter), so lanes never wait for the longest traversal of their warp.
+//     shade  : ray query result -> SurfaceHit, propagation, surface interaction (Fresnel
+//              reflect / transmit / detect) or volume scatter, responses, event callbacks,
+//              then the preparation of the next ray query. Live paths are appended to the
+//              next queue with one atomic per warp (ballot + prefix popcount).
+//     with a target guide, volume scatter events emit two shadow rays instead (phase sample,
+//     guide sample); a second trace + shade pass turns them into responses, performs the
+//     deferred phase function scatter and prepares the next query.
+//
+// Per path the sequence of arithmetic operations and of random draws is exactly that of the
+// monolithic kernel (trace_scene.cuh) and of the reference shader, so results are identical;
+// only the order in which hits reach the response differs.
+#pragma once
+#include "trace_scene.cuh"
+#include <cooperative_groups.h>
+
+namespace theia {
+
+// ------------------------------------------------------------------ workspace
+enum : uint32_t {
+    WF_PX, WF_PY, WF_PZ, WF_DX, WF_DY, WF_DZ, WF_MED_LO, WF_MED_HI, WF_LAMBDA, WF_TIME, WF_LIN, WF_LOG,
+    WF_N, WF_VG, WF_MUS, WF_MUE, WF_DIM, WF_FLAGS, WF_NFIELDS_UNPOL,
+    WF_S0 = WF_NFIELDS_UNPOL, WF_S1, WF_S2, WF_S3, WF_R0, WF_R1, WF_R2, WF_NFIELDS_POL
+};
+// WF_FLAGS: bits 0-15 segment number "it", bit 16 allowResponse, bit 17 mis_target
+enum : uint32_t { WF_ALLOW = 1u << 16, WF_MIS_TARGET = 1u << 17 };
+enum : uint32_t { WF_CNT_QUEUE0 = 0, WF_CNT_QUEUE1 = 1, WF_CNT_SHADOW = 2, WF_CNT_CURSOR = 3, WF_NCOUNTERS = 8 };
+
+struct Workspace {
+    uint32_t capacity;   // slots = paths per batch
+    uint32_t* counters;  // [WF_NCOUNTERS]
+    uint32_t* state;     // [nFields][capacity] words
+    float4* ray;         // [capacity][2]: (origin, tmax), (direction, sampledDist)
+    uint4* result;       // [capacity]: instance slot (0xFFFFFFFF = miss), primitive, u, v
+    float4* shadowRay;   // [2 * capacity][2]: (origin, tmax), (direction, weight)
+    uint4* shadowResult; // [2 * capacity]
+    uint32_t* queue[2];  // [capacity] live slots, ping-pong
+    uint32_t* shadowQueue;  // [capacity] slots with a pending pair of shadow rays
+};
+
+static inline size_t wfAlign(size_t v) { return (v + 255) & ~size_t(255); }
+
+// Carves the workspace out of a caller supplied buffer (base may be null to get the size).
+static inline size_t layoutWorkspace(void* base, uint32_t capacity, bool polarized, bool guide, Workspace* ws) {
+    size_t off = 0;
+    char* b = (char*)base;
+    auto take = [&](size_t bytes) { void* p = b ? b + off : nullptr; off += wfAlign(bytes); return p; };
+    const size_t C = capacity > 0 ? capacity : 1;
+    const size_t nFields = polarized ? WF_NFIELDS_POL : WF_NFIELDS_UNPOL;
+    Workspace w;
+    w.capacity = capacity;
+    w.counters = (uint32_t*)take(4 * WF_NCOUNTERS);
+    w.state = (uint32_t*)take(4 * nFields * C);
+    w.ray = (float4*)take(32 * C);
+    w.result = (uint4*)take(16 * C);
+    w.queue[0] = (uint32_t*)take(4 * C);
+    w.queue[1] = (uint32_t*)take(4 * C);
+    if (guide) {
+        w.shadowRay = (float4*)take(64 * C);
+        w.shadowResult = (uint4*)take(32 * C);
+        w.shadowQueue = (uint32_t*)take(4 * C);
+    } else {
+        w.shadowRay = nullptr; w.shadowResult = nullptr; w.shadowQueue = nullptr;
+    }
+    if (ws) *ws = w;
+    return off;
+}
+
+// ------------------------------------------------------------------ state access
+template <bool POL>
+TDEV void storeState(const Workspace& ws, uint32_t slot, const Ray& r, uint32_t dim, uint32_t flags) {
+    uint32_t* s = ws.state + slot;
+    const size_t C = ws.capacity;
+    s[WF_PX * C] = f2u(r.position.x); s[WF_PY * C] = f2u(r.position.y); s[WF_PZ * C] = f2u(r.position.z);
+    s[WF_DX * C] = f2u(r.direction.x); s[WF_DY * C] = f2u(r.direction.y); s[WF_DZ * C] = f2u(r.direction.z);
+    s[WF_MED_LO * C] = (uint32_t)r.medium; s[WF_MED_HI * C] = (uint32_t)(r.medium >> 32);
+    s[WF_LAMBDA * C] = f2u(r.wavelength); s[WF_TIME * C] = f2u(r.time);
+    s[WF_LIN * C] = f2u(r.lin_contrib); s[WF_LOG * C] = f2u(r.log_contrib);
+    s[WF_N * C] = f2u(r.constants.n); s[WF_VG * C] = f2u(r.constants.vg);
+    s[WF_MUS * C] = f2u(r.constants.mu_s); s[WF_MUE * C] = f2u(r.constants.mu_e);
+    s[WF_DIM * C] = dim; s[WF_FLAGS * C] = flags;
+    if (POL) {
+        s[WF_S0 * C] = f2u(r.stokes.x); s[WF_S1 * C] = f2u(r.stokes.y); s[WF_S2 * C] = f2u(r.stokes.z);
+        s[WF_S3 * C] = f2u(r.stokes.w);
+        s[WF_R0 * C] = f2u(r.polRef.x); s[WF_R1 * C] = f2u(r.polRef.y); s[WF_R2 * C] = f2u(r.polRef.z);
+    }
+}
+template <bool POL>
+TDEV void loadState(const Workspace& ws, uint32_t slot, Ray& r, uint32_t& dim, uint32_t& flags) {
+    const uint32_t* s = ws.state + slot;
+    const size_t C = ws.capacity;
+    r.position = {u2f(s[WF_PX * C]), u2f(s[WF_PY * C]), u2f(s[WF_PZ * C])};
+    r.direction = {u2f(s[WF_DX * C]), u2f(s[WF_DY * C]), u2f(s[WF_DZ * C])};
+    r.medium = (uint64_t)s[WF_MED_LO * C] | ((uint64_t)s[WF_MED_HI * C] << 32);
+    r.wavelength = u2f(s[WF_LAMBDA * C]); r.time = u2f(s[WF_TIME * C]);
+    r.lin_contrib = u2f(s[WF_LIN * C]); r.log_contrib = u2f(s[WF_LOG * C]);
+    r.constants = {u2f(s[WF_N * C]), u2f(s[WF_VG * C]), u2f(s[WF_MUS * C]), u2f(s[WF_MUE * C])};
+    dim = s[WF_DIM * C]; flags = s[WF_FLAGS * C];
+    if (POL) {
+        r.stokes = {u2f(s[WF_S0 * C]), u2f(s[WF_S1 * C]), u2f(s[WF_S2 * C]), u2f(s[WF_S3 * C])};
+        r.polRef = {u2f(s[WF_R0 * C]), u2f(s[WF_R1 * C]), u2f(s[WF_R2 * C])};
+    } else {
+        r.stokes = {1.0f, 0.0f, 0.0f, 0.0f};
+        r.polRef = v3(0.0f);
+    }
+}
+
+// Appends the slots of the lanes with `push` to a queue: one atomic per warp.
+// MUST be called by all 32 lanes.
+TDEV void queuePush(uint32_t* queue, uint32_t* counter, bool push, uint32_t slot) {
+    uint32_t m = __ballot_sync(FULL_MASK, push);
+    if (m == 0) return;
+    uint32_t leader = __ffs(m) - 1, base = 0;
+    if (laneId() == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(FULL_MASK, base, leader);
+    if (push) queue[base + __popc(m & laneMaskLt())] = slot;
+}
+
+// ------------------------------------------------------------------ trace kernel
+// Ray queries of a queue. rays[2 r], rays[2 r + 1] hold ray r = slot * raysPerEntry + j of the
+// queue entries; results[r] receives (instance slot | ~0, primitive, u, v).
+// One loop iteration pops one stack entry (node, instance or leaf) per lane; a lane whose
+// stack runs empty writes its result and fetches the next ray (lanes take rays in private
+// chunks of WF_FETCH from a global cursor, one atomic per chunk and coalesced group).
+#define WF_FETCH 4u
+enum : uint32_t { WE_TLAS = 0u, WE_INST = 1u, WE_BLAS = 2u, WE_LEAF = 3u };
+
+__global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
+                                                         uint4* __restrict__ results, const uint32_t* __restrict__ queue,
+                                                         const uint32_t* __restrict__ countPtr, uint32_t* cursor,
+                                                         uint32_t raysPerEntry) {
+    namespace cg = cooperative_groups;
+    __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
+    WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
+    const uint32_t nTop = stageTopNodes(tlas, sharedTop);
+    __syncthreads();
+    const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
+    const uint32_t total = *countPtr * raysPerEntry;
+
+    uint32_t stackKey[THEIA_STACK_SIZE];
+    float stackT[THEIA_STACK_SIZE];
+    int sp = 0;
+    bool have = false;
+    uint32_t chunkNext = 0, chunkEnd = 0, rid = 0;
+    float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 0, tmax = 0;
+    SlabRay world = {0, 0, 0, 0, 0, 0}, obj = {0, 0, 0, 0, 0, 0};
+    WoopRay wr;
+    wr.kx = wr.ky = wr.kz = 0; wr.Sx = wr.Sy = wr.Sz = 0.0f;
+    wr.o[0] = wr.o[1] = wr.o[2] = wr.d[0] = wr.d[1] = wr.d[2] = 0.0f;
+    int32_t curInst = -1, curSlot = -1;
+    const WideNode* blasNodes = nullptr;
+    const TriRec* blasTris = nullptr;
+    bool bestValid = false;
+    int32_t bestInst = -1, bestSlot = -1, bestPrim = -1;
+    float bestT = 0.0f, bestU = 0.0f, bestV = 0.0f;
+
+    while (true) {
+        if (sp == 0) {
+            if (have) {
+                results[rid] = make_uint4(bestValid ? (uint32_t)bestSlot : 0xFFFFFFFFu, (uint32_t)bestPrim, f2u(bestU), f2u(bestV));
+                have = false;
+            }
+            if (chunkNext == chunkEnd) {
+                cg::coalesced_group g = cg::coalesced_threads();
+                uint32_t base = 0;
+                if (g.thread_rank() == 0) base = atomicAdd(cursor, WF_FETCH * g.size());
+                base = g.shfl(base, 0);
+                chunkNext = base + WF_FETCH * g.thread_rank();
+                chunkEnd = chunkNext + WF_FETCH;
+            }
+            const uint32_t i = chunkNext++;
+            if (i >= total) break;
+            rid = __ldg(queue + i / raysPerEntry) * raysPerEntry + i % raysPerEntry;
+            const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
+            ox = a.x; oy = a.y; oz = a.z; tmax = a.w; dx = b.x; dy = b.y; dz = b.z;
+            world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
+            bestValid = false; bestInst = -1; bestSlot = -1; bestPrim = -1; bestT = 0.0f; bestU = 0.0f; bestV = 0.0f;
+            stackKey[0] = WE_TLAS << 30;
+            stackT[0] = 0.0f;
+            sp = 1;
+            have = true;
+        }
+        --sp;
+        const uint32_t key = stackKey[sp];
+        const float tEntry = stackT[sp];
+        const float lim = bestValid ? bestT : tmax;
+        if (tEntry > lim) continue;
+        const uint32_t type = key >> 30, payload = key & 0x3FFFFFFFu;
+
+        if (type == WE_LEAF) {
+            const uint32_t first = payload >> 2, count = (payload & 3u) + 1u;
+            for (uint32_t k = 0; k < count; ++k) {
+                const float4* tp = reinterpret_cast<const float4*>(blasTris + first + k);
+                const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                const float v0[3] = {a.x, a.y, a.z}, v1[3] = {b.x, b.y, b.z}, v2[3] = {c.x, c.y, c.z};
+                const int32_t prim = (int32_t)f2u(a.w);
+                float t, u, v;
+                if (!woopIntersect(wr, v0, v1, v2, tmax, &t, &u, &v)) continue;
+                const bool better = !bestValid || t < bestT ||
+                                    (t == bestT && (curInst < bestInst || (curInst == bestInst && prim < bestPrim)));
+                if (better) { bestValid = true; bestInst = curInst; bestSlot = curSlot; bestPrim = prim; bestT = t; bestU = u; bestV = v; }
+            }
+            continue;
+        }
+        if (type == WE_INST) {
+            const InstanceRec* in = sc.instances + payload;
+            const float4* q = reinterpret_cast<const float4*>(in);
+            const float4 r0 = __ldg(q), r1 = __ldg(q + 1), r2 = __ldg(q + 2);
+            const float m[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
+            const float o[3] = {ox, oy, oz}, d[3] = {dx, dy, dz};
+            transformPoint(m, o, wr.o);
+            transformVector(m, d, wr.d);
+            woopSetup(wr);
+            obj = {wr.o[0], wr.o[1], wr.o[2], safeInv(wr.d[0]), safeInv(wr.d[1]), safeInv(wr.d[2])};
+            const uint4 ptrs = __ldg(reinterpret_cast<const uint4*>(in) + 3);
+            blasNodes = reinterpret_cast<const WideNode*>((uint64_t)ptrs.x | ((uint64_t)ptrs.y << 32));
+            blasTris = reinterpret_cast<const TriRec*>((uint64_t)ptrs.z | ((uint64_t)ptrs.w << 32));
+            curSlot = (int32_t)payload;
+            curInst = (int32_t)__ldg(&in->pad);
+            stackKey[sp] = WE_BLAS << 30;
+            stackT[sp] = tEntry;
+            ++sp;
+            continue;
+        }
+        const bool inBlas = type == WE_BLAS;
+        NodeRegs n;
+        if (inBlas) n = loadNode(blasNodes + payload);
+        else if (payload < sc.nTop) n = loadNodeShared(sc.topNodes + payload);
+        else n = loadNode(sc.nodes + payload);
+        float tmin[8];
+        uint32_t mask = testChildren(n, inBlas ? obj : world, lim, tmin);
+        if (mask == 0) continue;
+        const uint32_t imask = n.a.w >> 24;
+        const uint32_t axis = n.b.x >> 30, childBase = n.b.x & 0x3FFFFFFFu;
+        const SlabRay& rr = inBlas ? obj : world;
+        const float idirAxis = axis == 0 ? rr.ix : (axis == 1 ? rr.iy : rr.iz);
+        const bool forward = idirAxis >= 0.0f;
+        while (mask) {
+            const int i = forward ? (31 - __clz(mask)) : (__ffs(mask) - 1);  // farthest slot first
+            mask &= ~(1u << i);
+            const uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, i & 3);
+            uint32_t k;
+            if ((imask >> i) & 1u) k = ((inBlas ? WE_BLAS : WE_TLAS) << 30) | (childBase + meta - 1u);
+            else if (inBlas) k = (WE_LEAF << 30) | ((n.b.y + (meta >> 3)) << 2) | ((meta & 7u) - 1u);
+            else k = (WE_INST << 30) | (n.b.y + (meta >> 3));
+            if (sp < THEIA_STACK_SIZE) {
+                stackKey[sp] = k;
+                stackT[sp] = tmin[i];
+                ++sp;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ shading side
+enum : uint32_t { WF_SEQ1 = 1u << 18 };  // one response was already committed in this event
+
+// First half of trace() (sh/scene.traverse.glsl:280-323): health check, free path sample,
+// extension towards the target guide; writes the ray query of the slot.
+template <bool POL>
+TDEV bool prepareQuery(const DeviceLaunch& P, const Workspace& ws, uint32_t slot, const Ray& ray, Rng& rng,
+                       bool allowResponse, bool GUIDE, bool& misTarget) {
+    misTarget = false;
+    if (isRayBad(ray)) return false;
+    vec3 dir = normalize(ray.direction);
+    float dist = sampleScatterLength(ray, P.propagation, rng.next());
+    float sampledDist = dist;
+    if (GUIDE) {
+        TargetGuideSample guideSample = evalTargetGuide(P.guide, ray.position, dir);
+        bool mis = allowResponse && guideSample.prob > 0.0f;
+        if (mis) {
+            mis = guideSample.dist > dist;
+            dist = max_(guideSample.dist, dist);
+        }
+        misTarget = mis;
+    }
+    ws.ray[2 * (size_t)slot] = make_float4(ray.position.x, ray.position.y, ray.position.z, dist);
+    ws.ray[2 * (size_t)slot + 1] = make_float4(dir.x, dir.y, dir.z, sampledDist);
+    return true;
+}
+
+// End of a segment (sh/tracer.scene.forward.glsl:87-104): event callback, stop conditions,
+// then the next ray query. MUST be called by all 32 lanes.
+template <bool POL>
+TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* sh, bool active, uint32_t slot, Ray& ray,
+                        Rng& rng, int result, uint32_t it, bool GUIDE, uint32_t* nextQueue, uint32_t* nextCounter,
+                        uint32_t& nSegments) {
+    onEvent<POL>(P.callback, sh, active, ray, result, slot, it);
+    bool cont = active && result >= 0;
+    bool maxIter = false, allow = true;
+    if (cont) {
+        allow = GUIDE ? (result != THEIA_RESULT_RAY_SCATTERED) : true;
+        if (it == P.path_length) { maxIter = true; cont = false; }
+        else it++;
+    }
+    onEvent<POL>(P.callback, sh, maxIter, ray, THEIA_RESULT_MAX_ITER, slot, P.path_length + 1);
+    bool ok = false, mis = false;
+    if (cont) {
+        nSegments++;
+        ok = prepareQuery<POL>(P, ws, slot, ray, rng, allow, GUIDE, mis);
+    }
+    onEvent<POL>(P.callback, sh, cont && !ok, ray, THEIA_ERROR_RAY_BAD, slot, it);
+    if (ok) storeState<POL>(ws, slot, ray, rng.dim, it | (allow ? WF_ALLOW : 0u) | (mis ? WF_MIS_TARGET : 0u));
+    queuePush(nextQueue, nextCounter, ok, slot);
+}
+
+TDEV uint32_t wfWarpBase(uint32_t& stride) {
+    const uint32_t warpsPerCta = blockDim.x >> 5;
+    stride = gridDim.x * warpsPerCta * 32u;
+    return (blockIdx.x * warpsPerCta + (threadIdx.x >> 5)) * 32u;
+}
+
+// generate: sh/tracer.scene.forward.glsl:50-66
+template <bool POL>
+__global__ void __launch_bounds__(128, 4) wfGenerateKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws) {
+    __shared__ SinkShared sh;
+    sinkInit(P, &sh, nullptr);
+    const bool GUIDE = P.guide.kind != THEIA_GUIDE_NONE;
+    uint32_t nSegments = 0, nPaths = 0, stride;
+    for (uint32_t base = wfWarpBase(stride); base < P.batch_size; base += stride) {
+        const uint32_t k = base + laneId();
+        const bool active = k < P.batch_size;
+        Ray ray;
+        Rng rng = makeRng(&P.rng, P.first_path + k);
+        bool ok = false, mis = false;
+        const bool allow = P.disable_direct_lighting == 0;
+        if (active) {
+            ray = sampleRay<POL>(P.wavelength, P.light, P.medium, rng);
+            nPaths++;
+        }
+        onEvent<POL>(P.callback, &sh, active, ray, THEIA_RESULT_RAY_CREATED, k, 0);
+        if (active) {
+            nSegments++;
+            ok = prepareQuery<POL>(P, ws, k, ray, rng, allow, GUIDE, mis);
+        }
+        onEvent<POL>(P.callback, &sh, active && !ok, ray, THEIA_ERROR_RAY_BAD, k, 1);
+        if (ok) storeState<POL>(ws, k, ray, rng.dim, 1u | (allow ? WF_ALLOW : 0u) | (mis ? WF_MIS_TARGET : 0u));
+        queuePush(ws.queue[0], ws.counters + WF_CNT_QUEUE0, ok, k);
+    }
+    sinkFinish(P, &sh, nullptr, nSegments, 0, 0, nPaths);
+}
+
+TDEV RayHit resultToHit(uint4 r) {
+    RayHit q;
+    q.valid = r.x != 0xFFFFFFFFu;
+    q.slot = (int32_t)r.x; q.instance = -1; q.prim = (int32_t)r.y; q.t = 0.0f; q.u = u2f(r.z); q.v = u2f(r.w);
+    return q;
+}
+
+// shade: second half of trace() (sh/scene.traverse.glsl:324-352) + processInteraction (:361-397)
+template <bool POL>
+__global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
+                                                         uint32_t cur) {
+    extern __shared__ float sharedHist[];
+    __shared__ SinkShared sh;
+    sinkInit(P, &sh, sharedHist);
+    float* hist = sinkHist(P, sharedHist);
+    const SceneView sc = makeSceneView(P.tlas, nullptr, 0);
+    const bool GUIDE = P.guide.kind != THEIA_GUIDE_NONE;
+    const uint32_t count = ws.counters[cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0];
+    const uint32_t* queue = ws.queue[cur];
+    uint32_t* nextQueue = ws.queue[cur ^ 1u];
+    uint32_t* nextCounter = ws.counters + (cur ? WF_CNT_QUEUE0 : WF_CNT_QUEUE1);
+    uint32_t nSegments = 0, nResponses = 0, nShadow = 0, stride;
+
+    for (uint32_t base = wfWarpBase(stride); base < count; base += stride) {
+        const uint32_t i = base + laneId();
+        const bool active = i < count;
+        const uint32_t slot = active ? queue[i] : 0u;
+        const uint32_t idx = P.first_path + slot;
+        Ray ray;
+        uint32_t dim = 0, flags = 1u;
+        if (active) loadState<POL>(ws, slot, ray, dim, flags);
+        Rng rng = makeRng(&P.rng, idx);
+        rng.dim = dim;
+        const uint32_t it = flags & 0xFFFFu;
+        const bool allowResponse = (flags & WF_ALLOW) != 0, misTarget = (flags & WF_MIS_TARGET) != 0;
+        const uint32_t tagEvent = it - 1;
+        uint32_t hitSeq = 0;
+        HitItem item;
+        bool has = false;
+        SurfaceHit hit;
+        hit.valid = false;
+        int result = 0;
+        if (active) {
+            const float4 ra = ws.ray[2 * (size_t)slot], rb = ws.ray[2 * (size_t)slot + 1];
+            const RayHit q = resultToHit(ws.result[slot]);
+            float dist = ra.w;
+            const float sampledDist = rb.w;
+            int queryResult = processRayQuery(sc, ray, q, hit);
+            if (hit.valid) dist = distance(ray.position, hit.worldPos);
+            if (GUIDE && misTarget && hit.valid && dist > sampledDist && queryResult >= 0) {
+                has = processShadowRay<POL>(P, ray, hit, item);
+                hit.valid = false;
+                dist = sampledDist;
+            }
+            int propResult = propagateRay(ray, dist, P.propagation);
+            updateRayIS(ray, dist, P.propagation, hit.valid);
+            result = queryResult <= THEIA_ERROR_MAX_VALUE ? queryResult : propResult;
+        }
+        commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
+        hitSeq += has ? 1u : 0u;
+        has = false;
+
+        const bool interact = active && result >= 0;
+        const bool last = it == P.path_length;
+        bool wantMIS = false;
+        if (interact && hit.valid) {
+            // processHit (:73-154)
+            result = propagateRayToHit<POL>(ray, hit.worldPos, hit.rayNrm, P.propagation);
+            if (result >= 0) {
+                result = THEIA_RESULT_RAY_HIT;
+                bool isAbs = (hit.flags & MATERIAL_BLACK_BODY_BIT) != 0;
+                bool isTarget = (hit.flags & MATERIAL_DETECTOR_BIT) != 0;
+                bool volBorder = (hit.flags & MATERIAL_VOLUME_BORDER_BIT) != 0;
+                bool canTransmit = (hit.flags & MATERIAL_NO_TRANSMIT_BWD_BIT) == 0;  // sic (:96-97)
+                bool canReflect = (hit.flags & MATERIAL_NO_REFLECT_BWD_BIT) == 0;
+                Reflectance surface = fresnelReflect(ray, hit);
+                if (allowResponse && isTarget && (P.objectId < 0 || hit.customId == P.objectId)) {
+                    sceneCreateResponse<POL>(P, ray, hit, surface, isAbs, item);
+                    has = true;
+                    result = THEIA_RESULT_RAY_DETECTED;
+                }
+                if (isAbs) {
+                    result = THEIA_RESULT_RAY_ABSORBED;
+                } else if (P.disable_volume_border == 0 && volBorder) {
+                    crossBorder(ray, hit);
+                    result = THEIA_RESULT_VOLUME_HIT;
+                } else if (P.disable_transmission == 0) {
+                    float r = 0.5f * (surface.r_s * surface.r_s + surface.r_p * surface.r_p);
+                    if (canReflect && canTransmit) {
+                        if (rng.next() < r) reflectRayIS<POL>(ray, hit, surface);
+                        else transmitRayIS<POL>(ray, hit, surface);
+                    } else if (canReflect) {
+                        reflectRay<POL>(ray, hit, surface);
+                    } else if (canTransmit) {
+                        transmitRay<POL>(ray, hit, surface);
+                    } else {
+                        result = THEIA_RESULT_RAY_ABSORBED;
+                    }
+                } else {
+                    if (canReflect) reflectRay<POL>(ray, hit, surface);
+                    else result = THEIA_RESULT_RAY_ABSORBED;
+                }
+            }
+        } else if (interact) {
+            result = THEIA_RESULT_RAY_SCATTERED;
+            wantMIS = GUIDE && !last;
+        }
+        commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
+
+        if (wantMIS) {
+            // sampleTargetMIS (:234-269): the two shadow rays are traced by the next trace pass
+            float pPP;
+            vec3 dirPhase = scatter(ray.medium, ray.direction, rng.next2(), &pPP);
+            TargetGuideSample targetSample = sampleTargetGuide(P.guide, ray.position, rng);
+            float pTT = targetSample.prob;
+            TargetGuideSample phaseSample = evalTargetGuide(P.guide, ray.position, dirPhase);
+            float pTP = phaseSample.prob;
+            float pPT = scatterProb(ray.medium, ray.direction, targetSample.dir);
+            float wTarget = pTT * pPT / (pTT * pTT + pPT * pPT);
+            float wPhase = pPP * pPP / (pPP * pPP + pTP * pTP);
+            float4* sr = ws.shadowRay + 4 * (size_t)slot;
+            sr[0] = make_float4(ray.position.x, ray.position.y, ray.position.z, phaseSample.dist);
+            sr[1] = make_float4(dirPhase.x, dirPhase.y, dirPhase.z, wPhase);
+            sr[2] = make_float4(ray.position.x, ray.position.y, ray.position.z, targetSample.dist);
+            sr[3] = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, wTarget);
+            nShadow += 2;
+            storeState<POL>(ws, slot, ray, rng.dim, it | (hitSeq ? WF_SEQ1 : 0u));
+        } else if (interact && !hit.valid && !last) {
+            scatterRay<POL>(ray, rng.next2());  // volume scatter (:386-393)
+        }
+        queuePush(ws.shadowQueue, ws.counters + WF_CNT_SHADOW, wantMIS, slot);
+        finishSegment<POL>(P, ws, &sh, active && !wantMIS, slot, ray, rng, result, it, GUIDE, nextQueue, nextCounter,
+                           nSegments);
+    }
+    sinkFinish(P, &sh, sharedHist, nSegments, nResponses, nShadow, 0);
+}
+
+// second shading pass (target guide only): shadow ray results -> responses
+// (traceShadowRay, sh/scene.traverse.glsl:185-214), then the deferred volume scatter
+template <bool POL>
+__global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
+                                                               uint32_t cur) {
+    extern __shared__ float sharedHist[];
+    __shared__ SinkShared sh;
+    sinkInit(P, &sh, sharedHist);
+    float* hist = sinkHist(P, sharedHist);
+    const SceneView sc = makeSceneView(P.tlas, nullptr, 0);
+    const uint32_t count = ws.counters[WF_CNT_SHADOW];
+    uint32_t* nextQueue = ws.queue[cur ^ 1u];
+    uint32_t* nextCounter = ws.counters + (cur ? WF_CNT_QUEUE0 : WF_CNT_QUEUE1);
+    uint32_t nSegments = 0, nResponses = 0, stride;
+
+    for (uint32_t base = wfWarpBase(stride); base < count; base += stride) {
+        const uint32_t i = base + laneId();
+        const bool active = i < count;
+        const uint32_t slot = active ? ws.shadowQueue[i] : 0u;
+        const uint32_t idx = P.first_path + slot;
+        Ray ray;
+        uint32_t dim = 0, flags = 1u;
+        if (active) loadState<POL>(ws, slot, ray, dim, flags);
+        Rng rng = makeRng(&P.rng, idx);
+        rng.dim = dim;
+        const uint32_t it = flags & 0xFFFFu;
+        const uint32_t tagEvent = it - 1;
+        uint32_t hitSeq = (flags & WF_SEQ1) ? 1u : 0u;
+#pragma unroll 1
+        for (uint32_t j = 0; j < 2; ++j) {
+            HitItem item;
+            bool has = false;
+            if (active) {
+                const float4 a = ws.shadowRay[4 * (size_t)slot + 2 * j], b = ws.shadowRay[4 * (size_t)slot + 2 * j + 1];
+                const RayHit q = resultToHit(ws.shadowResult[2 * (size_t)slot + j]);
+                Ray r2 = ray;
+                scatterRayIS<POL>(r2, vec3{b.x, b.y, b.z});
+                SurfaceHit hit;
+                if (processRayQuery(sc, r2, q, hit) >= 0) {
+                    r2.lin_contrib *= b.w;
+                    has = processShadowRay<POL>(P, r2, hit, item);
+                }
+            }
+            commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
+            hitSeq += has ? 1u : 0u;
+        }
+        if (active) scatterRay<POL>(ray, rng.next2());
+        finishSegment<POL>(P, ws, &sh, active, slot, ray, rng, THEIA_RESULT_RAY_SCATTERED, it, true, nextQueue, nextCounter,
+                           nSegments);
+    }
+    sinkFinish(P, &sh, sharedHist, nSegments, nResponses, 0, 0);
+}
+
+}  // namespace theia
+

@@ -501,9 +501,16 @@ class SceneForwardTracer(Tracer):
                  sourceMedium: int | None = None, maxTime: float = 1000.0 * u.ns, polarized: bool = False,
                  disableDirectLighting: bool = False, disableTransmission: bool = False,
                  disableVolumeBorder: bool = False, useRefractedHitDir: bool = False, blockSize: int = 128,
-                 code: bytes | None = None) -> None:
+                 code: bytes | None = None, mode: str = "auto") -> None:
         if callback is None:
             callback = EmptyEventCallback()
+        if mode not in ("auto", "wavefront", "single"):
+            raise ValueError("mode must be 'auto', 'wavefront' or 'single'")
+        # B200 extension: "wavefront" keeps the path state in HBM and runs one trace + one
+        # shade kernel per path segment; "single" runs the whole batch in one launch with the
+        # paths resident in registers (small batches). Results are identical.
+        self._mode = mode
+        self._workspace = None
         # budgets (trace.py:1176-1187)
         maxHits = maxPathLength - 1
         rngStride = 4
@@ -601,3 +608,17 @@ class SceneForwardTracer(Tracer):
         L.guide = _component(self._targetGuide, i, keep)
         tlas = self._scene.tlas
         L.tlas = 0 if tlas is None else tlas.data_ptr()
+        if self.wavefront and self._device == "cuda":
+            need = ctypes.c_uint64()
+            _lib.check(_lib.load().theia_trace_workspace_size(byref(L), byref(need)))
+            if self._workspace is None or self._workspace.numel() < need.value:
+                self._workspace = _device.alloc(need.value, "cuda", zero=False)
+            L.workspace = self._workspace.data_ptr()
+            L.workspace_bytes = self._workspace.numel()
+
+    @property
+    def wavefront(self) -> bool:
+        """True if batches run in wavefront form (B200 extension, see ``mode``)"""
+        if self._mode == "auto":
+            return self.capacity >= 65536
+        return self._mode == "wavefront"
