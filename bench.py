@@ -240,15 +240,17 @@ def runB200(args) -> None:
     evs = []
     kernelEvs = []
     for _ in range(args.steps):
-        flush.fill_(step & 0xFF)  # untimed L2 flush
-        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-        e0.record()
+        # host side of the step (parameter update, launch description) happens before the
+        # timed region: "value" is the device time with everything resident
         setBatch(step * world + rank)
         pipe.update(0)
         L, keep = tr._launch(0)
+        p = reducer._block("Params", 0)
+        flush.fill_(step & 0xFF)  # untimed L2 flush
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
         _lib.check(lib.theia_trace_forward(byref(L)))
         e1.record()
-        p = reducer._block("Params", 0)
         _lib.check(lib.theia_hist_reduce(reducer.histIn.data_ptr(), p.nHist, resp.nBins, p.normalization,
                                          reducer.histOut.data_ptr(), 1, _device.currentStream("cuda")))
         acc += reducer.histOut

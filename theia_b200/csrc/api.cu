@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include "trace_volume.cuh"
 #include "wavefront.cuh"
@@ -299,6 +300,11 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     if (gShade > need128) gShade = need128;
     if (gShadow > need128) gShadow = need128;
     if (gTrace > need128) gTrace = need128;
+    // tuning knob of the trace kernel (lanes that must still be in the node phase to keep it going)
+    static const uint32_t minNodeLanes = [] {
+        const char* e = getenv("THEIA_WF_MIN_NODE_LANES");
+        return e ? (uint32_t)atoi(e) : 12u;
+    }();
     wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 0xFFu);
     {
         void* args[] = {(void*)&D, (void*)&ws};
@@ -310,7 +316,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         wfResetKernel<<<1, 32, 0, st>>>(ws.counters, nextBit | (1u << WF_CNT_SHADOW) | (1u << WF_CNT_CURSOR));
         wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.ray, ws.result, ws.queue[cur],
                                                         ws.counters + (cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0),
-                                                        ws.counters + WF_CNT_CURSOR, 1u);
+                                                        ws.counters + WF_CNT_CURSOR, 1u, minNodeLanes);
         {
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadeFn, dim3(gShade), dim3(TRACE_THREADS), args, histSmem, st));
@@ -318,7 +324,8 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         if (guide && it < D.path_length) {
             wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 1u << WF_CNT_CURSOR);
             wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.shadowRay, ws.shadowResult, ws.shadowQueue,
-                                                            ws.counters + WF_CNT_SHADOW, ws.counters + WF_CNT_CURSOR, 2u);
+                                                            ws.counters + WF_CNT_SHADOW, ws.counters + WF_CNT_CURSOR, 2u,
+                                                            minNodeLanes);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadowFn, dim3(gShadow), dim3(TRACE_THREADS), args, histSmem, st));
         }

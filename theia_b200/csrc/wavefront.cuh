@@ -129,17 +129,22 @@ TDEV void queuePush(uint32_t* queue, uint32_t* counter, bool push, uint32_t slot
 // ------------------------------------------------------------------ trace kernel
 // Ray queries of a queue. rays[2 r], rays[2 r + 1] hold ray r = slot * raysPerEntry + j of the
 // queue entries; results[r] receives (instance slot | ~0, primitive, u, v).
-// One loop iteration pops one stack entry (node, instance or leaf) per lane; a lane whose
-// stack runs empty writes its result and fetches the next ray (lanes take rays in private
-// chunks of WF_FETCH from a global cursor, one atomic per chunk and coalesced group).
+//
+// Persistent warps, three phases per round so that the lanes of a warp do the same kind of
+// work at the same time (the traversal steps differ a lot in cost, and a mixed warp would
+// execute them one after the other):
+//   F  lanes whose stack ran empty write their result and fetch the next ray (private chunks
+//      of WF_FETCH rays from a global cursor, one atomic per round and warp)
+//   N  every lane pops nodes / instances until it meets a leaf or runs out of stack
+//   L  lanes with a pending leaf test its triangles
+// so a lane never waits for the longest traversal of its warp, only for the end of a phase.
 #define WF_FETCH 4u
 enum : uint32_t { WE_TLAS = 0u, WE_INST = 1u, WE_BLAS = 2u, WE_LEAF = 3u };
 
 __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                          uint4* __restrict__ results, const uint32_t* __restrict__ queue,
                                                          const uint32_t* __restrict__ countPtr, uint32_t* cursor,
-                                                         uint32_t raysPerEntry) {
-    namespace cg = cooperative_groups;
+                                                         uint32_t raysPerEntry, uint32_t minNodeLanes) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
     const uint32_t nTop = stageTopNodes(tlas, sharedTop);
@@ -150,8 +155,9 @@ __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__
     uint32_t stackKey[THEIA_STACK_SIZE];
     float stackT[THEIA_STACK_SIZE];
     int sp = 0;
-    bool have = false;
+    bool have = false, done = false;
     uint32_t chunkNext = 0, chunkEnd = 0, rid = 0;
+    uint32_t pending = 0xFFFFFFFFu;  // leaf waiting for phase L
     float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 0, tmax = 0;
     SlabRay world = {0, 0, 0, 0, 0, 0}, obj = {0, 0, 0, 0, 0, 0};
     WoopRay wr;
@@ -165,40 +171,107 @@ __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__
     float bestT = 0.0f, bestU = 0.0f, bestV = 0.0f;
 
     while (true) {
-        if (sp == 0) {
-            if (have) {
-                results[rid] = make_uint4(bestValid ? (uint32_t)bestSlot : 0xFFFFFFFFu, (uint32_t)bestPrim, f2u(bestU), f2u(bestV));
-                have = false;
-            }
-            if (chunkNext == chunkEnd) {
-                cg::coalesced_group g = cg::coalesced_threads();
-                uint32_t base = 0;
-                if (g.thread_rank() == 0) base = atomicAdd(cursor, WF_FETCH * g.size());
-                base = g.shfl(base, 0);
-                chunkNext = base + WF_FETCH * g.thread_rank();
+        // ---- phase F
+        const bool idle = sp == 0 && !done;
+        if (idle && have) {
+            results[rid] = make_uint4(bestValid ? (uint32_t)bestSlot : 0xFFFFFFFFu, (uint32_t)bestPrim, f2u(bestU), f2u(bestV));
+            have = false;
+        }
+        const uint32_t needChunk = __ballot_sync(FULL_MASK, idle && chunkNext == chunkEnd);
+        if (needChunk) {
+            const uint32_t leader = __ffs(needChunk) - 1;
+            uint32_t base = 0;
+            if (laneId() == leader) base = atomicAdd(cursor, WF_FETCH * (uint32_t)__popc(needChunk));
+            base = __shfl_sync(FULL_MASK, base, leader);
+            if (idle && chunkNext == chunkEnd) {
+                chunkNext = base + WF_FETCH * (uint32_t)__popc(needChunk & laneMaskLt());
                 chunkEnd = chunkNext + WF_FETCH;
             }
-            const uint32_t i = chunkNext++;
-            if (i >= total) break;
-            rid = __ldg(queue + i / raysPerEntry) * raysPerEntry + i % raysPerEntry;
-            const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
-            ox = a.x; oy = a.y; oz = a.z; tmax = a.w; dx = b.x; dy = b.y; dz = b.z;
-            world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
-            bestValid = false; bestInst = -1; bestSlot = -1; bestPrim = -1; bestT = 0.0f; bestU = 0.0f; bestV = 0.0f;
-            stackKey[0] = WE_TLAS << 30;
-            stackT[0] = 0.0f;
-            sp = 1;
-            have = true;
         }
-        --sp;
-        const uint32_t key = stackKey[sp];
-        const float tEntry = stackT[sp];
-        const float lim = bestValid ? bestT : tmax;
-        if (tEntry > lim) continue;
-        const uint32_t type = key >> 30, payload = key & 0x3FFFFFFFu;
+        if (idle) {
+            const uint32_t i = chunkNext++;
+            if (i >= total) {
+                done = true;
+            } else {
+                rid = __ldg(queue + i / raysPerEntry) * raysPerEntry + i % raysPerEntry;
+                const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
+                ox = a.x; oy = a.y; oz = a.z; tmax = a.w; dx = b.x; dy = b.y; dz = b.z;
+                world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
+                bestValid = false; bestInst = -1; bestSlot = -1; bestPrim = -1; bestT = 0.0f; bestU = 0.0f; bestV = 0.0f;
+                stackKey[0] = WE_TLAS << 30;
+                stackT[0] = 0.0f;
+                sp = 1;
+                have = true;
+            }
+        }
+        if (__all_sync(FULL_MASK, done)) break;
 
-        if (type == WE_LEAF) {
-            const uint32_t first = payload >> 2, count = (payload & 3u) + 1u;
+        // ---- phase N (left early once only a few lanes are still looking for a leaf: they
+        // resume in the next round instead of holding up the triangle tests of the others)
+        const uint32_t nodeLimit = min(minNodeLanes, (uint32_t)__popc(__ballot_sync(FULL_MASK, sp > 0)));
+        while (sp > 0) {
+            if ((uint32_t)__popc(__activemask()) < nodeLimit) break;  // the first iteration always runs
+            --sp;
+            const uint32_t key = stackKey[sp];
+            const float tEntry = stackT[sp];
+            const float lim = bestValid ? bestT : tmax;
+            if (tEntry > lim) continue;
+            const uint32_t type = key >> 30, payload = key & 0x3FFFFFFFu;
+            if (type == WE_LEAF) { pending = payload; break; }
+            if (type == WE_INST) {
+                const InstanceRec* in = sc.instances + payload;
+                const float4* q = reinterpret_cast<const float4*>(in);
+                const float4 r0 = __ldg(q), r1 = __ldg(q + 1), r2 = __ldg(q + 2);
+                const float m[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
+                const float o[3] = {ox, oy, oz}, d[3] = {dx, dy, dz};
+                transformPoint(m, o, wr.o);
+                transformVector(m, d, wr.d);
+                woopSetup(wr);
+                obj = {wr.o[0], wr.o[1], wr.o[2], safeInv(wr.d[0]), safeInv(wr.d[1]), safeInv(wr.d[2])};
+                const uint4 ptrs = __ldg(reinterpret_cast<const uint4*>(in) + 3);
+                blasNodes = reinterpret_cast<const WideNode*>((uint64_t)ptrs.x | ((uint64_t)ptrs.y << 32));
+                blasTris = reinterpret_cast<const TriRec*>((uint64_t)ptrs.z | ((uint64_t)ptrs.w << 32));
+                curSlot = (int32_t)payload;
+                curInst = (int32_t)__ldg(&in->pad);
+                stackKey[sp] = WE_BLAS << 30;
+                stackT[sp] = tEntry;
+                ++sp;
+                continue;
+            }
+            const bool inBlas = type == WE_BLAS;
+            NodeRegs n;
+            if (inBlas) n = loadNode(blasNodes + payload);
+            else if (payload < sc.nTop) n = loadNodeShared(sc.topNodes + payload);
+            else n = loadNode(sc.nodes + payload);
+            float tmin[8];
+            uint32_t mask = testChildren(n, inBlas ? obj : world, lim, tmin);
+            if (mask == 0) continue;
+            const uint32_t imask = n.a.w >> 24;
+            const uint32_t axis = n.b.x >> 30, childBase = n.b.x & 0x3FFFFFFFu;
+            const SlabRay& rr = inBlas ? obj : world;
+            const float idirAxis = axis == 0 ? rr.ix : (axis == 1 ? rr.iy : rr.iz);
+            const bool forward = idirAxis >= 0.0f;
+            while (mask) {
+                const int i = forward ? (31 - __clz(mask)) : (__ffs(mask) - 1);  // farthest slot first
+                mask &= ~(1u << i);
+                const uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, i & 3);
+                uint32_t k;
+                if ((imask >> i) & 1u) k = ((inBlas ? WE_BLAS : WE_TLAS) << 30) | (childBase + meta - 1u);
+                else if (inBlas) k = (WE_LEAF << 30) | ((n.b.y + (meta >> 3)) << 2) | ((meta & 7u) - 1u);
+                else k = (WE_INST << 30) | (n.b.y + (meta >> 3));
+                if (sp < THEIA_STACK_SIZE) {
+                    stackKey[sp] = k;
+                    stackT[sp] = tmin[i];
+                    ++sp;
+                }
+            }
+        }
+
+        // ---- phase L (reconverge first: the compiler would otherwise run it per exit path of N)
+        __syncwarp();
+        if (pending != 0xFFFFFFFFu) {
+            const uint32_t first = pending >> 2, count = (pending & 3u) + 1u;
+            pending = 0xFFFFFFFFu;
             for (uint32_t k = 0; k < count; ++k) {
                 const float4* tp = reinterpret_cast<const float4*>(blasTris + first + k);
                 const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
@@ -209,54 +282,6 @@ __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__
                 const bool better = !bestValid || t < bestT ||
                                     (t == bestT && (curInst < bestInst || (curInst == bestInst && prim < bestPrim)));
                 if (better) { bestValid = true; bestInst = curInst; bestSlot = curSlot; bestPrim = prim; bestT = t; bestU = u; bestV = v; }
-            }
-            continue;
-        }
-        if (type == WE_INST) {
-            const InstanceRec* in = sc.instances + payload;
-            const float4* q = reinterpret_cast<const float4*>(in);
-            const float4 r0 = __ldg(q), r1 = __ldg(q + 1), r2 = __ldg(q + 2);
-            const float m[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
-            const float o[3] = {ox, oy, oz}, d[3] = {dx, dy, dz};
-            transformPoint(m, o, wr.o);
-            transformVector(m, d, wr.d);
-            woopSetup(wr);
-            obj = {wr.o[0], wr.o[1], wr.o[2], safeInv(wr.d[0]), safeInv(wr.d[1]), safeInv(wr.d[2])};
-            const uint4 ptrs = __ldg(reinterpret_cast<const uint4*>(in) + 3);
-            blasNodes = reinterpret_cast<const WideNode*>((uint64_t)ptrs.x | ((uint64_t)ptrs.y << 32));
-            blasTris = reinterpret_cast<const TriRec*>((uint64_t)ptrs.z | ((uint64_t)ptrs.w << 32));
-            curSlot = (int32_t)payload;
-            curInst = (int32_t)__ldg(&in->pad);
-            stackKey[sp] = WE_BLAS << 30;
-            stackT[sp] = tEntry;
-            ++sp;
-            continue;
-        }
-        const bool inBlas = type == WE_BLAS;
-        NodeRegs n;
-        if (inBlas) n = loadNode(blasNodes + payload);
-        else if (payload < sc.nTop) n = loadNodeShared(sc.topNodes + payload);
-        else n = loadNode(sc.nodes + payload);
-        float tmin[8];
-        uint32_t mask = testChildren(n, inBlas ? obj : world, lim, tmin);
-        if (mask == 0) continue;
-        const uint32_t imask = n.a.w >> 24;
-        const uint32_t axis = n.b.x >> 30, childBase = n.b.x & 0x3FFFFFFFu;
-        const SlabRay& rr = inBlas ? obj : world;
-        const float idirAxis = axis == 0 ? rr.ix : (axis == 1 ? rr.iy : rr.iz);
-        const bool forward = idirAxis >= 0.0f;
-        while (mask) {
-            const int i = forward ? (31 - __clz(mask)) : (__ffs(mask) - 1);  // farthest slot first
-            mask &= ~(1u << i);
-            const uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, i & 3);
-            uint32_t k;
-            if ((imask >> i) & 1u) k = ((inBlas ? WE_BLAS : WE_TLAS) << 30) | (childBase + meta - 1u);
-            else if (inBlas) k = (WE_LEAF << 30) | ((n.b.y + (meta >> 3)) << 2) | ((meta & 7u) - 1u);
-            else k = (WE_INST << 30) | (n.b.y + (meta >> 3));
-            if (sp < THEIA_STACK_SIZE) {
-                stackKey[sp] = k;
-                stackT[sp] = tmin[i];
-                ++sp;
             }
         }
     }
