@@ -107,7 +107,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._stop.wait(0.2)  # NVML queries take driver locks: keep them rare
 
     def start(self) -> None:
         if self._nv is not None:
@@ -220,9 +220,15 @@ def runB200(args) -> None:
 
     # ---------------- warm-up
     step = 0
-    for _ in range(max(args.warmup, 3)):
+    tWarm = time.perf_counter()
+    nWarm = 0
+    # W warm-up steps, then keep going until the GPU has been busy for a second (clock ramp)
+    while nWarm < max(args.warmup, 3) or time.perf_counter() - tWarm < 1.0:
         deviceStep(step * world + rank)
         step += 1
+        nWarm += 1
+        if nWarm % 4 == 0:
+            torch.cuda.synchronize()
     torch.cuda.synchronize()
     counters.zero_()
     launch0, _k = tr._launch(0)
@@ -237,6 +243,7 @@ def runB200(args) -> None:
         dist.barrier()
     torch.cuda.synchronize()
     sampler.start()
+    launches0 = int(lib.theia_kernel_launches())
     evs = []
     kernelEvs = []
     for _ in range(args.steps):
@@ -246,7 +253,8 @@ def runB200(args) -> None:
         pipe.update(0)
         L, keep = tr._launch(0)
         p = reducer._block("Params", 0)
-        flush.fill_(step & 0xFF)  # untimed L2 flush
+        if not os.environ.get("THEIA_BENCH_NOFLUSH"):  # diagnostic switch only
+            flush.fill_(step & 0xFF)  # untimed L2 flush
         e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
         e0.record()
         _lib.check(lib.theia_trace_forward(byref(L)))
@@ -258,6 +266,7 @@ def runB200(args) -> None:
         evs.append((e0, e2))
         kernelEvs.append((e0, e1))
         step += 1
+    launches = int(lib.theia_kernel_launches()) - launches0
     eA, eB = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     eA.record()
     if world > 1:
@@ -322,7 +331,7 @@ def runB200(args) -> None:
     issuePerSeg = ISSUE_PER_SEGMENT[kind + ("_pol" if polarized and kind == "volume_mis" else "")]
     issueAchieved = issuePerSeg * segsPerLaunch / (kernelMs * 1e-3)
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": nWarm,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "description": desc, "paths_per_step_per_gpu": args.batch,
@@ -341,7 +350,7 @@ def runB200(args) -> None:
         "clocks": clocks,
         "e2e": {"value": e2eSegs / e2eSec, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2eSec * 1e3 / args.steps},
-        "gpu_launches": 2 * args.steps,
+        "gpu_launches": launches,
         "light_curve_sum": float(acc.sum().item()),
     }
     if not args.no_cpu and world == 1:

@@ -288,6 +288,8 @@ typedef struct theia_trace_launch {
 /* ------------------------------------------------------------------ library */
 const char *theia_last_error(void);
 int theia_abi_version(void);
+/* Number of CUDA kernels this library has launched in this process (measurement aid). */
+uint64_t theia_kernel_launches(void);
 /* Number of SMs etc. of the current device; used by the host to size buffers. */
 int theia_device_info(int *sm_count, int *cc_major, int *cc_minor);
 

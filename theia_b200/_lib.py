@@ -19,6 +19,7 @@ _lib = None
 SYMBOLS = {
     "theia_last_error": (c_char_p, []),
     "theia_abi_version": (c_int, []),
+    "theia_kernel_launches": (c_uint64, []),
     "theia_device_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "theia_philox_fill": (c_int, [POINTER(_abi.PhiloxParams), c_uint32, c_uint32, c_uint32, c_uint32, c_uint32,
                                   c_void_p, c_void_p]),

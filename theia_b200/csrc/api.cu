@@ -2,6 +2,7 @@
 // validation and translation into the device launch block, plus the small kernels behind
 // the RNG sink, the histogram reducer, the hit replay and the ray query test seam.
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -12,6 +13,8 @@
 namespace theia {
 
 static thread_local char g_error[512] = "";
+static std::atomic<unsigned long long> g_launches{0};  // kernels launched by this library
+void countLaunches(unsigned n) { g_launches += n; }
 
 void setError(const char* fmt, ...) {
     va_list ap;
@@ -259,12 +262,19 @@ __global__ void wfResetKernel(uint32_t* counters, uint32_t mask) {
 }
 
 static int persistentGrid(const void* fn, size_t smem, uint32_t* grid) {
+    // occupancy queries are not free: remember the answer per (device, kernel, shared memory)
+    struct Entry { int dev; const void* fn; size_t smem; uint32_t grid; };
+    static thread_local Entry cache[16];
+    static thread_local int nCache = 0;
     int dev = 0, sms = 0, perSm = 0;
     CUDA_TRY(cudaGetDevice(&dev));
+    for (int i = 0; i < nCache; ++i)
+        if (cache[i].dev == dev && cache[i].fn == fn && cache[i].smem == smem) { *grid = cache[i].grid; return 0; }
     CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fn, (int)TRACE_THREADS, smem));
     if (perSm < 1) { setError("wavefront kernel does not fit on an SM"); return -1; }
     *grid = (uint32_t)sms * (uint32_t)perSm;
+    if (nCache < 16) cache[nCache++] = Entry{dev, fn, smem, *grid};
     return 0;
 }
 
@@ -311,7 +321,9 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         CUDA_TRY(cudaLaunchKernel(genFn, dim3(gGen), dim3(TRACE_THREADS), args, 0, st));
     }
     uint32_t cur = 0;
+    countLaunches(2);
     for (uint32_t it = 1; it <= D.path_length; ++it) {
+        countLaunches((guide && it < D.path_length) ? 6 : 3);
         const uint32_t nextBit = cur ? (1u << WF_CNT_QUEUE0) : (1u << WF_CNT_QUEUE1);
         wfResetKernel<<<1, 32, 0, st>>>(ws.counters, nextBit | (1u << WF_CNT_SHADOW) | (1u << WF_CNT_CURSOR));
         wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.ray, ws.result, ws.queue[cur],
@@ -343,6 +355,7 @@ extern "C" {
 
 const char* theia_last_error(void) { return g_error; }
 int theia_abi_version(void) { return THEIA_ABI_VERSION; }
+uint64_t theia_kernel_launches(void) { return g_launches.load(); }
 
 int theia_device_info(int* sm_count, int* cc_major, int* cc_minor) {
     int dev = 0;
@@ -359,6 +372,7 @@ int theia_philox_fill(const theia_philox_params_t* params, uint32_t baseStream, 
     uint64_t n = (uint64_t)streams * samples;
     if (n == 0) return 0;
     philoxFillKernel<<<blocksFor(n, 256), 256, 0, (cudaStream_t)stream>>>(*params, baseStream, baseCount, streams, samples, dim, out_dev);
+    countLaunches(1);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -367,6 +381,7 @@ int theia_philox_raw(const uint32_t* ctr_dev, const uint32_t* key_dev, uint32_t 
     if (!ctr_dev || !key_dev || !out_dev) { setError("theia_philox_raw: null argument"); return -1; }
     if (n == 0) return 0;
     philoxRawKernel<<<blocksFor(n, 256), 256, 0, (cudaStream_t)stream>>>(ctr_dev, key_dev, n, out_dev);
+    countLaunches(1);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -375,6 +390,7 @@ int theia_math_eval(uint32_t fn, const float* x_dev, const float* y_dev, uint32_
     if (fn > 4 || !x_dev || !out_dev || (fn == 4 && !y_dev)) { setError("theia_math_eval: bad argument"); return -1; }
     if (n == 0) return 0;
     mathEvalKernel<<<blocksFor(n, 256), 256, 0, (cudaStream_t)stream>>>(fn, x_dev, y_dev, n, out_dev);
+    countLaunches(1);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -384,6 +400,7 @@ int theia_hist_reduce(float* partials_dev, uint32_t n_hist, uint32_t n_bins, flo
     if (!partials_dev || !out_dev) { setError("theia_hist_reduce: null argument"); return -1; }
     if (n_bins == 0) return 0;
     histReduceKernel<<<blocksFor(n_bins, 128), 128, 0, (cudaStream_t)stream>>>(partials_dev, n_hist, n_bins, norm, out_dev, clear);
+    countLaunches(1);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -400,6 +417,7 @@ int theia_hit_replay(const uint32_t* queue_dev, uint32_t capacity, uint32_t pola
     if (r.kind == THEIA_RESPONSE_HISTOGRAM && grid > r.hist_capacity) grid = r.hist_capacity;
     if (grid > 148 * 8) grid = 148 * 8;
     hitReplayKernel<<<grid, 128, smem, (cudaStream_t)stream>>>(queue_dev, capacity, polarized, r);
+    countLaunches(1);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -410,6 +428,7 @@ int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, in
     if (n == 0) return 0;
     tlasQueryKernel<<<blocksFor(n, 128), 128, 0, (cudaStream_t)stream>>>(tlas_dev, rays_dev, n, out_dev, out_bary_dev,
                                                                          (unsigned long long*)stats_dev);
+    countLaunches(1);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -442,6 +461,7 @@ int theia_trace_forward(const theia_trace_launch_t* launch) {
     if (plan(launch, D, K)) return -1;
     void* args[] = {&D};
     CUDA_TRY(cudaLaunchKernel(K.fn, dim3(K.grid), dim3(TRACE_THREADS), args, K.smem, (cudaStream_t)launch->stream));
+    countLaunches(1);
     return 0;
 }
 

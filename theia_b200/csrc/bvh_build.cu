@@ -23,6 +23,7 @@
 namespace theia {
 
 void setError(const char* fmt, ...);  // api.cu
+void countLaunches(unsigned n);      // api.cu
 
 // ------------------------------------------------------------------ scratch layout
 struct BuildScratch {
@@ -482,6 +483,7 @@ static int buildBinaryTree(BuildScratch& s, uint32_t n, cudaStream_t st, const u
     if (n > 1) radixTreeKernel<<<blocksFor(n - 1, bs), bs, 0, st>>>(s, keys, n);
     refitKernel<<<blocksFor(n, bs), bs, 0, st>>>(s, *order, n);
     CUDA_OK(cudaGetLastError());
+    countLaunches(n > 1 ? 4 : 3);  // morton, sort (>= 1 kernel), radix tree, refit
     return 0;
 }
 
@@ -540,6 +542,7 @@ extern "C" int theia_blas_build(const float* vertices_dev, uint32_t n_vertices, 
     A.headerBounds = (float*)(out + offsetof(BlasHeader, lo));
     collapseKernel<<<1, COLLAPSE_THREADS, 0, st>>>(s, A);
     CUDA_OK(cudaGetLastError());
+    countLaunches(3);  // init, boxes, collapse
     // the host copy of h must outlive the async copy
     CUDA_OK(cudaStreamSynchronize(st));
     return 0;
@@ -622,6 +625,7 @@ extern "C" int theia_tlas_build(const theia_instance_desc_t* instances, uint32_t
     A.headerBounds = (float*)(out + offsetof(TlasHeader, lo));
     collapseKernel<<<1, COLLAPSE_THREADS, 0, st>>>(s, A);
     CUDA_OK(cudaGetLastError());
+    countLaunches(3);  // init, boxes, collapse
     TlasHeader back;
     CUDA_OK(cudaMemcpyAsync(&back, out, sizeof(back), cudaMemcpyDeviceToHost, st));
     CUDA_OK(cudaStreamSynchronize(st));

@@ -71,9 +71,27 @@ static __device__ __noinline__ float particle_sampleEmissionAngle(float n, float
     return cos_chev - sign_(u) * x;
 }
 
+// One trial of the rejection loop of sampleGamma; constants as in sampleGamma.
+struct GammaConsts { float alpha, a, b, c; };
+TDEV GammaConsts gammaConsts(float alpha) {  // alpha >= 1 (after the rescaling step)
+    return {alpha, sqrtf(2.0f * alpha - 1.0f), alpha - dm_log(4.0f), alpha + 1.0f / alpha};
+}
+TDEV bool gammaTrial(const GammaConsts& g, Rng& rng, float* X_out) {
+    vec2 u = rng.next2();
+    float V = g.a * dm_log(u.x / (1.0f - u.x));
+    float X = g.alpha * dm_exp(V);
+    *X_out = X;
+    return g.b + g.c * V - X >= dm_log(u.x * u.x * u.y);
+}
+
+// Gamma variate sampled ahead of sampleLight (wavefront generate kernel): the value and the
+// draw counter after the rejection loop.
+struct PreGamma { bool valid; float value; uint32_t dimAfter; };
+
 // ------------------------------------------------------------------ light sources (forward)
 template <bool POL>
-TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants medium, Rng& rng) {
+TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants medium, Rng& rng,
+                           PreGamma pre = PreGamma{false, 0.0f, 0u}) {
     switch (c.kind) {
     case THEIA_LIGHT_SPHERICAL: {  // sh/lightsource.spherical.glsl:16-34
         const theia_light_spherical_t& p = c.p.spherical;
@@ -111,7 +129,10 @@ TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants 
     }
     case THEIA_LIGHT_CASCADE: {  // sh/lightsource.particles.cascade.glsl:40-69
         const theia_light_cascade_t& p = c.p.cascade;
-        float z = sampleGamma(p.a_long, rng) * p.b_long;
+        float gamma;
+        if (pre.valid) { gamma = pre.value; rng.dim = pre.dimAfter; }
+        else gamma = sampleGamma(p.a_long, rng);
+        float z = gamma * p.b_long;
         vec3 dir = v3(p.direction);
         vec3 rayPos = fma3(z, dir, v3(p.startPosition));
         float time = fmaf(z, T_INV_SPEED_OF_LIGHT, p.startTime);
@@ -149,10 +170,11 @@ TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants 
 
 // sh/tracer.volume.forward.glsl:223-229, sh/tracer.scene.forward.glsl:50-56
 template <bool POL>
-TDEV Ray sampleRay(const WavelengthSel& wl, const LightSel& light, uint64_t medium, Rng& rng) {
+TDEV Ray sampleRay(const WavelengthSel& wl, const LightSel& light, uint64_t medium, Rng& rng,
+                   PreGamma pre = PreGamma{false, 0.0f, 0u}) {
     WavelengthSample photon = sampleWavelength(wl, rng);
     MediumConstants constants = lookUpMedium(medium, photon.wavelength);
-    SourceRay lightRay = sampleLight<POL>(light, photon.wavelength, constants, rng);
+    SourceRay lightRay = sampleLight<POL>(light, photon.wavelength, constants, rng, pre);
     return createRay(lightRay, medium, constants, photon);
 }
 

@@ -345,22 +345,75 @@ TDEV uint32_t wfWarpBase(uint32_t& stride) {
     return (blockIdx.x * warpsPerCta + (threadIdx.x >> 5)) * 32u;
 }
 
-// generate: sh/tracer.scene.forward.glsl:50-66
+// Cascade light: the gamma variate of the shower depth comes from a rejection loop with a
+// data dependent number of trials (sh/random.gamma.glsl:9-29). Run per path inside sampleLight
+// a warp would wait for its unluckiest lane; here the warp runs the trials of its path range
+// with refill (a lane that accepted takes the next path), parking value and draw counter in
+// the state slots of the path. Same draws, same arithmetic as sampleGamma.
+TDEV void pregenerateGamma(const DeviceLaunch& P, const Workspace& ws, uint32_t first, uint32_t end) {
+    const float alpha0 = P.light.p.cascade.a_long;
+    const bool rescale = alpha0 < 1.0f;
+    const GammaConsts g = gammaConsts(rescale ? alpha0 + 1.0f : alpha0);
+    const uint32_t skip = P.wavelength.kind == THEIA_WAVELENGTH_CONST ? 0u : 1u;  // draws of sampleWavelength
+    const size_t C = ws.capacity;
+    uint32_t next = first;
+    bool busy = false;
+    uint32_t k = 0;
+    float scale = 1.0f;
+    Rng rng = makeRng(&P.rng, 0);
+    for (uint32_t guard = 0; guard < 100000000u; ++guard) {
+        uint32_t idle = __ballot_sync(FULL_MASK, !busy);
+        if (idle) {
+            uint32_t avail = end - next, rank = __popc(idle & laneMaskLt());
+            if (!busy && rank < avail) {
+                busy = true;
+                k = next + rank;
+                rng = makeRng(&P.rng, P.first_path + k);
+                rng.dim = skip;
+                scale = 1.0f;
+                if (rescale) scale = dm_pow(rng.next(), 1.0f / alpha0);
+            }
+            next += min((uint32_t)__popc(idle), avail);
+        }
+        if (!__any_sync(FULL_MASK, busy)) break;
+        if (busy) {
+            float X;
+            if (gammaTrial(g, rng, &X)) {
+                ws.state[WF_PX * C + k] = f2u(scale * X);
+                ws.state[WF_DIM * C + k] = rng.dim;
+                busy = false;
+            }
+        }
+    }
+}
+
+// generate: sh/tracer.scene.forward.glsl:50-66. Each warp owns a contiguous range of paths.
 template <bool POL>
 __global__ void __launch_bounds__(128, 4) wfGenerateKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws) {
     __shared__ SinkShared sh;
     sinkInit(P, &sh, nullptr);
     const bool GUIDE = P.guide.kind != THEIA_GUIDE_NONE;
-    uint32_t nSegments = 0, nPaths = 0, stride;
-    for (uint32_t base = wfWarpBase(stride); base < P.batch_size; base += stride) {
+    const bool PREGAMMA = P.light.kind == THEIA_LIGHT_CASCADE;
+    const uint32_t warpsPerCta = blockDim.x >> 5, nWarps = gridDim.x * warpsPerCta;
+    const uint32_t warp = blockIdx.x * warpsPerCta + (threadIdx.x >> 5);
+    const uint32_t perWarp = ((P.batch_size + nWarps - 1) / nWarps + 31u) & ~31u;
+    const uint32_t first = min(warp * perWarp, P.batch_size), end = min(first + perWarp, P.batch_size);
+    if (PREGAMMA) {
+        pregenerateGamma(P, ws, first, end);
+        __syncwarp();
+    }
+    uint32_t nSegments = 0, nPaths = 0;
+    for (uint32_t base = first; base < end; base += 32u) {
         const uint32_t k = base + laneId();
-        const bool active = k < P.batch_size;
+        const bool active = k < end;
         Ray ray;
         Rng rng = makeRng(&P.rng, P.first_path + k);
         bool ok = false, mis = false;
         const bool allow = P.disable_direct_lighting == 0;
         if (active) {
-            ray = sampleRay<POL>(P.wavelength, P.light, P.medium, rng);
+            PreGamma pre = {false, 0.0f, 0u};
+            if (PREGAMMA) pre = {true, u2f(ws.state[WF_PX * (size_t)ws.capacity + k]), ws.state[WF_DIM * (size_t)ws.capacity + k]};
+            ray = sampleRay<POL>(P.wavelength, P.light, P.medium, rng, pre);
             nPaths++;
         }
         onEvent<POL>(P.callback, &sh, active, ray, THEIA_RESULT_RAY_CREATED, k, 0);
