@@ -257,3 +257,75 @@ def compareHits(a, b, *, rtol: float = 0.0, atol: float = 0.0):
             worst = max(worst, float(err.max(initial=0.0)))
             assert (err <= 1.0).all(), f"field {f}: max error ratio {err.max()}"
     return worst
+
+
+# ---------------------------------------------------------------------------------------------
+# analytic scenarios ported from the reference's own tests
+class EnergyModel(material.DispersionFreeMedium, material.HenyeyGreensteinPhaseFunction,
+                  material.KokhanovskyOceanWaterPhaseMatrix, material.MediumModel):
+    """tests/test_trace_energy.py:31-45 of the reference"""
+
+    ModelName = "homogenous"
+
+    def __init__(self, a, s, g, *, n=1.33, ng=1.33) -> None:
+        material.DispersionFreeMedium.__init__(self, n=n, ng=ng, mu_a=a, mu_s=s)
+        material.HenyeyGreensteinPhaseFunction.__init__(self, g)
+        material.KokhanovskyOceanWaterPhaseMatrix.__init__(self, p90=0.66, theta0=0.25, alpha=4.0, xi=25.6)
+
+
+def beamSplitter(N: int, flag: str, targetId: int, **kw):
+    """tests/test_trace.py:1196-1275 of the reference: 45 degree BK7 plate, two detectors."""
+    glass = material.BK7Model().createMedium()
+    mat = material.Material("mat", glass, None, flags=(flag, "T"))
+    det = material.Material("det", glass, None, flags="DB")
+    store = material.MaterialStore([mat, det])
+    meshes = scene.MeshStore({"cube": os.path.join(ASSETS, "cube.ply")})
+    T = scene.Transform
+    splitter = meshes.createInstance("cube", "mat", T.TRS(scale=(0.1, 5.0, 5.0), rotate=(0.0, 0.0, 1.0, 45.0),
+                                                          translate=(0.141, 0.0, 0.0)))
+    refDet = meshes.createInstance("cube", "det", T.TRS(scale=(50.0, 0.5, 50.0), translate=(0.0, -50.0, 0.0)),
+                                   detectorId=1)
+    transDet = meshes.createInstance("cube", "det", T.TRS(scale=(0.5, 50.0, 50.0), translate=(50.0, 0.0, 0.0)),
+                                     detectorId=2)
+    sc = scene.Scene([splitter, transDet, refDet], store.material)
+    rng = random.PhiloxRNG(key=0xC01DC0FFEE)
+    photons = light.UniformWavelengthSource(lambdaRange=(500.0, 500.0))
+    src = light.PencilLightSource(position=(-20.0, 0.0, 0.0), direction=(1.0, 0.0, 0.0), timeRange=(0.0, 0.0), budget=1.0)
+    rec = response.HitRecorder()
+    rec.enableTags()
+    tr = trace.SceneForwardTracer(N, src, photons, rec, rng, scene=sc, targetId=targetId, maxPathLength=4, **kw)
+    return {"tracer": tr, "response": rec, "callback": None, "rng": rng, "store": store, "scene": sc}
+
+
+def innerSphereEnergy(N: int, mu_a, mu_s, mu_sample, g, disableDirect, sampleTarget, polarized):
+    """tests/test_trace_energy.py:833-938 of the reference: point source inside a spherical target."""
+    position, radius = (12.0, 15.0, 0.2), 100.0
+    model = EnergyModel(mu_a, mu_s, g)
+    med = model.createMedium()
+    store = material.MaterialStore([], media=[med])
+    rng = random.PhiloxRNG(key=0xC0FFEE)
+    photons = light.UniformWavelengthSource(lambdaRange=(400.0, 400.0))
+    src = light.SphericalLightSource(position=position, timeRange=(10.0, 10.0), budget=1e9)
+    tgt = target.InnerSphereTarget(position=position, radius=radius)
+    rec = response.HitRecorder(polarized=polarized)
+    rec.enableTags()
+    tr = trace.VolumeForwardTracer(N, src, tgt, photons, rec, rng, medium=store.media["homogenous"],
+                                   maxTime=float("inf"), nScattering=10, scatterCoefficient=mu_sample,
+                                   polarized=polarized, disableDirectLighting=disableDirect,
+                                   disableTargetSampling=not sampleTarget)
+    rng.autoAdvance = tr.nRNGSamples
+    return {"tracer": tr, "response": rec, "callback": None, "rng": rng, "store": store, "model": model}
+
+
+def runAny(cfg, i: int = 0):
+    """Runs one batch on whatever device the scenario was built for."""
+    if cfg["tracer"]._device == "cuda":
+        runGpu(cfg, i)
+    else:
+        runOracle(cfg, i)
+
+
+def hitView(cfg, i: int = 0):
+    r = cfg["response"]
+    v = r.queue.view(i)
+    return v[: min(v.count, r.capacity)]

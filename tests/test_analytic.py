@@ -1,0 +1,79 @@
+"""
+Analytic acceptance tests ported from the reference's own test-suite (they need no reference
+binary). Each runs on the CPU oracle (pinning the restatement; part of the "not gpu" suite,
+at reduced statistics) and on the CUDA path (marked gpu, at the reference's statistics).
+"""
+
+import numpy as np
+import pytest
+
+import harness as H
+import theia_b200.units as u
+from theia_b200 import _device
+
+DEVICES = [pytest.param("cpu", id="oracle"), pytest.param("cuda", id="cuda", marks=pytest.mark.gpu)]
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("flag,reflectance,err", [("T", 0.0, 0.0), ("R", 1.0, 0.0), ("TR", 0.0516, 0.005)])
+def test_beam_splitter_reflectance(device, flag, reflectance, err):
+    # tests/test_trace.py:1196-1275: Fresnel reflectance of BK7 at 45 degrees, 500 nm
+    N = 32 * 256
+    counts = []
+    with _device.useDevice(device):
+        for targetId in (1, 2):
+            cfg = H.beamSplitter(N, flag, targetId)
+            H.runAny(cfg)
+            counts.append(cfg["response"].queue.view(0).count)
+    assert counts[0] + counts[1] == N
+    assert abs(counts[0] / N - reflectance) <= err
+
+
+ENERGY_ROWS = [
+    (0.0, 0.005, 0.05, 0.0, False, True, False, 4.5e-4),
+    (0.0, 0.005, 0.05, 0.0, False, False, False, 0.011),
+    (0.0, 0.005, 0.05, 0.0, True, True, False, 0.011),
+    (0.05, 0.01, 0.05, 0.0, False, True, False, 1.8e-3),
+    (0.05, 0.01, 0.05, 0.0, True, True, False, 2.6e-3),
+    (0.05, 0.01, 0.05, -0.9, False, True, False, 0.012),
+    (0.05, 0.01, 0.05, 0.9, True, True, False, 2.8e-4),
+    (0.05, 0.01, 0.05, 0.9, True, False, False, 2.9e-3),
+    (0.05, 0.01, np.nan, 0.9, False, True, True, 2.9e-3),
+    (0.0, 0.005, 0.05, 0.0, False, True, True, 5e-4),
+    (0.0, 0.005, 0.05, 0.0, True, True, True, 1.2e-3),
+    (0.05, 0.01, 0.05, -0.9, False, True, True, 0.012),
+]
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("mu_a,mu_s,mu_sample,g,disableDirect,sampleTarget,polarized,err", ENERGY_ROWS)
+def test_volume_tracer_energy_conservation(device, mu_a, mu_s, mu_sample, g, disableDirect, sampleTarget, polarized, err):
+    # tests/test_trace_energy.py:816-938: point source inside an InnerSphereTarget; the
+    # un-attenuated contributions must add up to the light budget
+    if device == "cuda":
+        N, nBatches, tol = 512 * 1024, 10, err
+    else:
+        N, nBatches = 256 * 1024, 4
+        tol = max(3.0 * err * np.sqrt(5.0), 3e-3)  # 5 times fewer paths than the reference's test
+    budget, radius, t0 = 1e9, 100.0, 10.0
+    with _device.useDevice(device):
+        cfg = H.innerSphereEnergy(N, mu_a, mu_s, mu_sample, g, disableDirect, sampleTarget, polarized)
+        total, stokes = 0.0, []
+        for b in range(nBatches):
+            H.runAny(cfg, b % 2)
+            v = H.hitView(cfg, b % 2)
+            vg = 1.0 / cfg["model"].ng * u.c
+            d = vg * (v["time"].astype(np.float64) - t0)
+            total += float((v["contrib"].astype(np.float64) * np.exp(mu_a * d)).sum())
+            if polarized:
+                stokes.append(np.array(v["stokes"]))
+    direct = budget * np.exp(-mu_s * radius)
+    expected = budget - direct if disableDirect else budget
+    estimate = total / (N * nBatches)
+    print(f"rel.err {estimate / expected - 1.0:+.2e} (tol {tol:.1e})")
+    assert abs(estimate / expected - 1.0) < tol
+    if polarized:
+        s = np.concatenate(stokes)
+        assert np.abs(s[:, 0] - 1.0).max() < 1e-5
+        assert s[:, 1:].max() <= 1.0 and s[:, 1:].min() >= -1.0
+        assert np.all(np.square(s[:, 1:]).sum(-1) <= 1.0 + 1e-5)

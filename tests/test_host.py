@@ -1,0 +1,145 @@
+"""
+Host side of the boundary without a GPU: budget arithmetic of the tracers, parameter
+blocks, pipeline addressing and error behaviour, checked against the reference's formulas
+(src/theia/trace.py:623-634, 1176-1187; docs/pipeline/pipeline.md:57-64).
+"""
+
+import ctypes
+
+import numpy as np
+import pytest
+
+import harness as H
+from theia_b200 import _abi, _device, light, material, pipeline, random, response, target, trace
+
+
+def build(builder, *a, **kw):
+    with _device.useDevice("cpu"):
+        return builder(*a, **kw)
+
+
+@pytest.mark.parametrize("nScattering", [1, 6, 10])
+@pytest.mark.parametrize("mis", [True, False])
+@pytest.mark.parametrize("direct", [True, False])
+@pytest.mark.parametrize("lightKind,nLight", [("spherical", 3), ("cone", 3), ("pencil", 1), ("cascade", 12), ("muon", 3)])
+def test_volume_tracer_budgets(nScattering, mis, direct, lightKind, nLight):
+    cfg = build(H.volumeScenario, 256, nScattering=nScattering, mis=mis, direct=direct, lightKind=lightKind,
+                wavelength="uniform")
+    tr = cfg["tracer"]
+    hits = nScattering * (2 if mis else 1) + (1 if direct else 0)
+    pathLength = nScattering - 1 if mis else nScattering
+    assert tr.maxHitsPerThread == hits
+    assert tr.maxHits == hits * 256
+    assert tr.nRNGSamples == nLight + 1 + (7 if mis else 3) * pathLength
+    assert tr.source.nRNGForward == nLight
+    assert tr.batchSize == 256 and tr.capacity == 256 and tr.blockSize == 128
+    assert tr.normalization == pytest.approx(1.0 / 256)
+    assert cfg["response"].capacity == tr.maxHits
+
+
+@pytest.mark.parametrize("guide", [False, True])
+@pytest.mark.parametrize("direct", [True, False])
+def test_scene_tracer_budgets(guide, direct):
+    with _device.useDevice("cpu"):
+        cfg = H.sceneC3(512, guide=guide, disableDirectLighting=not direct) if "guide" in H.sceneC3.__code__.co_varnames \
+            else H.sceneC3(512, disableDirectLighting=not direct)
+    tr = cfg["tracer"]
+    hasGuide = tr.targetGuide is not None
+    L = tr.maxPathLength
+    hits = (L - 1) * (2 if hasGuide else 1) + (1 if direct else 0)
+    assert tr.maxHitsPerThread == hits
+    assert tr.nRNGSamples == 3 + 0 + (4 + (2 if hasGuide else 0)) * L
+
+
+def test_batch_size_can_shrink_but_not_grow():
+    cfg = build(H.volumeScenario, 1024)
+    tr = cfg["tracer"]
+    tr.batchSize = 100
+    assert tr.batchSize == 100 and tr.capacity == 1024
+    assert tr.normalization == pytest.approx(1.0 / 100)
+    with pytest.raises(ValueError):
+        tr.batchSize = 2048
+
+
+def test_launch_description_of_a_volume_tracer():
+    cfg = build(H.volumeScenario, 512, polarized=True, water=True, callback="stat")
+    tr = cfg["tracer"]
+    for _, st in tr.collectStages():
+        st.update(0)
+    L, keep = tr._launch(0)
+    assert L.tracer == _abi.TRACER_VOLUME_FORWARD
+    assert L.batch_size == 512 and L.polarized == 1
+    assert L.light.kind == _abi.LIGHT_SPHERICAL and L.wavelength.kind == _abi.WAVELENGTH_CONST
+    assert L.target.kind == _abi.TARGET_SPHERE
+    assert L.response.kind == _abi.RESPONSE_RECORD and L.response.queue_capacity == tr.maxHits
+    assert L.callback.kind == _abi.CALLBACK_STAT
+    assert L.rng.key[0] == 42 and L.rng.key[1] == 0
+    assert L.workspace is None  # volume tracer: register resident, no wavefront state
+
+
+def test_philox_parameter_block_and_auto_advance():
+    with _device.useDevice("cpu"):
+        rng = random.PhiloxRNG(key=0x1122334455667788, offset=(1 << 96) + 5)
+    rng.autoAdvance = 10
+    rng.update(0)
+    p = rng._block("PhiloxParams", 0) if hasattr(rng, "_block") else None
+    raw = bytes(p)
+    words = np.frombuffer(raw, np.uint32)
+    assert words[0] == 0x55667788 and words[1] == 0x11223344
+    # src/theia/random.py:278-282: the offset is advanced first, then uploaded
+    assert list(words[2:6]) == [15, 0, 0, 1]
+    rng.update(1)
+    assert rng.getParam("offset") == (1 << 96) + 25
+
+
+def test_pipeline_addresses_parameters_by_stage_name():
+    cfg = build(H.volumeScenario, 256)
+    tr = cfg["tracer"]
+    pipe = pipeline.Pipeline(tr.collectStages())
+    names = [n for n, _ in pipe.stages]
+    assert names == ["rng", "photons", "lightSource", "target", "tracer", "response"][: len(names)] or "tracer" in names
+    pipe.setParams(lightSource__budget=5.0, tracer__maxTime=123.0, target__radius=0.25)
+    assert tr.source.getParam("budget") == 5.0
+    assert tr.getParam("maxTime") == 123.0
+    assert tr.target.getParam("radius") == 0.25
+    got = pipe.getParams()
+    assert got["lightSource__budget"] == 5.0 and got["tracer__maxTime"] == 123.0
+
+
+def test_tracers_refuse_to_run_without_a_gpu():
+    cfg = build(H.volumeScenario, 256)
+    with pytest.raises(RuntimeError):
+        pipeline.runPipeline(cfg["tracer"].collectStages())
+    with pytest.raises(RuntimeError):
+        with _device.useDevice("cuda"):
+            pass
+
+
+def test_material_flags():
+    # src/theia/material.py:531-557
+    F = material.MaterialFlags
+    P = material.parseMaterialFlags
+    assert P("") == F.NO_REFLECT | F.NO_TRANSMIT
+    assert P("T") == F.NO_REFLECT and P("R") == F.NO_TRANSMIT and P("TR") == F(0)
+    assert P("Tf") == F.NO_REFLECT | F.NO_TRANSMIT_BWD
+    assert P("DB") == F.DETECTOR | F.BLACK_BODY | F.NO_REFLECT | F.NO_TRANSMIT
+    assert P("V") & F.VOLUME_BORDER
+    with pytest.raises(ValueError):
+        material.parseMaterialFlags("X")
+    m = material.Material("m", None, None, flags=("TR", "B"))
+    assert m.flagsInward == material.parseMaterialFlags("TR") and m.flagsOutward == material.parseMaterialFlags("B")
+
+
+def test_hit_queue_layout():
+    # sh/response.queue.glsl:6-33: count, then field-major arrays of length capacity
+    from theia_b200.queue import QueueView
+    n = 5
+    raw = np.zeros(4 + 13 * 4 * n, np.uint8)
+    v = QueueView(raw, response.HitItem, n)
+    assert v.fields[:3] == ["position", "direction", "normal"]
+    v.count = 3
+    v["position"][1] = (1.0, 2.0, 3.0)
+    f = raw[4:].view(np.float32)
+    assert raw[:4].view(np.uint32)[0] == 3
+    assert f[1] == 1.0 and f[n + 1] == 2.0 and f[2 * n + 1] == 3.0
+    assert v[1:3]["position"].shape == (2, 3) and v[1:3].count == 2
