@@ -615,6 +615,13 @@ class DispersionFreeMedium:
         self.mu_a = mu_a
         self.mu_s = mu_s
 
+    # Properties backed by _n, _ng, _mu_a, _mu_s like the reference's: a model that also mixes in
+    # FournierForandPhaseFunction shares `_n` with it there, and is reproduced as is.
+    n = property(lambda self: self._n, lambda self, v: setattr(self, "_n", v), doc="Refractive index")
+    ng = property(lambda self: self._ng, lambda self, v: setattr(self, "_ng", v), doc="Group index")
+    mu_a = property(lambda self: self._mu_a, lambda self, v: setattr(self, "_mu_a", v), doc="Absorption coefficient")
+    mu_s = property(lambda self: self._mu_s, lambda self, v: setattr(self, "_mu_s", v), doc="Scattering coefficient")
+
     def refractive_index(self, wavelength):
         return np.ones_like(wavelength) * self.n
 
