@@ -33,8 +33,22 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
 METRIC = "photon path segments/s"
 UNIT = "segments/s"
 
-# declared algorithmic work per segment (BASELINE.md section 4 / DESIGN.md "Roofline")
-HBM_BYTES_PER_SEGMENT = {False: 2 * 64, True: 2 * 96}
+# declared algorithmic HBM bytes per unit of each kernel class: state words
+# (18 unpolarised / 25 polarised) + ray query (32 B) + result (16 B) + queue entry (4 B)
+def algorithmicBytes(polarized: bool) -> dict:
+    state = 4 * (25 if polarized else 18)
+    return {
+        "volumeForwardKernel": 0,                                  # per segment: register resident
+        "sceneForwardKernel": 0,
+        "wfGenerateKernel": state + 32 + 4,                       # per path: write state, ray, queue
+        "wfTraceKernel": 32 + 16 + 4,                             # per ray: read ray + queue, write result
+        "wfShadeKernel": 2 * state + 2 * 32 + 16 + 2 * 4,          # per segment: read+write state/ray/queue, read result
+        "wfTraceKernel(shadow)": 32 + 16 + 2,                     # per shadow ray (two rays share a queue entry)
+        "wfShadeShadowKernel": 2 * state + 2 * (32 + 16) + 32 + 2 * 4,  # per scatter event with guide
+        "histReduceKernel": 0,
+    }
+
+
 ISSUE_PER_SEGMENT = {"volume_mis": 1100, "volume": 400, "volume_mis_pol": 1700, "scene": 450, "scene_pol": 650}
 
 
@@ -280,6 +294,7 @@ def runB200(args) -> None:
     if world > 1:
         dist.barrier()
     clocks = sampler.stop()
+    lightSum = float(acc.sum().item())
     ms = sum(a.elapsed_time(b) for a, b in evs) + eA.elapsed_time(eB)
     kernelMs = sum(a.elapsed_time(b) for a, b in kernelEvs) / args.steps
     work = counters.cpu().numpy().astype(np.int64)
@@ -298,6 +313,27 @@ def runB200(args) -> None:
     e2eSec = time.perf_counter() - t0
     e2eSegs = int(counters.cpu().numpy()[0])
     h2d = ctypes.sizeof(launch0) + 512  # launch description + parameter blocks -> kernel argument space
+
+    # ---------------- per kernel durations, live (CUDA events around every launch inside the library)
+    counters.zero_()
+    torch.cuda.synchronize()
+    _lib.check(lib.theia_profile_enable(1))
+    for _ in range(args.steps):
+        if not os.environ.get("THEIA_BENCH_NOFLUSH"):
+            flush.fill_(step & 0xFF)
+        deviceStep(step * world + rank)
+        step += 1
+    torch.cuda.synchronize()
+    nCls = 8
+    clsMs = (ctypes.c_double * nCls)()
+    clsN = (ctypes.c_uint64 * nCls)()
+    lib.theia_profile_read(clsMs, clsN, nCls)
+    _lib.check(lib.theia_profile_enable(0))
+    profWork = counters.cpu().numpy().astype(np.int64)
+    kernels = {}
+    for k in range(nCls):
+        if clsN[k]:
+            kernels[lib.theia_profile_class_name(k).decode()] = {"launches": int(clsN[k]), "ms": float(clsMs[k])}
     d2h = resp.nBins * 4
 
     stats = torch.tensor([ms, float(segs), float(hits), float(shadow), float(paths), e2eSec, float(e2eSegs)],
@@ -326,14 +362,33 @@ def runB200(args) -> None:
         pass
     hbmPeak = float(peaks.get("hbm_gbs", 6650.0))
     peakSrc = "measured (MEASURED_PEAKS.json)" if peaks else "fallback"
-    segsPerLaunch = segs / (args.steps * world)
-    algBytes = HBM_BYTES_PER_SEGMENT[polarized] * segsPerLaunch
-    achievedGBs = algBytes / (kernelMs * 1e-3) / 1e9
+    segsPerStep = segs / (args.steps * world)
+    # units each kernel class processed during the profiled pass (rank 0)
+    pSegs, _pHits, pShadow, pPaths = (int(x) for x in profWork)
+    units = {"volumeForwardKernel": pSegs, "sceneForwardKernel": pSegs, "wfGenerateKernel": pPaths,
+             "wfTraceKernel": pSegs, "wfShadeKernel": pSegs, "wfTraceKernel(shadow)": pShadow,
+             "wfShadeShadowKernel": pShadow // 2, "histReduceKernel": 0}
+    perUnit = algorithmicBytes(polarized)
+    totalMs = sum(k["ms"] for k in kernels.values()) or 1.0
+    for name, k in kernels.items():
+        k["share"] = k["ms"] / totalMs
+        k["ms_per_launch"] = k["ms"] / k["launches"]
+        k["algorithmic_bytes_per_launch"] = perUnit[name] * units[name] / k["launches"]
+        k["achieved_gbs"] = perUnit[name] * units[name] / (k["ms"] * 1e-3) / 1e9
+    dominant = max(kernels, key=lambda n: kernels[n]["ms"])
+    dom = kernels[dominant]
+    achievedGBs = dom["achieved_gbs"]
+    traffic = None
+    try:  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(args.workload, {}).get(dominant)
+    except Exception:
+        pass
     smMHz = clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
     sms = _lib.smCount()
     issuePeak = sms * 128 * smMHz * 1e6
     issuePerSeg = ISSUE_PER_SEGMENT[kind + ("_pol" if polarized and kind == "volume_mis" else "")]
-    issueAchieved = issuePerSeg * segsPerLaunch / (kernelMs * 1e-3)
+    issueAchieved = issuePerSeg * segsPerStep / (kernelMs * 1e-3)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": nWarm,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -343,10 +398,13 @@ def runB200(args) -> None:
                    "rng": "Philox4x32-10, disjoint counter ranges per batch", "l2": "flushed between timed steps (256 MiB write)",
                    "parallelism": f"dp{world}: batches dealt round robin, one NCCL all-reduce of the light curve"},
         "hits_per_s": hits / sec, "shadow_rays_per_s": shadow / sec, "paths_per_s": paths / sec,
-        "roofline": {"bound": "hbm", "achieved": achievedGBs, "peak": hbmPeak, "unit": "GB/s", "frac": achievedGBs / hbmPeak,
-                     "traffic": None, "peak_source": peakSrc, "kernel_ms": kernelMs,
-                     "note": "path state is register resident (no wavefront stream through HBM): the kernel is "
-                             "issue/latency bound, see roofline_issue and DESIGN.md"},
+        "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achievedGBs, "peak": hbmPeak, "unit": "GB/s",
+                     "frac": achievedGBs / hbmPeak, "traffic": traffic, "peak_source": peakSrc,
+                     "ms_per_launch": dom["ms_per_launch"], "share_of_step": dom["share"],
+                     "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_launch"],
+                     "tracer_ms_per_step": kernelMs, "kernels": kernels,
+                     "note": "dominant kernel by live CUDA-event time; it is latency/issue bound, not HBM bound "
+                             "(see roofline_issue, profiles/ and DESIGN.md section 6)"},
         "roofline_issue": {"bound": "sm_issue", "achieved": issueAchieved, "peak": issuePeak, "unit": "lane-instr/s",
                            "frac": issueAchieved / issuePeak, "declared_instr_per_segment": issuePerSeg,
                            "sm_mhz": smMHz, "sms": sms,
@@ -355,7 +413,7 @@ def runB200(args) -> None:
         "e2e": {"value": e2eSegs / e2eSec, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2eSec * 1e3 / args.steps},
         "gpu_launches": launches,
-        "light_curve_sum": float(acc.sum().item()),
+        "light_curve_sum": lightSum,
     }
     if not args.no_cpu and world == 1:
         try:

@@ -290,6 +290,16 @@ const char *theia_last_error(void);
 int theia_abi_version(void);
 /* Number of CUDA kernels this library has launched in this process (measurement aid). */
 uint64_t theia_kernel_launches(void);
+
+/* Optional per kernel timing for benchmarks (no counterpart in the reference, which times
+ * whole pipelines only): while enabled, every launch of a tracing kernel is bracketed by CUDA
+ * events on its stream. theia_profile_enable(1) clears the accumulators; theia_profile_read
+ * waits for the pending events and returns, per kernel class k < n, the summed duration in
+ * milliseconds and the number of launches; its return value is the number of classes.
+ * Not thread safe; meant for a single benchmarking thread. */
+int theia_profile_enable(int on);
+int theia_profile_read(double *ms, uint64_t *launches, uint32_t n);
+const char *theia_profile_class_name(uint32_t cls);
 /* Number of SMs etc. of the current device; used by the host to size buffers. */
 int theia_device_info(int *sm_count, int *cc_major, int *cc_minor);
 

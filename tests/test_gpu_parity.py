@@ -237,3 +237,36 @@ def test_histogram_matches_oracle(cuda, orc, builder, kw):
     # same hits, different float summation order (the reference compares with rtol 1e-4:
     # tests/test_response.py:92-99)
     assert np.allclose(got, want, rtol=1e-4, atol=1e-7 * want.max())
+
+
+# ------------------------------------------------------------------ sharded run / profiler
+def test_sharded_run_single_rank_matches_oracle(cuda, orc):
+    from theia_b200 import distributed
+    N, nBatches = 8192, 3
+    g, c = both(H.volumeScenario, N, resp="hist", callback="stat")
+    res = distributed.ShardedRun(g["tracer"], offset0=11).run(nBatches)
+    want = distributed.ShardedRun(c["tracer"], offset0=11, launcher=lambda i: H.runOracle(c, i)).run(nBatches)
+    assert res.localBatches == [0, 1, 2]
+    assert res.counters == want.counters
+    assert res.counters["created"] == N * nBatches
+    assert np.allclose(res.lightCurve, want.lightCurve, rtol=1e-5, atol=1e-12)
+
+
+def test_profile_counters(cuda):
+    lib = _lib.load()
+    with _device.useDevice("cuda"):
+        cfg = H.sceneC2(1 << 16, resp="hist", lightKind="cone", mode="wavefront")
+    _lib.check(lib.theia_profile_enable(1))
+    H.runGpu(cfg)
+    torch.cuda.synchronize()
+    ms = (ctypes.c_double * 8)()
+    n = (ctypes.c_uint64 * 8)()
+    assert lib.theia_profile_read(ms, n, 8) == 8
+    _lib.check(lib.theia_profile_enable(0))
+    names = [lib.theia_profile_class_name(k).decode() for k in range(8)]
+    got = {names[k]: (int(n[k]), float(ms[k])) for k in range(8) if n[k]}
+    assert got["wfGenerateKernel"][0] == 1
+    assert got["wfTraceKernel"][0] == 10 and got["wfShadeKernel"][0] == 10
+    assert all(v[1] > 0.0 for v in got.values())
+    H.runGpu(cfg)  # disabled again: nothing accumulates
+    assert lib.theia_profile_read(ms, n, 8) == 8 and int(n[3]) == 10

@@ -20,6 +20,9 @@ SYMBOLS = {
     "theia_last_error": (c_char_p, []),
     "theia_abi_version": (c_int, []),
     "theia_kernel_launches": (c_uint64, []),
+    "theia_profile_enable": (c_int, [c_int]),
+    "theia_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_uint64), c_uint32]),
+    "theia_profile_class_name": (c_char_p, [c_uint32]),
     "theia_device_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "theia_philox_fill": (c_int, [POINTER(_abi.PhiloxParams), c_uint32, c_uint32, c_uint32, c_uint32, c_uint32,
                                   c_void_p, c_void_p]),

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 #include "trace_volume.cuh"
 #include "wavefront.cuh"
 
@@ -15,6 +16,55 @@ namespace theia {
 static thread_local char g_error[512] = "";
 static std::atomic<unsigned long long> g_launches{0};  // kernels launched by this library
 void countLaunches(unsigned n) { g_launches += n; }
+
+// ------------------------------------------------------------------ per kernel timing
+// Optional (theia_profile_enable): brackets every launch of the tracing kernels with CUDA
+// events on the launching stream so that bench.py can report live per-kernel durations.
+// Off by default: the events cost a few microseconds per launch.
+enum KernelClass : int { KC_VOLUME, KC_SCENE, KC_GENERATE, KC_TRACE, KC_SHADE, KC_SHADOW_TRACE, KC_SHADE_SHADOW,
+                         KC_REDUCE, KC_COUNT };
+static const char* const g_classNames[KC_COUNT] = {"volumeForwardKernel", "sceneForwardKernel", "wfGenerateKernel",
+                                                   "wfTraceKernel", "wfShadeKernel", "wfTraceKernel(shadow)",
+                                                   "wfShadeShadowKernel", "histReduceKernel"};
+struct PendingTiming { int cls; cudaEvent_t a, b; };
+static struct {
+    bool on = false;
+    std::vector<PendingTiming> pending;
+    std::vector<cudaEvent_t> pool;
+    double ms[KC_COUNT] = {};
+    unsigned long long n[KC_COUNT] = {};
+} g_prof;
+static cudaEvent_t profEvent() {
+    cudaEvent_t e = nullptr;
+    if (!g_prof.pool.empty()) { e = g_prof.pool.back(); g_prof.pool.pop_back(); }
+    else cudaEventCreate(&e);
+    return e;
+}
+struct Timed {
+    PendingTiming t{};
+    cudaStream_t st;
+    bool active;
+    Timed(int cls, cudaStream_t s) : st(s), active(g_prof.on) {
+        if (!active) return;
+        t.cls = cls; t.a = profEvent(); t.b = profEvent();
+        cudaEventRecord(t.a, st);
+    }
+    ~Timed() {
+        if (!active) return;
+        cudaEventRecord(t.b, st);
+        g_prof.pending.push_back(t);
+    }
+};
+static void profCollect() {
+    for (auto& t : g_prof.pending) {
+        float ms = 0.0f;
+        cudaEventSynchronize(t.b);
+        if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) { g_prof.ms[t.cls] += ms; g_prof.n[t.cls] += 1; }
+        g_prof.pool.push_back(t.a);
+        g_prof.pool.push_back(t.b);
+    }
+    g_prof.pending.clear();
+}
 
 void setError(const char* fmt, ...) {
     va_list ap;
@@ -313,10 +363,11 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     // tuning knob of the trace kernel (lanes that must still be in the node phase to keep it going)
     static const uint32_t minNodeLanes = [] {
         const char* e = getenv("THEIA_WF_MIN_NODE_LANES");
-        return e ? (uint32_t)atoi(e) : 12u;
+        return e ? (uint32_t)atoi(e) : 16u;
     }();
     wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 0xFFu);
     {
+        Timed tm(KC_GENERATE, st);
         void* args[] = {(void*)&D, (void*)&ws};
         CUDA_TRY(cudaLaunchKernel(genFn, dim3(gGen), dim3(TRACE_THREADS), args, 0, st));
     }
@@ -326,18 +377,26 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         countLaunches((guide && it < D.path_length) ? 6 : 3);
         const uint32_t nextBit = cur ? (1u << WF_CNT_QUEUE0) : (1u << WF_CNT_QUEUE1);
         wfResetKernel<<<1, 32, 0, st>>>(ws.counters, nextBit | (1u << WF_CNT_SHADOW) | (1u << WF_CNT_CURSOR));
-        wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.ray, ws.result, ws.queue[cur],
-                                                        ws.counters + (cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0),
-                                                        ws.counters + WF_CNT_CURSOR, 1u, minNodeLanes);
         {
+            Timed tm(KC_TRACE, st);
+            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.ray, ws.result, ws.queue[cur],
+                                                            ws.counters + (cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0),
+                                                            ws.counters + WF_CNT_CURSOR, 1u, minNodeLanes);
+        }
+        {
+            Timed tm(KC_SHADE, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadeFn, dim3(gShade), dim3(TRACE_THREADS), args, histSmem, st));
         }
         if (guide && it < D.path_length) {
             wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 1u << WF_CNT_CURSOR);
-            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.shadowRay, ws.shadowResult, ws.shadowQueue,
-                                                            ws.counters + WF_CNT_SHADOW, ws.counters + WF_CNT_CURSOR, 2u,
-                                                            minNodeLanes);
+            {
+                Timed tm(KC_SHADOW_TRACE, st);
+                wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.shadowRay, ws.shadowResult, ws.shadowQueue,
+                                                                ws.counters + WF_CNT_SHADOW, ws.counters + WF_CNT_CURSOR,
+                                                                2u, minNodeLanes);
+            }
+            Timed tm(KC_SHADE_SHADOW, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadowFn, dim3(gShadow), dim3(TRACE_THREADS), args, histSmem, st));
         }
@@ -356,6 +415,23 @@ extern "C" {
 const char* theia_last_error(void) { return g_error; }
 int theia_abi_version(void) { return THEIA_ABI_VERSION; }
 uint64_t theia_kernel_launches(void) { return g_launches.load(); }
+
+int theia_profile_enable(int on) {
+    profCollect();
+    if (on) { for (int k = 0; k < KC_COUNT; ++k) { g_prof.ms[k] = 0.0; g_prof.n[k] = 0; } }
+    g_prof.on = on != 0;
+    return 0;
+}
+int theia_profile_read(double* ms, uint64_t* launches, uint32_t n) {
+    if (!ms || !launches) { setError("theia_profile_read: null argument"); return -1; }
+    profCollect();
+    for (uint32_t k = 0; k < n; ++k) {
+        ms[k] = k < KC_COUNT ? g_prof.ms[k] : 0.0;
+        launches[k] = k < KC_COUNT ? g_prof.n[k] : 0;
+    }
+    return KC_COUNT;
+}
+const char* theia_profile_class_name(uint32_t cls) { return cls < KC_COUNT ? g_classNames[cls] : ""; }
 
 int theia_device_info(int* sm_count, int* cc_major, int* cc_minor) {
     int dev = 0;
@@ -399,7 +475,10 @@ int theia_hist_reduce(float* partials_dev, uint32_t n_hist, uint32_t n_bins, flo
                       void* stream) {
     if (!partials_dev || !out_dev) { setError("theia_hist_reduce: null argument"); return -1; }
     if (n_bins == 0) return 0;
-    histReduceKernel<<<blocksFor(n_bins, 128), 128, 0, (cudaStream_t)stream>>>(partials_dev, n_hist, n_bins, norm, out_dev, clear);
+    {
+        Timed tm(KC_REDUCE, (cudaStream_t)stream);
+        histReduceKernel<<<blocksFor(n_bins, 128), 128, 0, (cudaStream_t)stream>>>(partials_dev, n_hist, n_bins, norm, out_dev, clear);
+    }
     countLaunches(1);
     CUDA_TRY(cudaGetLastError());
     return 0;
@@ -460,7 +539,10 @@ int theia_trace_forward(const theia_trace_launch_t* launch) {
     if (launch->tracer == THEIA_TRACER_SCENE_FORWARD && launch->workspace) return launchWavefront(launch, D);
     if (plan(launch, D, K)) return -1;
     void* args[] = {&D};
-    CUDA_TRY(cudaLaunchKernel(K.fn, dim3(K.grid), dim3(TRACE_THREADS), args, K.smem, (cudaStream_t)launch->stream));
+    {
+        Timed tm(launch->tracer == THEIA_TRACER_VOLUME_FORWARD ? KC_VOLUME : KC_SCENE, (cudaStream_t)launch->stream);
+        CUDA_TRY(cudaLaunchKernel(K.fn, dim3(K.grid), dim3(TRACE_THREADS), args, K.smem, (cudaStream_t)launch->stream));
+    }
     countLaunches(1);
     return 0;
 }
