@@ -115,17 +115,34 @@ __global__ void mathEvalKernel(uint32_t fn, const float* x, const float* y, uint
     }
 }
 // sh/estimator.reduce.glsl:17-35: per bin Kahan sum over the partial histograms (precise)
+// The order of the sum is the reference's (row 0, 1, 2, ...); only the loads are batched so
+// that 16 rows are in flight per thread instead of one dependent load per row.
 __global__ void histReduceKernel(float* partials, uint32_t nHist, uint32_t nBins, float norm, float* out, int clear) {
     uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= nBins) return;
+    constexpr uint32_t BATCH = 16;
     float result = 0.0f, c = 0.0f;
-    for (uint32_t n = 0; n < nHist; ++n) {
-        float* p = partials + (size_t)n * nBins + b;
-        float y = __fsub_rn(*p, c);
-        float t = __fadd_rn(result, y);
-        c = __fsub_rn(__fsub_rn(t, result), y);
-        result = t;
-        if (clear) *p = 0.0f;
+    for (uint32_t n0 = 0; n0 < nHist; n0 += BATCH) {
+        float v[BATCH];
+#pragma unroll
+        for (uint32_t k = 0; k < BATCH; ++k) {
+            float* p = partials + (size_t)(n0 + k) * nBins + b;
+            v[k] = (n0 + k < nHist) ? __ldcg(p) : 0.0f;
+        }
+        if (clear) {
+#pragma unroll
+            for (uint32_t k = 0; k < BATCH; ++k)
+                if (n0 + k < nHist) partials[(size_t)(n0 + k) * nBins + b] = 0.0f;
+        }
+#pragma unroll
+        for (uint32_t k = 0; k < BATCH; ++k) {
+            if (n0 + k < nHist) {
+                float y = __fsub_rn(v[k], c);
+                float t = __fadd_rn(result, y);
+                c = __fsub_rn(__fsub_rn(t, result), y);
+                result = t;
+            }
+        }
     }
     out[b] = result * norm;
 }

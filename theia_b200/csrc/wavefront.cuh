@@ -151,6 +151,10 @@ __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__
     __syncthreads();
     const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
     const uint32_t total = *countPtr * raysPerEntry;
+    // rays a lane takes per fetch: 4 while there is plenty of work (fewer atomics), 1 once the
+    // queue is short, so that the tail is spread over all lanes instead of queued up in a few
+    const uint32_t lanes = gridDim.x * blockDim.x;
+    const uint32_t fetch = total / lanes >= 4u * WF_FETCH ? WF_FETCH : 1u;
 
     uint32_t stackKey[THEIA_STACK_SIZE];
     float stackT[THEIA_STACK_SIZE];
@@ -181,11 +185,11 @@ __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__
         if (needChunk) {
             const uint32_t leader = __ffs(needChunk) - 1;
             uint32_t base = 0;
-            if (laneId() == leader) base = atomicAdd(cursor, WF_FETCH * (uint32_t)__popc(needChunk));
+            if (laneId() == leader) base = atomicAdd(cursor, fetch * (uint32_t)__popc(needChunk));
             base = __shfl_sync(FULL_MASK, base, leader);
             if (idle && chunkNext == chunkEnd) {
-                chunkNext = base + WF_FETCH * (uint32_t)__popc(needChunk & laneMaskLt());
-                chunkEnd = chunkNext + WF_FETCH;
+                chunkNext = base + fetch * (uint32_t)__popc(needChunk & laneMaskLt());
+                chunkEnd = chunkNext + fetch;
             }
         }
         if (idle) {
@@ -208,7 +212,9 @@ __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__
 
         // ---- phase N (left early once only a few lanes are still looking for a leaf: they
         // resume in the next round instead of holding up the triangle tests of the others)
-        const uint32_t nodeLimit = min(minNodeLanes, (uint32_t)__popc(__ballot_sync(FULL_MASK, sp > 0)));
+        // (at most half of the lanes that entered may be dropped this way, or a warp with few
+        // busy lanes would leave after every node)
+        const uint32_t nodeLimit = min(minNodeLanes, ((uint32_t)__popc(__ballot_sync(FULL_MASK, sp > 0)) + 1u) >> 1);
         while (sp > 0) {
             if ((uint32_t)__popc(__activemask()) < nodeLimit) break;  // the first iteration always runs
             --sp;

@@ -24,6 +24,7 @@ for combo in itertools.product(*[v for _, v in sweeps]) if sweeps else [()]:
             r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=120)
             d = json.loads(r.stdout.strip().splitlines()[-1])
             print(" ".join(f"{k}={v}" for (k, _), v in zip(sweeps, combo)), w, f"{d['value']:.4g} seg/s", f"{d['ms_per_step']:.3f} ms/step",
-                  f"e2e {d['e2e']['value']:.4g}", flush=True)
+                  f"e2e {d['e2e']['value']:.4g}",
+                  " ".join(f"{n.replace('Kernel', '')}={v['ms_per_launch']:.3f}" for n, v in d["roofline"]["kernels"].items()), flush=True)
         except Exception as e:  # noqa: BLE001
             print(combo, w, "FAILED", repr(e)[:200], flush=True)
