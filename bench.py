@@ -146,17 +146,18 @@ def cpuBaseline(workload: str, paths: int, steps: int = 1, warmup: int = 0):
     import oracle
     from theia_b200 import _device
     import harness as H
-    cores = os.cpu_count() or 1
+    # explicit thread count: torchrun exports OMP_NUM_THREADS=1
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     with _device.useDevice("cpu"):
         cfg, _, _ = buildWorkload(workload, paths)
         tr = cfg["tracer"]
         osc = oracle.OracleScene(tr.scene) if hasattr(tr, "scene") else None
         for _ in range(warmup):
-            H.runOracle(cfg, 0, oracleScene=osc)
+            H.runOracle(cfg, 0, oracleScene=osc, threads=cores)
         segs = hits = 0
         t0 = time.perf_counter()
         for _ in range(steps):
-            c = H.runOracle(cfg, 0, oracleScene=osc)
+            c = H.runOracle(cfg, 0, oracleScene=osc, threads=cores)
             segs += int(c[0])
             hits += int(c[1])
         dt = time.perf_counter() - t0

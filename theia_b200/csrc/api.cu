@@ -494,7 +494,7 @@ int theia_hist_reduce(float* partials_dev, uint32_t n_hist, uint32_t n_bins, flo
     if (n_bins == 0) return 0;
     {
         Timed tm(KC_REDUCE, (cudaStream_t)stream);
-        histReduceKernel<<<blocksFor(n_bins, 128), 128, 0, (cudaStream_t)stream>>>(partials_dev, n_hist, n_bins, norm, out_dev, clear);
+        histReduceKernel<<<blocksFor(n_bins, 32), 32, 0, (cudaStream_t)stream>>>(partials_dev, n_hist, n_bins, norm, out_dev, clear);
     }
     countLaunches(1);
     CUDA_TRY(cudaGetLastError());
@@ -534,6 +534,19 @@ int theia_trace_grid_size(const theia_trace_launch_t* launch, uint32_t* n_blocks
     KernelPlan K;
     if (!n_blocks) { setError("theia_trace_grid_size: null argument"); return -1; }
     if (translate(launch, D)) return -1;
+    if (launch->tracer == THEIA_TRACER_SCENE_FORWARD && launch->workspace) {
+        // wavefront: the shading grids are the ones that write partial histograms
+        const bool pol = launch->polarized != 0;
+        const size_t smem = (D.response.kind == THEIA_RESPONSE_HISTOGRAM && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
+        uint32_t gShade = 0, gShadow = 0;
+        if (persistentGrid(pol ? (const void*)wfShadeKernel<true> : (const void*)wfShadeKernel<false>, smem, &gShade) ||
+            persistentGrid(pol ? (const void*)wfShadeShadowKernel<true> : (const void*)wfShadeShadowKernel<false>, smem, &gShadow))
+            return -1;
+        const uint32_t need = blocksFor(D.batch_size, TRACE_THREADS);
+        uint32_t g = gShade > gShadow ? gShade : gShadow;
+        *n_blocks = g < need ? g : (need > 0 ? need : 1u);
+        return 0;
+    }
     if (plan(launch, D, K)) return -1;
     *n_blocks = K.grid;
     return 0;

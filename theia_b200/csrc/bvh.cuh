@@ -104,15 +104,13 @@ TDEV float safeInv(float d) {
     return inv;
 }
 TDEV uint32_t byteOf(uint32_t w, int i) { return (w >> (8 * i)) & 0xFFu; }
-// float(byte i of w), exactly, without the conversion unit (I2F.U8 runs on the quarter rate XU
-// pipe and 48 of them per node made the traversal XU bound): one byte permute builds the
-// float 2^23 + b, one exact subtraction removes the 2^23.
-TDEV float byteToFloat(uint32_t w, int i) {
-#ifdef __CUDA_ARCH__
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440u | (uint32_t)i)) - 8388608.0f;
-#else
-    return (float)byteOf(w, i);
-#endif
+// 32768 + (byte i of w) as a float, built by ONE byte permute: bytes {0, b, 0, 0x47} are the
+// float 2^15 * (1 + b * 2^-15). (I2F.U8 runs on the quarter rate conversion unit, and 48 of
+// them per node made the traversal bound by it.) The caller folds the 2^15 into its constant.
+#define THEIA_BYTE_BIAS 32768.0f
+static __constant__ uint32_t g_byteMagic = 0x47000000u;
+TDEV float biasedByte(uint32_t w, int i, uint32_t magic /* 0x47000000 in a register */) {
+    return __uint_as_float(__byte_perm(w, magic, 0x7504u | ((uint32_t)i << 4)));
 }
 
 // Ray in the space of the structure being traversed.
@@ -124,15 +122,23 @@ struct SlabRay {
 // Tests the eight quantised child boxes of a node against [0, lim]; returns the hit mask and
 // the entry distances. Each axis interval is widened by ~5 ulp of its operands.
 TDEV uint32_t testChildren(const NodeRegs& n, const SlabRay& r, float lim, float tmin[8]) {
-    const float EPS = 6e-7f;
+    // slack per axis: ~5 ulp of the operands (EPS) plus the rounding of the biased constant
+    // below, 2^-24 * 2^15 |a| = 2^-9 |a|, covered twice over by 2^-8 |a| (0.4 % of a grid cell)
+    const float EPS = 6e-7f, SLACK_A = 256.0f * 6e-7f + 0.00390625f;
     float px = u2f(n.a.x), py = u2f(n.a.y), pz = u2f(n.a.z);
     float sx = u2f(byteOf(n.a.w, 0) << 23), sy = u2f(byteOf(n.a.w, 1) << 23), sz = u2f(byteOf(n.a.w, 2) << 23);
     float ax = sx * r.ix, ay = sy * r.iy, az = sz * r.iz;
     float bx = (px - r.ox) * r.ix, by = (py - r.oy) * r.iy, bz = (pz - r.oz) * r.iz;
-    float ex = EPS * fmaf(256.0f, fabsf(ax), fabsf(bx));
-    float ey = EPS * fmaf(256.0f, fabsf(ay), fabsf(by));
-    float ez = EPS * fmaf(256.0f, fabsf(az), fabsf(bz));
-    float bxl = bx - ex, bxh = bx + ex, byl = by - ey, byh = by + ey, bzl = bz - ez, bzh = bz + ez;
+    float ex = fmaf(SLACK_A, fabsf(ax), EPS * fabsf(bx));
+    float ey = fmaf(SLACK_A, fabsf(ay), EPS * fabsf(by));
+    float ez = fmaf(SLACK_A, fabsf(az), EPS * fabsf(bz));
+    // plane distance = q * a + b with the byte q read as 32768 + q: subtract 32768 a from b once
+    float cx = fmaf(-THEIA_BYTE_BIAS, ax, bx), cy = fmaf(-THEIA_BYTE_BIAS, ay, by), cz = fmaf(-THEIA_BYTE_BIAS, az, bz);
+    float bxl = cx - ex, bxh = cx + ex, byl = cy - ey, byh = cy + ey, bzl = cz - ez, bzh = cz + ez;
+    // read from constant memory so that the permute takes it as its constant bank operand and
+    // the selector as its immediate (as a literal it would claim the immediate slot and every
+    // selector would need a register of its own)
+    const uint32_t magic = g_byteMagic;
     // per axis: words holding the near / far plane bytes of children 0-3 and 4-7
     // layout: b = {childBase, primBase, meta0-3, meta4-7}, c = {qlox, qlox, qloy, qloy},
     //         d = {qloz, qloz, qhix, qhix}, e = {qhiy, qhiy, qhiz, qhiz}
@@ -145,12 +151,12 @@ TDEV uint32_t testChildren(const NodeRegs& n, const SlabRay& r, float lim, float
     for (int i = 0; i < 8; ++i) {
         const int j = i & 3;
         uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, j);
-        float tnx = fmaf(byteToFloat(i < 4 ? xn0 : xn1, j), ax, bxl);
-        float tfx = fmaf(byteToFloat(i < 4 ? xf0 : xf1, j), ax, bxh);
-        float tny = fmaf(byteToFloat(i < 4 ? yn0 : yn1, j), ay, byl);
-        float tfy = fmaf(byteToFloat(i < 4 ? yf0 : yf1, j), ay, byh);
-        float tnz = fmaf(byteToFloat(i < 4 ? zn0 : zn1, j), az, bzl);
-        float tfz = fmaf(byteToFloat(i < 4 ? zf0 : zf1, j), az, bzh);
+        float tnx = fmaf(biasedByte(i < 4 ? xn0 : xn1, j, magic), ax, bxl);
+        float tfx = fmaf(biasedByte(i < 4 ? xf0 : xf1, j, magic), ax, bxh);
+        float tny = fmaf(biasedByte(i < 4 ? yn0 : yn1, j, magic), ay, byl);
+        float tfy = fmaf(biasedByte(i < 4 ? yf0 : yf1, j, magic), ay, byh);
+        float tnz = fmaf(biasedByte(i < 4 ? zn0 : zn1, j, magic), az, bzl);
+        float tfz = fmaf(biasedByte(i < 4 ? zf0 : zf1, j, magic), az, bzh);
         float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
         float tf = fminf(fminf(tfx, tfy), fminf(tfz, lim));
         tmin[i] = tn;

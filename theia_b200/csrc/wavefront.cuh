@@ -115,6 +115,20 @@ TDEV void loadState(const Workspace& ws, uint32_t slot, Ray& r, uint32_t& dim, u
     }
 }
 
+// Pulls the state, ray query and result of a slot towards L2 ahead of the iteration that
+// shades it: the shading kernels gather ~150 bytes per path through a queue and were bound
+// by the latency of those loads (few warps fit next to 128 registers per thread).
+template <bool POL>
+TDEV void prefetchSlot(const Workspace& ws, uint32_t slot) {
+    const uint32_t* s = ws.state + slot;
+    const size_t C = ws.capacity;
+    constexpr uint32_t nF = POL ? WF_NFIELDS_POL : WF_NFIELDS_UNPOL;
+#pragma unroll
+    for (uint32_t f = 0; f < nF; ++f) asm volatile("prefetch.global.L2 [%0];" ::"l"(s + f * C));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(ws.ray + 2 * (size_t)slot));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(ws.result + slot));
+}
+
 // Appends the slots of the lanes with `push` to a queue: one atomic per warp.
 // MUST be called by all 32 lanes.
 TDEV void queuePush(uint32_t* queue, uint32_t* counter, bool push, uint32_t slot) {
@@ -211,17 +225,22 @@ __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__
         if (__all_sync(FULL_MASK, done)) break;
 
         // ---- phase N (left early once only a few lanes are still looking for a leaf: they
-        // resume in the next round instead of holding up the triangle tests of the others)
-        // (at most half of the lanes that entered may be dropped this way, or a warp with few
+        // resume in the next round instead of holding up the triangle tests of the others;
+        // at most half of the lanes that entered may be dropped this way, or a warp with few
         // busy lanes would leave after every node)
         const uint32_t nodeLimit = min(minNodeLanes, ((uint32_t)__popc(__ballot_sync(FULL_MASK, sp > 0)) + 1u) >> 1);
         while (sp > 0) {
             if ((uint32_t)__popc(__activemask()) < nodeLimit) break;  // the first iteration always runs
-            --sp;
-            const uint32_t key = stackKey[sp];
-            const float tEntry = stackT[sp];
+            // pop until an entry that is still in front of the closest hit
             const float lim = bestValid ? bestT : tmax;
-            if (tEntry > lim) continue;
+            uint32_t key;
+            float tEntry;
+            do {
+                --sp;
+                key = stackKey[sp];
+                tEntry = stackT[sp];
+            } while (tEntry > lim && sp > 0);
+            if (tEntry > lim) break;
             const uint32_t type = key >> 30, payload = key & 0x3FFFFFFFu;
             if (type == WE_LEAF) { pending = payload; break; }
             if (type == WE_INST) {
@@ -245,10 +264,11 @@ __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__
                 continue;
             }
             const bool inBlas = type == WE_BLAS;
-            NodeRegs n;
-            if (inBlas) n = loadNode(blasNodes + payload);
-            else if (payload < sc.nTop) n = loadNodeShared(sc.topNodes + payload);
-            else n = loadNode(sc.nodes + payload);
+            // one load sequence for all three homes of a node (generic address: the top of the
+            // TLAS lives in shared memory)
+            const WideNode* np = inBlas ? blasNodes + payload
+                                        : (payload < sc.nTop ? sc.topNodes + payload : sc.nodes + payload);
+            const NodeRegs n = loadNodeShared(np);
             float tmin[8];
             uint32_t mask = testChildren(n, inBlas ? obj : world, lim, tmin);
             if (mask == 0) continue;
@@ -457,10 +477,17 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
     uint32_t* nextCounter = ws.counters + (cur ? WF_CNT_QUEUE0 : WF_CNT_QUEUE1);
     uint32_t nSegments = 0, nResponses = 0, nShadow = 0, stride;
 
+    uint32_t slotNext = 0;
+    {
+        const uint32_t i0 = wfWarpBase(stride) + laneId();
+        if (i0 < count) slotNext = queue[i0];
+    }
     for (uint32_t base = wfWarpBase(stride); base < count; base += stride) {
         const uint32_t i = base + laneId();
         const bool active = i < count;
-        const uint32_t slot = active ? queue[i] : 0u;
+        const uint32_t slot = slotNext;
+        const bool activeNext = i + stride < count;
+        if (activeNext) slotNext = queue[i + stride];
         const uint32_t idx = P.first_path + slot;
         Ray ray;
         uint32_t dim = 0, flags = 1u;
@@ -495,6 +522,7 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
         commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
         hitSeq += has ? 1u : 0u;
         has = false;
+        if (activeNext) prefetchSlot<POL>(ws, slotNext);  // this iteration's loads are consumed by now
 
         const bool interact = active && result >= 0;
         const bool last = it == P.path_length;

@@ -395,6 +395,10 @@ class HistogramHitResponse(HitResponse):
         r.hist_partials = self._reducer.histIn.data_ptr()
         return r
 
+    def _setRows(self, i: int, rows: int) -> None:
+        """Called by the tracer while it assembles launch i: partial histograms it will write."""
+        self._reducer._block("Params", i).nHist = rows
+
     def update(self, i: int) -> None:
         if self._reducer is None:
             self._reducer = self._initReducer()

@@ -222,6 +222,7 @@ class Tracer(PipelineStage):
         self._polarized = polarized
         self._firstPath = 0
         self._workCounters = None
+        self._rowCache: dict = {}
         self.setParams(batchSize=batchSize, _groupCountY=1, _groupCountZ=1)
         response.prepare(self._getTraceConfig())
 
@@ -341,7 +342,24 @@ class Tracer(PipelineStage):
         L.stream = _device.currentStream(self._device)
         if self._workCounters is not None:
             L.work_counters = self._workCounters.data_ptr()
+        if L.response.kind == _abi.RESPONSE_HISTOGRAM:
+            # only the rows the launch really writes are summed (and cleared) by the reducer
+            rows = min(self._histRows(L), L.response.hist_capacity)
+            L.response.hist_capacity = rows
+            self.response._setRows(i, rows)
         return L, keep
+
+    def _histRows(self, L: _abi.TraceLaunch) -> int:
+        """Number of partial histograms a launch writes: one per CTA of its (persistent) grid."""
+        if self._device != "cuda":
+            return -(L.batch_size // -self.blockSize)
+        key = (L.batch_size, bool(L.workspace), L.polarized, L.response.n_bins)
+        rows = self._rowCache.get(key)
+        if rows is None:
+            g = c_uint32()
+            _lib.check(_lib.load().theia_trace_grid_size(byref(L), byref(g)))
+            rows = self._rowCache[key] = int(g.value)
+        return rows
 
     def run(self, i: int) -> list[Command]:
         def cmd() -> None:
