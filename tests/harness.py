@@ -329,3 +329,44 @@ def hitView(cfg, i: int = 0):
     r = cfg["response"]
     v = r.queue.view(i)
     return v[: min(v.count, r.capacity)]
+
+
+def volumeC4(N: int, *, key: int = 0xABBA, nBins: int = 100, binSize: float = 5.0):
+    """
+    Config C4 (examples/03_multiple_lightsources.ipynb cells 4-8 of the reference): several
+    VolumeForwardTracer pipelines that share target, wavelength source, response and rng and are
+    configured by tasks. Returns the named pipelines, the task list and the shared stages.
+    """
+    from theia_b200 import pipeline as pl
+    med = WaterTestModel().createMedium()
+    store = material.MaterialStore([], media=[med])
+    rng = random.PhiloxRNG(key=key)
+    resp = response.HistogramHitResponse(response.UniformValueResponse(), nBins=nBins, binSize=binSize)
+    tgt = target.SphereTarget(position=(-1.0, 0.0, 0.0), radius=0.5)
+    wl = light.ConstWavelengthSource(500.0)
+    sources = {
+        "sphere": light.SphericalLightSource(),
+        "pencil": light.PencilLightSource(),
+        "cone": light.ConeLightSource(),
+        "cascade": makeLight("cascade"),
+        "muon": makeLight("muon"),
+    }
+    tracers = {name: trace.VolumeForwardTracer(N, src, tgt, wl, resp, rng, nScattering=10,
+                                               medium=store.media[med.name]) for name, src in sources.items()}
+    rng.autoAdvance = max(t.nRNGSamples for t in tracers.values())
+    pipelines = {name: pl.Pipeline(t.collectStages()) for name, t in tracers.items()}
+    tasks = [
+        ("sphere", {"lightSource__budget": 1e5, "lightSource__timeRange": (0.0, 10.0),
+                    "lightSource__position": (1.0, 0.0, 0.0)}),
+        ("sphere", {}),
+        ("pencil", {"lightSource__position": (0.0, 1.0, 0.0), "lightSource__direction": (-0.8, -0.36, -0.24),
+                    "lightSource__budget": 5e6, "lightSource__timeRange": (8.0, 8.5)}),
+        ("pencil", {}),
+        ("cone", {"lightSource__position": (1.0, 0.5, 0.0), "lightSource__direction": (-1.0, 0.0, 0.0),
+                  "lightSource__cosOpeningAngle": 0.7, "lightSource__budget": 1e5,
+                  "lightSource__timeRange": (0.0, 5.0)}),
+        ("cascade", {}),
+        ("muon", {}),
+        ("sphere", {"lightSource__position": (0.0, 2.0, 0.0)}),
+    ]
+    return {"pipelines": pipelines, "tracers": tracers, "tasks": tasks, "response": resp, "rng": rng, "store": store}

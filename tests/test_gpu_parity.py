@@ -270,3 +270,34 @@ def test_profile_counters(cuda):
     assert all(v[1] > 0.0 for v in got.values())
     H.runGpu(cfg)  # disabled again: nothing accumulates
     assert lib.theia_profile_read(ms, n, 8) == 8 and int(n[3]) == 10
+
+
+# ------------------------------------------------------------------ C4: several pipelines, shared stages, tasks
+def test_c4_multiple_light_sources_scheduler_matches_oracle(cuda, orc):
+    # examples/03_multiple_lightsources.ipynb: tasks dealt to named pipelines that share the
+    # target, response and rng; every batch must equal the oracle run of the same task
+    from theia_b200 import pipeline as pl
+    N = 16384
+    with _device.useDevice("cuda"):
+        g = H.volumeC4(N)
+    with _device.useDevice("cpu"):
+        c = H.volumeC4(N)
+    hists = []
+
+    def process(config, batch, args):
+        hists.append(g["response"].result(config).copy())
+
+    sched = pl.PipelineScheduler(g["pipelines"], processFn=process)
+    sched.schedule(g["tasks"])
+    sched.wait()
+    sched.destroy()
+    assert len(hists) == len(g["tasks"])
+    for n, (name, params) in enumerate(c["tasks"]):
+        i = n % 2
+        c["pipelines"][name].setParams(**params)
+        cfg = {"tracer": c["tracers"][name], "response": c["response"]}
+        H.runOracle(cfg, i)
+        want = c["response"].result(i)
+        assert want.sum() > 0, name
+        assert np.allclose(hists[n], want, rtol=2e-4, atol=1e-9 * want.max()), (n, name)
+    assert g["rng"].getParam("offset") == c["rng"].getParam("offset") == len(g["tasks"]) * g["rng"].autoAdvance

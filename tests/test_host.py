@@ -143,3 +143,35 @@ def test_hit_queue_layout():
     assert raw[:4].view(np.uint32)[0] == 3
     assert f[1] == 1.0 and f[n + 1] == 2.0 and f[2 * n + 1] == 3.0
     assert v[1:3]["position"].shape == (2, 3) and v[1:3].count == 2
+
+
+def test_scheduler_with_named_pipelines():
+    # examples/03_multiple_lightsources.ipynb cell 6-8: tasks are (pipeline name, params)
+    class Stage(pipeline.PipelineStage):
+        name = "stage"
+
+        class P(ctypes.Structure):
+            _fields_ = [("value", ctypes.c_float)]
+
+        def __init__(self, log, tag):
+            super().__init__({"P": self.P})
+            self._log, self._tag = log, tag
+
+        def run(self, i):
+            return [lambda: self._log.append((self._tag, i, self._block("P", i).value))]
+
+    log = []
+    with _device.useDevice("cpu"):
+        a, b = Stage(log, "a"), Stage(log, "b")
+        pa, pb = pipeline.Pipeline([("s", a)]), pipeline.Pipeline([("s", b)])
+    done = []
+    sched = pipeline.PipelineScheduler({"a": pa, "b": pb}, processFn=lambda i, n, args: done.append((i, n)))
+    sched.schedule([("a", {"s__value": 1.0}), ("b", {"s__value": 2.0}), ("a", {}), ("b", {"s__value": 4.0})])
+    sched.wait()
+    assert log == [("a", 0, 1.0), ("b", 1, 2.0), ("a", 0, 1.0), ("b", 1, 4.0)]
+    assert done == [(0, 0), (1, 1), (0, 2), (1, 3)]
+    with pytest.raises(ValueError):
+        sched.schedule([{"s__value": 1.0}])
+    with pytest.raises(KeyError):
+        sched.schedule([("c", {})])
+    sched.destroy()

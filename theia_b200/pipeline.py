@@ -297,17 +297,28 @@ class PipelineScheduler:
     an update thread prepares configuration ``n % 2`` and enqueues the GPU work, a process
     thread waits for the GPU and calls ``processFn(config, batch, args)``. A configuration
     is only reused once its previous result has been processed.
+
+    ``pipeline`` may also be a dict of named pipelines (examples/03_multiple_lightsources.ipynb
+    cell 6); tasks are then ``(name, params)`` tuples. The pipelines may share stages (target,
+    response, rng, ...): configurations alternate over all tasks, whichever pipeline runs them.
     """
 
     def __init__(
         self,
-        pipeline: Pipeline,
+        pipeline: "Pipeline | dict[str, Pipeline]",
         *,
         queueSize: int = 0,
         processFn: Callable[[int, int, Any], None] | None = None,
         processArgs: Any = None,
     ) -> None:
-        self._pipeline = pipeline
+        if isinstance(pipeline, dict):
+            if not pipeline:
+                raise ValueError("no pipeline given")
+            self._pipelines = dict(pipeline)
+            self._pipeline = next(iter(self._pipelines.values()))
+        else:
+            self._pipelines = None
+            self._pipeline = pipeline
         self._processFn = processFn
         self._processArgs = processArgs
         self._tasks: _queue.Queue = _queue.Queue(queueSize)
@@ -319,7 +330,8 @@ class PipelineScheduler:
         self._cond = threading.Condition()
         self._error: BaseException | None = None
         self._alive = True
-        self._stream = torch.cuda.Stream() if pipeline._device == "cuda" else None
+        devices = {p._device for p in (self._pipelines.values() if self._pipelines else [self._pipeline])}
+        self._stream = torch.cuda.Stream() if "cuda" in devices else None
         self._tUpdate = threading.Thread(target=self._updateLoop, daemon=True)
         self._tProcess = threading.Thread(target=self._processLoop, daemon=True)
         self._tUpdate.start()
@@ -337,11 +349,21 @@ class PipelineScheduler:
     def totalTasks(self) -> int:
         return self._total
 
-    def schedule(self, tasks: Iterable[dict], *, timeout: float | None = None) -> None:
+    def schedule(self, tasks: Iterable, *, timeout: float | None = None) -> None:
+        """Queues tasks: parameter dicts, or ``(pipelineName, params)`` with named pipelines."""
         for t in tasks:
+            if self._pipelines is not None:
+                if not (isinstance(t, tuple) and len(t) == 2):
+                    raise ValueError("with named pipelines a task is a tuple (name, params)")
+                name, params = t
+                if name not in self._pipelines:
+                    raise KeyError(f"unknown pipeline '{name}'")
+                item = (name, dict(params))
+            else:
+                item = (None, dict(t))
             with self._cond:
                 self._total += 1
-            self._tasks.put(dict(t), timeout=timeout)
+            self._tasks.put(item, timeout=timeout)
 
     def _fail(self, err: BaseException) -> None:
         with self._cond:
@@ -361,12 +383,14 @@ class PipelineScheduler:
             ev = None
             try:
                 if self._error is None:
-                    self._pipeline.setParams(**task)
+                    name, params = task
+                    pipeline = self._pipeline if name is None else self._pipelines[name]
+                    pipeline.setParams(**params)
                     if self._stream is not None:
                         with torch.cuda.stream(self._stream):
-                            ev = self._pipeline.runAsync(i)
+                            ev = pipeline.runAsync(i)
                     else:
-                        ev = self._pipeline.runAsync(i)
+                        ev = pipeline.runAsync(i)
             except BaseException as err:  # surfaced by wait()
                 self._fail(err)
             self._submitted += 1
