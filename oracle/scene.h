@@ -100,12 +100,16 @@ static inline bool hitBox(const AABB& b, const float o[3], const float inv[3], f
     return tn <= tf * 1.0000005f + 1e-30f;
 }
 
-// Per (ray, instance) setup of the watertight test.
+// Per (ray, instance) setup of the watertight test. The permutation (kx, ky, kz) and shear
+// (Sx, Sy, Sz) of the paper are folded into three vectors and offsets: the sheared
+// coordinates of a vertex v are x' = v . mx + cx, y' = v . my + cy, z' = v . mz + cz with
+// mx = e_kx - Sx e_kz, my = e_ky - Sy e_kz, mz = Sz e_kz, c = -(o . m), each one fma chain.
 struct WoopRay {
     float o[3], d[3];
-    int kx, ky, kz;
-    float Sx, Sy, Sz;
+    float mx[3], my[3], mz[3];
+    float cx, cy, cz;
 };
+static inline float dot3(const float a[3], const float b[3]) { return fmaf(a[2], b[2], fmaf(a[1], b[1], a[0] * b[0])); }
 static inline void woopSetup(WoopRay& r) {
     float ax = abs_(r.d[0]), ay = abs_(r.d[1]), az = abs_(r.d[2]);
     int kz = 0;
@@ -115,20 +119,27 @@ static inline void woopSetup(WoopRay& r) {
     int kx = kz + 1; if (kx == 3) kx = 0;
     int ky = kx + 1; if (ky == 3) ky = 0;
     if (r.d[kz] < 0.0f) { int t = kx; kx = ky; ky = t; }
-    r.kx = kx; r.ky = ky; r.kz = kz;
-    r.Sz = 1.0f / r.d[kz];
-    r.Sx = r.d[kx] * r.Sz;
-    r.Sy = r.d[ky] * r.Sz;
+    const float Sz = 1.0f / r.d[kz];
+    const float Sx = r.d[kx] * Sz;
+    const float Sy = r.d[ky] * Sz;
+    for (int k = 0; k < 3; ++k) {
+        r.mx[k] = k == kz ? -Sx : (k == kx ? 1.0f : 0.0f);
+        r.my[k] = k == kz ? -Sy : (k == ky ? 1.0f : 0.0f);
+        r.mz[k] = k == kz ? Sz : 0.0f;
+    }
+    r.cx = -dot3(r.o, r.mx);
+    r.cy = -dot3(r.o, r.my);
+    r.cz = -dot3(r.o, r.mz);
+}
+static inline float shear(const float* v, const float m[3], float c) {
+    return fmaf(v[2], m[2], fmaf(v[1], m[1], fmaf(v[0], m[0], c)));
 }
 // returns true and (t,u,v) if the triangle is hit with t in (0, tmax)
 static inline bool woopIntersect(const WoopRay& r, const float* v0, const float* v1, const float* v2,
                                  float tmax, float* t_out, float* u_out, float* v_out) {
-    float A[3] = {v0[0] - r.o[0], v0[1] - r.o[1], v0[2] - r.o[2]};
-    float B[3] = {v1[0] - r.o[0], v1[1] - r.o[1], v1[2] - r.o[2]};
-    float C[3] = {v2[0] - r.o[0], v2[1] - r.o[1], v2[2] - r.o[2]};
-    float Ax = fmaf(-r.Sx, A[r.kz], A[r.kx]), Ay = fmaf(-r.Sy, A[r.kz], A[r.ky]);
-    float Bx = fmaf(-r.Sx, B[r.kz], B[r.kx]), By = fmaf(-r.Sy, B[r.kz], B[r.ky]);
-    float Cx = fmaf(-r.Sx, C[r.kz], C[r.kx]), Cy = fmaf(-r.Sy, C[r.kz], C[r.ky]);
+    float Ax = shear(v0, r.mx, r.cx), Ay = shear(v0, r.my, r.cy);
+    float Bx = shear(v1, r.mx, r.cx), By = shear(v1, r.my, r.cy);
+    float Cx = shear(v2, r.mx, r.cx), Cy = shear(v2, r.my, r.cy);
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
@@ -143,7 +154,7 @@ static inline bool woopIntersect(const WoopRay& r, const float* v0, const float*
     if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
     float det = U + V + W;
     if (det == 0.0f) return false;
-    float Az = r.Sz * A[r.kz], Bz = r.Sz * B[r.kz], Cz = r.Sz * C[r.kz];
+    float Az = shear(v0, r.mz, r.cz), Bz = shear(v1, r.mz, r.cz), Cz = shear(v2, r.mz, r.cz);
     float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
     if (det < 0.0f) {
         if (!(T < 0.0f) || !(T > tmax * det)) return false;

@@ -12,7 +12,9 @@ from ctypes import POINTER, c_char_p, c_float, c_int, c_int32, c_uint32, c_uint6
 
 from theia_b200 import _abi
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libtheia_b200.so")
+# THEIA_B200_LIB selects another build of the same library (A/B measurements of kernel variants)
+_LIB_PATH = os.environ.get("THEIA_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)),
+                                                             "libtheia_b200.so")
 _lib = None
 
 #: every symbol include/theia_b200.h declares: name -> (restype, argtypes)

@@ -98,8 +98,10 @@ TDEV NodeRegs loadNodeShared(const WideNode* n) {
     return r;
 }
 
+// (feeds the conservative box tests only: the 1 ulp of rcp.approx is inside their slack)
 TDEV float safeInv(float d) {
-    float inv = 1.0f / d;
+    float inv;
+    asm("rcp.approx.f32 %0, %1;" : "=f"(inv) : "f"(d));
     if (!(abs_(inv) <= 1e30f)) inv = copysignf(1e30f, d);
     return inv;
 }
@@ -165,13 +167,20 @@ TDEV uint32_t testChildren(const NodeRegs& n, const SlabRay& r, float lim, float
     return mask;
 }
 
-// Per (ray, instance) setup of the watertight test
+// Per (ray, instance) setup of the watertight test (Woop, Benthin, Wald, JCGT 2013). The
+// permutation (kx, ky, kz) and the shear (Sx, Sy, Sz) of the paper are folded into three
+// vectors and offsets, so that the sheared coordinates of a vertex v are plain fma chains
+//   x' = v . mx + cx,  y' = v . my + cy,  z' = v . mz + cz
+// with mx = e_kx - Sx e_kz, my = e_ky - Sy e_kz, mz = Sz e_kz and c = -(o . m): no per
+// triangle selects by axis. Shared vertices get identical sheared coordinates in every
+// triangle, which is what makes the edge tests watertight.
 struct WoopRay {
-    float o[3], d[3];
-    int kx, ky, kz;
-    float Sx, Sy, Sz;
+    float o[3], d[3];  // object space ray (setup input)
+    float mx[3], my[3], mz[3];
+    float cx, cy, cz;
 };
 TDEV float pick(const float v[3], int k) { return k == 0 ? v[0] : (k == 1 ? v[1] : v[2]); }
+TDEV float dot3(const float a[3], const float b[3]) { return fmaf(a[2], b[2], fmaf(a[1], b[1], a[0] * b[0])); }
 TDEV void woopSetup(WoopRay& r) {
     float ax = abs_(r.d[0]), ay = abs_(r.d[1]), az = abs_(r.d[2]);
     int kz = 0;
@@ -181,20 +190,25 @@ TDEV void woopSetup(WoopRay& r) {
     int kx = kz + 1; if (kx == 3) kx = 0;
     int ky = kx + 1; if (ky == 3) ky = 0;
     if (pick(r.d, kz) < 0.0f) { int t = kx; kx = ky; ky = t; }
-    r.kx = kx; r.ky = ky; r.kz = kz;
-    r.Sz = 1.0f / pick(r.d, kz);
-    r.Sx = pick(r.d, kx) * r.Sz;
-    r.Sy = pick(r.d, ky) * r.Sz;
+    const float Sz = 1.0f / pick(r.d, kz);
+    const float Sx = pick(r.d, kx) * Sz;
+    const float Sy = pick(r.d, ky) * Sz;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        r.mx[k] = k == kz ? -Sx : (k == kx ? 1.0f : 0.0f);
+        r.my[k] = k == kz ? -Sy : (k == ky ? 1.0f : 0.0f);
+        r.mz[k] = k == kz ? Sz : 0.0f;
+    }
+    r.cx = -dot3(r.o, r.mx);
+    r.cy = -dot3(r.o, r.my);
+    r.cz = -dot3(r.o, r.mz);
 }
+TDEV float shear(const float v[3], const float m[3], float c) { return fmaf(v[2], m[2], fmaf(v[1], m[1], fmaf(v[0], m[0], c))); }
 TDEV bool woopIntersect(const WoopRay& r, const float v0[3], const float v1[3], const float v2[3], float tmax,
                         float* t_out, float* u_out, float* v_out) {
-    float A[3] = {v0[0] - r.o[0], v0[1] - r.o[1], v0[2] - r.o[2]};
-    float B[3] = {v1[0] - r.o[0], v1[1] - r.o[1], v1[2] - r.o[2]};
-    float C[3] = {v2[0] - r.o[0], v2[1] - r.o[1], v2[2] - r.o[2]};
-    float Akz = pick(A, r.kz), Bkz = pick(B, r.kz), Ckz = pick(C, r.kz);
-    float Ax = fmaf(-r.Sx, Akz, pick(A, r.kx)), Ay = fmaf(-r.Sy, Akz, pick(A, r.ky));
-    float Bx = fmaf(-r.Sx, Bkz, pick(B, r.kx)), By = fmaf(-r.Sy, Bkz, pick(B, r.ky));
-    float Cx = fmaf(-r.Sx, Ckz, pick(C, r.kx)), Cy = fmaf(-r.Sy, Ckz, pick(C, r.ky));
+    float Ax = shear(v0, r.mx, r.cx), Ay = shear(v0, r.my, r.cy);
+    float Bx = shear(v1, r.mx, r.cx), By = shear(v1, r.my, r.cy);
+    float Cx = shear(v2, r.mx, r.cx), Cy = shear(v2, r.my, r.cy);
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
@@ -209,7 +223,7 @@ TDEV bool woopIntersect(const WoopRay& r, const float v0[3], const float v1[3], 
     if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
     float det = U + V + W;
     if (det == 0.0f) return false;
-    float Az = r.Sz * Akz, Bz = r.Sz * Bkz, Cz = r.Sz * Ckz;
+    float Az = shear(v0, r.mz, r.cz), Bz = shear(v1, r.mz, r.cz), Cz = shear(v2, r.mz, r.cz);
     float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
     if (det < 0.0f) {
         if (!(T < 0.0f) || !(T > tmax * det)) return false;

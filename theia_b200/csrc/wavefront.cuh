@@ -115,20 +115,6 @@ TDEV void loadState(const Workspace& ws, uint32_t slot, Ray& r, uint32_t& dim, u
     }
 }
 
-// Pulls the state, ray query and result of a slot towards L2 ahead of the iteration that
-// shades it: the shading kernels gather ~150 bytes per path through a queue and were bound
-// by the latency of those loads (few warps fit next to 128 registers per thread).
-template <bool POL>
-TDEV void prefetchSlot(const Workspace& ws, uint32_t slot) {
-    const uint32_t* s = ws.state + slot;
-    const size_t C = ws.capacity;
-    constexpr uint32_t nF = POL ? WF_NFIELDS_POL : WF_NFIELDS_UNPOL;
-#pragma unroll
-    for (uint32_t f = 0; f < nF; ++f) asm volatile("prefetch.global.L2 [%0];" ::"l"(s + f * C));
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(ws.ray + 2 * (size_t)slot));
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(ws.result + slot));
-}
-
 // Appends the slots of the lanes with `push` to a queue: one atomic per warp.
 // MUST be called by all 32 lanes.
 TDEV void queuePush(uint32_t* queue, uint32_t* counter, bool push, uint32_t slot) {
@@ -155,7 +141,7 @@ TDEV void queuePush(uint32_t* queue, uint32_t* counter, bool push, uint32_t slot
 #define WF_FETCH 4u
 enum : uint32_t { WE_TLAS = 0u, WE_INST = 1u, WE_BLAS = 2u, WE_LEAF = 3u };
 
-__global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
+__global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                          uint4* __restrict__ results, const uint32_t* __restrict__ queue,
                                                          const uint32_t* __restrict__ countPtr, uint32_t* cursor,
                                                          uint32_t raysPerEntry, uint32_t minNodeLanes) {
@@ -179,7 +165,8 @@ __global__ void __launch_bounds__(128, 6) wfTraceKernel(const void* __restrict__
     float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 0, tmax = 0;
     SlabRay world = {0, 0, 0, 0, 0, 0}, obj = {0, 0, 0, 0, 0, 0};
     WoopRay wr;
-    wr.kx = wr.ky = wr.kz = 0; wr.Sx = wr.Sy = wr.Sz = 0.0f;
+    wr.cx = wr.cy = wr.cz = 0.0f;
+    wr.mx[0] = wr.mx[1] = wr.mx[2] = wr.my[0] = wr.my[1] = wr.my[2] = wr.mz[0] = wr.mz[1] = wr.mz[2] = 0.0f;
     wr.o[0] = wr.o[1] = wr.o[2] = wr.d[0] = wr.d[1] = wr.d[2] = 0.0f;
     int32_t curInst = -1, curSlot = -1;
     const WideNode* blasNodes = nullptr;
@@ -477,17 +464,10 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
     uint32_t* nextCounter = ws.counters + (cur ? WF_CNT_QUEUE0 : WF_CNT_QUEUE1);
     uint32_t nSegments = 0, nResponses = 0, nShadow = 0, stride;
 
-    uint32_t slotNext = 0;
-    {
-        const uint32_t i0 = wfWarpBase(stride) + laneId();
-        if (i0 < count) slotNext = queue[i0];
-    }
     for (uint32_t base = wfWarpBase(stride); base < count; base += stride) {
         const uint32_t i = base + laneId();
         const bool active = i < count;
-        const uint32_t slot = slotNext;
-        const bool activeNext = i + stride < count;
-        if (activeNext) slotNext = queue[i + stride];
+        const uint32_t slot = active ? queue[i] : 0u;
         const uint32_t idx = P.first_path + slot;
         Ray ray;
         uint32_t dim = 0, flags = 1u;
@@ -522,7 +502,6 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
         commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
         hitSeq += has ? 1u : 0u;
         has = false;
-        if (activeNext) prefetchSlot<POL>(ws, slotNext);  // this iteration's loads are consumed by now
 
         const bool interact = active && result >= 0;
         const bool last = it == P.path_length;
