@@ -175,3 +175,58 @@ def test_scheduler_with_named_pipelines():
     with pytest.raises(KeyError):
         sched.schedule([("c", {})])
     sched.destroy()
+
+
+def test_converge_histogram_task_on_a_stub_pipeline():
+    # src/theia/task.py:22-196: batches are issued until the standard error of the bin sum is small
+    from theia_b200 import task
+
+    class FakeResponse:
+        nBins, retrieve = 4, True
+
+        def __init__(self):
+            self.rng = np.random.default_rng(5)
+            self.buffers = [np.zeros(4), np.zeros(4)]
+
+        def result(self, i):
+            return self.buffers[i]
+
+    resp = FakeResponse()
+
+    class Producer(pipeline.PipelineStage):
+        name = "producer"
+
+        class P(ctypes.Structure):
+            _fields_ = [("sigma", ctypes.c_float)]
+
+        def __init__(self):
+            super().__init__({"P": self.P})
+
+        def run(self, i):
+            def cmd():
+                resp.buffers[i][:] = 10.0 + self._block("P", i).sigma * resp.rng.standard_normal(4)
+            return [cmd]
+
+    with _device.useDevice("cpu"):
+        pipe = pipeline.Pipeline([("src", Producer())])
+    finished = []
+    sched = pipeline.DynamicTaskScheduler(pipe)
+    quiet = task.ConvergeHistogramTask(resp, {"src__sigma": 0.01}, atol=0.05, rtol=0.0, finishedCallback=finished.append)
+    noisy = task.ConvergeHistogramTask(resp, {"src__sigma": 2.0}, atol=0.5, rtol=0.0, maxBatchCount=200,
+                                       finishedCallback=finished.append)
+    sched.scheduleTasks([quiet, noisy])
+    sched.wait()
+    sched.destroy()
+    assert quiet.converged and quiet.totalBatches == 4 and quiet.isFinished
+    assert noisy.converged and noisy.totalBatches > 4 and noisy.error <= 0.5
+    assert abs(noisy.result.sum() - 40.0) < 3 * 0.5
+    assert finished == [quiet, noisy] or finished == [noisy, quiet]
+    with pytest.raises(ValueError):
+        task.ConvergeHistogramTask(resp, {}, initialBatchCount=1)
+    hopeless = task.ConvergeHistogramTask(resp, {"src__sigma": 5.0}, atol=1e-6, rtol=0.0, maxBatchCount=6)
+    sched = pipeline.DynamicTaskScheduler(pipe)
+    with pytest.warns(UserWarning, match="Failed to converge"):
+        sched.scheduleTask(hopeless)
+        sched.wait()
+    sched.destroy()
+    assert not hopeless.converged and hopeless.totalBatches == 6

@@ -434,3 +434,105 @@ class PipelineScheduler:
             self.destroy()
         except Exception:
             pass
+
+
+class DynamicTask:
+    """
+    A task that decides, batch by batch, whether it needs more batches (the role of
+    ``hephaistos.pipeline.DynamicTask`` in src/theia/task.py:22-196): the scheduler issues
+    ``initialBatchCount`` batches with ``parameters`` on ``pipeline``; every finished batch is
+    handed to ``processBatch(config)``, whose return value is the number of further batches to
+    issue. Once nothing is in flight and nothing more was requested, ``onTaskFinished`` runs.
+    """
+
+    def __init__(self, parameters: dict, pipeline: str | None = None, *, initialBatchCount: int = 1) -> None:
+        if initialBatchCount < 1:
+            raise ValueError("initialBatchCount must be at least 1")
+        self._parameters = dict(parameters)
+        self._pipelineName = pipeline
+        self._initialBatchCount = initialBatchCount
+        self._inFlight = 0
+        self._issued = 0
+        self._finished = False
+
+    @property
+    def parameters(self) -> dict:
+        return self._parameters
+
+    @property
+    def pipeline(self) -> str | None:
+        return self._pipelineName
+
+    @property
+    def initialBatchCount(self) -> int:
+        return self._initialBatchCount
+
+    @property
+    def batchesRemaining(self) -> int:
+        """Batches issued for this task that have not been processed yet"""
+        return self._inFlight
+
+    @property
+    def totalBatchesIssued(self) -> int:
+        return self._issued
+
+    @property
+    def isFinished(self) -> bool:
+        return self._finished
+
+    def processBatch(self, config: int) -> int:
+        """Consumes the result of configuration ``config``; returns how many more batches to issue."""
+        return 0
+
+    def onTaskFinished(self) -> None:
+        pass
+
+
+class DynamicTaskScheduler:
+    """
+    Runs ``DynamicTask``s on one pipeline or on named pipelines: batches of different tasks
+    interleave on the two configurations exactly like plain tasks of a ``PipelineScheduler``.
+    """
+
+    def __init__(self, pipeline: "Pipeline | dict[str, Pipeline]", *, queueSize: int = 0) -> None:
+        self._named = isinstance(pipeline, dict)
+        self._owners: _queue.Queue = _queue.Queue()
+        self._lock = threading.Lock()
+        self._scheduler = PipelineScheduler(pipeline, queueSize=queueSize, processFn=self._process)
+
+    def _issue(self, task: DynamicTask, n: int) -> None:
+        if n <= 0:
+            return
+        with self._lock:
+            task._inFlight += n
+            task._issued += n
+            for _ in range(n):
+                self._owners.put(task)
+        item = (task.pipeline, task.parameters) if self._named else task.parameters
+        self._scheduler.schedule([item] * n)
+
+    def _process(self, config: int, batch: int, args) -> None:
+        task: DynamicTask = self._owners.get()  # batches finish in the order they were issued
+        with self._lock:
+            task._inFlight -= 1
+        more = int(task.processBatch(config) or 0)
+        if more > 0:
+            self._issue(task, more)
+        elif task._inFlight == 0 and not task._finished:
+            task._finished = True
+            task.onTaskFinished()
+
+    def scheduleTask(self, task: DynamicTask) -> None:
+        if self._named and task.pipeline is None:
+            raise ValueError("the task must name its pipeline")
+        self._issue(task, task.initialBatchCount)
+
+    def scheduleTasks(self, tasks: Iterable[DynamicTask]) -> None:
+        for t in tasks:
+            self.scheduleTask(t)
+
+    def wait(self) -> None:
+        self._scheduler.wait()
+
+    def destroy(self) -> None:
+        self._scheduler.destroy()
