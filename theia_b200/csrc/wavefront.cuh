@@ -471,7 +471,16 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
         const uint32_t idx = P.first_path + slot;
         Ray ray;
         uint32_t dim = 0, flags = 1u;
-        if (active) loadState<POL>(ws, slot, ray, dim, flags);
+        // everything the segment needs is requested in one go: issued after the first use of
+        // the state, the query and result loads would add a second memory latency
+        float queryDist = 0.0f, sampledDist = 0.0f;
+        uint4 queryResult4 = make_uint4(0xFFFFFFFFu, 0u, 0u, 0u);
+        if (active) {
+            queryDist = ws.ray[2 * (size_t)slot].w;
+            sampledDist = ws.ray[2 * (size_t)slot + 1].w;
+            queryResult4 = ws.result[slot];
+            loadState<POL>(ws, slot, ray, dim, flags);
+        }
         Rng rng = makeRng(&P.rng, idx);
         rng.dim = dim;
         const uint32_t it = flags & 0xFFFFu;
@@ -484,10 +493,8 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
         hit.valid = false;
         int result = 0;
         if (active) {
-            const float4 ra = ws.ray[2 * (size_t)slot], rb = ws.ray[2 * (size_t)slot + 1];
-            const RayHit q = resultToHit(ws.result[slot]);
-            float dist = ra.w;
-            const float sampledDist = rb.w;
+            const RayHit q = resultToHit(queryResult4);
+            float dist = queryDist;
             int queryResult = processRayQuery(sc, ray, q, hit);
             if (hit.valid) dist = distance(ray.position, hit.worldPos);
             if (GUIDE && misTarget && hit.valid && dist > sampledDist && queryResult >= 0) {
