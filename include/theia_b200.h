@@ -291,6 +291,15 @@ int theia_abi_version(void);
 /* Number of CUDA kernels this library has launched in this process (measurement aid). */
 uint64_t theia_kernel_launches(void);
 
+/* Tuning / test seam (no counterpart in the reference). Options:
+ *   "wf_trace_kernel", "wf_shadow_trace_kernel": ray query kernel of the wavefront scene tracer for
+ *       primary / shadow rays: -1 (default) = picked per scene from timings of the first six
+ *       batches, 0 = phased persistent kernel, 1 = one thread per ray. Results do not depend on it.
+ *   "wf_min_node_lanes": 1..32, node phase threshold of the phased kernel (default 16).
+ * theia_get_trace_choice reports what was picked for a scene (-1 = still measuring). */
+int theia_set_option(const char *name, int value);
+int theia_get_trace_choice(const void *tlas_dev, uint32_t batch_size, int guide, int *primary, int *shadow);
+
 /* Optional per kernel timing for benchmarks (no counterpart in the reference, which times
  * whole pipelines only): while enabled, every launch of a tracing kernel is bracketed by CUDA
  * events on its stream. theia_profile_enable(1) clears the accumulators; theia_profile_read

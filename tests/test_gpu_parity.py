@@ -179,16 +179,25 @@ SCENE_CASES = [
 ]
 
 
-@pytest.mark.parametrize("mode", ["single", "wavefront"])
+@pytest.mark.parametrize("mode", ["single", "wavefront", "wavefront-simple"])
 @pytest.mark.parametrize("builder,kw", SCENE_CASES, ids=lambda v: getattr(v, "__name__", None) or ",".join(
     f"{a}={b}" for a, b in v.items()) or "default")
 def test_scene_tracer_hits_bit_exact(cuda, orc, builder, kw, mode):
     N = 1 << 14
     kw = dict(kw)
     kw.setdefault("resp", "record")
-    kw["mode"] = mode
-    g, c = both(builder, N, **kw)
-    H.runGpu(g)
+    kw["mode"] = mode.split("-")[0]
+    # both ray query kernels of the wavefront tracer (normally picked by timing) are covered
+    lib = _lib.load()
+    forced = 1 if mode.endswith("simple") else 0
+    lib.theia_set_option(b"wf_trace_kernel", forced)
+    lib.theia_set_option(b"wf_shadow_trace_kernel", forced)
+    try:
+        g, c = both(builder, N, **kw)
+        H.runGpu(g)
+    finally:
+        lib.theia_set_option(b"wf_trace_kernel", -1)
+        lib.theia_set_option(b"wf_shadow_trace_kernel", -1)
     H.runOracle(c)
     a, b = H.sortedHits(g), H.sortedHits(c)
     assert b["count"] > 0
@@ -301,3 +310,31 @@ def test_c4_multiple_light_sources_scheduler_matches_oracle(cuda, orc):
         assert want.sum() > 0, name
         assert np.allclose(hists[n], want, rtol=2e-4, atol=1e-9 * want.max()), (n, name)
     assert g["rng"].getParam("offset") == c["rng"].getParam("offset") == len(g["tasks"]) * g["rng"].autoAdvance
+
+
+def test_trace_kernel_is_picked_by_timing(cuda):
+    # the first four batches time the two ray query kernels; afterwards a choice is reported and
+    # the results of all batches are those of a run with a forced kernel
+    lib = _lib.load()
+    N = 1 << 17
+    with _device.useDevice("cuda"):
+        a = H.sceneC2(N, resp="hist", lightKind="cone", mode="wavefront")
+        b = H.sceneC2(N, resp="hist", lightKind="cone", mode="wavefront")
+    got, want = [], []
+    for k in range(8):
+        H.runGpu(a, k % 2)
+        torch.cuda.synchronize()
+        got.append(a["response"].result(k % 2).copy())
+    lib.theia_set_option(b"wf_trace_kernel", 0)
+    try:
+        for k in range(8):
+            H.runGpu(b, k % 2)
+            torch.cuda.synchronize()
+            want.append(b["response"].result(k % 2).copy())
+    finally:
+        lib.theia_set_option(b"wf_trace_kernel", -1)
+    p, s = ctypes.c_int(-2), ctypes.c_int(-2)
+    _lib.check(lib.theia_get_trace_choice(a["scene"].tlas.data_ptr(), N, 0, ctypes.byref(p), ctypes.byref(s)))
+    assert p.value in (0, 1) and s.value == 0
+    for x, y in zip(got, want):
+        assert x.sum() > 0 and np.allclose(x, y, rtol=1e-4, atol=1e-9 * y.max())

@@ -22,6 +22,8 @@ SYMBOLS = {
     "theia_last_error": (c_char_p, []),
     "theia_abi_version": (c_int, []),
     "theia_kernel_launches": (c_uint64, []),
+    "theia_set_option": (c_int, [c_char_p, c_int]),
+    "theia_get_trace_choice": (c_int, [c_void_p, c_uint32, c_int, POINTER(c_int), POINTER(c_int)]),
     "theia_profile_enable": (c_int, [c_int]),
     "theia_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_uint64), c_uint32]),
     "theia_profile_class_name": (c_char_p, [c_uint32]),

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 #include "trace_volume.cuh"
 #include "wavefront.cuh"
@@ -207,6 +208,36 @@ __global__ void __launch_bounds__(128) tlasQueryKernel(const void* tlas, const f
     }
 }
 
+// the same seam through the wavefront trace kernel (THEIA_QUERY_WAVEFRONT=1): identity queue
+__global__ void wfQuerySetupKernel(uint32_t* queue, uint32_t* counters, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) queue[i] = i;
+    if (i == 0) { counters[0] = n; counters[1] = 0u; }
+}
+__global__ void wfQueryConvertKernel(const void* tlas, const float* rays, const uint4* results, uint32_t n, int32_t* out,
+                                     float* outBary) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const SceneView sc = makeSceneView(tlas, nullptr, 0);
+    const RayHit h = resultToHit(results[i]);
+    out[4 * i + 0] = h.valid ? (int32_t)sc.instances[h.slot].pad : -1;
+    out[4 * i + 1] = h.valid ? h.prim : -1;
+    out[4 * i + 2] = h.valid ? sc.instances[h.slot].customIndex : -1;
+    out[4 * i + 3] = 0;
+    float t = 0.0f;
+    if (h.valid) {
+        // the trace kernel keeps (slot, primitive, u, v); t follows from the hit point like in
+        // processRayQuery: recompute it with the triangle test of the query kernel
+        const float* r = rays + 8 * (size_t)i;
+        TraversalStats st = {0, 0, 0};
+        t = closestHit<false>(sc, v3(r), v3(r + 4), r[3], &st).t;
+    }
+    outBary[4 * i + 0] = t;
+    outBary[4 * i + 1] = h.valid ? h.u : 0.0f;
+    outBary[4 * i + 2] = h.valid ? h.v : 0.0f;
+    outBary[4 * i + 3] = 0.0f;
+}
+
 // ------------------------------------------------------------------ launch translation
 #define HIST_SHARED_MAX_BINS 8192u
 
@@ -350,6 +381,68 @@ static size_t workspaceBytes(const theia_trace_launch_t* L) {
     return layoutWorkspace(nullptr, L->batch_size, L->polarized != 0, L->guide.kind != THEIA_GUIDE_NONE, nullptr);
 }
 
+// ------------------------------------------------------------------ options, trace kernel selection
+enum : int { TRACE_PHASED = 0, TRACE_SIMPLE = 1 };
+static int envInt(const char* name, int fallback) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : fallback;
+}
+// per ray class (primary, shadow): -1 = pick by measurement; the environment sets the defaults
+static int g_optTraceKernel[2] = {envInt("THEIA_WF_TRACE_KERNEL", -1), envInt("THEIA_WF_SHADOW_TRACE_KERNEL", -1)};
+static int g_optMinNodeLanes = envInt("THEIA_WF_MIN_NODE_LANES", 16);
+static std::mutex g_tunerMutex;
+
+// Picks the trace kernel of a (scene, batch size) from the first six batches: even ones run the
+// phased kernel, odd ones the one-thread-per-ray kernel, each trace launch bracketed by events;
+// once the events of a timed batch have completed (polled, never waited for) they are summed
+// per ray class, and after the sixth the sums of batches 2-5 are compared. Both kernels return identical results, so tuning is invisible.
+struct TraceTuner {
+    const void* tlas;
+    uint32_t batch;
+    bool guide;
+    int choice[2] = {-1, -1};
+    int step = 0;
+    int candidate = 0;
+    bool inFlight = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending[2];
+    double ms[2][2] = {{0, 0}, {0, 0}};
+};
+static std::vector<TraceTuner*> g_tuners;
+static TraceTuner* tunerFor(const void* tlas, uint32_t batch, bool guide) {
+    for (TraceTuner* t : g_tuners)
+        if (t->tlas == tlas && t->batch == batch && t->guide == guide) return t;
+    if (g_tuners.size() >= 64) {  // scenes come and go: forget the oldest entry
+        for (auto& v : g_tuners.front()->pending)
+            for (auto& e : v) { g_prof.pool.push_back(e.first); g_prof.pool.push_back(e.second); }
+        delete g_tuners.front();
+        g_tuners.erase(g_tuners.begin());
+    }
+    TraceTuner* t = new TraceTuner;
+    t->tlas = tlas; t->batch = batch; t->guide = guide;
+    if (!guide) t->choice[1] = TRACE_PHASED;  // no shadow rays to decide about
+    g_tuners.push_back(t);
+    return t;
+}
+static void tunerPoll(TraceTuner* t) {
+    if (!t->inFlight) return;
+    for (int c = 0; c < 2; ++c)
+        if (!t->pending[c].empty() && cudaEventQuery(t->pending[c].back().second) != cudaSuccess) return;
+    for (int c = 0; c < 2; ++c) {
+        for (auto& e : t->pending[c]) {
+            float ms = 0.0f;
+            // the first pair of batches only warms up (clocks, caches, lazy module loading)
+            if (t->step >= 2 && cudaEventElapsedTime(&ms, e.first, e.second) == cudaSuccess) t->ms[c][t->candidate] += ms;
+            g_prof.pool.push_back(e.first);
+            g_prof.pool.push_back(e.second);
+        }
+        t->pending[c].clear();
+    }
+    t->inFlight = false;
+    if (++t->step >= 6)
+        for (int c = 0; c < 2; ++c)
+            if (t->choice[c] < 0) t->choice[c] = t->ms[c][TRACE_SIMPLE] < t->ms[c][TRACE_PHASED] ? TRACE_SIMPLE : TRACE_PHASED;
+}
+
 // Scene tracer, wavefront form: generate, then per segment trace + shade (+ shadow trace +
 // shadow shade with a target guide). All launches are asynchronous on the caller's stream.
 static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D) {
@@ -377,11 +470,39 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     if (gShade > need128) gShade = need128;
     if (gShadow > need128) gShadow = need128;
     if (gTrace > need128) gTrace = need128;
-    // tuning knob of the trace kernel (lanes that must still be in the node phase to keep it going)
-    static const uint32_t minNodeLanes = [] {
-        const char* e = getenv("THEIA_WF_MIN_NODE_LANES");
-        return e ? (uint32_t)atoi(e) : 16u;
-    }();
+    const uint32_t minNodeLanes = (uint32_t)g_optMinNodeLanes;
+    const uint32_t gSimple = need128 > 0 ? need128 : 1u;
+
+    // ---- which trace kernel (per ray class: 0 primary, 1 shadow): forced by option, or timed
+    TraceTuner* tuner = nullptr;
+    int kernelOf[2] = {g_optTraceKernel[0], g_optTraceKernel[1]};
+    bool timeIt = false;
+    if (kernelOf[0] < 0 || kernelOf[1] < 0) {
+        std::lock_guard<std::mutex> lock(g_tunerMutex);
+        tuner = tunerFor(D.tlas, D.batch_size, guide);
+        tunerPoll(tuner);
+        for (int c = 0; c < 2; ++c) {
+            if (kernelOf[c] >= 0) continue;
+            if (tuner->choice[c] >= 0) kernelOf[c] = tuner->choice[c];
+            else if (!tuner->inFlight) { kernelOf[c] = tuner->step & 1; timeIt = true; }
+            else kernelOf[c] = TRACE_PHASED;  // a timed batch is still running: do not queue up events
+        }
+        if (timeIt) { tuner->inFlight = true; tuner->candidate = tuner->step & 1; }
+    }
+    auto launchTrace = [&](int cls, const float4* rays, uint4* results, const uint32_t* queue, const uint32_t* countPtr,
+                           uint32_t rpe) {
+        Timed tm(cls == 0 ? KC_TRACE : KC_SHADOW_TRACE, st);
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        const bool timed = timeIt && tuner && tuner->choice[cls] < 0 && g_optTraceKernel[cls] < 0;
+        if (timed) { e0 = profEvent(); e1 = profEvent(); cudaEventRecord(e0, st); }
+        if (kernelOf[cls] == TRACE_SIMPLE)
+            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, queue, countPtr, rpe);
+        else
+            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, queue, countPtr,
+                                                            ws.counters + WF_CNT_CURSOR, rpe, minNodeLanes);
+        if (timed) { cudaEventRecord(e1, st); tuner->pending[cls].push_back({e0, e1}); }
+    };
+
     wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 0xFFu);
     {
         Timed tm(KC_GENERATE, st);
@@ -394,12 +515,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         countLaunches((guide && it < D.path_length) ? 6 : 3);
         const uint32_t nextBit = cur ? (1u << WF_CNT_QUEUE0) : (1u << WF_CNT_QUEUE1);
         wfResetKernel<<<1, 32, 0, st>>>(ws.counters, nextBit | (1u << WF_CNT_SHADOW) | (1u << WF_CNT_CURSOR));
-        {
-            Timed tm(KC_TRACE, st);
-            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.ray, ws.result, ws.queue[cur],
-                                                            ws.counters + (cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0),
-                                                            ws.counters + WF_CNT_CURSOR, 1u, minNodeLanes);
-        }
+        launchTrace(0, ws.ray, ws.result, ws.queue[cur], ws.counters + (cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0), 1u);
         {
             Timed tm(KC_SHADE, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
@@ -407,12 +523,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         }
         if (guide && it < D.path_length) {
             wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 1u << WF_CNT_CURSOR);
-            {
-                Timed tm(KC_SHADOW_TRACE, st);
-                wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, ws.shadowRay, ws.shadowResult, ws.shadowQueue,
-                                                                ws.counters + WF_CNT_SHADOW, ws.counters + WF_CNT_CURSOR,
-                                                                2u, minNodeLanes);
-            }
+            launchTrace(1, ws.shadowRay, ws.shadowResult, ws.shadowQueue, ws.counters + WF_CNT_SHADOW, 2u);
             Timed tm(KC_SHADE_SHADOW, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadowFn, dim3(gShadow), dim3(TRACE_THREADS), args, histSmem, st));
@@ -432,6 +543,27 @@ extern "C" {
 const char* theia_last_error(void) { return g_error; }
 int theia_abi_version(void) { return THEIA_ABI_VERSION; }
 uint64_t theia_kernel_launches(void) { return g_launches.load(); }
+
+int theia_set_option(const char* name, int value) {
+    if (!name) { setError("theia_set_option: null name"); return -1; }
+    if (!strcmp(name, "wf_trace_kernel")) { g_optTraceKernel[0] = value; return 0; }
+    if (!strcmp(name, "wf_shadow_trace_kernel")) { g_optTraceKernel[1] = value; return 0; }
+    if (!strcmp(name, "wf_min_node_lanes")) { g_optMinNodeLanes = value < 1 ? 1 : (value > 32 ? 32 : value); return 0; }
+    setError("theia_set_option: unknown option '%s'", name);
+    return -1;
+}
+int theia_get_trace_choice(const void* tlas_dev, uint32_t batch_size, int guide, int* primary, int* shadow) {
+    std::lock_guard<std::mutex> lock(g_tunerMutex);
+    for (TraceTuner* t : g_tuners)
+        if (t->tlas == tlas_dev && t->batch == batch_size && t->guide == (guide != 0)) {
+            if (primary) *primary = t->choice[0];
+            if (shadow) *shadow = t->choice[1];
+            return 0;
+        }
+    if (primary) *primary = -1;
+    if (shadow) *shadow = -1;
+    return 0;
+}
 
 int theia_profile_enable(int on) {
     profCollect();
@@ -522,8 +654,38 @@ int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, in
                      uint64_t* stats_dev, void* stream) {
     if (!tlas_dev || !rays_dev || !out_dev || !out_bary_dev) { setError("theia_tlas_query: null argument"); return -1; }
     if (n == 0) return 0;
-    tlasQueryKernel<<<blocksFor(n, 128), 128, 0, (cudaStream_t)stream>>>(tlas_dev, rays_dev, n, out_dev, out_bary_dev,
-                                                                         (unsigned long long*)stats_dev);
+    static const bool viaWavefront = getenv("THEIA_QUERY_WAVEFRONT") != nullptr;
+    if (viaWavefront) {
+        // measurement seam: the ray queries of the wavefront tracer on a caller supplied ray list
+        cudaStream_t st = (cudaStream_t)stream;
+        uint32_t *queue = nullptr, *counters = nullptr;
+        uint4* results = nullptr;
+        CUDA_TRY(cudaMallocAsync(&queue, 4 * (size_t)n, st));
+        CUDA_TRY(cudaMallocAsync(&counters, 16, st));
+        CUDA_TRY(cudaMallocAsync(&results, 16 * (size_t)n, st));
+        uint32_t gTrace = 0;
+        if (persistentGrid((const void*)wfTraceKernel, 0, &gTrace)) return -1;
+        const uint32_t need = blocksFor(n, TRACE_THREADS);
+        if (gTrace > need) gTrace = need;
+        wfQuerySetupKernel<<<blocksFor(n, 256), 256, 0, st>>>(queue, counters, n);
+        {
+            Timed tm(KC_TRACE, st);
+            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
+                                                            queue, counters, counters + 1, 1u, 16u);
+        }
+        wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
+        CUDA_TRY(cudaFreeAsync(queue, st));
+        CUDA_TRY(cudaFreeAsync(counters, st));
+        CUDA_TRY(cudaFreeAsync(results, st));
+        countLaunches(3);
+        CUDA_TRY(cudaGetLastError());
+        return 0;
+    }
+    {
+        Timed tm(KC_SCENE, (cudaStream_t)stream);
+        tlasQueryKernel<<<blocksFor(n, 128), 128, 0, (cudaStream_t)stream>>>(tlas_dev, rays_dev, n, out_dev, out_bary_dev,
+                                                                             (unsigned long long*)stats_dev);
+    }
     countLaunches(1);
     CUDA_TRY(cudaGetLastError());
     return 0;

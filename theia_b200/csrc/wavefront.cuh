@@ -300,6 +300,33 @@ __global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__
     }
 }
 
+// The same ray queries with one thread per ray and the single-loop traversal of traverse.cuh
+// (leaf triangles are tested inside the node iteration). No refill, no phases: a warp lasts as
+// long as its longest ray, but every iteration does node and triangle work for all lanes that
+// have any. Faster where all rays of a launch cost about the same (C2: -20 %), slower where
+// trivial and heavy rays mix (shadow rays of C3: +60 %, C5: +18 %), so api.cu picks the kernel
+// per tracer and ray class from timings of the first batches. (A third form, persistent lanes
+// around this traversal step with Aila & Laine's refill threshold, lay between the two on
+// every workload for every threshold and was dropped.)
+__global__ void __launch_bounds__(128, 5) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
+                                                               uint4* __restrict__ results,
+                                                               const uint32_t* __restrict__ queue,
+                                                               const uint32_t* __restrict__ countPtr, uint32_t raysPerEntry) {
+    __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
+    WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
+    const uint32_t total = *countPtr * raysPerEntry;
+    if (blockIdx.x * blockDim.x >= total) return;
+    const uint32_t nTop = stageTopNodes(tlas, sharedTop);
+    __syncthreads();
+    const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const uint32_t rid = raysPerEntry == 1u ? __ldg(queue + i) : __ldg(queue + (i >> 1)) * 2u + (i & 1u);
+        const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
+        const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr);
+        results[rid] = make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v));
+    }
+}
+
 // ------------------------------------------------------------------ shading side
 enum : uint32_t { WF_SEQ1 = 1u << 18 };  // one response was already committed in this event
 
