@@ -351,6 +351,14 @@ def runB200(args) -> None:
             dist.destroy_process_group()
         return
 
+    # which ray query kernel the library picked for this scene (wavefront scene tracer only)
+    traceChoice = None
+    if hasattr(tr, "scene") and getattr(tr, "wavefront", False):
+        cp, cs = ctypes.c_int(-1), ctypes.c_int(-1)
+        lib.theia_get_trace_choice(tr.scene.tlas.data_ptr(), args.batch, int(tr.targetGuide is not None), byref(cp), byref(cs))
+        names = {-1: "undecided", 0: "phased persistent", 1: "one thread per ray"}
+        traceChoice = {"primary": names.get(cp.value), "shadow": names.get(cs.value) if tr.targetGuide is not None else None}
+
     # ---------------- report (rank 0)
     sec = ms * 1e-3
     value = segs / sec
@@ -397,7 +405,8 @@ def runB200(args) -> None:
         "config": {"workload": args.workload, "description": desc, "paths_per_step_per_gpu": args.batch,
                    "segments_per_path": segs / max(paths, 1), "grid_ctas": int(g.value), "block": 128,
                    "rng": "Philox4x32-10, disjoint counter ranges per batch", "l2": "flushed between timed steps (256 MiB write)",
-                   "parallelism": f"dp{world}: batches dealt round robin, one NCCL all-reduce of the light curve"},
+                   "parallelism": f"dp{world}: batches dealt round robin, one NCCL all-reduce of the light curve",
+                   "ray_query_kernel": traceChoice},
         "hits_per_s": hits / sec, "shadow_rays_per_s": shadow / sec, "paths_per_s": paths / sec,
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achievedGBs, "peak": hbmPeak, "unit": "GB/s",
                      "frac": achievedGBs / hbmPeak, "traffic": traffic, "peak_source": peakSrc,

@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__
 // per tracer and ray class from timings of the first batches. (A third form, persistent lanes
 // around this traversal step with Aila & Laine's refill threshold, lay between the two on
 // every workload for every threshold and was dropped.)
-__global__ void __launch_bounds__(128, 5) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
+__global__ void __launch_bounds__(128, 6) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                                uint4* __restrict__ results,
                                                                const uint32_t* __restrict__ queue,
                                                                const uint32_t* __restrict__ countPtr, uint32_t raysPerEntry) {
