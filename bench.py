@@ -387,10 +387,11 @@ def runB200(args) -> None:
     dominant = max(kernels, key=lambda n: kernels[n]["ms"])
     dom = kernels[dominant]
     achievedGBs = dom["achieved_gbs"]
-    traffic = None
-    try:  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+    traffic, ncuStatic = None, None
+    try:  # figures of the dominant kernel from the committed ncu --set full capture (not measured live)
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get(args.workload, {}).get(dominant)
+            ncuStatic = json.load(f).get(args.workload, {}).get(dominant)
+        traffic = ncuStatic.get("dram_bytes") if ncuStatic else None
     except Exception:
         pass
     smMHz = clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
@@ -412,7 +413,7 @@ def runB200(args) -> None:
                      "frac": achievedGBs / hbmPeak, "traffic": traffic, "peak_source": peakSrc,
                      "ms_per_launch": dom["ms_per_launch"], "share_of_step": dom["share"],
                      "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_launch"],
-                     "tracer_ms_per_step": kernelMs, "kernels": kernels,
+                     "tracer_ms_per_step": kernelMs, "kernels": kernels, "ncu_capture": ncuStatic,
                      "note": "dominant kernel by live CUDA-event time; it is latency/issue bound, not HBM bound "
                              "(see roofline_issue, profiles/ and DESIGN.md section 6)"},
         "roofline_issue": {"bound": "sm_issue", "achieved": issueAchieved, "peak": issuePeak, "unit": "lane-instr/s",

@@ -35,9 +35,10 @@ class HomogenousModel(material.DispersionFreeMedium, material.HenyeyGreensteinPh
         material.HenyeyGreensteinPhaseFunction.__init__(self, g)
 
 
-def makeResponse(kind: str, *, polarized: bool = False, nBins: int = 100, binSize: float = 5.0, t0: float = 0.0):
+def makeResponse(kind: str, *, polarized: bool = False, nBins: int = 100, binSize: float = 5.0, t0: float = 0.0,
+                 capacity: int = 0):
     if kind == "record":
-        r = response.HitRecorder(polarized=polarized)
+        r = response.HitRecorder(polarized=polarized, capacity=capacity)
         r.enableTags()
         return r
     if kind == "hist":
@@ -77,7 +78,8 @@ def makeLight(kind: str, *, polarized: bool = False, position=(1.0, 0.0, 0.0), d
 def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None, mis: bool = True, direct: bool = True,
                    polarized: bool = False, lightKind: str = "spherical", targetKind: str = "sphere",
                    wavelength: str = "const", water: bool = False, nScattering: int = 10, key: int = 42,
-                   scatterCoefficient: float = 0.05, nBins: int = 100, binSize: float = 5.0, maxTime: float = 1000.0):
+                   scatterCoefficient: float = 0.05, nBins: int = 100, binSize: float = 5.0, maxTime: float = 1000.0,
+                   respCapacity: int = 0):
     """Config C1 (examples/01 of the reference) and its flag variations (tests/test_trace.py:90-212)."""
     model = WaterTestModel() if water else HomogenousModel()
     med = model.createMedium()
@@ -90,7 +92,7 @@ def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None,
         src = makeLight(lightKind, polarized=polarized, position=(0.5, 0.2, -0.1), direction=(0.0, 0.6, 0.8))
     wl = light.ConstWavelengthSource(500.0) if wavelength == "const" else light.UniformWavelengthSource(
         lambdaRange=(400.0, 700.0))
-    r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize)
+    r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize, capacity=respCapacity)
     rng = random.PhiloxRNG(key=key)
     cb = makeCallback(callback, N, nScattering + 2, polarized)
     tr = trace.VolumeForwardTracer(N, src, tgt, wl, r, rng, medium=store.media[med.name], nScattering=nScattering,
@@ -103,7 +105,7 @@ def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None,
 def _sceneCommon(N, instances, store, medium, src, wl, resp, callback, polarized, maxPathLength, targetId, guide, key,
                  nBins, binSize, **kw):
     sc = scene.Scene(instances, store, medium=medium)
-    r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize)
+    r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize, capacity=kw.pop("respCapacity", 0))
     rng = random.PhiloxRNG(key=key)
     cb = makeCallback(callback, N, maxPathLength + 1, polarized)
     tr = trace.SceneForwardTracer(N, src, wl, r, rng, sc, maxPathLength=maxPathLength, targetId=targetId,
@@ -134,7 +136,7 @@ def sceneC2(N: int, *, resp: str = "record", callback: str | None = None, polari
                                     timeRange=(0.0, 1.0), budget=1e3, polarized=polarized,
                                     stokes=(1.0, 0.8, 0.2, 0.1))
     wl = light.UniformWavelengthSource(lambdaRange=(400.0, 700.0))
-    return _sceneCommon(N, inst, store, store.media["water"], src, wl, resp, callback, polarized, 10, 1, None, key,
+    return _sceneCommon(N, inst, store, store.media["water"], src, wl, resp, callback, polarized, kw.pop("maxPathLength", 10), 1, None, key,
                         nBins, binSize, **kw)
 
 
