@@ -90,6 +90,20 @@ def mortonKey(p: np.ndarray, lo: np.ndarray, hi: np.ndarray, bits: int) -> np.nd
     return key
 
 
+if os.environ.get("COHERENCE_EXPERIMENT"):
+    # upper bound of what coherence can buy: every warp gets 32 copies of one ray (no divergence
+    # at all) against the same rays in path order
+    for name in sys.argv[1:] or ["c2", "c3", "c5"]:
+        rays, cfg = workloadRays(name, 1 << 18)
+        rays = rays[: len(rays) // 32 * 32].copy()
+        rays[:, 3] = 1000.0
+        same = rays.reshape(-1, 32, 8)[:, :1, :].repeat(32, axis=1).reshape(-1, 8)
+        t0, t1 = timeQuery(cfg["scene"].tlas.data_ptr(), rays), timeQuery(cfg["scene"].tlas.data_ptr(), same)
+        mode = "wavefront trace kernel" if os.environ.get("THEIA_QUERY_WAVEFRONT") else "query kernel"
+        print(f"{name}: {len(rays)} rays, {mode}: {t0:.3f} ms in path order, {t1:.3f} ms with 32 identical rays per warp",
+              flush=True)
+    sys.exit(0)
+
 if os.environ.get("SORT_EXPERIMENT"):
     # how much does ray coherence buy? time the (one thread per ray) query kernel on the rays
     # of a workload in path order and sorted by the point where they enter the scene box
