@@ -167,6 +167,28 @@ typedef struct theia_target_sphere {
     float prob;
 } theia_target_sphere_t;
 
+/* src/theia/target.py:262-270, sh/target.flat.glsl:6-13; the same block serves the flat target
+ * guide (src/theia/target.py:574-582, sh/target_guide.flat.glsl:6-13). objToWorld is GLSL's
+ * column major mat3: element [3 c + r]. */
+typedef struct theia_target_flat {
+    float width;
+    float length; /* "height" in the shader and in the guide */
+    float position[3];
+    float normal[3];
+    float prob;
+    float objToWorld[9];
+} theia_target_flat_t;
+
+/* src/theia/target.py:363-370, sh/target.disk.glsl:6-12; the same block serves the disk target
+ * guide (src/theia/target.py:672-679, sh/target_guide.disk.glsl:6-12) */
+typedef struct theia_target_disk {
+    float position[3];
+    float radius;
+    float normal[3];
+    float prob;
+    float objToWorld[9];
+} theia_target_disk_t;
+
 /* src/theia/target.py:497-502, sh/target_guide.sphere.glsl:7-10 */
 typedef struct theia_guide_sphere {
     float position[3];
@@ -196,8 +218,9 @@ enum { THEIA_LIGHT_SPHERICAL = 1, THEIA_LIGHT_CONE = 2, THEIA_LIGHT_PENCIL = 3,
 enum { THEIA_LIGHT_FLAG_POLARIZED = 1,     /* LIGHTSOURCE_POLARIZED, light.py:1009-1011 */
        THEIA_LIGHT_FLAG_FRANK_TAMM_IS = 2  /* FRANK_TAMM_IS, light.py:1517-1519 */ };
 enum { THEIA_WAVELENGTH_CONST = 1, THEIA_WAVELENGTH_UNIFORM = 2 };
-enum { THEIA_TARGET_NONE = 0, THEIA_TARGET_SPHERE = 1, THEIA_TARGET_INNER_SPHERE = 2 };
-enum { THEIA_GUIDE_NONE = 0, THEIA_GUIDE_SPHERE = 1 };
+enum { THEIA_TARGET_NONE = 0, THEIA_TARGET_SPHERE = 1, THEIA_TARGET_INNER_SPHERE = 2, THEIA_TARGET_FLAT = 3,
+       THEIA_TARGET_DISK = 4 };
+enum { THEIA_GUIDE_NONE = 0, THEIA_GUIDE_SPHERE = 1, THEIA_GUIDE_FLAT = 2, THEIA_GUIDE_DISK = 3 };
 enum { THEIA_RESPONSE_EMPTY = 0, THEIA_RESPONSE_RECORD = 1, THEIA_RESPONSE_HISTOGRAM = 2 };
 enum { THEIA_VALUE_UNIFORM = 1 };
 enum { THEIA_CALLBACK_EMPTY = 0, THEIA_CALLBACK_STAT = 1, THEIA_CALLBACK_TRACK = 2 };

@@ -149,8 +149,88 @@ static inline TargetSample createTargetSampleMiss() {  // :77-91
     return t;
 }
 
-// sh/target.sphere.glsl:18-43 and sh/target.sphere.inner.glsl:18-36
+// GLSL column major mat3 of a parameter block
+static inline mat3 mat3Of(const float m[9]) { return {{m[0], m[1], m[2]}, {m[3], m[4], m[5]}, {m[6], m[7], m[8]}}; }
+static inline mat3 transposeOf(const float m[9]) { return {{m[0], m[3], m[6]}, {m[1], m[4], m[7]}, {m[2], m[5], m[8]}}; }
+
+// sh/util.sample.glsl:31-52 (concentric mapping)
+static inline vec3 sampleUnitDisk(vec2 rng) {
+    rng = {2.0f * rng.x - 1.0f, 2.0f * rng.y - 1.0f};
+    if (rng.x == 0.0f && rng.y == 0.0f) return v3(0.0f);
+    float phi, r;
+    if (abs_(rng.x) > abs_(rng.y)) {
+        r = rng.x;
+        phi = ORC_PI_OVER_FOUR * (rng.y / rng.x);
+    } else {
+        r = rng.y;
+        phi = ORC_PI_OVER_TWO - ORC_PI_OVER_FOUR * (rng.x / rng.y);
+    }
+    float sp, cp;
+    dm_sincos(phi, &sp, &cp);
+    return {r * cp, r * sp, 0.0f};
+}
+static inline float length2(float x, float y) { return std::sqrt(fmaf(y, y, x * x)); }
+
+// the plane shapes (flat, disk) as (objToWorld, centre, normal, prob) + an inside test
+struct PlaneShape { const float* objToWorld; vec3 center, normal; float prob; bool flat; float width, length, radius; };
+static inline PlaneShape planeShape(bool flat, const void* params) {
+    PlaneShape s{};
+    s.flat = flat;
+    if (flat) {
+        const auto* p = (const theia_target_flat_t*)params;
+        s.objToWorld = p->objToWorld; s.center = v3(p->position); s.normal = v3(p->normal); s.prob = p->prob;
+        s.width = p->width; s.length = p->length;
+    } else {
+        const auto* p = (const theia_target_disk_t*)params;
+        s.objToWorld = p->objToWorld; s.center = v3(p->position); s.normal = v3(p->normal); s.prob = p->prob;
+        s.radius = p->radius;
+    }
+    return s;
+}
+static inline vec3 planeLocalSample(const PlaneShape& s, Rng& rng) {
+    if (s.flat) {  // sh/target.flat.glsl:17-20, sh/target_guide.flat.glsl:17-20
+        vec2 u = rng.next2();
+        return {s.width * (u.x - 0.5f), s.length * (u.y - 0.5f), 0.0f};
+    }
+    return s.radius * sampleUnitDisk(rng.next2());  // sh/target.disk.glsl:17, sh/target_guide.disk.glsl:16
+}
+static inline bool planeInside(const PlaneShape& s, vec3 localPos) {
+    if (s.flat) return 2.0f * abs_(localPos.x) <= s.width && 2.0f * abs_(localPos.y) <= s.length;
+    return length2(localPos.x, localPos.y) <= s.radius;
+}
+struct PlaneHit { vec3 localPos, pos, normal; float t, side; };
+// sh/target.flat.glsl:46-62, sh/target.disk.glsl:42-57, sh/target_guide.flat.glsl:28-36, sh/target_guide.disk.glsl:23-31
+static inline PlaneHit planeIntersect(const PlaneShape& s, vec3 observer, vec3 direction) {
+    mat3 worldToObj = transposeOf(s.objToWorld);
+    vec3 localObs = worldToObj * (observer - s.center);
+    vec3 localDir = worldToObj * direction;
+    PlaneHit h;
+    h.t = -localObs.z / localDir.z;
+    h.localPos = fma3(h.t, localDir, localObs);
+    h.pos = mat3Of(s.objToWorld) * h.localPos + s.center;
+    h.side = signBit(localObs.z);
+    h.normal = s.normal * h.side;
+    return h;
+}
+static inline bool isPlaneTarget(uint32_t kind) { return kind == THEIA_TARGET_FLAT || kind == THEIA_TARGET_DISK; }
+
+// sh/target.sphere.glsl:18-43 and sh/target.sphere.inner.glsl:18-36; sh/target.flat.glsl:15-44,
+// sh/target.disk.glsl:15-40
 static inline TargetSample sampleTarget(const theia_component_t& c, vec3 observer, Rng& rng) {
+    if (isPlaneTarget(c.kind)) {
+        PlaneShape s = planeShape(c.kind == THEIA_TARGET_FLAT, c.params);
+        vec3 localPos = planeLocalSample(s, rng);
+        vec3 pos = mat3Of(s.objToWorld) * localPos + s.center;
+        float side = sign_(dot(s.normal, observer - pos));
+        vec3 normal = s.normal * side;
+        TargetSample t{};
+        t.position = pos; t.normal = normal; t.dist = distance(observer, pos);
+        t.objPosition = localPos; t.objNormal = {0.0f, 0.0f, side};
+        t.prob = s.prob; t.valid = dot(normal, normal) != 0.0f;
+        t.worldToObj = transposeOf(s.objToWorld);
+        t.offset = -(t.worldToObj * s.center);
+        return t;
+    }
     const auto* p = (const theia_target_sphere_t*)c.params;
     vec3 center = v3(p->position);
     TargetSample t{};
@@ -177,6 +257,18 @@ static inline TargetSample sampleTarget(const theia_component_t& c, vec3 observe
 }
 // sh/target.sphere.glsl:45-78 and sh/target.sphere.inner.glsl:38-56
 static inline TargetSample intersectTarget(const theia_component_t& c, vec3 observer, vec3 direction) {
+    if (isPlaneTarget(c.kind)) {  // sh/target.flat.glsl:46-74, sh/target.disk.glsl:42-68
+        PlaneShape s = planeShape(c.kind == THEIA_TARGET_FLAT, c.params);
+        PlaneHit h = planeIntersect(s, observer, direction);
+        bool valid = h.t > 0.0f && planeInside(s, h.localPos);
+        TargetSample r{};
+        r.position = h.pos; r.normal = h.normal; r.dist = h.t;
+        r.objPosition = h.localPos; r.objNormal = {0.0f, 0.0f, h.side};
+        r.prob = s.prob * (valid ? 1.0f : 0.0f); r.valid = valid;
+        r.worldToObj = transposeOf(s.objToWorld);
+        r.offset = -(r.worldToObj * s.center);
+        return r;
+    }
     const auto* p = (const theia_target_sphere_t*)c.params;
     vec3 center = v3(p->position);
     vec2 ts = intersectSphere(center, p->radius, observer, direction);
@@ -207,13 +299,34 @@ static inline TargetSample intersectTarget(const theia_component_t& c, vec3 obse
 }
 // sh/target.sphere.glsl:80-83, sh/target.sphere.inner.glsl:58-60
 static inline bool isOccludedByTarget(const theia_component_t& c, vec3 position) {
+    if (isPlaneTarget(c.kind)) return false;  // sh/target.flat.glsl:76-79, sh/target.disk.glsl:70-73
     const auto* p = (const theia_target_sphere_t*)c.params;
     float d = distance(position, v3(p->position));
     return c.kind == THEIA_TARGET_SPHERE ? d <= p->radius : d >= p->radius;
 }
 
-// ------------------------------------------------------------------ sh/target_guide.sphere.glsl
+// ------------------------------------------------------------------ sh/target_guide.*.glsl
 struct TargetGuideSample { vec3 dir; float dist, prob; };
+
+// sh/target_guide.common.glsl:11-33 (from a sampled point) and :35-52 (from a direction)
+static inline TargetGuideSample guideSampleFromPoint(vec3 observer, vec3 targetPos, vec3 targetNrm, float targetProb) {
+    vec3 dir = targetPos - observer;
+    float d2 = dot(dir, dir);
+    dir = normalize(dir);
+    float cosNormal = dot(dir, targetNrm);
+    float prob = targetProb * d2 / abs_(cosNormal);
+    if (isinf_(prob)) prob = 0.0f;
+    prob *= (cosNormal < 0.0f) ? 1.0f : 0.0f;
+    return {dir, distance(targetPos, observer), prob};
+}
+static inline TargetGuideSample guideSampleFromDir(vec3 dir, float dist, vec3 targetNrm, float targetProb) {
+    float cosNormal = dot(dir, targetNrm);
+    float prob = targetProb * dist * dist / abs_(cosNormal);
+    if (isinf_(prob)) prob = 0.0f;
+    prob *= (cosNormal < 0.0f) ? 1.0f : 0.0f;
+    return {dir, dist, prob};
+}
+static inline bool isPlaneGuide(uint32_t kind) { return kind == THEIA_GUIDE_FLAT || kind == THEIA_GUIDE_DISK; }
 
 static inline void guideCone(const theia_guide_sphere_t* p, vec3 observer, float* d, vec3* viewDir,
                              float* cosMin, float* prob) {
@@ -231,6 +344,12 @@ static inline void guideCone(const theia_guide_sphere_t* p, vec3 observer, float
 }
 // :15-51
 static inline TargetGuideSample sampleTargetGuide(const theia_component_t& c, vec3 observer, Rng& rng) {
+    if (isPlaneGuide(c.kind)) {  // sh/target_guide.flat.glsl:15-26, sh/target_guide.disk.glsl:14-21
+        PlaneShape s = planeShape(c.kind == THEIA_GUIDE_FLAT, c.params);
+        vec3 localPos = planeLocalSample(s, rng);
+        vec3 pos = mat3Of(s.objToWorld) * localPos + s.center;
+        return guideSampleFromPoint(observer, pos, s.normal, s.prob);
+    }
     const auto* p = (const theia_guide_sphere_t*)c.params;
     float d, cosMin, prob;
     vec3 viewDir;
@@ -245,6 +364,12 @@ static inline TargetGuideSample sampleTargetGuide(const theia_component_t& c, ve
 }
 // :53-81
 static inline TargetGuideSample evalTargetGuide(const theia_component_t& c, vec3 observer, vec3 direction) {
+    if (isPlaneGuide(c.kind)) {  // sh/target_guide.flat.glsl:28-47, sh/target_guide.disk.glsl:23-43
+        PlaneShape s = planeShape(c.kind == THEIA_GUIDE_FLAT, c.params);
+        PlaneHit h = planeIntersect(s, observer, direction);
+        bool valid = h.t > 0.0f && !isinf_(h.t) && !(h.t != h.t) && planeInside(s, h.localPos);
+        return guideSampleFromDir(direction, h.t, s.normal, s.prob * (valid ? 1.0f : 0.0f));
+    }
     const auto* p = (const theia_guide_sphere_t*)c.params;
     float d, cosMin, prob;
     vec3 viewDir;

@@ -10,8 +10,8 @@ ABI_VERSION = 1
 LIGHT_SPHERICAL, LIGHT_CONE, LIGHT_PENCIL, LIGHT_CASCADE, LIGHT_MUON = 1, 2, 3, 4, 5
 LIGHT_FLAG_POLARIZED, LIGHT_FLAG_FRANK_TAMM_IS = 1, 2
 WAVELENGTH_CONST, WAVELENGTH_UNIFORM = 1, 2
-TARGET_NONE, TARGET_SPHERE, TARGET_INNER_SPHERE = 0, 1, 2
-GUIDE_NONE, GUIDE_SPHERE = 0, 1
+TARGET_NONE, TARGET_SPHERE, TARGET_INNER_SPHERE, TARGET_FLAT, TARGET_DISK = 0, 1, 2, 3, 4
+GUIDE_NONE, GUIDE_SPHERE, GUIDE_FLAT, GUIDE_DISK = 0, 1, 2, 3
 RESPONSE_EMPTY, RESPONSE_RECORD, RESPONSE_HISTOGRAM = 0, 1, 2
 VALUE_UNIFORM = 1
 CALLBACK_EMPTY, CALLBACK_STAT, CALLBACK_TRACK = 0, 1, 2

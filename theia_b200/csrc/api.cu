@@ -208,11 +208,9 @@ __global__ void __launch_bounds__(128) tlasQueryKernel(const void* tlas, const f
     }
 }
 
-// the same seam through the wavefront trace kernel (THEIA_QUERY_WAVEFRONT=1): identity queue
-__global__ void wfQuerySetupKernel(uint32_t* queue, uint32_t* counters, uint32_t n) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) queue[i] = i;
-    if (i == 0) { counters[0] = n; counters[1] = 0u; }
+// the same seam through the wavefront trace kernel (THEIA_QUERY_WAVEFRONT=1)
+__global__ void wfQuerySetupKernel(uint32_t* counters, uint32_t n) {
+    if (threadIdx.x == 0) { counters[0] = n; counters[1] = 0u; }
 }
 __global__ void wfQueryConvertKernel(const void* tlas, const float* rays, const uint4* results, uint32_t n, int32_t* out,
                                      float* outBary) {
@@ -285,8 +283,12 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
         memcpy(&p, L->trace_params, sizeof(p));
         D.medium = p.medium; D.objectId = p.objectId; D.propagation = p.propagation;
         D.target.kind = L->target.kind;
-        if (L->target.kind != THEIA_TARGET_SPHERE && L->target.kind != THEIA_TARGET_INNER_SPHERE) { setError("volume tracer: unsupported target kind %u", L->target.kind); return -1; }
-        if (copyBlock(L->target, D.target.p, "target")) return -1;
+        switch (L->target.kind) {
+        case THEIA_TARGET_SPHERE: case THEIA_TARGET_INNER_SPHERE: if (copyBlock(L->target, D.target.p.sphere, "sphere target")) return -1; break;
+        case THEIA_TARGET_FLAT: if (copyBlock(L->target, D.target.p.flat, "flat target")) return -1; break;
+        case THEIA_TARGET_DISK: if (copyBlock(L->target, D.target.p.disk, "disk target")) return -1; break;
+        default: setError("volume tracer: unsupported target kind %u", L->target.kind); return -1;
+        }
     } else if (L->tracer == THEIA_TRACER_SCENE_FORWARD) {
         if (!L->trace_params || L->trace_params_size != sizeof(theia_scene_trace_params_t)) { setError("scene tracer: bad TraceParams block"); return -1; }
         theia_scene_trace_params_t p;
@@ -296,8 +298,13 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
         if (L->path_length == 0) { setError("scene tracer: path_length must be at least 1"); return -1; }
         D.tlas = L->tlas;
         D.guide.kind = L->guide.kind;
-        if (L->guide.kind == THEIA_GUIDE_SPHERE) { if (copyBlock(L->guide, D.guide.p, "target guide")) return -1; }
-        else if (L->guide.kind != THEIA_GUIDE_NONE) { setError("scene tracer: unsupported guide kind %u", L->guide.kind); return -1; }
+        switch (L->guide.kind) {
+        case THEIA_GUIDE_NONE: break;
+        case THEIA_GUIDE_SPHERE: if (copyBlock(L->guide, D.guide.p.sphere, "sphere target guide")) return -1; break;
+        case THEIA_GUIDE_FLAT: if (copyBlock(L->guide, D.guide.p.flat, "flat target guide")) return -1; break;
+        case THEIA_GUIDE_DISK: if (copyBlock(L->guide, D.guide.p.disk, "disk target guide")) return -1; break;
+        default: setError("scene tracer: unsupported guide kind %u", L->guide.kind); return -1;
+        }
     } else {
         setError("unknown tracer kind %u", L->tracer);
         return -1;
@@ -489,17 +496,16 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         }
         if (timeIt) { tuner->inFlight = true; tuner->candidate = tuner->step & 1; }
     }
-    auto launchTrace = [&](int cls, const float4* rays, uint4* results, const uint32_t* queue, const uint32_t* countPtr,
-                           uint32_t rpe) {
+    auto launchTrace = [&](int cls, const float4* rays, uint4* results, const uint32_t* countPtr, uint32_t rpe) {
         Timed tm(cls == 0 ? KC_TRACE : KC_SHADOW_TRACE, st);
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         const bool timed = timeIt && tuner && tuner->choice[cls] < 0 && g_optTraceKernel[cls] < 0;
         if (timed) { e0 = profEvent(); e1 = profEvent(); cudaEventRecord(e0, st); }
         if (kernelOf[cls] == TRACE_SIMPLE)
-            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, queue, countPtr, rpe);
+            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, rpe);
         else
-            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, queue, countPtr,
-                                                            ws.counters + WF_CNT_CURSOR, rpe, minNodeLanes);
+            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, ws.counters + WF_CNT_CURSOR, rpe,
+                                                            minNodeLanes);
         if (timed) { cudaEventRecord(e1, st); tuner->pending[cls].push_back({e0, e1}); }
     };
 
@@ -515,7 +521,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         countLaunches((guide && it < D.path_length) ? 6 : 3);
         const uint32_t nextBit = cur ? (1u << WF_CNT_QUEUE0) : (1u << WF_CNT_QUEUE1);
         wfResetKernel<<<1, 32, 0, st>>>(ws.counters, nextBit | (1u << WF_CNT_SHADOW) | (1u << WF_CNT_CURSOR));
-        launchTrace(0, ws.ray, ws.result, ws.queue[cur], ws.counters + (cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0), 1u);
+        launchTrace(0, ws.ray[cur], ws.result, ws.counters + (cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0), 1u);
         {
             Timed tm(KC_SHADE, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
@@ -523,7 +529,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         }
         if (guide && it < D.path_length) {
             wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 1u << WF_CNT_CURSOR);
-            launchTrace(1, ws.shadowRay, ws.shadowResult, ws.shadowQueue, ws.counters + WF_CNT_SHADOW, 2u);
+            launchTrace(1, ws.shadowRay, ws.shadowResult, ws.counters + WF_CNT_SHADOW, 2u);
             Timed tm(KC_SHADE_SHADOW, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadowFn, dim3(gShadow), dim3(TRACE_THREADS), args, histSmem, st));
@@ -658,23 +664,21 @@ int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, in
     if (viaWavefront) {
         // measurement seam: the ray queries of the wavefront tracer on a caller supplied ray list
         cudaStream_t st = (cudaStream_t)stream;
-        uint32_t *queue = nullptr, *counters = nullptr;
+        uint32_t* counters = nullptr;
         uint4* results = nullptr;
-        CUDA_TRY(cudaMallocAsync(&queue, 4 * (size_t)n, st));
         CUDA_TRY(cudaMallocAsync(&counters, 16, st));
         CUDA_TRY(cudaMallocAsync(&results, 16 * (size_t)n, st));
         uint32_t gTrace = 0;
         if (persistentGrid((const void*)wfTraceKernel, 0, &gTrace)) return -1;
         const uint32_t need = blocksFor(n, TRACE_THREADS);
         if (gTrace > need) gTrace = need;
-        wfQuerySetupKernel<<<blocksFor(n, 256), 256, 0, st>>>(queue, counters, n);
+        wfQuerySetupKernel<<<1, 32, 0, st>>>(counters, n);
         {
             Timed tm(KC_TRACE, st);
             wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
-                                                            queue, counters, counters + 1, 1u, 16u);
+                                                            counters, counters + 1, 1u, 16u);
         }
         wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
-        CUDA_TRY(cudaFreeAsync(queue, st));
         CUDA_TRY(cudaFreeAsync(counters, st));
         CUDA_TRY(cudaFreeAsync(results, st));
         countLaunches(3);

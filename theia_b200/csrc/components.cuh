@@ -21,8 +21,18 @@ union WavelengthBlock {
 };
 struct LightSel { uint32_t kind, flags; LightBlock p; };
 struct WavelengthSel { uint32_t kind; WavelengthBlock p; };
-struct TargetSel { uint32_t kind; theia_target_sphere_t p; };
-struct GuideSel { uint32_t kind; theia_guide_sphere_t p; };
+union TargetBlock {
+    theia_target_sphere_t sphere;
+    theia_target_flat_t flat;
+    theia_target_disk_t disk;
+};
+union GuideBlock {
+    theia_guide_sphere_t sphere;
+    theia_target_flat_t flat;
+    theia_target_disk_t disk;
+};
+struct TargetSel { uint32_t kind; TargetBlock p; };
+struct GuideSel { uint32_t kind; GuideBlock p; };
 
 // ------------------------------------------------------------------ wavelength sources
 // sh/wavelengthsource.const.glsl:10-12, sh/wavelengthsource.uniform.glsl:12-16
@@ -179,28 +189,93 @@ TDEV Ray sampleRay(const WavelengthSel& wl, const LightSel& light, uint64_t medi
 }
 
 // ------------------------------------------------------------------ sh/target.common.glsl
-// The sphere targets only ever produce worldToObj = mat3(invRad): carried as a scalar.
+// The world -> object transformation of a sample (TargetSample.offset / .worldToObj of the
+// reference) depends on the parameter block only: targetWorldToObj() rebuilds it where a hit is
+// created instead of carrying a matrix per sample.
 struct TargetSample {
     vec3 position, normal;
     float dist;
     vec3 objPosition, objNormal;
     float prob;
     bool valid;
-    float invRad;
 };
 TDEV TargetSample createTargetSampleMiss() {  // :77-91
     TargetSample t;
     t.position = v3(0.0f); t.normal = v3(0.0f); t.objPosition = v3(0.0f); t.objNormal = v3(0.0f);
-    t.dist = T_INF; t.prob = 0.0f; t.valid = false; t.invRad = 1.0f;
+    t.dist = T_INF; t.prob = 0.0f; t.valid = false;
     return t;
 }
+// GLSL column major mat3 of a parameter block; transposeOf = transpose(objToWorld)
+TDEV mat3 mat3Of(const float m[9]) { return {{m[0], m[1], m[2]}, {m[3], m[4], m[5]}, {m[6], m[7], m[8]}}; }
+TDEV mat3 transposeOf(const float m[9]) { return {{m[0], m[3], m[6]}, {m[1], m[4], m[7]}, {m[2], m[5], m[8]}}; }
+TDEV mat3 targetWorldToObj(const TargetSel& c) {
+    switch (c.kind) {
+    case THEIA_TARGET_FLAT: return transposeOf(c.p.flat.objToWorld);
+    case THEIA_TARGET_DISK: return transposeOf(c.p.disk.objToWorld);
+    default: return mat3_diag(c.p.sphere.invRad);
+    }
+}
 
-// sh/target.sphere.glsl:18-43, sh/target.sphere.inner.glsl:18-36
+// sh/util.sample.glsl:31-52 (concentric mapping)
+TDEV vec3 sampleUnitDisk(vec2 rng) {
+    rng = {2.0f * rng.x - 1.0f, 2.0f * rng.y - 1.0f};
+    if (rng.x == 0.0f && rng.y == 0.0f) return v3(0.0f);
+    float phi, r;
+    if (abs_(rng.x) > abs_(rng.y)) {
+        r = rng.x;
+        phi = T_PI_OVER_FOUR * (rng.y / rng.x);
+    } else {
+        r = rng.y;
+        phi = T_PI_OVER_TWO - T_PI_OVER_FOUR * (rng.x / rng.y);
+    }
+    float sp, cp;
+    dm_sincos(phi, &sp, &cp);
+    return {r * cp, r * sp, 0.0f};
+}
+TDEV float length2(float x, float y) { return sqrtf(fmaf(y, y, x * x)); }
+
+// Plane shapes share everything but the local sample / the inside test:
+// sh/target.flat.glsl:15-44 and sh/target.disk.glsl:15-40 (sample), :46-74 and :42-68 (intersect)
+TDEV TargetSample planeSample(vec3 localPos, const float objToWorld[9], vec3 center, vec3 nrm, float prob, vec3 observer) {
+    vec3 pos = mat3Of(objToWorld) * localPos + center;
+    float side = sign_(dot(nrm, observer - pos));
+    vec3 normal = nrm * side;
+    TargetSample t;
+    t.position = pos; t.normal = normal; t.dist = distance(observer, pos);
+    t.objPosition = localPos; t.objNormal = {0.0f, 0.0f, side};
+    t.prob = prob; t.valid = dot(normal, normal) != 0.0f;
+    return t;
+}
+struct PlaneHit { vec3 localPos, pos, normal; float t, side; };
+TDEV PlaneHit planeIntersect(const float objToWorld[9], vec3 center, vec3 nrm, vec3 observer, vec3 direction) {
+    mat3 worldToObj = transposeOf(objToWorld);
+    vec3 localObs = worldToObj * (observer - center);
+    vec3 localDir = worldToObj * direction;
+    PlaneHit h;
+    h.t = -localObs.z / localDir.z;
+    h.localPos = fma3(h.t, localDir, localObs);
+    h.pos = mat3Of(objToWorld) * h.localPos + center;
+    h.side = signBit(localObs.z);
+    h.normal = nrm * h.side;
+    return h;
+}
+
+// sh/target.sphere.glsl:18-43, sh/target.sphere.inner.glsl:18-36, flat / disk as above
 TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
-    const theia_target_sphere_t& p = c.p;
+    if (c.kind == THEIA_TARGET_FLAT) {
+        const theia_target_flat_t& p = c.p.flat;
+        vec2 u = rng.next2();
+        vec3 localPos = {p.width * (u.x - 0.5f), p.length * (u.y - 0.5f), 0.0f};
+        return planeSample(localPos, p.objToWorld, v3(p.position), v3(p.normal), p.prob, observer);
+    }
+    if (c.kind == THEIA_TARGET_DISK) {
+        const theia_target_disk_t& p = c.p.disk;
+        vec3 localPos = p.radius * sampleUnitDisk(rng.next2());
+        return planeSample(localPos, p.objToWorld, v3(p.position), v3(p.normal), p.prob, observer);
+    }
+    const theia_target_sphere_t& p = c.p.sphere;
     vec3 center = v3(p.position);
     TargetSample t;
-    t.invRad = p.invRad;
     if (c.kind == THEIA_TARGET_SPHERE) {
         vec3 dir = normalize(observer - center);
         float d = distance(observer, center);
@@ -220,13 +295,24 @@ TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
     }
     return t;
 }
-// sh/target.sphere.glsl:45-78, sh/target.sphere.inner.glsl:38-56
+// sh/target.sphere.glsl:45-78, sh/target.sphere.inner.glsl:38-56, flat / disk as above
 TDEV TargetSample intersectTarget(const TargetSel& c, vec3 observer, vec3 direction) {
-    const theia_target_sphere_t& p = c.p;
+    TargetSample r;
+    if (c.kind == THEIA_TARGET_FLAT || c.kind == THEIA_TARGET_DISK) {
+        const bool flat = c.kind == THEIA_TARGET_FLAT;
+        PlaneHit h = flat ? planeIntersect(c.p.flat.objToWorld, v3(c.p.flat.position), v3(c.p.flat.normal), observer, direction)
+                          : planeIntersect(c.p.disk.objToWorld, v3(c.p.disk.position), v3(c.p.disk.normal), observer, direction);
+        bool valid = h.t > 0.0f;
+        if (flat) valid = valid && 2.0f * abs_(h.localPos.x) <= c.p.flat.width && 2.0f * abs_(h.localPos.y) <= c.p.flat.length;
+        else valid = valid && length2(h.localPos.x, h.localPos.y) <= c.p.disk.radius;
+        r.position = h.pos; r.normal = h.normal; r.dist = h.t;
+        r.objPosition = h.localPos; r.objNormal = {0.0f, 0.0f, h.side};
+        r.prob = (flat ? c.p.flat.prob : c.p.disk.prob) * (valid ? 1.0f : 0.0f); r.valid = valid;
+        return r;
+    }
+    const theia_target_sphere_t& p = c.p.sphere;
     vec3 center = v3(p.position);
     vec2 ts = intersectSphere(center, p.radius, observer, direction);
-    TargetSample r;
-    r.invRad = p.invRad;
     if (c.kind == THEIA_TARGET_SPHERE) {
         float t = ts.x;
         bool hit = (t > 0.0f) && !isinf_(t);
@@ -250,14 +336,35 @@ TDEV TargetSample intersectTarget(const TargetSel& c, vec3 observer, vec3 direct
     r.prob = p.prob; r.valid = hit;
     return r;
 }
-// sh/target.sphere.glsl:80-83, sh/target.sphere.inner.glsl:58-60
+// sh/target.sphere.glsl:80-83, sh/target.sphere.inner.glsl:58-60, sh/target.flat.glsl:76-79,
+// sh/target.disk.glsl:70-73 (planes never occlude)
 TDEV bool isOccludedByTarget(const TargetSel& c, vec3 position) {
-    float d = distance(position, v3(c.p.position));
-    return c.kind == THEIA_TARGET_SPHERE ? d <= c.p.radius : d >= c.p.radius;
+    if (c.kind == THEIA_TARGET_FLAT || c.kind == THEIA_TARGET_DISK) return false;
+    float d = distance(position, v3(c.p.sphere.position));
+    return c.kind == THEIA_TARGET_SPHERE ? d <= c.p.sphere.radius : d >= c.p.sphere.radius;
 }
 
-// ------------------------------------------------------------------ sh/target_guide.sphere.glsl
+// ------------------------------------------------------------------ sh/target_guide.*.glsl
 struct TargetGuideSample { vec3 dir; float dist, prob; };
+
+// sh/target_guide.common.glsl:11-33 (from a sampled point) and :35-52 (from a direction)
+TDEV TargetGuideSample guideSampleFromPoint(vec3 observer, vec3 targetPos, vec3 targetNrm, float targetProb) {
+    vec3 dir = targetPos - observer;
+    float d2 = dot(dir, dir);
+    dir = normalize(dir);
+    float cosNormal = dot(dir, targetNrm);
+    float prob = targetProb * d2 / abs_(cosNormal);
+    if (isinf_(prob)) prob = 0.0f;
+    prob *= (cosNormal < 0.0f) ? 1.0f : 0.0f;
+    return {dir, distance(targetPos, observer), prob};
+}
+TDEV TargetGuideSample guideSampleFromDir(vec3 dir, float dist, vec3 targetNrm, float targetProb) {
+    float cosNormal = dot(dir, targetNrm);
+    float prob = targetProb * dist * dist / abs_(cosNormal);
+    if (isinf_(prob)) prob = 0.0f;
+    prob *= (cosNormal < 0.0f) ? 1.0f : 0.0f;
+    return {dir, dist, prob};
+}
 
 TDEV void guideCone(const theia_guide_sphere_t& p, vec3 observer, float* d, vec3* viewDir, float* cosMin,
                     float* prob) {
@@ -273,27 +380,50 @@ TDEV void guideCone(const theia_guide_sphere_t& p, vec3 observer, float* d, vec3
     pr *= (*d > p.radius) ? 1.0f : 0.0f;
     *prob = pr;
 }
-// :15-51
+// sh/target_guide.sphere.glsl:15-51, sh/target_guide.flat.glsl:15-26, sh/target_guide.disk.glsl:14-21
 TDEV TargetGuideSample sampleTargetGuide(const GuideSel& c, vec3 observer, Rng& rng) {
+    if (c.kind == THEIA_GUIDE_FLAT) {
+        const theia_target_flat_t& p = c.p.flat;
+        vec2 u = rng.next2();
+        vec3 localPos = {p.width * (u.x - 0.5f), p.length * (u.y - 0.5f), 0.0f};
+        vec3 pos = mat3Of(p.objToWorld) * localPos + v3(p.position);
+        return guideSampleFromPoint(observer, pos, v3(p.normal), p.prob);
+    }
+    if (c.kind == THEIA_GUIDE_DISK) {
+        const theia_target_disk_t& p = c.p.disk;
+        vec3 localPos = p.radius * sampleUnitDisk(rng.next2());
+        vec3 pos = mat3Of(p.objToWorld) * localPos + v3(p.position);
+        return guideSampleFromPoint(observer, pos, v3(p.normal), p.prob);
+    }
     float d, cosMin, prob;
     vec3 viewDir;
-    guideCone(c.p, observer, &d, &viewDir, &cosMin, &prob);
+    guideCone(c.p.sphere, observer, &d, &viewDir, &cosMin, &prob);
     float cosTheta = 1.0f - cosMin * rng.next();
     float sinTheta = sqrtf(max_(1.0f - cosTheta * cosTheta, 0.0f));
     float phi = T_TWO_PI * rng.next();
     float sp, cp;
     dm_sincos(phi, &sp, &cp);
     vec3 dir = createLocalCOSY(viewDir) * vec3{sinTheta * sp, sinTheta * cp, cosTheta};
-    return {dir, d + c.p.radius, prob};
+    return {dir, d + c.p.sphere.radius, prob};
 }
-// :53-81
+// sh/target_guide.sphere.glsl:53-81, sh/target_guide.flat.glsl:28-47, sh/target_guide.disk.glsl:23-43
 TDEV TargetGuideSample evalTargetGuide(const GuideSel& c, vec3 observer, vec3 direction) {
+    if (c.kind == THEIA_GUIDE_FLAT || c.kind == THEIA_GUIDE_DISK) {
+        const bool flat = c.kind == THEIA_GUIDE_FLAT;
+        PlaneHit h = flat ? planeIntersect(c.p.flat.objToWorld, v3(c.p.flat.position), v3(c.p.flat.normal), observer, direction)
+                          : planeIntersect(c.p.disk.objToWorld, v3(c.p.disk.position), v3(c.p.disk.normal), observer, direction);
+        bool valid = h.t > 0.0f && !isinf_(h.t) && !(h.t != h.t);
+        if (flat) valid = valid && 2.0f * abs_(h.localPos.x) <= c.p.flat.width && 2.0f * abs_(h.localPos.y) <= c.p.flat.length;
+        else valid = valid && length2(h.localPos.x, h.localPos.y) <= c.p.disk.radius;
+        float prob = (flat ? c.p.flat.prob : c.p.disk.prob) * (valid ? 1.0f : 0.0f);
+        return guideSampleFromDir(direction, h.t, flat ? v3(c.p.flat.normal) : v3(c.p.disk.normal), prob);
+    }
     float d, cosMin, prob;
     vec3 viewDir;
-    guideCone(c.p, observer, &d, &viewDir, &cosMin, &prob);
+    guideCone(c.p.sphere, observer, &d, &viewDir, &cosMin, &prob);
     float cosDir = dot(viewDir, direction);
     prob *= (cosMin >= 1.0f - cosDir) ? 1.0f : 0.0f;
-    return {direction, d + c.p.radius, prob};
+    return {direction, d + c.p.sphere.radius, prob};
 }
 
 }  // namespace theia

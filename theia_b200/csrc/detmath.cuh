@@ -230,6 +230,8 @@ TDEV vec3 mulT(vec3 v, const mat3& m) { return {dot(v, m.c0), dot(v, m.c1), dot(
 
 #define T_PI 3.141592653589793238f
 #define T_TWO_PI 6.283185307179586477f
+#define T_PI_OVER_FOUR 0.7853981633974483096f
+#define T_PI_OVER_TWO 1.570796326794896619f
 #define T_INV_4PI 0.0795774715459476679f
 #define T_SPEED_OF_LIGHT 0.299792458f
 #define T_INV_SPEED_OF_LIGHT 3.335640951981521f

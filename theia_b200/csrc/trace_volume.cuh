@@ -34,7 +34,7 @@ TDEV bool volumeCreateResponse(const DeviceLaunch& P, Ray ray, const TargetSampl
     int code = propagateRayToHit<POL>(ray, hit.position, hit.normal, P.propagation);
     if (code < 0) return false;
     ray.lin_contrib *= weight;
-    item = createHit<POL>(ray, hit.objPosition, hit.objNormal, P.objectId, mat3_diag(hit.invRad));
+    item = createHit<POL>(ray, hit.objPosition, hit.objNormal, P.objectId, targetWorldToObj(P.target));
     return true;
 }
 
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(128) volumeForwardKernel(const __grid_constant
             if (result >= 0) {
                 if (hitValid && allowResponse) {
                     alignRayToHit<POL>(ray, hit.normal);
-                    item = createHit<POL>(ray, hit.objPosition, hit.objNormal, P.objectId, mat3_diag(hit.invRad));
+                    item = createHit<POL>(ray, hit.objPosition, hit.objNormal, P.objectId, targetWorldToObj(P.target));
                     has = true;
                     result = THEIA_RESULT_RAY_DETECTED;
                 } else if (hitValid) {

@@ -1,8 +1,13 @@
 // Wavefront form of the SceneForwardTracer (sh/tracer.scene.forward.glsl +
 // sh/scene.traverse.glsl of the reference).
 //
-// The path state lives in HBM as structure-of-arrays (one slot per path of the batch, slot =
-// path number) and each path segment is split into kernels joined by queues of live slots:
+// The path state lives in HBM as structure-of-arrays and each path segment is split into kernels.
+// Live paths are kept DENSE: a kernel that keeps a path alive allocates the next free index of
+// the output buffer (one atomic per warp: ballot + prefix popcount) and writes state and ray
+// query there, so every kernel reads and writes contiguous indices 0 .. count-1 (coalesced,
+// every sector fully used) and there is no queue of slot numbers to gather through. The path
+// number (RNG stream, hit tags, track index) travels as one more state word. State and ray
+// buffers ping-pong between segments:
 //
 //   generate : sample wavelength + light, create the ray, prepare the first ray query
 //   per segment:
@@ -11,8 +16,7 @@
 //              counter), so lanes never wait for the longest traversal of their warp.
 //     shade  : ray query result -> SurfaceHit, propagation, surface interaction (Fresnel
 //              reflect / transmit / detect) or volume scatter, responses, event callbacks,
-//              then the preparation of the next ray query. Live paths are appended to the
-//              next queue with one atomic per warp (ballot + prefix popcount).
+//              then the preparation of the next ray query, appended to the other buffer.
 //     with a target guide, volume scatter events emit two shadow rays instead (phase sample,
 //     guide sample); a second trace + shade pass turns them into responses, performs the
 //     deferred phase function scatter and prepares the next query.
@@ -29,7 +33,7 @@ namespace theia {
 // ------------------------------------------------------------------ workspace
 enum : uint32_t {
     WF_PX, WF_PY, WF_PZ, WF_DX, WF_DY, WF_DZ, WF_MED_LO, WF_MED_HI, WF_LAMBDA, WF_TIME, WF_LIN, WF_LOG,
-    WF_N, WF_VG, WF_MUS, WF_MUE, WF_DIM, WF_FLAGS, WF_NFIELDS_UNPOL,
+    WF_N, WF_VG, WF_MUS, WF_MUE, WF_DIM, WF_FLAGS, WF_PATH, WF_NFIELDS_UNPOL,
     WF_S0 = WF_NFIELDS_UNPOL, WF_S1, WF_S2, WF_S3, WF_R0, WF_R1, WF_R2, WF_NFIELDS_POL
 };
 // WF_FLAGS: bits 0-15 segment number "it", bit 16 allowResponse, bit 17 mis_target
@@ -37,15 +41,14 @@ enum : uint32_t { WF_ALLOW = 1u << 16, WF_MIS_TARGET = 1u << 17 };
 enum : uint32_t { WF_CNT_QUEUE0 = 0, WF_CNT_QUEUE1 = 1, WF_CNT_SHADOW = 2, WF_CNT_CURSOR = 3, WF_NCOUNTERS = 8 };
 
 struct Workspace {
-    uint32_t capacity;   // slots = paths per batch
-    uint32_t* counters;  // [WF_NCOUNTERS]
-    uint32_t* state;     // [nFields][capacity] words
-    float4* ray;         // [capacity][2]: (origin, tmax), (direction, sampledDist)
-    uint4* result;       // [capacity]: instance slot (0xFFFFFFFF = miss), primitive, u, v
-    float4* shadowRay;   // [2 * capacity][2]: (origin, tmax), (direction, weight)
-    uint4* shadowResult; // [2 * capacity]
-    uint32_t* queue[2];  // [capacity] live slots, ping-pong
-    uint32_t* shadowQueue;  // [capacity] slots with a pending pair of shadow rays
+    uint32_t capacity;      // paths per batch
+    uint32_t* counters;     // [WF_NCOUNTERS]: live entries of buffer 0 / 1, of the shadow buffer, trace cursor
+    uint32_t* state[2];     // ping-pong, [nFields][capacity] words, dense
+    float4* ray[2];         // ping-pong, [capacity][2]: (origin, tmax), (direction, sampledDist)
+    uint4* result;          // [capacity]: instance slot (0xFFFFFFFF = miss), primitive, u, v
+    uint32_t* shadowState;  // [nFields][capacity]: paths with a pending pair of shadow rays, dense
+    float4* shadowRay;      // [2 * capacity][2]: (origin, tmax), (direction, weight)
+    uint4* shadowResult;    // [2 * capacity]
 };
 
 static inline size_t wfAlign(size_t v) { return (v + 255) & ~size_t(255); }
@@ -60,17 +63,17 @@ static inline size_t layoutWorkspace(void* base, uint32_t capacity, bool polariz
     Workspace w;
     w.capacity = capacity;
     w.counters = (uint32_t*)take(4 * WF_NCOUNTERS);
-    w.state = (uint32_t*)take(4 * nFields * C);
-    w.ray = (float4*)take(32 * C);
+    w.state[0] = (uint32_t*)take(4 * nFields * C);
+    w.state[1] = (uint32_t*)take(4 * nFields * C);
+    w.ray[0] = (float4*)take(32 * C);
+    w.ray[1] = (float4*)take(32 * C);
     w.result = (uint4*)take(16 * C);
-    w.queue[0] = (uint32_t*)take(4 * C);
-    w.queue[1] = (uint32_t*)take(4 * C);
     if (guide) {
+        w.shadowState = (uint32_t*)take(4 * nFields * C);
         w.shadowRay = (float4*)take(64 * C);
         w.shadowResult = (uint4*)take(32 * C);
-        w.shadowQueue = (uint32_t*)take(4 * C);
     } else {
-        w.shadowRay = nullptr; w.shadowResult = nullptr; w.shadowQueue = nullptr;
+        w.shadowState = nullptr; w.shadowRay = nullptr; w.shadowResult = nullptr;
     }
     if (ws) *ws = w;
     return off;
@@ -78,9 +81,8 @@ static inline size_t layoutWorkspace(void* base, uint32_t capacity, bool polariz
 
 // ------------------------------------------------------------------ state access
 template <bool POL>
-TDEV void storeState(const Workspace& ws, uint32_t slot, const Ray& r, uint32_t dim, uint32_t flags) {
-    uint32_t* s = ws.state + slot;
-    const size_t C = ws.capacity;
+TDEV void storeState(uint32_t* state, size_t C, uint32_t slot, const Ray& r, uint32_t dim, uint32_t flags, uint32_t path) {
+    uint32_t* s = state + slot;
     s[WF_PX * C] = f2u(r.position.x); s[WF_PY * C] = f2u(r.position.y); s[WF_PZ * C] = f2u(r.position.z);
     s[WF_DX * C] = f2u(r.direction.x); s[WF_DY * C] = f2u(r.direction.y); s[WF_DZ * C] = f2u(r.direction.z);
     s[WF_MED_LO * C] = (uint32_t)r.medium; s[WF_MED_HI * C] = (uint32_t)(r.medium >> 32);
@@ -88,7 +90,7 @@ TDEV void storeState(const Workspace& ws, uint32_t slot, const Ray& r, uint32_t 
     s[WF_LIN * C] = f2u(r.lin_contrib); s[WF_LOG * C] = f2u(r.log_contrib);
     s[WF_N * C] = f2u(r.constants.n); s[WF_VG * C] = f2u(r.constants.vg);
     s[WF_MUS * C] = f2u(r.constants.mu_s); s[WF_MUE * C] = f2u(r.constants.mu_e);
-    s[WF_DIM * C] = dim; s[WF_FLAGS * C] = flags;
+    s[WF_DIM * C] = dim; s[WF_FLAGS * C] = flags; s[WF_PATH * C] = path;
     if (POL) {
         s[WF_S0 * C] = f2u(r.stokes.x); s[WF_S1 * C] = f2u(r.stokes.y); s[WF_S2 * C] = f2u(r.stokes.z);
         s[WF_S3 * C] = f2u(r.stokes.w);
@@ -96,16 +98,15 @@ TDEV void storeState(const Workspace& ws, uint32_t slot, const Ray& r, uint32_t 
     }
 }
 template <bool POL>
-TDEV void loadState(const Workspace& ws, uint32_t slot, Ray& r, uint32_t& dim, uint32_t& flags) {
-    const uint32_t* s = ws.state + slot;
-    const size_t C = ws.capacity;
+TDEV void loadState(const uint32_t* state, size_t C, uint32_t slot, Ray& r, uint32_t& dim, uint32_t& flags, uint32_t& path) {
+    const uint32_t* s = state + slot;
     r.position = {u2f(s[WF_PX * C]), u2f(s[WF_PY * C]), u2f(s[WF_PZ * C])};
     r.direction = {u2f(s[WF_DX * C]), u2f(s[WF_DY * C]), u2f(s[WF_DZ * C])};
     r.medium = (uint64_t)s[WF_MED_LO * C] | ((uint64_t)s[WF_MED_HI * C] << 32);
     r.wavelength = u2f(s[WF_LAMBDA * C]); r.time = u2f(s[WF_TIME * C]);
     r.lin_contrib = u2f(s[WF_LIN * C]); r.log_contrib = u2f(s[WF_LOG * C]);
     r.constants = {u2f(s[WF_N * C]), u2f(s[WF_VG * C]), u2f(s[WF_MUS * C]), u2f(s[WF_MUE * C])};
-    dim = s[WF_DIM * C]; flags = s[WF_FLAGS * C];
+    dim = s[WF_DIM * C]; flags = s[WF_FLAGS * C]; path = s[WF_PATH * C];
     if (POL) {
         r.stokes = {u2f(s[WF_S0 * C]), u2f(s[WF_S1 * C]), u2f(s[WF_S2 * C]), u2f(s[WF_S3 * C])};
         r.polRef = {u2f(s[WF_R0 * C]), u2f(s[WF_R1 * C]), u2f(s[WF_R2 * C])};
@@ -115,20 +116,20 @@ TDEV void loadState(const Workspace& ws, uint32_t slot, Ray& r, uint32_t& dim, u
     }
 }
 
-// Appends the slots of the lanes with `push` to a queue: one atomic per warp.
-// MUST be called by all 32 lanes.
-TDEV void queuePush(uint32_t* queue, uint32_t* counter, bool push, uint32_t slot) {
+// Hands the lanes with `push` consecutive indices of a dense buffer: one atomic per warp.
+// MUST be called by all 32 lanes; the value returned to the other lanes is meaningless.
+TDEV uint32_t denseAlloc(uint32_t* counter, bool push) {
     uint32_t m = __ballot_sync(FULL_MASK, push);
-    if (m == 0) return;
+    if (m == 0) return 0u;
     uint32_t leader = __ffs(m) - 1, base = 0;
     if (laneId() == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
     base = __shfl_sync(FULL_MASK, base, leader);
-    if (push) queue[base + __popc(m & laneMaskLt())] = slot;
+    return base + __popc(m & laneMaskLt());
 }
 
 // ------------------------------------------------------------------ trace kernel
-// Ray queries of a queue. rays[2 r], rays[2 r + 1] hold ray r = slot * raysPerEntry + j of the
-// queue entries; results[r] receives (instance slot | ~0, primitive, u, v).
+// Ray queries of a dense buffer: rays[2 r], rays[2 r + 1] hold ray r < *countPtr * raysPerEntry;
+// results[r] receives (instance slot | ~0, primitive, u, v).
 //
 // Persistent warps, three phases per round so that the lanes of a warp do the same kind of
 // work at the same time (the traversal steps differ a lot in cost, and a mixed warp would
@@ -142,7 +143,7 @@ TDEV void queuePush(uint32_t* queue, uint32_t* counter, bool push, uint32_t slot
 enum : uint32_t { WE_TLAS = 0u, WE_INST = 1u, WE_BLAS = 2u, WE_LEAF = 3u };
 
 __global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
-                                                         uint4* __restrict__ results, const uint32_t* __restrict__ queue,
+                                                         uint4* __restrict__ results,
                                                          const uint32_t* __restrict__ countPtr, uint32_t* cursor,
                                                          uint32_t raysPerEntry, uint32_t minNodeLanes) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
@@ -198,7 +199,7 @@ __global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__
             if (i >= total) {
                 done = true;
             } else {
-                rid = __ldg(queue + i / raysPerEntry) * raysPerEntry + i % raysPerEntry;
+                rid = i;
                 const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
                 ox = a.x; oy = a.y; oz = a.z; tmax = a.w; dx = b.x; dy = b.y; dz = b.z;
                 world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
@@ -310,7 +311,6 @@ __global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__
 // every workload for every threshold and was dropped.)
 __global__ void __launch_bounds__(128, 6) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                                uint4* __restrict__ results,
-                                                               const uint32_t* __restrict__ queue,
                                                                const uint32_t* __restrict__ countPtr, uint32_t raysPerEntry) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
@@ -320,7 +320,7 @@ __global__ void __launch_bounds__(128, 6) wfTraceSimpleKernel(const void* __rest
     __syncthreads();
     const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const uint32_t rid = raysPerEntry == 1u ? __ldg(queue + i) : __ldg(queue + (i >> 1)) * 2u + (i & 1u);
+        const uint32_t rid = i;
         const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
         const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr);
         results[rid] = make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v));
@@ -330,13 +330,14 @@ __global__ void __launch_bounds__(128, 6) wfTraceSimpleKernel(const void* __rest
 // ------------------------------------------------------------------ shading side
 enum : uint32_t { WF_SEQ1 = 1u << 18 };  // one response was already committed in this event
 
-// First half of trace() (sh/scene.traverse.glsl:280-323): health check, free path sample,
-// extension towards the target guide; writes the ray query of the slot.
+// First half of trace() (sh/scene.traverse.glsl:280-323): free path sample, extension towards
+// the target guide; writes the ray query to `rayOut` (the entry the path was given in the
+// output buffer). The health check of :285 (isRayBad) is done by the caller, which needs its
+// outcome to allocate the entry.
 template <bool POL>
-TDEV bool prepareQuery(const DeviceLaunch& P, const Workspace& ws, uint32_t slot, const Ray& ray, Rng& rng,
-                       bool allowResponse, bool GUIDE, bool& misTarget) {
+TDEV void prepareQuery(const DeviceLaunch& P, float4* rayOut, const Ray& ray, Rng& rng, bool allowResponse, bool GUIDE,
+                       bool& misTarget) {
     misTarget = false;
-    if (isRayBad(ray)) return false;
     vec3 dir = normalize(ray.direction);
     float dist = sampleScatterLength(ray, P.propagation, rng.next());
     float sampledDist = dist;
@@ -349,18 +350,16 @@ TDEV bool prepareQuery(const DeviceLaunch& P, const Workspace& ws, uint32_t slot
         }
         misTarget = mis;
     }
-    ws.ray[2 * (size_t)slot] = make_float4(ray.position.x, ray.position.y, ray.position.z, dist);
-    ws.ray[2 * (size_t)slot + 1] = make_float4(dir.x, dir.y, dir.z, sampledDist);
-    return true;
+    rayOut[0] = make_float4(ray.position.x, ray.position.y, ray.position.z, dist);
+    rayOut[1] = make_float4(dir.x, dir.y, dir.z, sampledDist);
 }
 
 // End of a segment (sh/tracer.scene.forward.glsl:87-104): event callback, stop conditions,
-// then the next ray query. MUST be called by all 32 lanes.
+// then the next ray query, appended to the output buffer. MUST be called by all 32 lanes.
 template <bool POL>
-TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* sh, bool active, uint32_t slot, Ray& ray,
-                        Rng& rng, int result, uint32_t it, bool GUIDE, uint32_t* nextQueue, uint32_t* nextCounter,
-                        uint32_t& nSegments) {
-    onEvent<POL>(P.callback, sh, active, ray, result, slot, it);
+TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* sh, bool active, uint32_t path, Ray& ray,
+                        Rng& rng, int result, uint32_t it, bool GUIDE, uint32_t next, uint32_t& nSegments) {
+    onEvent<POL>(P.callback, sh, active, ray, result, path, it);
     bool cont = active && result >= 0;
     bool maxIter = false, allow = true;
     if (cont) {
@@ -368,15 +367,16 @@ TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* 
         if (it == P.path_length) { maxIter = true; cont = false; }
         else it++;
     }
-    onEvent<POL>(P.callback, sh, maxIter, ray, THEIA_RESULT_MAX_ITER, slot, P.path_length + 1);
-    bool ok = false, mis = false;
-    if (cont) {
-        nSegments++;
-        ok = prepareQuery<POL>(P, ws, slot, ray, rng, allow, GUIDE, mis);
+    onEvent<POL>(P.callback, sh, maxIter, ray, THEIA_RESULT_MAX_ITER, path, P.path_length + 1);
+    if (cont) nSegments++;
+    const bool ok = cont && !isRayBad(ray);
+    onEvent<POL>(P.callback, sh, cont && !ok, ray, THEIA_ERROR_RAY_BAD, path, it);
+    const uint32_t j = denseAlloc(ws.counters + (next ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0), ok);
+    if (ok) {
+        bool mis;
+        prepareQuery<POL>(P, ws.ray[next] + 2 * (size_t)j, ray, rng, allow, GUIDE, mis);
+        storeState<POL>(ws.state[next], ws.capacity, j, ray, rng.dim, it | (allow ? WF_ALLOW : 0u) | (mis ? WF_MIS_TARGET : 0u), path);
     }
-    onEvent<POL>(P.callback, sh, cont && !ok, ray, THEIA_ERROR_RAY_BAD, slot, it);
-    if (ok) storeState<POL>(ws, slot, ray, rng.dim, it | (allow ? WF_ALLOW : 0u) | (mis ? WF_MIS_TARGET : 0u));
-    queuePush(nextQueue, nextCounter, ok, slot);
 }
 
 TDEV uint32_t wfWarpBase(uint32_t& stride) {
@@ -388,8 +388,9 @@ TDEV uint32_t wfWarpBase(uint32_t& stride) {
 // Cascade light: the gamma variate of the shower depth comes from a rejection loop with a
 // data dependent number of trials (sh/random.gamma.glsl:9-29). Run per path inside sampleLight
 // a warp would wait for its unluckiest lane; here the warp runs the trials of its path range
-// with refill (a lane that accepted takes the next path), parking value and draw counter in
-// the state slots of the path. Same draws, same arithmetic as sampleGamma.
+// with refill (a lane that accepted takes the next path), parking value and draw counter at
+// the path's index of state buffer 1 (unused until the first shade). Same draws, same
+// arithmetic as sampleGamma.
 TDEV void pregenerateGamma(const DeviceLaunch& P, const Workspace& ws, uint32_t first, uint32_t end) {
     const float alpha0 = P.light.p.cascade.a_long;
     const bool rescale = alpha0 < 1.0f;
@@ -419,8 +420,8 @@ TDEV void pregenerateGamma(const DeviceLaunch& P, const Workspace& ws, uint32_t 
         if (busy) {
             float X;
             if (gammaTrial(g, rng, &X)) {
-                ws.state[WF_PX * C + k] = f2u(scale * X);
-                ws.state[WF_DIM * C + k] = rng.dim;
+                ws.state[1][WF_PX * C + k] = f2u(scale * X);
+                ws.state[1][WF_DIM * C + k] = rng.dim;
                 busy = false;
             }
         }
@@ -448,22 +449,23 @@ __global__ void __launch_bounds__(128, 4) wfGenerateKernel(const __grid_constant
         const bool active = k < end;
         Ray ray;
         Rng rng = makeRng(&P.rng, P.first_path + k);
-        bool ok = false, mis = false;
         const bool allow = P.disable_direct_lighting == 0;
         if (active) {
             PreGamma pre = {false, 0.0f, 0u};
-            if (PREGAMMA) pre = {true, u2f(ws.state[WF_PX * (size_t)ws.capacity + k]), ws.state[WF_DIM * (size_t)ws.capacity + k]};
+            if (PREGAMMA) pre = {true, u2f(ws.state[1][WF_PX * (size_t)ws.capacity + k]), ws.state[1][WF_DIM * (size_t)ws.capacity + k]};
             ray = sampleRay<POL>(P.wavelength, P.light, P.medium, rng, pre);
             nPaths++;
+            nSegments++;
         }
         onEvent<POL>(P.callback, &sh, active, ray, THEIA_RESULT_RAY_CREATED, k, 0);
-        if (active) {
-            nSegments++;
-            ok = prepareQuery<POL>(P, ws, k, ray, rng, allow, GUIDE, mis);
-        }
+        const bool ok = active && !isRayBad(ray);
         onEvent<POL>(P.callback, &sh, active && !ok, ray, THEIA_ERROR_RAY_BAD, k, 1);
-        if (ok) storeState<POL>(ws, k, ray, rng.dim, 1u | (allow ? WF_ALLOW : 0u) | (mis ? WF_MIS_TARGET : 0u));
-        queuePush(ws.queue[0], ws.counters + WF_CNT_QUEUE0, ok, k);
+        const uint32_t j = denseAlloc(ws.counters + WF_CNT_QUEUE0, ok);
+        if (ok) {
+            bool mis;
+            prepareQuery<POL>(P, ws.ray[0] + 2 * (size_t)j, ray, rng, allow, GUIDE, mis);
+            storeState<POL>(ws.state[0], ws.capacity, j, ray, rng.dim, 1u | (allow ? WF_ALLOW : 0u) | (mis ? WF_MIS_TARGET : 0u), k);
+        }
     }
     sinkFinish(P, &sh, nullptr, nSegments, 0, 0, nPaths);
 }
@@ -486,28 +488,27 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
     const SceneView sc = makeSceneView(P.tlas, nullptr, 0);
     const bool GUIDE = P.guide.kind != THEIA_GUIDE_NONE;
     const uint32_t count = ws.counters[cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0];
-    const uint32_t* queue = ws.queue[cur];
-    uint32_t* nextQueue = ws.queue[cur ^ 1u];
-    uint32_t* nextCounter = ws.counters + (cur ? WF_CNT_QUEUE0 : WF_CNT_QUEUE1);
+    const uint32_t next = cur ^ 1u;
+    const uint32_t* stateIn = ws.state[cur];
+    const float4* rayIn = ws.ray[cur];
     uint32_t nSegments = 0, nResponses = 0, nShadow = 0, stride;
 
     for (uint32_t base = wfWarpBase(stride); base < count; base += stride) {
         const uint32_t i = base + laneId();
         const bool active = i < count;
-        const uint32_t slot = active ? queue[i] : 0u;
-        const uint32_t idx = P.first_path + slot;
         Ray ray;
-        uint32_t dim = 0, flags = 1u;
+        uint32_t dim = 0, flags = 1u, path = 0;
         // everything the segment needs is requested in one go: issued after the first use of
         // the state, the query and result loads would add a second memory latency
         float queryDist = 0.0f, sampledDist = 0.0f;
         uint4 queryResult4 = make_uint4(0xFFFFFFFFu, 0u, 0u, 0u);
         if (active) {
-            queryDist = ws.ray[2 * (size_t)slot].w;
-            sampledDist = ws.ray[2 * (size_t)slot + 1].w;
-            queryResult4 = ws.result[slot];
-            loadState<POL>(ws, slot, ray, dim, flags);
+            queryDist = rayIn[2 * (size_t)i].w;
+            sampledDist = rayIn[2 * (size_t)i + 1].w;
+            queryResult4 = ws.result[i];
+            loadState<POL>(stateIn, ws.capacity, i, ray, dim, flags, path);
         }
+        const uint32_t idx = P.first_path + path;
         Rng rng = makeRng(&P.rng, idx);
         rng.dim = dim;
         const uint32_t it = flags & 0xFFFFu;
@@ -584,6 +585,9 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
         }
         commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
 
+        // paths that wait for shadow rays are parked in the shadow buffer (warp collective)
+        uint32_t js = 0u;
+        if (GUIDE) js = denseAlloc(ws.counters + WF_CNT_SHADOW, wantMIS);
         if (wantMIS) {
             // sampleTargetMIS (:234-269): the two shadow rays are traced by the next trace pass
             float pPP;
@@ -595,19 +599,17 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
             float pPT = scatterProb(ray.medium, ray.direction, targetSample.dir);
             float wTarget = pTT * pPT / (pTT * pTT + pPT * pPT);
             float wPhase = pPP * pPP / (pPP * pPP + pTP * pTP);
-            float4* sr = ws.shadowRay + 4 * (size_t)slot;
+            float4* sr = ws.shadowRay + 4 * (size_t)js;
             sr[0] = make_float4(ray.position.x, ray.position.y, ray.position.z, phaseSample.dist);
             sr[1] = make_float4(dirPhase.x, dirPhase.y, dirPhase.z, wPhase);
             sr[2] = make_float4(ray.position.x, ray.position.y, ray.position.z, targetSample.dist);
             sr[3] = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, wTarget);
             nShadow += 2;
-            storeState<POL>(ws, slot, ray, rng.dim, it | (hitSeq ? WF_SEQ1 : 0u));
+            storeState<POL>(ws.shadowState, ws.capacity, js, ray, rng.dim, it | (hitSeq ? WF_SEQ1 : 0u), path);
         } else if (interact && !hit.valid && !last) {
             scatterRay<POL>(ray, rng.next2());  // volume scatter (:386-393)
         }
-        queuePush(ws.shadowQueue, ws.counters + WF_CNT_SHADOW, wantMIS, slot);
-        finishSegment<POL>(P, ws, &sh, active && !wantMIS, slot, ray, rng, result, it, GUIDE, nextQueue, nextCounter,
-                           nSegments);
+        finishSegment<POL>(P, ws, &sh, active && !wantMIS, path, ray, rng, result, it, GUIDE, next, nSegments);
     }
     sinkFinish(P, &sh, sharedHist, nSegments, nResponses, nShadow, 0);
 }
@@ -623,18 +625,17 @@ __global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_const
     float* hist = sinkHist(P, sharedHist);
     const SceneView sc = makeSceneView(P.tlas, nullptr, 0);
     const uint32_t count = ws.counters[WF_CNT_SHADOW];
-    uint32_t* nextQueue = ws.queue[cur ^ 1u];
-    uint32_t* nextCounter = ws.counters + (cur ? WF_CNT_QUEUE0 : WF_CNT_QUEUE1);
+    const uint32_t next = cur ^ 1u;
     uint32_t nSegments = 0, nResponses = 0, stride;
 
     for (uint32_t base = wfWarpBase(stride); base < count; base += stride) {
         const uint32_t i = base + laneId();
         const bool active = i < count;
-        const uint32_t slot = active ? ws.shadowQueue[i] : 0u;
-        const uint32_t idx = P.first_path + slot;
+        const uint32_t slot = i;
         Ray ray;
-        uint32_t dim = 0, flags = 1u;
-        if (active) loadState<POL>(ws, slot, ray, dim, flags);
+        uint32_t dim = 0, flags = 1u, path = 0;
+        if (active) loadState<POL>(ws.shadowState, ws.capacity, i, ray, dim, flags, path);
+        const uint32_t idx = P.first_path + path;
         Rng rng = makeRng(&P.rng, idx);
         rng.dim = dim;
         const uint32_t it = flags & 0xFFFFu;
@@ -659,8 +660,7 @@ __global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_const
             hitSeq += has ? 1u : 0u;
         }
         if (active) scatterRay<POL>(ray, rng.next2());
-        finishSegment<POL>(P, ws, &sh, active, slot, ray, rng, THEIA_RESULT_RAY_SCATTERED, it, true, nextQueue, nextCounter,
-                           nSegments);
+        finishSegment<POL>(P, ws, &sh, active, path, ray, rng, THEIA_RESULT_RAY_SCATTERED, it, true, next, nSegments);
     }
     sinkFinish(P, &sh, sharedHist, nSegments, nResponses, 0, 0);
 }
