@@ -49,6 +49,10 @@ def lib() -> ctypes.CDLL:
         l.orc_math_eval.argtypes = [c_uint32, c_void_p, c_void_p, c_uint32, c_void_p]
         l.orc_tlas_query.argtypes = [c_void_p, c_void_p, c_uint32, c_void_p, c_void_p, c_void_p]
         l.orc_hist_reduce.argtypes = [c_void_p, c_uint32, c_uint32, c_float, c_void_p, c_int]
+        for fn in ("orc_target_sample", "orc_guide_sample"):
+            getattr(l, fn).argtypes = [POINTER(_abi.Component), POINTER(_abi.PhiloxParams), c_void_p, c_uint32, c_void_p]
+        for fn in ("orc_target_intersect", "orc_guide_eval"):
+            getattr(l, fn).argtypes = [POINTER(_abi.Component), c_void_p, c_void_p, c_uint32, c_void_p]
         l.orc_hit_replay.argtypes = [c_void_p, c_uint32, c_uint32, POINTER(_abi.Response), c_uint32]
         _lib = l
     return _lib
@@ -150,3 +154,55 @@ def histReduce(partials: np.ndarray, norm: float, *, clear: bool = False) -> np.
     out = np.zeros(nBins, dtype=np.float32)
     lib().orc_hist_reduce(_ptr(partials), nHist, nBins, norm, _ptr(out), int(clear))
     return out
+
+
+def _componentOf(stage):
+    """(Component, keep-alive) of a target / target guide stage with its current parameters"""
+    from theia_b200.trace import _component
+    stage.update(0)
+    keep: list = []
+    return _component(stage, 0, keep), keep
+
+
+_TARGET_FIELDS = [("position", 0, 3), ("normal", 3, 6), ("dist", 6, 7), ("objPosition", 7, 10), ("objNormal", 10, 13),
+                  ("prob", 13, 14), ("valid", 14, 15)]
+
+
+def _unpack(out: np.ndarray, fields) -> dict:
+    return {name: (out[:, a] if b - a == 1 else out[:, a:b]) for name, a, b in fields}
+
+
+def targetSample(target, observer: np.ndarray, *, key: int = 1, offset: int = 0) -> dict:
+    """sampleTarget(observer[i], idx=i, dim=0) of a Target stage"""
+    comp, keep = _componentOf(target)
+    obs = np.ascontiguousarray(observer, dtype=np.float32)
+    out = np.zeros((len(obs), 15), np.float32)
+    lib().orc_target_sample(ctypes.byref(comp), ctypes.byref(philoxParams(key, offset)), _ptr(obs), len(obs), _ptr(out))
+    return _unpack(out, _TARGET_FIELDS)
+
+
+def targetIntersect(target, observer: np.ndarray, direction: np.ndarray) -> dict:
+    comp, keep = _componentOf(target)
+    obs, d = np.ascontiguousarray(observer, dtype=np.float32), np.ascontiguousarray(direction, dtype=np.float32)
+    out = np.zeros((len(obs), 15), np.float32)
+    lib().orc_target_intersect(ctypes.byref(comp), _ptr(obs), _ptr(d), len(obs), _ptr(out))
+    return _unpack(out, _TARGET_FIELDS)
+
+
+_GUIDE_FIELDS = [("dir", 0, 3), ("dist", 3, 4), ("prob", 4, 5)]
+
+
+def guideSample(guide, observer: np.ndarray, *, key: int = 1, offset: int = 0) -> dict:
+    comp, keep = _componentOf(guide)
+    obs = np.ascontiguousarray(observer, dtype=np.float32)
+    out = np.zeros((len(obs), 5), np.float32)
+    lib().orc_guide_sample(ctypes.byref(comp), ctypes.byref(philoxParams(key, offset)), _ptr(obs), len(obs), _ptr(out))
+    return _unpack(out, _GUIDE_FIELDS)
+
+
+def guideEval(guide, observer: np.ndarray, direction: np.ndarray) -> dict:
+    comp, keep = _componentOf(guide)
+    obs, d = np.ascontiguousarray(observer, dtype=np.float32), np.ascontiguousarray(direction, dtype=np.float32)
+    out = np.zeros((len(obs), 5), np.float32)
+    lib().orc_guide_eval(ctypes.byref(comp), _ptr(obs), _ptr(d), len(obs), _ptr(out))
+    return _unpack(out, _GUIDE_FIELDS)

@@ -57,6 +57,47 @@ int orc_math_eval(uint32_t fn, const float* x, const float* y, uint32_t n, float
     return 0;
 }
 
+// ---- component seams (pins of the target / target guide restatements, tests/test_components.py)
+// out[i] = {position xyz, normal xyz, dist, objPosition xyz, objNormal xyz, prob, valid} (15 floats)
+static void packTargetSample(const TargetSample& t, float* o) {
+    o[0] = t.position.x; o[1] = t.position.y; o[2] = t.position.z;
+    o[3] = t.normal.x; o[4] = t.normal.y; o[5] = t.normal.z; o[6] = t.dist;
+    o[7] = t.objPosition.x; o[8] = t.objPosition.y; o[9] = t.objPosition.z;
+    o[10] = t.objNormal.x; o[11] = t.objNormal.y; o[12] = t.objNormal.z; o[13] = t.prob; o[14] = t.valid ? 1.0f : 0.0f;
+}
+int orc_target_sample(const theia_component_t* c, const theia_philox_params_t* rng, const float* observer, uint32_t n,
+                      float* out) {
+    for (uint32_t i = 0; i < n; ++i) {
+        Rng r{rng, i, 0u};
+        packTargetSample(sampleTarget(*c, v3(observer + 3 * i), r), out + 15 * i);
+    }
+    return 0;
+}
+int orc_target_intersect(const theia_component_t* c, const float* observer, const float* dir, uint32_t n, float* out) {
+    for (uint32_t i = 0; i < n; ++i)
+        packTargetSample(intersectTarget(*c, v3(observer + 3 * i), v3(dir + 3 * i)), out + 15 * i);
+    return 0;
+}
+// out[i] = {dir xyz, dist, prob}
+int orc_guide_sample(const theia_component_t* c, const theia_philox_params_t* rng, const float* observer, uint32_t n,
+                     float* out) {
+    for (uint32_t i = 0; i < n; ++i) {
+        Rng r{rng, i, 0u};
+        TargetGuideSample g = sampleTargetGuide(*c, v3(observer + 3 * i), r);
+        float* o = out + 5 * i;
+        o[0] = g.dir.x; o[1] = g.dir.y; o[2] = g.dir.z; o[3] = g.dist; o[4] = g.prob;
+    }
+    return 0;
+}
+int orc_guide_eval(const theia_component_t* c, const float* observer, const float* dir, uint32_t n, float* out) {
+    for (uint32_t i = 0; i < n; ++i) {
+        TargetGuideSample g = evalTargetGuide(*c, v3(observer + 3 * i), v3(dir + 3 * i));
+        float* o = out + 5 * i;
+        o[0] = g.dir.x; o[1] = g.dir.y; o[2] = g.dir.z; o[3] = g.dist; o[4] = g.prob;
+    }
+    return 0;
+}
+
 // ---- scene
 void* orc_scene_create(const theia_instance_desc_t* desc, uint32_t n, const uint32_t* nVerts, const uint32_t* nTris,
                        int bruteForce) {

@@ -87,6 +87,13 @@ def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None,
     if targetKind == "sphere":
         tgt = target.SphereTarget(position=(-1.0, 0.0, 0.0), radius=0.5)
         src = makeLight(lightKind, polarized=polarized)
+    elif targetKind == "flat":
+        tgt = target.FlatTarget(width=1.2, length=0.8, position=(-1.0, 0.1, 0.0), direction=(1.0, 0.2, -0.1),
+                                up=(0.0, 0.0, 1.0))
+        src = makeLight(lightKind, polarized=polarized)
+    elif targetKind == "disk":
+        tgt = target.DiskTarget(position=(-1.0, 0.0, 0.1), radius=0.6, normal=(0.9, -0.3, 0.2))
+        src = makeLight(lightKind, polarized=polarized)
     else:
         tgt = target.InnerSphereTarget(position=(0.0, 0.0, 0.0), radius=8.0)
         src = makeLight(lightKind, polarized=polarized, position=(0.5, 0.2, -0.1), direction=(0.0, 0.6, 0.8))
@@ -140,7 +147,7 @@ def sceneC2(N: int, *, resp: str = "record", callback: str | None = None, polari
                         nBins, binSize, **kw)
 
 
-def sceneC3(N: int, *, resp: str = "record", callback: str | None = None, polarized: bool = False, guide: bool = True,
+def sceneC3(N: int, *, resp: str = "record", callback: str | None = None, polarized: bool = False, guide=True,
             key: int = 0xC01DC0FFEE, nBins: int = 200, binSize: float = 1.0, **kw):
     """Config C3: suzanne detector inside a glass torus, scattering medium, target guide."""
     med = HomogenousModel(mu_a=0.05, mu_s=0.05, g=0.9).createMedium()
@@ -155,7 +162,14 @@ def sceneC3(N: int, *, resp: str = "record", callback: str | None = None, polari
     ]
     src = light.SphericalLightSource(position=(0.0, -6.0, 0.0), timeRange=(0.0, 5.0), budget=1e5)
     wl = light.ConstWavelengthSource(450.0)
-    g = target.SphereTargetGuide(position=(0.0, 0.0, 0.0), radius=1.5) if guide else None
+    # guide: True / "sphere", "flat", "disk" (planes facing the light source at y = -6), or False
+    if guide == "flat":
+        g = target.FlatTargetGuide(width=3.0, height=3.0, position=(0.0, -1.2, 0.0), normal=(0.0, -1.0, 0.0),
+                                   up=(0.0, 0.0, 1.0))
+    elif guide == "disk":
+        g = target.DiskTargetGuide(position=(0.0, -1.2, 0.0), radius=1.6, normal=(0.1, -1.0, 0.05))
+    else:
+        g = target.SphereTargetGuide(position=(0.0, 0.0, 0.0), radius=1.5) if guide else None
     return _sceneCommon(N, inst, store, store.media[med.name], src, wl, resp, callback, polarized, 10, 1, g, key,
                         nBins, binSize, **kw)
 

@@ -77,3 +77,52 @@ def test_volume_tracer_energy_conservation(device, mu_a, mu_s, mu_sample, g, dis
         assert np.abs(s[:, 0] - 1.0).max() < 1e-5
         assert s[:, 1:].max() <= 1.0 and s[:, 1:].min() >= -1.0
         assert np.all(np.square(s[:, 1:]).sum(-1) <= 1.0 + 1e-5)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("shape", ["disk", "flat"])
+def test_plane_target_solid_angle(device, shape):
+    # Flat / disk targets (sh/target.flat.glsl, sh/target.disk.glsl): the unscattered light an
+    # isotropic point source on the axis of the target deposits on it is budget * Omega / 4 pi,
+    # Omega = solid angle of the shape. Only first-segment hits are summed: behind them the
+    # reference clamps every free path at the target's PLANE whether or not the shape was hit
+    # (dist = min(hit.dist, dist) with hit.dist = t also for invalid samples,
+    # sh/tracer.volume.forward.glsl:163-167 with sh/target.flat.glsl:52-73), which is reproduced
+    # here as it is and has no closed form.
+    from theia_b200 import light, material, random, response, target, trace
+    h, N = 2.0, 256 * 1024
+    with _device.useDevice(device):
+        med = H.HomogenousModel(mu_a=0.0, mu_s=1e-4).createMedium()
+        store = material.MaterialStore([], media=[med])
+        if shape == "disk":
+            R = 1.5
+            tgt = target.DiskTarget(position=(1.0, 2.0, 3.0), radius=R, normal=(0.0, 0.6, 0.8))
+            omega = 2.0 * np.pi * (1.0 - h / np.hypot(h, R))
+        else:
+            a, b = 1.0, 2.5
+            tgt = target.FlatTarget(width=a, length=b, position=(1.0, 2.0, 3.0), direction=(0.0, 0.6, 0.8),
+                                    up=(1.0, 0.0, 0.0))
+            omega = 4.0 * np.arctan(a * b / (2.0 * h * np.sqrt(4.0 * h * h + a * a + b * b)))
+        src = light.SphericalLightSource(position=(1.0, 2.0 + 0.6 * h, 3.0 + 0.8 * h), timeRange=(0.0, 0.0), budget=1.0)
+        rec = response.HitRecorder()
+        rec.enableTags()
+        rng = random.PhiloxRNG(key=0xD15C)
+        tr = trace.VolumeForwardTracer(N, src, tgt, light.ConstWavelengthSource(500.0), rec, rng,
+                                       medium=store.media[med.name], nScattering=2, scatterCoefficient=1e-4,
+                                       disableTargetSampling=True, maxTime=float("inf"))
+        cfg = {"tracer": tr, "response": rec, "callback": None, "rng": rng, "store": store}
+        H.runAny(cfg)
+        hits = H.sortedHits(cfg)
+    first = (hits["tag"] & 0xFFFF) == 0
+    total = float(hits["contrib"][first].astype(np.float64).sum()) / N
+    # hits are reported in the target's frame: on the plane, inside the shape, normal +z = source side
+    pos, nrm = hits["position"][first], hits["normal"][first]
+    assert np.abs(pos[:, 2]).max() < 1e-5 and np.all(nrm[:, 2] == 1.0)
+    if shape == "disk":
+        assert np.hypot(pos[:, 0], pos[:, 1]).max() <= R * (1.0 + 1e-6)
+    else:
+        assert np.abs(pos[:, 0]).max() <= 0.5 * a * (1.0 + 1e-6) and np.abs(pos[:, 1]).max() <= 0.5 * b * (1.0 + 1e-6)
+    expected = omega / (4.0 * np.pi)
+    tol = 4.0 * np.sqrt((1.0 - expected) / (expected * N)) + 3e-4
+    print(f"{shape}: {total:.6f} vs {expected:.6f}")
+    assert abs(total / expected - 1.0) < tol

@@ -153,6 +153,10 @@ VOLUME_CASES = [
     dict(lightKind="muon", water=True, wavelength="uniform"),
     dict(targetKind="inner", mis=True),
     dict(targetKind="inner", mis=False, polarized=True, water=True),
+    dict(targetKind="flat"),
+    dict(targetKind="flat", mis=False, polarized=True, water=True, lightKind="cone"),
+    dict(targetKind="disk"),
+    dict(targetKind="disk", direct=False, polarized=True, water=True),
 ]
 
 
@@ -175,6 +179,8 @@ SCENE_CASES = [
     (H.sceneC3, dict()),
     (H.sceneC3, dict(guide=False)),
     (H.sceneC3, dict(polarized=True, disableDirectLighting=True)),
+    (H.sceneC3, dict(guide="flat")),
+    (H.sceneC3, dict(guide="disk", polarized=True)),
     (H.sceneC5, dict(resp="record", lattice=(6, 6, 6), pitch=(4.0, 4.0, 4.0))),
 ]
 
