@@ -143,7 +143,25 @@ typedef struct theia_light_muon {
     float b_angular;
 } theia_light_muon_t;
 
+/* src/theia/light.py:692-766 (HostLightSource), sh/lightsource.host.glsl:6-17 with the queue of
+ * sh/lightsource.queue.glsl:11-33: field major float arrays of `capacity` entries each, NO count
+ * word - posXYZ, dirXYZ, [stokes IQUV, polRef XYZ when polarized], startTime, contrib.
+ * Path k of a launch (RNG stream first_path + k) reads entry k. */
+typedef struct theia_light_host {
+    uint64_t queue; /* dev: float[8 or 15][capacity] */
+    uint32_t capacity;
+    uint32_t polarized; /* LIGHT_QUEUE_POLARIZED */
+} theia_light_host_t;
+
 /* wavelength sources ---------------------------------------------------------- */
+/* src/theia/light.py:87-144 (HostWavelengthSource), sh/wavelengthsource.host.glsl:6-13 with the
+ * queue of sh/wavelengthsource.queue.glsl:11-14: float wavelength[capacity], contrib[capacity] */
+typedef struct theia_wavelength_host {
+    uint64_t queue; /* dev: float[2][capacity] */
+    uint32_t capacity;
+    uint32_t _pad;
+} theia_wavelength_host_t;
+
 /* src/theia/light.py:272-273, sh/wavelengthsource.const.glsl:6-8 */
 typedef struct theia_wavelength_const {
     float lambda;
@@ -213,11 +231,11 @@ typedef struct theia_geometry {
 
 /* ------------------------------------------------------------------ component kinds */
 enum { THEIA_LIGHT_SPHERICAL = 1, THEIA_LIGHT_CONE = 2, THEIA_LIGHT_PENCIL = 3,
-       THEIA_LIGHT_CASCADE = 4, THEIA_LIGHT_MUON = 5 };
+       THEIA_LIGHT_CASCADE = 4, THEIA_LIGHT_MUON = 5, THEIA_LIGHT_HOST = 6 };
 /* light flags (reference: preamble macros of the light source snippets) */
 enum { THEIA_LIGHT_FLAG_POLARIZED = 1,     /* LIGHTSOURCE_POLARIZED, light.py:1009-1011 */
        THEIA_LIGHT_FLAG_FRANK_TAMM_IS = 2  /* FRANK_TAMM_IS, light.py:1517-1519 */ };
-enum { THEIA_WAVELENGTH_CONST = 1, THEIA_WAVELENGTH_UNIFORM = 2 };
+enum { THEIA_WAVELENGTH_CONST = 1, THEIA_WAVELENGTH_UNIFORM = 2, THEIA_WAVELENGTH_HOST = 3 };
 enum { THEIA_TARGET_NONE = 0, THEIA_TARGET_SPHERE = 1, THEIA_TARGET_INNER_SPHERE = 2, THEIA_TARGET_FLAT = 3,
        THEIA_TARGET_DISK = 4 };
 enum { THEIA_GUIDE_NONE = 0, THEIA_GUIDE_SPHERE = 1, THEIA_GUIDE_FLAT = 2, THEIA_GUIDE_DISK = 3 };

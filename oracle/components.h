@@ -9,10 +9,18 @@ namespace orc {
 
 // ------------------------------------------------------------------ wavelength sources
 // sh/wavelengthsource.const.glsl:10-12, sh/wavelengthsource.uniform.glsl:12-16
-static inline WavelengthSample sampleWavelength(const theia_component_t& c, Rng& rng) {
+// (first = RNG stream of the first path of the launch: host queues are indexed by idx - first)
+static inline WavelengthSample sampleWavelength(const theia_component_t& c, Rng& rng, uint32_t first = 0) {
     if (c.kind == THEIA_WAVELENGTH_CONST) {
         const auto* p = (const theia_wavelength_const_t*)c.params;
         return {p->lambda, 1.0f};
+    }
+    if (c.kind == THEIA_WAVELENGTH_HOST) {  // sh/wavelengthsource.host.glsl:10-13
+        const auto* p = (const theia_wavelength_host_t*)c.params;
+        const float* q = (const float*)(uintptr_t)p->queue;
+        const uint32_t k = rng.idx - first;
+        if (k >= p->capacity) return {F_NAN, 0.0f};
+        return {q[k], q[p->capacity + k]};
     }
     const auto* p = (const theia_wavelength_uniform_t*)c.params;
     float u = rng.next();
@@ -60,7 +68,7 @@ static inline float particle_sampleEmissionAngle(float n, float a, float b, floa
 
 // ------------------------------------------------------------------ light sources (forward)
 static inline SourceRay sampleLight(const theia_component_t& c, float wavelength, MediumConstants medium,
-                                    Rng& rng, bool polarized) {
+                                    Rng& rng, bool polarized, uint32_t first = 0) {
     switch (c.kind) {
     case THEIA_LIGHT_SPHERICAL: {  // sh/lightsource.spherical.glsl:16-34
         const auto* p = (const theia_light_spherical_t*)c.params;
@@ -125,6 +133,22 @@ static inline SourceRay sampleLight(const theia_component_t& c, float wavelength
         vec3 rayDir = createLocalCOSY(trackDir) * sphericalToCartessian(phi, cos_theta);
         if (!(c.flags & THEIA_LIGHT_FLAG_FRANK_TAMM_IS)) contrib *= frank_tamm(wavelength, medium.n);
         return createSourceRay(position, rayDir, startTime, contrib, polarized);
+    }
+    case THEIA_LIGHT_HOST: {  // sh/lightsource.host.glsl:10-17, LOAD_SAMPLE of sh/lightsource.queue.glsl:40-56
+        const auto* p = (const theia_light_host_t*)c.params;
+        const float* q = (const float*)(uintptr_t)p->queue;
+        const size_t C = p->capacity;
+        const uint32_t k = rng.idx - first;
+        if (k >= p->capacity) break;
+        const float* e = q + k;
+        vec3 pos = {e[0], e[C], e[2 * C]};
+        vec3 dir = {e[3 * C], e[4 * C], e[5 * C]};
+        if (p->polarized) {
+            vec4 stokes = {e[6 * C], e[7 * C], e[8 * C], e[9 * C]};
+            vec3 polRef = {e[10 * C], e[11 * C], e[12 * C]};
+            return createSourceRay(pos, dir, stokes, polRef, e[13 * C], e[14 * C]);
+        }
+        return createSourceRay(pos, dir, e[6 * C], e[7 * C], polarized);
     }
     }
     SourceRay bad{};  // sh/lightsource.common.glsl:28-37

@@ -95,9 +95,9 @@ struct Sink {
 // sh/tracer.*.forward.glsl sampleRay
 static inline Ray sampleRay(const theia_trace_launch_t& L, uint64_t medium, Rng& rng) {
     bool pol = L.polarized != 0;
-    WavelengthSample photon = sampleWavelength(L.wavelength, rng);
+    WavelengthSample photon = sampleWavelength(L.wavelength, rng, L.first_path);
     MediumConstants constants = lookUpMedium(medium, photon.wavelength);
-    SourceRay lightRay = sampleLight(L.light, photon.wavelength, constants, rng, pol);
+    SourceRay lightRay = sampleLight(L.light, photon.wavelength, constants, rng, pol, L.first_path);
     return createRay(lightRay, medium, constants, photon);
 }
 

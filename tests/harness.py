@@ -56,6 +56,27 @@ def makeCallback(kind: str | None, capacity: int, length: int, polarized: bool =
     return None
 
 
+def hostSourceData(n: int, *, polarized: bool, seed: int = 11, origin=(1.0, 0.0, 0.0), axis=(-1.0, 0.0, 0.0)):
+    """Pre-sampled light rays and wavelengths as a host program (PROPOSAL, Geant ...) would provide them."""
+    g = np.random.default_rng(seed)
+    d = g.normal(size=(n, 3)) * 0.6 + np.asarray(axis)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = {"position": (np.asarray(origin) + g.normal(size=(n, 3)) * 0.05).astype(np.float32),
+            "direction": d.astype(np.float32),
+            "startTime": g.uniform(0.0, 10.0, n).astype(np.float32),
+            "contrib": g.uniform(0.5, 2.0, n).astype(np.float32) * 1e3}
+    if polarized:
+        ref = np.cross(d, g.normal(size=(n, 3)))
+        ref /= np.linalg.norm(ref, axis=1, keepdims=True)
+        pol = g.normal(size=(n, 3))
+        pol /= np.linalg.norm(pol, axis=1, keepdims=True) * g.uniform(1.0, 3.0, (n, 1))
+        rays["stokes"] = np.concatenate([np.ones((n, 1)), pol], 1).astype(np.float32)
+        rays["polarizationRef"] = ref.astype(np.float32)
+    photons = {"wavelength": g.uniform(350.0, 650.0, n).astype(np.float32),
+               "contrib": g.uniform(0.8, 1.2, n).astype(np.float32)}
+    return rays, photons
+
+
 def makeLight(kind: str, *, polarized: bool = False, position=(1.0, 0.0, 0.0), direction=(-1.0, 0.0, 0.0)):
     if kind == "spherical":
         return light.SphericalLightSource(position=position, timeRange=(0.0, 10.0), budget=1e5)
@@ -84,7 +105,9 @@ def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None,
     model = WaterTestModel() if water else HomogenousModel()
     med = model.createMedium()
     store = material.MaterialStore([], media=[med])
-    if targetKind == "sphere":
+    if lightKind == "host":
+        tgt, src = target.SphereTarget(position=(-1.0, 0.0, 0.0), radius=0.5), None
+    elif targetKind == "sphere":
         tgt = target.SphereTarget(position=(-1.0, 0.0, 0.0), radius=0.5)
         src = makeLight(lightKind, polarized=polarized)
     elif targetKind == "flat":
@@ -99,6 +122,12 @@ def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None,
         src = makeLight(lightKind, polarized=polarized, position=(0.5, 0.2, -0.1), direction=(0.0, 0.6, 0.8))
     wl = light.ConstWavelengthSource(500.0) if wavelength == "const" else light.UniformWavelengthSource(
         lambdaRange=(400.0, 700.0))
+    if lightKind == "host":
+        # two batches worth of host generated rays / photons, streamed batch by batch
+        rays, photons = hostSourceData(2 * N, polarized=polarized)
+        src = light.StreamingHostLightSource(N, data=rays, polarized=polarized)
+        if wavelength == "host":
+            wl = light.StreamingHostWavelengthSource(N, data=photons)
     r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize, capacity=respCapacity)
     rng = random.PhiloxRNG(key=key)
     cb = makeCallback(callback, N, nScattering + 2, polarized)
@@ -138,6 +167,9 @@ def sceneC2(N: int, *, resp: str = "record", callback: str | None = None, polari
     if lightKind == "pencil":
         src = light.PencilLightSource(position=(0.0, 0.05, 0.02), direction=(1.0, 0.0, 0.0), timeRange=(0.0, 1.0),
                                       stokes=(1.0, 1.0, 0.0, 0.0), polarizationRef=(0.0, 1.0, 0.0), budget=1e3)
+    elif lightKind == "host":
+        rays, _ = hostSourceData(2 * N, polarized=polarized, origin=(0.0, 0.0, 0.0), axis=(3.0, 0.0, 0.0))
+        src = light.StreamingHostLightSource(N, data=rays, polarized=polarized)
     else:
         src = light.ConeLightSource(position=(0.0, 0.0, 0.0), direction=(1.0, 0.0, 0.0), cosOpeningAngle=0.95,
                                     timeRange=(0.0, 1.0), budget=1e3, polarized=polarized,
@@ -218,7 +250,14 @@ def runOracle(cfg, i: int = 0, *, threads: int = 0, oracleScene=None):
     """Runs the same batch on the CPU oracle; results land in the response's host buffers."""
     import oracle
     tr = cfg["tracer"]
-    counters = oracle.trace(tr, i, scene=oracleScene, threads=threads)
+    stages = [s for _, s in tr.collectStages()]
+    at = next(k for k, s in enumerate(stages) if s is tr)
+    for s in stages:
+        s.update(i)
+    for s in stages[:at]:  # stages ahead of the tracer feed it (host source queues)
+        for cmd in s.run(i):
+            cmd()
+    counters = oracle.trace(tr, i, scene=oracleScene, threads=threads, update=False)
     r = cfg["response"]
     if isinstance(r, response.HistogramHitResponse):
         red = r._reducer
@@ -228,9 +267,7 @@ def runOracle(cfg, i: int = 0, *, threads: int = 0, oracleScene=None):
         red.histIn.zero_()
         red._buffer[i].numpy()[:] = out
     else:
-        for _, stage in tr.collectStages():
-            if stage is tr:
-                continue
+        for stage in stages[at + 1:]:
             for cmd in stage.run(i):
                 cmd()
     return counters

@@ -153,6 +153,8 @@ VOLUME_CASES = [
     dict(lightKind="muon", water=True, wavelength="uniform"),
     dict(targetKind="inner", mis=True),
     dict(targetKind="inner", mis=False, polarized=True, water=True),
+    dict(lightKind="host"),
+    dict(lightKind="host", wavelength="host", polarized=True, water=True, mis=False),
     dict(targetKind="flat"),
     dict(targetKind="flat", mis=False, polarized=True, water=True, lightKind="cone"),
     dict(targetKind="disk"),
@@ -179,6 +181,7 @@ SCENE_CASES = [
     (H.sceneC3, dict()),
     (H.sceneC3, dict(guide=False)),
     (H.sceneC3, dict(polarized=True, disableDirectLighting=True)),
+    (H.sceneC2, dict(lightKind="host")),
     (H.sceneC3, dict(guide="flat")),
     (H.sceneC3, dict(guide="disk", polarized=True)),
     (H.sceneC5, dict(resp="record", lattice=(6, 6, 6), pitch=(4.0, 4.0, 4.0))),

@@ -230,3 +230,52 @@ def test_converge_histogram_task_on_a_stub_pipeline():
         sched.wait()
     sched.destroy()
     assert not hopeless.converged and hopeless.totalBatches == 6
+
+
+def test_host_sources_stream_batches():
+    # src/theia/light.py:147-255, 775-880: Streaming*Source walk through the data batch by batch;
+    # new data rewinds; running dry warns and leaves the queue as it is
+    import warnings
+    from theia_b200 import light
+    with _device.useDevice("cpu"):
+        rays, photons = H.hostSourceData(96, polarized=True)
+        src = light.StreamingHostLightSource(64, data=rays, polarized=True)
+        wl = light.StreamingHostWavelengthSource(64, data=photons, ignoreContrib=True)
+        assert src.queue.view(0).fields == ["position", "direction", "stokes", "polarizationRef", "startTime", "contrib"]
+        assert src.queue.buffer(0).numel() == 4 * 15 * 64  # no count word (skipCounter)
+        src.update(0); wl.update(0)
+        assert np.array_equal(src.queue.view(0)["direction"], rays["direction"][:64])
+        assert np.array_equal(wl.queue.view(0)["wavelength"], photons["wavelength"][:64])
+        assert np.all(wl.queue.view(0)["contrib"] == 1.0)
+        src.update(1)
+        assert np.array_equal(src.queue.view(1)["startTime"][:32], rays["startTime"][64:])
+        with warnings.catch_warnings(record=True) as w:
+            warnings.simplefilter("always")
+            src.update(0)
+        assert any("ran out of data" in str(x.message) for x in w)
+        src.data = rays  # rewind
+        src.update(1)
+        assert np.array_equal(src.queue.view(1)["position"], rays["position"][:64])
+        with pytest.raises(ValueError):
+            src.data = {"position": rays["position"]}
+        # the parameter block handed to the C-ABI names the device queue
+        blk = src._firstBlock(1)
+        assert blk._queue == src.queue.tensor.data_ptr() and blk._capacity == 64 and blk._polarized == 1
+        for cmd in src.run(1):
+            cmd()
+        dev = src.queue.tensor.numpy().view(np.float32).reshape(15, 64)
+        assert np.array_equal(dev[3:6].T, rays["direction"][:64])
+
+
+def test_host_sources_on_the_oracle():
+    # a path starts exactly where the host says: first track vertex = queue entry
+    with _device.useDevice("cpu"):
+        cfg = H.volumeScenario(256, lightKind="host", wavelength="host", callback="track", polarized=True, water=True)
+        H.runOracle(cfg)
+        q = cfg["tracer"].source.queue.view(0)
+        tracks, lengths, codes = cfg["callback"].result(0)
+        assert np.array_equal(tracks[:, 0, :3], q["position"])
+        assert np.array_equal(tracks[:, 0, 3], q["startTime"])
+        hits = H.hitView(cfg)
+        wl = cfg["tracer"].wavelengthSource.queue.view(0)["wavelength"]
+        assert hits.count > 10 and np.all(np.isin(hits["wavelength"], wl))

@@ -7,9 +7,9 @@ from ctypes import POINTER, Structure, c_float, c_int32, c_uint32, c_uint64, c_v
 ABI_VERSION = 1
 
 # component kinds
-LIGHT_SPHERICAL, LIGHT_CONE, LIGHT_PENCIL, LIGHT_CASCADE, LIGHT_MUON = 1, 2, 3, 4, 5
+LIGHT_SPHERICAL, LIGHT_CONE, LIGHT_PENCIL, LIGHT_CASCADE, LIGHT_MUON, LIGHT_HOST = 1, 2, 3, 4, 5, 6
 LIGHT_FLAG_POLARIZED, LIGHT_FLAG_FRANK_TAMM_IS = 1, 2
-WAVELENGTH_CONST, WAVELENGTH_UNIFORM = 1, 2
+WAVELENGTH_CONST, WAVELENGTH_UNIFORM, WAVELENGTH_HOST = 1, 2, 3
 TARGET_NONE, TARGET_SPHERE, TARGET_INNER_SPHERE, TARGET_FLAT, TARGET_DISK = 0, 1, 2, 3, 4
 GUIDE_NONE, GUIDE_SPHERE, GUIDE_FLAT, GUIDE_DISK = 0, 1, 2, 3
 RESPONSE_EMPTY, RESPONSE_RECORD, RESPONSE_HISTOGRAM = 0, 1, 2

@@ -309,19 +309,27 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
         setError("unknown tracer kind %u", L->tracer);
         return -1;
     }
-    D.light.kind = L->light.kind; D.light.flags = L->light.flags;
+    D.light.kind = L->light.kind; D.light.flags = L->light.flags; D.light.first = L->first_path;
     switch (L->light.kind) {
     case THEIA_LIGHT_SPHERICAL: if (copyBlock(L->light, D.light.p.spherical, "spherical light")) return -1; break;
     case THEIA_LIGHT_CONE: if (copyBlock(L->light, D.light.p.cone, "cone light")) return -1; break;
     case THEIA_LIGHT_PENCIL: if (copyBlock(L->light, D.light.p.pencil, "pencil light")) return -1; break;
     case THEIA_LIGHT_CASCADE: if (copyBlock(L->light, D.light.p.cascade, "cascade light")) return -1; break;
     case THEIA_LIGHT_MUON: if (copyBlock(L->light, D.light.p.muon, "muon light")) return -1; break;
+    case THEIA_LIGHT_HOST:
+        if (copyBlock(L->light, D.light.p.host, "host light")) return -1;
+        if (!D.light.p.host.queue || D.light.p.host.capacity < L->batch_size) { setError("host light: queue holds %u samples, batch needs %u", D.light.p.host.capacity, L->batch_size); return -1; }
+        break;
     default: setError("unsupported light source kind %u", L->light.kind); return -1;
     }
-    D.wavelength.kind = L->wavelength.kind;
+    D.wavelength.kind = L->wavelength.kind; D.wavelength.first = L->first_path;
     switch (L->wavelength.kind) {
     case THEIA_WAVELENGTH_CONST: if (copyBlock(L->wavelength, D.wavelength.p.constant, "const wavelength")) return -1; break;
     case THEIA_WAVELENGTH_UNIFORM: if (copyBlock(L->wavelength, D.wavelength.p.uniform, "uniform wavelength")) return -1; break;
+    case THEIA_WAVELENGTH_HOST:
+        if (copyBlock(L->wavelength, D.wavelength.p.host, "host wavelength")) return -1;
+        if (!D.wavelength.p.host.queue || D.wavelength.p.host.capacity < L->batch_size) { setError("host wavelength: queue holds %u samples, batch needs %u", D.wavelength.p.host.capacity, L->batch_size); return -1; }
+        break;
     default: setError("unsupported wavelength source kind %u", L->wavelength.kind); return -1;
     }
     if (fillResponse(L->response, D.response)) return -1;

@@ -14,13 +14,16 @@ union LightBlock {
     theia_light_pencil_t pencil;
     theia_light_cascade_t cascade;
     theia_light_muon_t muon;
+    theia_light_host_t host;
 };
 union WavelengthBlock {
     theia_wavelength_const_t constant;
     theia_wavelength_uniform_t uniform;
+    theia_wavelength_host_t host;
 };
-struct LightSel { uint32_t kind, flags; LightBlock p; };
-struct WavelengthSel { uint32_t kind; WavelengthBlock p; };
+// first = RNG stream of the first path of the launch: host queues are indexed by idx - first
+struct LightSel { uint32_t kind, flags, first; LightBlock p; };
+struct WavelengthSel { uint32_t kind, first; WavelengthBlock p; };
 union TargetBlock {
     theia_target_sphere_t sphere;
     theia_target_flat_t flat;
@@ -38,6 +41,12 @@ struct GuideSel { uint32_t kind; GuideBlock p; };
 // sh/wavelengthsource.const.glsl:10-12, sh/wavelengthsource.uniform.glsl:12-16
 TDEV WavelengthSample sampleWavelength(const WavelengthSel& c, Rng& rng) {
     if (c.kind == THEIA_WAVELENGTH_CONST) return {c.p.constant.lambda, 1.0f};
+    if (c.kind == THEIA_WAVELENGTH_HOST) {  // sh/wavelengthsource.host.glsl:10-13
+        const float* q = reinterpret_cast<const float*>(c.p.host.queue);
+        const uint32_t k = rng.idx - c.first, C = c.p.host.capacity;
+        if (k >= C) return {T_NAN, 0.0f};
+        return {__ldg(q + k), __ldg(q + C + k)};
+    }
     float u = rng.next();
     float lam = mix_(c.p.uniform.lam_min, c.p.uniform.lam_max, u);
     return {lam, c.p.uniform.contrib};
@@ -169,6 +178,22 @@ TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants 
         vec3 rayDir = createLocalCOSY(trackDir) * sphericalToCartessian(phi, cos_theta);
         if (!(c.flags & THEIA_LIGHT_FLAG_FRANK_TAMM_IS)) contrib *= frank_tamm(wavelength, medium.n);
         return createSourceRay<POL>(position, rayDir, startTime, contrib);
+    }
+    case THEIA_LIGHT_HOST: {  // sh/lightsource.host.glsl:10-17, LOAD_SAMPLE of sh/lightsource.queue.glsl:40-56
+        const theia_light_host_t& p = c.p.host;
+        const float* q = reinterpret_cast<const float*>(p.queue);
+        const size_t C = p.capacity;
+        const uint32_t k = rng.idx - c.first;
+        if (k >= p.capacity) break;
+        const float* e = q + k;
+        vec3 pos = {__ldg(e), __ldg(e + C), __ldg(e + 2 * C)};
+        vec3 dir = {__ldg(e + 3 * C), __ldg(e + 4 * C), __ldg(e + 5 * C)};
+        if (p.polarized) {
+            vec4 stokes = {__ldg(e + 6 * C), __ldg(e + 7 * C), __ldg(e + 8 * C), __ldg(e + 9 * C)};
+            vec3 polRef = {__ldg(e + 10 * C), __ldg(e + 11 * C), __ldg(e + 12 * C)};
+            return createSourceRay(pos, dir, stokes, polRef, __ldg(e + 13 * C), __ldg(e + 14 * C));
+        }
+        return createSourceRay<POL>(pos, dir, __ldg(e + 6 * C), __ldg(e + 7 * C));
     }
     }
     SourceRay bad;  // sh/lightsource.common.glsl:28-37

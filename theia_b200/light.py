@@ -8,7 +8,9 @@ include/theia_b200.h; the device code is selected by ``_kind`` / ``_flags``.
 
 from __future__ import annotations
 
-from ctypes import Structure, c_float
+from ctypes import Structure, c_float, c_uint32, c_uint64
+from typing import Callable
+from warnings import warn
 
 import numpy as np
 
@@ -18,9 +20,11 @@ from theia_b200.glsl import vec2, vec3, vec4
 from theia_b200.pipeline import SourceCodeMixin
 
 __all__ = [
-    "ConeLightSource", "ConstWavelengthSource", "LightSampleItem", "LightSource", "MuonTrackLightSource",
-    "ParticleCascadeLightSource", "PencilLightSource", "PolarizedLightSampleItem", "SphericalLightSource",
-    "UniformWavelengthSource", "WavelengthSampleItem", "WavelengthSource", "frankTamm",
+    "ConeLightSource", "ConstWavelengthSource", "HostLightSource", "HostWavelengthSource", "LightSampleItem",
+    "LightSource", "MuonTrackLightSource", "ParticleCascadeLightSource", "PencilLightSource",
+    "PolarizedLightSampleItem", "SphericalLightSource", "StreamingHostLightSource",
+    "StreamingHostWavelengthSource", "UniformWavelengthSource", "WavelengthSampleItem", "WavelengthSource",
+    "frankTamm",
 ]
 
 
@@ -43,6 +47,115 @@ class WavelengthSource(SourceCodeMixin):
 
 class WavelengthSampleItem(Structure):
     _fields_ = [("wavelength", c_float), ("contrib", c_float)]
+
+
+class _HostQueueParams(Structure):
+    # theia_light_host_t / theia_wavelength_host_t of include/theia_b200.h (the reference binds the
+    # queue tensor by name instead: program.bindParams(LightQueueIn=...), src/theia/light.py:761)
+    _pack_ = 4
+    _fields_ = [("_queue", c_uint64), ("_capacity", c_uint32), ("_polarized", c_uint32)]
+
+
+def _streamInto(source, i: int, what: str) -> None:
+    """next ``capacity`` entries of source.data -> host copy i of the queue (src/theia/light.py:232-255, 856-880)"""
+    if source.data is None:
+        warn(f"{what}: New data was requested but no source was given!")
+        return
+    if source._offset >= source._dataSize:
+        warn(f"{what} ran out of data!")
+        return
+    start = source._offset
+    end = min(source._offset + source.capacity, source._dataSize)
+    source._offset = end
+    view = source.queue.view(i)
+    for field in source._dataFields:
+        view[field][: end - start] = source.data[field][start:end]
+
+
+class HostWavelengthSource(WavelengthSource):
+    """
+    Wavelength source passing samples from the host to the device: path k of a batch reads
+    entry k of ``queue`` (src/theia/light.py:87-144, sh/wavelengthsource.host.glsl). ``updateFn(source, i)``
+    is called before configuration i is committed and may refill ``queue.view(i)``.
+    """
+
+    name = "Host Wavelength Source"
+    _kind = _abi.WAVELENGTH_HOST
+
+    def __init__(self, capacity: int, *, updateFn: Callable[["HostWavelengthSource", int], None] | None = None,
+                 extra: set[str] = set()) -> None:
+        from theia_b200.queue import IOQueue
+        super().__init__(params={"HostParams": _HostQueueParams}, extra=extra)
+        self._capacity = capacity
+        self._updateFn = updateFn
+        self._queue = IOQueue(WavelengthSampleItem, capacity, mode="update", skipCounter=True)
+        self.setParams(_queue=self._queue.tensor.data_ptr(), _capacity=capacity, _polarized=0)
+
+    @property
+    def capacity(self) -> int:
+        """Maximum number of samples that can be drawn per run"""
+        return self._capacity
+
+    @property
+    def queue(self):
+        """Queue containing the data for the next batch"""
+        return self._queue
+
+    def update(self, i: int) -> None:
+        if self._updateFn is not None:
+            self._updateFn(self, i)
+        super().update(i)
+
+    def run(self, i: int):
+        return [*self.queue.run(i), *super().run(i)]
+
+
+class StreamingHostWavelengthSource(HostWavelengthSource):
+    """
+    Feeds pre-sampled wavelengths batch by batch from ``data`` (dict with ``wavelength`` and,
+    unless ``ignoreContrib``, ``contrib``); assigning new data rewinds the stream
+    (src/theia/light.py:147-255). Entries beyond the end of the data keep their old content.
+    """
+
+    name = "Streaming Host Wavelength Source"
+
+    def __init__(self, batchSize: int, *, data=None, ignoreContrib: bool = False) -> None:
+        super().__init__(batchSize, updateFn=self._updateData, extra={"data"})
+        if ignoreContrib:
+            self._dataFields = {"wavelength"}
+            self.queue.view(0)["contrib"] = 1.0
+            self.queue.view(1)["contrib"] = 1.0
+        else:
+            self._dataFields = {"contrib", "wavelength"}
+        self.data = data
+
+    @property
+    def data(self):
+        """Data used as streaming source"""
+        return self._data
+
+    @data.setter
+    def data(self, value) -> None:
+        self._offset = 0
+        self._dataSize = 0
+        if value is None:
+            self._data = None
+            return
+        if not self._dataFields.issubset(value.keys()):
+            raise ValueError(f"provided data misses expected fields: {self._dataFields.difference(value.keys())}")
+        self._dataSize = np.size(value["wavelength"], 0)
+        for field in self._dataFields:
+            if np.size(value[field], 0) != self._dataSize:
+                raise ValueError("fields of provided data differ in size!")
+        self._data = {f: np.asarray(value[f]) for f in self._dataFields}
+
+    @data.deleter
+    def data(self) -> None:
+        self.data = None
+
+    @staticmethod
+    def _updateData(source: HostWavelengthSource, i: int) -> None:
+        _streamInto(source, i, "StreamingHostWavelengthSource")
 
 
 class ConstWavelengthSource(WavelengthSource):
@@ -131,6 +244,102 @@ class LightSampleItem(Structure):
 class PolarizedLightSampleItem(Structure):
     _fields_ = [("position", c_float * 3), ("direction", c_float * 3), ("stokes", c_float * 4),
                 ("polarizationRef", c_float * 3), ("startTime", c_float), ("contrib", c_float)]
+
+
+class HostLightSource(LightSource):
+    """
+    Light source passing rays from the host to the device: path k of a batch starts from entry k
+    of ``queue`` (src/theia/light.py:692-772, sh/lightsource.host.glsl). Forward mode only.
+    ``updateFn(source, i)`` is called before configuration i is committed.
+    """
+
+    name = "Host Light Source"
+    _kind = _abi.LIGHT_HOST
+
+    def __init__(self, capacity: int, *, polarized: bool = False,
+                 updateFn: Callable[["HostLightSource", int], None] | None = None, extra: set[str] = set()) -> None:
+        from theia_b200.queue import IOQueue
+        super().__init__(supportForward=True, supportBackward=False, params={"HostParams": _HostQueueParams}, extra=extra)
+        self._capacity = capacity
+        self._polarized = polarized
+        self._updateFn = updateFn
+        item = PolarizedLightSampleItem if polarized else LightSampleItem
+        self._queue = IOQueue(item, capacity, mode="update", skipCounter=True)
+        self.setParams(_queue=self._queue.tensor.data_ptr(), _capacity=capacity, _polarized=int(polarized))
+
+    @property
+    def capacity(self) -> int:
+        """Maximum number of samples that can be drawn per run"""
+        return self._capacity
+
+    @property
+    def polarized(self) -> bool:
+        """Whether the light source provides polarization information"""
+        return self._polarized
+
+    @property
+    def queue(self):
+        """Queue containing the data for the next batch"""
+        return self._queue
+
+    @property
+    def _flags(self) -> int:
+        return _abi.LIGHT_FLAG_POLARIZED if self._polarized else 0
+
+    def update(self, i: int) -> None:
+        if self._updateFn is not None:
+            self._updateFn(self, i)
+        super().update(i)
+
+    def run(self, i: int):
+        return [*self.queue.run(i), *super().run(i)]
+
+
+class StreamingHostLightSource(HostLightSource):
+    """
+    Feeds light rays batch by batch from ``data`` (dict of arrays named like the fields of
+    ``LightSampleItem`` / ``PolarizedLightSampleItem``); assigning new data rewinds the stream
+    (src/theia/light.py:775-880).
+    """
+
+    name = "Streaming Host Light Source"
+
+    def __init__(self, batchSize: int, *, data=None, polarized: bool = False, ignoreContrib: bool = False) -> None:
+        super().__init__(batchSize, polarized=polarized, updateFn=self._updateData, extra={"data"})
+        self._dataFields = set(self.queue.view(0).fields)
+        if ignoreContrib:
+            self._dataFields.remove("contrib")
+            self.queue.view(0)["contrib"] = 1.0
+            self.queue.view(1)["contrib"] = 1.0
+        self.data = data
+
+    @property
+    def data(self):
+        """Data used as streaming source"""
+        return self._data
+
+    @data.setter
+    def data(self, value) -> None:
+        self._offset = 0
+        self._dataSize = 0
+        if value is None:
+            self._data = None
+            return
+        if not self._dataFields.issubset(value.keys()):
+            raise ValueError(f"provided data misses expected fields: {self._dataFields.difference(value.keys())}")
+        self._dataSize = np.size(value["startTime"], 0)
+        for field in self._dataFields:
+            if np.size(value[field], 0) != self._dataSize:
+                raise ValueError("fields of provided data differ in size!")
+        self._data = {f: np.asarray(value[f]) for f in self._dataFields}
+
+    @data.deleter
+    def data(self) -> None:
+        self.data = None
+
+    @staticmethod
+    def _updateData(source: HostLightSource, i: int) -> None:
+        _streamInto(source, i, "StreamingHostLightSource")
 
 
 class ConeLightSource(LightSource):

@@ -33,9 +33,9 @@ def _components(item: type[Structure]) -> list[tuple[str, type, int]]:
     return out
 
 
-def queueSize(item: type[Structure], capacity: int) -> int:
+def queueSize(item: type[Structure], capacity: int, *, skipCounter: bool = False) -> int:
     """Bytes needed for a queue of the given item type and capacity."""
-    return 4 + 4 * capacity * sum(n for _, _, n in _components(item))
+    return (0 if skipCounter else 4) + 4 * capacity * sum(n for _, _, n in _components(item))
 
 
 class QueueView:
@@ -44,7 +44,8 @@ class QueueView:
     ``(n, k)``), sliceable and indexable along the item axis like the reference's QueueView.
     """
 
-    def __init__(self, data: np.ndarray | None, item: type[Structure], capacity: int, *, _fields=None, _count=None):
+    def __init__(self, data: np.ndarray | None, item: type[Structure], capacity: int, *, skipCounter: bool = False,
+                 _fields=None, _count=None):
         self._item = item
         self._capacity = capacity
         self._header = None
@@ -53,9 +54,13 @@ class QueueView:
             self._fixedCount = _count
             return
         self._fixedCount = None
-        self._header = data[:4].view(np.uint32)
         self._fields = {}
-        off = 4
+        if skipCounter:  # queues that are always full (host sources): no count word
+            self._fixedCount = capacity
+            off = 0
+        else:
+            self._header = data[:4].view(np.uint32)
+            off = 4
         for name, dt, n in _components(item):
             arr = data[off : off + 4 * capacity * n].view(dt)
             self._fields[name] = arr if n == 1 else arr.reshape(n, capacity).T
@@ -102,11 +107,13 @@ class IOQueue:
     device count is cleared; ``mode="update"``: host -> device before the run.
     """
 
-    def __init__(self, item: type[Structure], capacity: int = 0, *, mode: str = "retrieve") -> None:
+    def __init__(self, item: type[Structure], capacity: int = 0, *, mode: str = "retrieve",
+                 skipCounter: bool = False) -> None:
         if mode not in ("retrieve", "update"):
             raise ValueError("mode must be 'retrieve' or 'update'")
         self._item = item
         self._mode = mode
+        self._skipCounter = skipCounter
         self._capacity = 0
         self._tensor = None
         self._buffers = None
@@ -135,11 +142,11 @@ class IOQueue:
         if self.initialized:
             raise RuntimeError("queue is already initialized")
         self._capacity = capacity
-        n = queueSize(self._item, capacity)
+        n = queueSize(self._item, capacity, skipCounter=self._skipCounter)
         self._nbytes = n
         self._tensor = _device.alloc(n, self._device)
         self._buffers = [_device.allocPinned(n) for _ in range(2)]
-        if self._mode == "update":
+        if self._mode == "update" and not self._skipCounter:
             for i in range(2):
                 self.view(i).count = capacity
 
@@ -148,13 +155,14 @@ class IOQueue:
 
     def view(self, i: int) -> QueueView:
         """View of the i-th host copy"""
-        return QueueView(self._buffers[i].numpy(), self._item, self._capacity)
+        return QueueView(self._buffers[i].numpy(), self._item, self._capacity, skipCounter=self._skipCounter)
 
     def run(self, i: int) -> list[Command]:
         if self._mode == "retrieve":
             def cmd() -> None:
                 self._buffers[i].copy_(self._tensor, non_blocking=True)
-                self._tensor[:4].zero_()  # reset count for the next batch
+                if not self._skipCounter:
+                    self._tensor[:4].zero_()  # reset count for the next batch
         else:
             def cmd() -> None:
                 self._tensor.copy_(self._buffers[i], non_blocking=True)
