@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define THEIA_ABI_VERSION 1
+#define THEIA_ABI_VERSION 2
 
 /* ------------------------------------------------------------------ result codes */
 /* sh/result.glsl:10-28, src/theia/trace.py:308-343 */
@@ -239,7 +239,10 @@ enum { THEIA_WAVELENGTH_CONST = 1, THEIA_WAVELENGTH_UNIFORM = 2, THEIA_WAVELENGT
 enum { THEIA_TARGET_NONE = 0, THEIA_TARGET_SPHERE = 1, THEIA_TARGET_INNER_SPHERE = 2, THEIA_TARGET_FLAT = 3,
        THEIA_TARGET_DISK = 4 };
 enum { THEIA_GUIDE_NONE = 0, THEIA_GUIDE_SPHERE = 1, THEIA_GUIDE_FLAT = 2, THEIA_GUIDE_DISK = 3 };
-enum { THEIA_RESPONSE_EMPTY = 0, THEIA_RESPONSE_RECORD = 1, THEIA_RESPONSE_HISTOGRAM = 2 };
+enum { THEIA_RESPONSE_EMPTY = 0, THEIA_RESPONSE_RECORD = 1, THEIA_RESPONSE_HISTOGRAM = 2,
+       THEIA_RESPONSE_STORE_TIME = 3,       /* sh/response.time.store.glsl */
+       THEIA_RESPONSE_KERNEL_HISTOGRAM = 4, /* sh/response.histogram.kernel.glsl */
+       THEIA_RESPONSE_OBJECT_HISTOGRAM = 5  /* B200 extension: one time histogram per objectId */ };
 enum { THEIA_VALUE_UNIFORM = 1 };
 enum { THEIA_CALLBACK_EMPTY = 0, THEIA_CALLBACK_STAT = 1, THEIA_CALLBACK_TRACK = 2 };
 enum { THEIA_TRACER_VOLUME_FORWARD = 1, THEIA_TRACER_SCENE_FORWARD = 2 };
@@ -270,6 +273,26 @@ typedef struct theia_response {
      * produced hit k are written to tag_path[k], tag_event[k]. */
     uint32_t *tag_path;
     uint32_t *tag_event;
+    /* kernel histogram: sh/response.histogram.kernel.glsl:13-20 (ResponseParams behind t0, binSize),
+     * src/theia/response.py:1424-1673. Uses hist, n_bins, hist_capacity, hist_partials like the
+     * plain histogram; every hit is spread over the bins within kernel_support of its time with
+     * the weights of a Gaussian of width kernel_bandwidth. */
+    float kernel_bandwidth;
+    float kernel_support;
+    /* store time: sh/response.time.store.glsl:4-26, src/theia/response.py:656-797. A hit is kept
+     * with probability responseValue(hit) (ONE draw of the path's RNG stream per hit, whatever
+     * the outcome). value_queue = uint32 count; float time[value_capacity];
+     * int32 objectId[value_capacity] (only if store_object_id). */
+    uint32_t *value_queue;
+    uint32_t value_capacity;
+    uint32_t store_object_id; /* RESPONSE_STORE_OBJECT_ID */
+    /* object histogram (B200 extension; what config C5's per module light curves need and the
+     * reference can only get from HitRecorder + host binning): hits with 0 <= objectId < n_objects
+     * add their value to object_hist[objectId][bin]; hist, n_bins give the binning. Accumulated
+     * in place with float atomics; the caller clears and normalises. */
+    float *object_hist; /* dev: float[n_objects][n_bins] */
+    uint32_t n_objects;
+    uint32_t _pad1;
 } theia_response_t;
 
 /* Trace event callback (sh/callback.*.glsl, src/theia/trace.py:77-305). */
@@ -427,7 +450,7 @@ int theia_hit_replay(const uint32_t *queue_dev, uint32_t capacity, uint32_t pola
 
 /* ------------------------------------------------------------------ device math test seam
  * Evaluates the library's deterministic float math on the device (fn: 0 sin, 1 cos, 2 exp,
- * 3 log, 4 pow(x,y)). Used by the parity tests only. */
+ * 3 log, 4 pow(x,y), 5 tanh, 6 atan). Used by the parity tests only. */
 int theia_math_eval(uint32_t fn, const float *x_dev, const float *y_dev, uint32_t n,
                     float *out_dev, void *stream);
 

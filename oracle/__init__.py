@@ -86,7 +86,7 @@ def philoxRaw(ctr: np.ndarray, key: np.ndarray) -> np.ndarray:
     return out
 
 
-MATH_FN = {"sin": 0, "cos": 1, "exp": 2, "log": 3, "pow": 4}
+MATH_FN = {"sin": 0, "cos": 1, "exp": 2, "log": 3, "pow": 4, "tanh": 5, "atan": 6}
 
 
 def mathEval(fn: str, x: np.ndarray, y: np.ndarray | None = None) -> np.ndarray:

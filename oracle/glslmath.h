@@ -106,6 +106,28 @@ static inline float dm_exp(float x) {
     return (p * s1) * s2;
 }
 
+// tanh(x) = 1 - 2 / (exp(2x) + 1) on |x| (odd extension); absolute error ~1e-7, which is what
+// its only user, the kernel CDF of sh/response.histogram.kernel.glsl:62-70, needs.
+static inline float dm_tanh(float x) {
+    if (x != x) return x;
+    float a = abs_(x);
+    float r = a > 10.0f ? 1.0f : 1.0f - 2.0f / (dm_exp(2.0f * a) + 1.0f);
+    return x < 0.0f ? -r : r;
+}
+// atan: Cephes atanf scheme (reduce by tan(3 pi / 8), tan(pi / 8); degree 4 odd polynomial in x^2)
+static inline float dm_atan(float x) {
+    if (x != x) return x;
+    float a = abs_(x), y = 0.0f;
+    if (a > 2.414213562373095f) { y = 1.5707963267948966f; a = -(1.0f / a); }
+    else if (a > 0.4142135623730950f) { y = 0.7853981633974483f; a = (a - 1.0f) / (a + 1.0f); }
+    float z = a * a;
+    float p = fmaf(8.05374449538e-2f, z, -1.38776856032e-1f);
+    p = fmaf(p, z, 1.99777106478e-1f);
+    p = fmaf(p, z, -3.33329491539e-1f);
+    y += fmaf(p * z, a, a);
+    return x < 0.0f ? -y : y;
+}
+
 // log: Cephes logf. Denormals are scaled by 2^23 first.
 static inline float dm_log(float x) {
     if (isnan_(x)) return x;

@@ -51,6 +51,8 @@ int orc_math_eval(uint32_t fn, const float* x, const float* y, uint32_t n, float
         case 2: out[i] = dm_exp(x[i]); break;
         case 3: out[i] = dm_log(x[i]); break;
         case 4: out[i] = dm_pow(x[i], y[i]); break;
+        case 5: out[i] = dm_tanh(x[i]); break;
+        case 6: out[i] = dm_atan(x[i]); break;
         default: return -1;
         }
     }
@@ -174,9 +176,10 @@ int orc_trace_forward(const theia_trace_launch_t* L, int nThreads, uint64_t* cou
     const theia_response_t& R = L->response;
     if (nThreads <= 0) nThreads = omp_get_max_threads();
     std::vector<std::vector<TaggedHit>> chunkHits(R.kind == THEIA_RESPONSE_RECORD ? nChunks : 0);
+    std::vector<std::vector<Sink::TimeHit>> chunkTimes(R.kind == THEIA_RESPONSE_STORE_TIME ? nChunks : 0);
     uint64_t stats[12] = {0};
     uint64_t segs = 0, resp = 0, trav[4] = {0, 0, 0, 0};
-    if (R.kind == THEIA_RESPONSE_HISTOGRAM && R.hist_capacity == 0) return -2;
+    if (Sink::hasHistogram(R.kind) && R.hist_capacity == 0) return -2;
 
 #pragma omp parallel num_threads(nThreads)
     {
@@ -194,12 +197,14 @@ int orc_trace_forward(const theia_trace_launch_t* L, int nThreads, uint64_t* cou
                               sink, pol, counters ? ttrav : nullptr};
                 for (uint32_t k = lo; k < hi; ++k) t.traceMain(L->first_path + k);
             }
-            if (R.kind == THEIA_RESPONSE_HISTOGRAM) {
+            if (Sink::hasHistogram(R.kind)) {
                 float* dst = R.hist_partials + (size_t)((uint32_t)c % R.hist_capacity) * R.n_bins;
 #pragma omp critical(orc_hist)
                 for (uint32_t b = 0; b < R.n_bins; ++b) dst[b] += sink.hist[b];
             } else if (R.kind == THEIA_RESPONSE_RECORD) {
                 chunkHits[c] = std::move(sink.hits);
+            } else if (R.kind == THEIA_RESPONSE_STORE_TIME) {
+                chunkTimes[c] = std::move(sink.times);
             }
             for (int k = 0; k < 12; ++k) tstats[k] += sink.stats[k];
             tresp += sink.nResponse;
@@ -224,6 +229,22 @@ int orc_trace_forward(const theia_trace_launch_t* L, int nThreads, uint64_t* cou
                 ++count;  // the reference's atomicAdd also runs past the capacity
             }
         R.queue[0] = count;
+    }
+    if (R.kind == THEIA_RESPONSE_STORE_TIME) {  // sh/response.time.store.glsl:4-10 (count, time[], objectId[])
+        uint32_t count = R.value_queue[0];
+        float* time = (float*)(R.value_queue + 1);
+        int32_t* ids = (int32_t*)(R.value_queue + 1) + R.value_capacity;
+        for (auto& v : chunkTimes)
+            for (auto& h : v) {
+                if (count < R.value_capacity) {
+                    time[count] = h.time;
+                    if (R.store_object_id) ids[count] = h.objectId;
+                    if (R.tag_path) R.tag_path[count] = h.path;
+                    if (R.tag_event) R.tag_event[count] = h.event;
+                }
+                ++count;
+            }
+        R.value_queue[0] = count;
     }
     if (L->callback.kind == THEIA_CALLBACK_STAT && L->callback.stats)
         for (int k = 0; k < 12; ++k) L->callback.stats[k] += stats[k];
@@ -256,6 +277,7 @@ int orc_hist_reduce(float* partials, uint32_t nHist, uint32_t nBins, float norm,
 // sh/response.replay.glsl:35-50
 int orc_hit_replay(const uint32_t* queue, uint32_t capacity, uint32_t polarized, const theia_response_t* response,
                    uint32_t block_size) {
+    if (response->kind == THEIA_RESPONSE_STORE_TIME) return -3;
     theia_trace_launch_t L{};
     L.response = *response;
     uint32_t count = queue[0] < capacity ? queue[0] : capacity;
@@ -264,8 +286,11 @@ int orc_hit_replay(const uint32_t* queue, uint32_t capacity, uint32_t polarized,
     std::vector<TaggedHit> all;
     for (uint32_t c = 0; c < nChunks; ++c) {
         Sink sink(&L);
-        for (uint32_t k = c * bs; k < (c + 1) * bs && k < count; ++k) sink.response(loadHit(queue, capacity, polarized != 0, k), k);
-        if (response->kind == THEIA_RESPONSE_HISTOGRAM) {
+        for (uint32_t k = c * bs; k < (c + 1) * bs && k < count; ++k) {
+            Rng none{nullptr, k, 0u};  // a replay has no random number stream
+            sink.response(loadHit(queue, capacity, polarized != 0, k), none);
+        }
+        if (Sink::hasHistogram(response->kind)) {
             float* dst = response->hist_partials + (size_t)(c % response->hist_capacity) * response->n_bins;
             for (uint32_t b = 0; b < response->n_bins; ++b) dst[b] += sink.hist[b];
         } else if (response->kind == THEIA_RESPONSE_RECORD) {

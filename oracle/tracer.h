@@ -23,15 +23,54 @@ struct Sink {
     uint64_t nSegments = 0;  // trace() executions
     uint32_t curEvent = 0;
     uint32_t seq = 0;  // running number of the path's hits inside the current event (test tags)
+    struct TimeHit { float time; int32_t objectId; uint32_t path, event; };
+    std::vector<TimeHit> times;     // store time response: accepted hits of this chunk in path order
 
+    static bool hasHistogram(uint32_t kind) { return kind == THEIA_RESPONSE_HISTOGRAM || kind == THEIA_RESPONSE_KERNEL_HISTOGRAM; }
     explicit Sink(const theia_trace_launch_t* l) : L(l) {
-        if (l->response.kind == THEIA_RESPONSE_HISTOGRAM) hist.assign(l->response.n_bins, 0.0f);
+        if (hasHistogram(l->response.kind)) hist.assign(l->response.n_bins, 0.0f);
     }
-    // sh/response.histogram.glsl:59-68, sh/response.record.glsl:23-26
-    void response(const HitItem& item, uint32_t idx) {
+    static int32_t floatToInt(float f) { return (f >= 2147483648.0f || f < -2147483648.0f || f != f) ? INT32_MIN : (int32_t)f; }
+    // sh/response.histogram.kernel.glsl:62-70: normal CDF after Vazquez-Leal et al. (2011), eq. 4.3
+    static float kernelCdf(float x) {
+        const float c1 = 7.779374467827938f, c2 = 55.5f, c3 = 0.1257926109373887f;
+        return 0.5f + 0.5f * dm_tanh(c1 * x - c2 * dm_atan(c3 * x));
+    }
+    // sh/response.histogram.glsl:59-68, sh/response.record.glsl:23-26, sh/response.histogram.kernel.glsl:72-101,
+    // sh/response.time.store.glsl:14-26
+    void response(const HitItem& item, Rng& rng) {
+        const uint32_t idx = rng.idx;
         nResponse++;
         const theia_response_t& r = L->response;
-        if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
+        if (r.kind == THEIA_RESPONSE_KERNEL_HISTOGRAM) {
+            const float value = item.contrib;  // sh/response.uniform.glsl:4-6
+            float t = item.time - r.hist.t0;
+            int32_t firstBin = floatToInt(std::floor((t - r.kernel_support) / r.hist.binSize));
+            int32_t lastBin = floatToInt(std::ceil((t + r.kernel_support) / r.hist.binSize));
+            firstBin = std::max(firstBin, 0);
+            lastBin = std::min(lastBin, (int32_t)r.n_bins) - 1;
+            t = (float)firstBin * r.hist.binSize + r.hist.t0 - item.time;
+            const float h = 1.0f / r.kernel_bandwidth;
+            float prev_cdf = kernelCdf(t * h);
+            for (int32_t i = firstBin; i <= lastBin; ++i) {
+                t += r.hist.binSize;
+                float cdf = kernelCdf(t * h);
+                float w = cdf - prev_cdf;
+                prev_cdf = cdf;
+                hist[i] += w * value;
+            }
+        } else if (r.kind == THEIA_RESPONSE_STORE_TIME) {
+            float value = item.contrib;
+            if (rng.next() < value) times.push_back(TimeHit{item.time, item.objectId, idx, curEvent | (seq << 16)});
+            seq++;
+        } else if (r.kind == THEIA_RESPONSE_OBJECT_HISTOGRAM) {
+            uint32_t bin = (uint32_t)floatToInt(std::floor((item.time - r.hist.t0) / r.hist.binSize));
+            if (bin < r.n_bins && (uint32_t)item.objectId < r.n_objects) {
+                float* dst = r.object_hist + (size_t)item.objectId * r.n_bins + bin;
+#pragma omp atomic
+                *dst += item.contrib;
+            }
+        } else if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
             float value = item.contrib;  // sh/response.uniform.glsl:4-6
             float fb = std::floor((item.time - r.hist.t0) / r.hist.binSize);
             // uint bin = int(floor(..)); negative values wrap to huge unsigned numbers
@@ -116,7 +155,7 @@ struct VolumeTracer {
         if (code < 0) return;
         ray.lin_contrib *= weight;
         HitItem item = createHit(ray, hit.objPosition, hit.objNormal, P.objectId, hit.worldToObj, pol);
-        if (item.contrib > 0.0f) sink.response(item, rng.idx);
+        if (item.contrib > 0.0f) sink.response(item, rng);
     }
     // :103-114
     static float jacobian_dAdW(vec3 obs, vec3 pos, vec3 nrm) {
@@ -157,7 +196,7 @@ struct VolumeTracer {
         if (hitValid && allowResponse) {
             alignRayToHit(ray, hit.normal, pol);
             HitItem item = createHit(ray, hit.objPosition, hit.objNormal, P.objectId, hit.worldToObj, pol);
-            if (item.contrib > 0.0f) sink.response(item, rng.idx);
+            if (item.contrib > 0.0f) sink.response(item, rng);
             return THEIA_RESULT_RAY_DETECTED;
         } else if (hitValid) {
             return THEIA_RESULT_RAY_ABSORBED;
@@ -215,7 +254,7 @@ struct SceneTracer {
             }
         }
         HitItem item = createHit(ray, hit.objPos, hit.objNrm, hit.customId, hit.worldToObj, pol);
-        if (item.contrib > 0.0f) sink.response(item, rng.idx);
+        if (item.contrib > 0.0f) sink.response(item, rng);
     }
     // :73-154
     int processHit(Ray& ray, const SurfaceHit& hit, Rng& rng, bool allowResponse) {

@@ -36,7 +36,7 @@ class HomogenousModel(material.DispersionFreeMedium, material.HenyeyGreensteinPh
 
 
 def makeResponse(kind: str, *, polarized: bool = False, nBins: int = 100, binSize: float = 5.0, t0: float = 0.0,
-                 capacity: int = 0):
+                 capacity: int = 0, **kw):
     if kind == "record":
         r = response.HitRecorder(polarized=polarized, capacity=capacity)
         r.enableTags()
@@ -45,6 +45,16 @@ def makeResponse(kind: str, *, polarized: bool = False, nBins: int = 100, binSiz
         return response.HistogramHitResponse(response.UniformValueResponse(), nBins=nBins, binSize=binSize, t0=t0)
     if kind == "empty":
         return response.EmptyResponse()
+    if kind == "kernel":
+        return response.KernelHistogramHitResponse(response.UniformValueResponse(), nBins=nBins, binSize=binSize, t0=t0,
+                                                   kernelBandwidth=0.8 * binSize, kernelSupport=2.5 * binSize)
+    if kind == "time":
+        r = response.StoreTimeHitResponse(response.UniformValueResponse(), capacity=capacity)
+        r.enableTags()
+        return r
+    if kind == "objhist":
+        return response.ObjectHistogramHitResponse(response.UniformValueResponse(), nObjects=kw["nObjects"], nBins=nBins,
+                                                   binSize=binSize, t0=t0)
     raise ValueError(kind)
 
 
@@ -141,7 +151,8 @@ def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None,
 def _sceneCommon(N, instances, store, medium, src, wl, resp, callback, polarized, maxPathLength, targetId, guide, key,
                  nBins, binSize, **kw):
     sc = scene.Scene(instances, store, medium=medium)
-    r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize, capacity=kw.pop("respCapacity", 0))
+    r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize, capacity=kw.pop("respCapacity", 0),
+                     nObjects=len(instances))
     rng = random.PhiloxRNG(key=key)
     cb = makeCallback(callback, N, maxPathLength + 1, polarized)
     tr = trace.SceneForwardTracer(N, src, wl, r, rng, sc, maxPathLength=maxPathLength, targetId=targetId,
@@ -259,7 +270,7 @@ def runOracle(cfg, i: int = 0, *, threads: int = 0, oracleScene=None):
             cmd()
     counters = oracle.trace(tr, i, scene=oracleScene, threads=threads, update=False)
     r = cfg["response"]
-    if isinstance(r, response.HistogramHitResponse):
+    if isinstance(r, response.HistogramHitResponse):  # incl. the kernel histogram
         red = r._reducer
         p = red._block("Params", i)
         parts = red.histIn.numpy().reshape(-1, r.nBins)
@@ -275,6 +286,20 @@ def runOracle(cfg, i: int = 0, *, threads: int = 0, oracleScene=None):
 
 FIELDS = ["position", "direction", "normal", "wavelength", "time", "contrib", "objectId"]
 POL_FIELDS = ["stokes", "polarizationRef"]
+
+
+def sortedTimes(cfg, i: int = 0):
+    """Stored (time, objectId) of a StoreTimeHitResponse sorted by (path, event tag)."""
+    r = cfg["response"]
+    v = r.result(i)
+    n = min(v.count, r.capacity)
+    path, tag = r.tags()
+    path, tag = path[:n].astype(np.int64), tag[:n].astype(np.int64)
+    order = np.lexsort((tag, path))
+    out = {"path": path[order], "tag": tag[order], "count": v.count, "time": np.array(v["time"][:n])[order]}
+    if r.storeObjectId:
+        out["objectId"] = np.array(v["objectId"][:n])[order]
+    return out
 
 
 def sortedHits(cfg, i: int = 0):

@@ -132,6 +132,19 @@ def test_deterministic_pow_accuracy(orc):
     assert rel.max() < 1e-6
 
 
+def test_deterministic_tanh_atan_accuracy(orc):
+    # the kernel CDF of sh/response.histogram.kernel.glsl:62-70 is built from these two
+    rng = np.random.default_rng(5)
+    x = rng.uniform(-30.0, 30.0, 1 << 16).astype(np.float32)
+    assert np.abs(orc.mathEval("tanh", x).astype(np.float64) - np.tanh(x.astype(np.float64))).max() < 2.5e-7
+    t = np.tan(rng.uniform(-1.57, 1.57, 1 << 16)).astype(np.float32)
+    got, want = orc.mathEval("atan", t).astype(np.float64), np.arctan(t.astype(np.float64))
+    assert (np.abs(got - want) / np.maximum(np.abs(want), 1e-30)).max() < 4e-7
+    assert orc.mathEval("tanh", np.array([0.0, 50.0, -50.0], np.float32)).tolist() == [0.0, 1.0, -1.0]
+    assert orc.mathEval("atan", np.array([0.0], np.float32))[0] == 0.0
+    assert orc.mathEval("atan", np.array([np.inf], np.float32))[0] == np.float32(np.pi / 2)
+
+
 def test_math_special_values(orc):
     assert orc.mathEval("exp", np.array([0.0], np.float32))[0] == 1.0
     assert orc.mathEval("log", np.array([1.0], np.float32))[0] == 0.0

@@ -4,7 +4,7 @@ from __future__ import annotations
 
 from ctypes import POINTER, Structure, c_float, c_int32, c_uint32, c_uint64, c_void_p
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # component kinds
 LIGHT_SPHERICAL, LIGHT_CONE, LIGHT_PENCIL, LIGHT_CASCADE, LIGHT_MUON, LIGHT_HOST = 1, 2, 3, 4, 5, 6
@@ -13,6 +13,7 @@ WAVELENGTH_CONST, WAVELENGTH_UNIFORM, WAVELENGTH_HOST = 1, 2, 3
 TARGET_NONE, TARGET_SPHERE, TARGET_INNER_SPHERE, TARGET_FLAT, TARGET_DISK = 0, 1, 2, 3, 4
 GUIDE_NONE, GUIDE_SPHERE, GUIDE_FLAT, GUIDE_DISK = 0, 1, 2, 3
 RESPONSE_EMPTY, RESPONSE_RECORD, RESPONSE_HISTOGRAM = 0, 1, 2
+RESPONSE_STORE_TIME, RESPONSE_KERNEL_HISTOGRAM, RESPONSE_OBJECT_HISTOGRAM = 3, 4, 5
 VALUE_UNIFORM = 1
 CALLBACK_EMPTY, CALLBACK_STAT, CALLBACK_TRACK = 0, 1, 2
 TRACER_VOLUME_FORWARD, TRACER_SCENE_FORWARD = 1, 2
@@ -56,6 +57,14 @@ class Response(Structure):
         ("queue_polarized", c_uint32),
         ("tag_path", c_void_p),
         ("tag_event", c_void_p),
+        ("kernel_bandwidth", c_float),
+        ("kernel_support", c_float),
+        ("value_queue", c_void_p),
+        ("value_capacity", c_uint32),
+        ("store_object_id", c_uint32),
+        ("object_hist", c_void_p),
+        ("n_objects", c_uint32),
+        ("_pad1", c_uint32),
     ]
 
 

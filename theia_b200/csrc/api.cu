@@ -112,7 +112,9 @@ __global__ void mathEvalKernel(uint32_t fn, const float* x, const float* y, uint
     case 1: dm_sincos(x[i], &s, &c); out[i] = c; break;
     case 2: out[i] = dm_exp(x[i]); break;
     case 3: out[i] = dm_log(x[i]); break;
-    default: out[i] = dm_pow(x[i], y[i]); break;
+    case 4: out[i] = dm_pow(x[i], y[i]); break;
+    case 5: out[i] = dm_tanh(x[i]); break;
+    default: out[i] = dm_atan(x[i]); break;
     }
 }
 // sh/estimator.reduce.glsl:17-35: per bin Kahan sum over the partial histograms (precise)
@@ -151,11 +153,11 @@ __global__ void histReduceKernel(float* partials, uint32_t nHist, uint32_t nBins
 __global__ void __launch_bounds__(128) hitReplayKernel(const uint32_t* queue, uint32_t capacity, uint32_t polarized,
                                                        ResponseDev r) {
     extern __shared__ float sharedHist[];
-    if (r.kind == THEIA_RESPONSE_HISTOGRAM && r.hist_shared)
+    if (responseHasHistogram(r.kind) && r.hist_shared)
         for (uint32_t b = threadIdx.x; b < r.n_bins; b += blockDim.x) sharedHist[b] = 0.0f;
     __syncthreads();
     float* hist = nullptr;
-    if (r.kind == THEIA_RESPONSE_HISTOGRAM)
+    if (responseHasHistogram(r.kind))
         hist = r.hist_shared ? sharedHist : r.hist_partials + (size_t)(blockIdx.x % r.hist_capacity) * r.n_bins;
     uint32_t count = min(queue[0], capacity);
     uint32_t nResp = 0;
@@ -166,10 +168,10 @@ __global__ void __launch_bounds__(128) hitReplayKernel(const uint32_t* queue, ui
         HitItem item;
         item.contrib = 0.0f; item.time = 0.0f;
         if (has) item = loadHit(queue, capacity, polarized != 0, k);
-        commitHit(r, hist, has, item, k, 0u, nResp);
+        commitHit(r, hist, has, item, k, 0u, nResp, 2.0f);
     }
     __syncthreads();
-    if (r.kind == THEIA_RESPONSE_HISTOGRAM && r.hist_shared) {
+    if (responseHasHistogram(r.kind) && r.hist_shared) {
         const bool exclusive = gridDim.x <= r.hist_capacity;
         float* dst = r.hist_partials + (size_t)(blockIdx.x % r.hist_capacity) * r.n_bins;
         for (uint32_t b = threadIdx.x; b < r.n_bins; b += blockDim.x) {
@@ -242,7 +244,21 @@ __global__ void wfQueryConvertKernel(const void* tlas, const float* rays, const 
 static int fillResponse(const theia_response_t& r, ResponseDev& d) {
     memset(&d, 0, sizeof(d));
     d.kind = r.kind;
-    if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
+    if (r.kind == THEIA_RESPONSE_STORE_TIME) {
+        if (r.value_kind != THEIA_VALUE_UNIFORM) { setError("store time response: unsupported value response %u", r.value_kind); return -1; }
+        if (!r.value_queue || r.value_capacity == 0) { setError("store time response: missing queue"); return -1; }
+        d.value_queue = r.value_queue; d.value_capacity = r.value_capacity; d.store_object_id = r.store_object_id;
+        d.tag_path = r.tag_path; d.tag_event = r.tag_event;
+    } else if (r.kind == THEIA_RESPONSE_OBJECT_HISTOGRAM) {
+        if (r.value_kind != THEIA_VALUE_UNIFORM) { setError("object histogram response: unsupported value response %u", r.value_kind); return -1; }
+        if (!r.object_hist || r.n_objects == 0 || r.n_bins == 0) { setError("object histogram response: missing histogram buffer"); return -1; }
+        if ((uint64_t)r.n_objects * r.n_bins > 0xFFFFFFFFull) { setError("object histogram response: more than 2^32 bins"); return -1; }
+        d.t0 = r.hist.t0; d.binSize = r.hist.binSize; d.n_bins = r.n_bins; d.object_hist = r.object_hist; d.n_objects = r.n_objects;
+    } else if (r.kind == THEIA_RESPONSE_HISTOGRAM || r.kind == THEIA_RESPONSE_KERNEL_HISTOGRAM) {
+        if (r.kind == THEIA_RESPONSE_KERNEL_HISTOGRAM) {
+            if (!(r.kernel_bandwidth > 0.0f) || !(r.kernel_support >= 0.0f)) { setError("kernel histogram response: bad kernel parameters"); return -1; }
+            d.kernel_bandwidth = r.kernel_bandwidth; d.kernel_support = r.kernel_support;
+        }
         if (r.value_kind != THEIA_VALUE_UNIFORM) { setError("histogram response: unsupported value response %u", r.value_kind); return -1; }
         if (!r.hist_partials || r.hist_capacity == 0 || r.n_bins == 0) { setError("histogram response: missing partial histogram buffer"); return -1; }
         d.t0 = r.hist.t0; d.binSize = r.hist.binSize; d.n_bins = r.n_bins; d.hist_capacity = r.hist_capacity;
@@ -348,7 +364,7 @@ struct KernelPlan { const void* fn; size_t smem; uint32_t grid; };
 
 static int plan(const theia_trace_launch_t* L, const DeviceLaunch& D, KernelPlan& K) {
     const bool pol = L->polarized != 0;
-    size_t smem = (D.response.kind == THEIA_RESPONSE_HISTOGRAM && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
+    size_t smem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
     if (L->tracer == THEIA_TRACER_VOLUME_FORWARD) {
         K.fn = pol ? (const void*)volumeForwardKernel<true> : (const void*)volumeForwardKernel<false>;
     } else {
@@ -471,7 +487,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
                  (unsigned long long)need);
         return -1;
     }
-    const size_t histSmem = (D.response.kind == THEIA_RESPONSE_HISTOGRAM && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
+    const size_t histSmem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
     const void* genFn = pol ? (const void*)wfGenerateKernel<true> : (const void*)wfGenerateKernel<false>;
     const void* shadeFn = pol ? (const void*)wfShadeKernel<true> : (const void*)wfShadeKernel<false>;
     const void* shadowFn = pol ? (const void*)wfShadeShadowKernel<true> : (const void*)wfShadeShadowKernel<false>;
@@ -626,7 +642,7 @@ int theia_philox_raw(const uint32_t* ctr_dev, const uint32_t* key_dev, uint32_t 
 }
 
 int theia_math_eval(uint32_t fn, const float* x_dev, const float* y_dev, uint32_t n, float* out_dev, void* stream) {
-    if (fn > 4 || !x_dev || !out_dev || (fn == 4 && !y_dev)) { setError("theia_math_eval: bad argument"); return -1; }
+    if (fn > 6 || !x_dev || !out_dev || (fn == 4 && !y_dev)) { setError("theia_math_eval: bad argument"); return -1; }
     if (n == 0) return 0;
     mathEvalKernel<<<blocksFor(n, 256), 256, 0, (cudaStream_t)stream>>>(fn, x_dev, y_dev, n, out_dev);
     countLaunches(1);
@@ -653,10 +669,11 @@ int theia_hit_replay(const uint32_t* queue_dev, uint32_t capacity, uint32_t pola
     if (!queue_dev || !response) { setError("theia_hit_replay: null argument"); return -1; }
     ResponseDev r;
     if (fillResponse(*response, r)) return -1;
+    if (r.kind == THEIA_RESPONSE_STORE_TIME) { setError("theia_hit_replay: the store time response needs a random number stream, which a replay does not have"); return -1; }
     if (capacity == 0) return 0;
-    size_t smem = (r.kind == THEIA_RESPONSE_HISTOGRAM && r.hist_shared) ? (size_t)r.n_bins * 4 : 0;
+    size_t smem = (responseHasHistogram(r.kind) && r.hist_shared) ? (size_t)r.n_bins * 4 : 0;
     uint32_t grid = blocksFor(capacity, 128);
-    if (r.kind == THEIA_RESPONSE_HISTOGRAM && grid > r.hist_capacity) grid = r.hist_capacity;
+    if (responseHasHistogram(r.kind) && grid > r.hist_capacity) grid = r.hist_capacity;
     if (grid > 148 * 8) grid = 148 * 8;
     hitReplayKernel<<<grid, 128, smem, (cudaStream_t)stream>>>(queue_dev, capacity, polarized, r);
     countLaunches(1);
@@ -711,7 +728,7 @@ int theia_trace_grid_size(const theia_trace_launch_t* launch, uint32_t* n_blocks
     if (launch->tracer == THEIA_TRACER_SCENE_FORWARD && launch->workspace) {
         // wavefront: the shading grids are the ones that write partial histograms
         const bool pol = launch->polarized != 0;
-        const size_t smem = (D.response.kind == THEIA_RESPONSE_HISTOGRAM && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
+        const size_t smem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
         uint32_t gShade = 0, gShadow = 0;
         if (persistentGrid(pol ? (const void*)wfShadeKernel<true> : (const void*)wfShadeKernel<false>, smem, &gShade) ||
             persistentGrid(pol ? (const void*)wfShadeShadowKernel<true> : (const void*)wfShadeShadowKernel<false>, smem, &gShadow))

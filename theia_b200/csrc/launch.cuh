@@ -22,7 +22,13 @@ struct ResponseDev {
     uint32_t queue_polarized;
     uint32_t* tag_path;
     uint32_t* tag_event;
+    float kernel_bandwidth, kernel_support;  // kernel histogram
+    uint32_t* value_queue;                   // store time
+    uint32_t value_capacity, store_object_id;
+    float* object_hist;                      // object histogram
+    uint32_t n_objects;
 };
+__host__ __device__ inline bool responseHasHistogram(uint32_t kind) { return kind == THEIA_RESPONSE_HISTOGRAM || kind == THEIA_RESPONSE_KERNEL_HISTOGRAM; }
 struct CallbackDev {
     uint32_t kind;
     uint32_t track_polarized;
@@ -99,10 +105,16 @@ TDEV HitItem loadHit(const uint32_t* queue, uint32_t cap, bool qpol, uint32_t k)
 }
 
 // sh/response.histogram.glsl:59-68: bin = uint(int(floor((t - t0) / binSize)))
+TDEV int32_t floatToInt(float f) {  // GLSL int(): out of range and NaN are undefined there, INT_MIN here
+    return (f >= 2147483648.0f || f < -2147483648.0f || f != f) ? INT32_MIN : (int32_t)f;
+}
 TDEV uint32_t histogramBin(const ResponseDev& r, float time) {
-    float fb = floorf((time - r.t0) / r.binSize);
-    int32_t ib = (fb >= 2147483648.0f || fb < -2147483648.0f || fb != fb) ? INT32_MIN : (int32_t)fb;
-    return (uint32_t)ib;
+    return (uint32_t)floatToInt(floorf((time - r.t0) / r.binSize));
+}
+// sh/response.histogram.kernel.glsl:62-70: normal CDF after Vazquez-Leal et al. (2011), eq. 4.3
+TDEV float kernelCdf(float x) {
+    const float c1 = 7.779374467827938f, c2 = 55.5f, c3 = 0.1257926109373887f;
+    return 0.5f + 0.5f * dm_tanh(c1 * x - c2 * dm_atan(c3 * x));
 }
 
 // Commits one optional hit per lane. MUST be called by all 32 lanes of the warp.
@@ -110,11 +122,78 @@ TDEV uint32_t histogramBin(const ResponseDev& r, float time) {
 //    the shared-memory float atomic (float atomics on shared memory are CAS loops, so
 //    same-bin collisions inside a warp are the expensive case, e.g. the direct-light peak).
 //  - record: one global atomic per warp hands out a contiguous run of queue slots.
-TDEV void commitHit(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
-                    uint32_t& nResponses) {
+//  - kernel histogram: every lane walks the bins its hit touches (plain shared-memory atomics).
+//  - store time: one draw of the path's stream per hit decides whether it is kept; slots like record.
+//  - object histogram: lanes with the same (object, bin) are combined, one global float atomic each.
+// The store-time response consumes one number of the path's stream per hit; it has to be drawn
+// where the reference calls response() (other draws of the path may follow before the warp
+// reaches commitHit): responseDraw() at that point, its value handed to commitHit.
+TDEV float responseDraw(const ResponseDev& r, Rng& rng, bool has, const HitItem& item) {
+    return (r.kind == THEIA_RESPONSE_STORE_TIME && has && item.contrib > 0.0f) ? rng.next() : 2.0f;
+}
+TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
+                        float u);
+// Returns whether the lane's hit reached the response (the call sites number a path's responses
+// inside an event with it: test tags).
+TDEV bool commitHit(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
+                    uint32_t& nResponses, float u) {
     has = has && item.contrib > 0.0f;  // "if (hit.contrib > 0.0) response(hit)" at every call site
     if (has) nResponses++;
-    if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
+    commitHitImpl(r, hist, has, item, path, tag, u);
+    return has;
+}
+TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
+                        float u) {
+    if (r.kind == THEIA_RESPONSE_KERNEL_HISTOGRAM) {  // sh/response.histogram.kernel.glsl:72-101
+        if (!has) return;
+        const float value = item.contrib;  // sh/response.uniform.glsl:4-6
+        float t = item.time - r.t0;
+        int32_t firstBin = floatToInt(floorf((t - r.kernel_support) / r.binSize));
+        int32_t lastBin = floatToInt(ceilf((t + r.kernel_support) / r.binSize));
+        firstBin = max(firstBin, 0);
+        lastBin = min(lastBin, (int32_t)r.n_bins) - 1;
+        t = (float)firstBin * r.binSize + r.t0 - item.time;
+        const float h = 1.0f / r.kernel_bandwidth;
+        float prev_cdf = kernelCdf(t * h);
+        for (int32_t i = firstBin; i <= lastBin; ++i) {
+            t += r.binSize;
+            float cdf = kernelCdf(t * h);
+            float w = cdf - prev_cdf;
+            prev_cdf = cdf;
+            atomicAdd(hist + i, w * value);
+        }
+    } else if (r.kind == THEIA_RESPONSE_STORE_TIME) {  // sh/response.time.store.glsl:14-26
+        bool keep = false;
+        if (has) keep = u < item.contrib;
+        uint32_t act = __ballot_sync(FULL_MASK, keep);
+        if (act == 0) return;
+        uint32_t leader = __ffs(act) - 1;
+        uint32_t base = 0;
+        if (laneId() == leader) base = atomicAdd(r.value_queue, (uint32_t)__popc(act));
+        base = __shfl_sync(FULL_MASK, base, leader);
+        if (!keep) return;
+        uint32_t slot = base + __popc(act & laneMaskLt());
+        if (slot < r.value_capacity) {
+            reinterpret_cast<float*>(r.value_queue + 1)[slot] = item.time;
+            if (r.store_object_id) reinterpret_cast<int32_t*>(r.value_queue + 1)[(size_t)r.value_capacity + slot] = item.objectId;
+            if (r.tag_path) r.tag_path[slot] = path;
+            if (r.tag_event) r.tag_event[slot] = tag;
+        }
+    } else if (r.kind == THEIA_RESPONSE_OBJECT_HISTOGRAM) {
+        uint32_t key = 0;
+        if (has) {
+            uint32_t bin = histogramBin(r, item.time);
+            has = bin < r.n_bins && (uint32_t)item.objectId < r.n_objects;
+            key = (uint32_t)item.objectId * r.n_bins + bin;
+        }
+        uint32_t act = __ballot_sync(FULL_MASK, has);
+        if (act == 0 || !has) return;
+        float value = item.contrib;
+        uint32_t peers = __match_any_sync(act, key);
+        float sum = 0.0f;
+        for (uint32_t m = peers; m; m &= m - 1) sum += __shfl_sync(peers, value, __ffs(m) - 1);
+        if (laneId() == (uint32_t)(__ffs(peers) - 1)) atomicAdd(r.object_hist + key, sum);
+    } else if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
         uint32_t bin = 0;
         if (has) {
             bin = histogramBin(r, item.time);
@@ -208,13 +287,13 @@ TDEV void sinkInit(const DeviceLaunch& P, SinkShared* sh, float* hist) {
     for (uint32_t i = threadIdx.x; i < 16; i += blockDim.x) {
         if (i < 12) sh->stats[i] = 0; else sh->work[i - 12] = 0;
     }
-    if (hist && P.response.kind == THEIA_RESPONSE_HISTOGRAM && P.response.hist_shared)
+    if (hist && responseHasHistogram(P.response.kind) && P.response.hist_shared)
         for (uint32_t b = threadIdx.x; b < P.response.n_bins; b += blockDim.x) hist[b] = 0.0f;
     __syncthreads();
 }
 TDEV float* sinkHist(const DeviceLaunch& P, float* sharedHist) {
     // n_bins too large for shared memory: accumulate straight into this CTA's partial
-    if (P.response.kind != THEIA_RESPONSE_HISTOGRAM) return nullptr;
+    if (!responseHasHistogram(P.response.kind)) return nullptr;
     if (P.response.hist_shared) return sharedHist;
     return P.response.hist_partials + (size_t)(blockIdx.x % P.response.hist_capacity) * P.response.n_bins;
 }
@@ -229,7 +308,7 @@ TDEV void sinkFinish(const DeviceLaunch& P, SinkShared* sh, const float* hist, u
         }
     }
     __syncthreads();
-    if (hist && P.response.kind == THEIA_RESPONSE_HISTOGRAM && P.response.hist_shared) {
+    if (hist && responseHasHistogram(P.response.kind) && P.response.hist_shared) {
         // sh/response.histogram.glsl:35-45: one partial histogram per work group
         const bool exclusive = gridDim.x <= P.response.hist_capacity;
         float* dst = P.response.hist_partials + (size_t)(blockIdx.x % P.response.hist_capacity) * P.response.n_bins;

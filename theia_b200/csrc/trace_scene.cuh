@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(128, 4) sceneForwardKernel(const __grid_consta
                 result = queryResult <= THEIA_ERROR_MAX_VALUE ? queryResult : propResult;
             }
         }
-        commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
+        has = commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
         has = false;
 
@@ -159,6 +159,7 @@ __global__ void __launch_bounds__(128, 4) sceneForwardKernel(const __grid_consta
         const bool interact = alive && result >= 0;
         const bool last = it == PATH_LENGTH;
         bool wantMIS = false;
+        float uResponse = 2.0f;
         if (interact && hit.valid) {
             // processHit (:73-154)
             result = propagateRayToHit<POL>(ray, hit.worldPos, hit.rayNrm, P.propagation);
@@ -173,6 +174,7 @@ __global__ void __launch_bounds__(128, 4) sceneForwardKernel(const __grid_consta
                 if (allowResponse && isTarget && (P.objectId < 0 || hit.customId == P.objectId)) {
                     sceneCreateResponse<POL>(P, ray, hit, surface, isAbs, item);
                     has = true;
+                    uResponse = responseDraw(P.response, rng, true, item);  // before the reflect / transmit draw
                     result = THEIA_RESULT_RAY_DETECTED;
                 }
                 if (isAbs) {
@@ -219,11 +221,11 @@ __global__ void __launch_bounds__(128, 4) sceneForwardKernel(const __grid_consta
             nShadow += 2;
             has = traceShadowRay<POL>(P, sc, ray, dirPhase, phaseSample.dist, wPhase, item);
         }
-        commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
+        has = commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, wantMIS ? responseDraw(P.response, rng, has, item) : uResponse);
         hitSeq += has ? 1u : 0u;
         has = false;
         if (wantMIS) has = traceShadowRay<POL>(P, sc, ray, dirTarget, distTarget, wTarget, item);
-        commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
+        has = commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
         // volume scatter (:386-393)
         if (interact && !hit.valid && !last) scatterRay<POL>(ray, rng.next2());
 

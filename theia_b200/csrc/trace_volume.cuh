@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(128) volumeForwardKernel(const __grid_constant
         onEvent<POL>(P.callback, &sh, created, ray, THEIA_RESULT_RAY_CREATED, k, 0);
         onEvent<POL>(P.callback, &sh, aborted, ray, THEIA_ERROR_TRACE_ABORT, k, 0);
         if (aborted) alive = false;
-        commitHit(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses);
+        has = commitHit(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
 
         // ---- stage 2: trace (:153-208)
@@ -152,12 +152,12 @@ __global__ void __launch_bounds__(128) volumeForwardKernel(const __grid_constant
             float wPhase = pPP * pPP / (pPP * pPP + pTP * pTP);
             has = volumeCreateResponse<POL>(P, ray, phaseHit, dirPhase, wPhase, true, item);
         }
-        commitHit(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses);
+        has = commitHit(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
         // ---- stage 4: MIS, target sample
         has = false;
         if (wantMIS) has = volumeCreateResponse<POL>(P, ray, targetHit, dirTarget, wTarget, true, item);
-        commitHit(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses);
+        has = commitHit(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
 
         // ---- events and path bookkeeping (:254-275)
         onEvent<POL>(P.callback, &sh, alive, ray, result, k, seg + 1);

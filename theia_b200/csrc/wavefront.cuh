@@ -534,13 +534,14 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
             updateRayIS(ray, dist, P.propagation, hit.valid);
             result = queryResult <= THEIA_ERROR_MAX_VALUE ? queryResult : propResult;
         }
-        commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
+        has = commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
         has = false;
 
         const bool interact = active && result >= 0;
         const bool last = it == P.path_length;
         bool wantMIS = false;
+        float uResponse = 2.0f;
         if (interact && hit.valid) {
             // processHit (:73-154)
             result = propagateRayToHit<POL>(ray, hit.worldPos, hit.rayNrm, P.propagation);
@@ -555,6 +556,7 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
                 if (allowResponse && isTarget && (P.objectId < 0 || hit.customId == P.objectId)) {
                     sceneCreateResponse<POL>(P, ray, hit, surface, isAbs, item);
                     has = true;
+                    uResponse = responseDraw(P.response, rng, true, item);  // before the reflect / transmit draw
                     result = THEIA_RESULT_RAY_DETECTED;
                 }
                 if (isAbs) {
@@ -583,7 +585,7 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
             result = THEIA_RESULT_RAY_SCATTERED;
             wantMIS = GUIDE && !last;
         }
-        commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
+        has = commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, uResponse);
 
         // paths that wait for shadow rays are parked in the shadow buffer (warp collective)
         uint32_t js = 0u;
@@ -656,7 +658,7 @@ __global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_const
                     has = processShadowRay<POL>(P, r2, hit, item);
                 }
             }
-            commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses);
+            has = commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
             hitSeq += has ? 1u : 0u;
         }
         if (active) scatterRay<POL>(ray, rng.next2());

@@ -24,7 +24,8 @@ from theia_b200.random import RNG
 
 __all__ = [
     "EmptyResponse", "HistogramHitResponse", "HistogramReducer", "HitItem", "HitRecorder", "HitReplay",
-    "HitResponse", "PolarizedHitItem", "TraceConfig", "UniformValueResponse", "ValueItem", "ValueResponse",
+    "HitResponse", "HitTimeAndIdItem", "HitTimeItem", "KernelHistogramHitResponse", "ObjectHistogramHitResponse",
+    "PolarizedHitItem", "StoreTimeHitResponse", "TraceConfig", "UniformValueResponse", "ValueItem", "ValueResponse",
 ]
 
 
@@ -49,6 +50,18 @@ class PolarizedHitItem(Structure):
 
 class ValueItem(Structure):
     _fields_ = [("value", c_float), ("time", c_float)]
+
+
+class HitTimeItem(Structure):
+    """Item of ``StoreTimeHitResponse`` storing only the time (src/theia/response.py:626-629)"""
+
+    _fields_ = [("time", c_float)]
+
+
+class HitTimeAndIdItem(Structure):
+    """Item of ``StoreTimeHitResponse`` storing time and object id (src/theia/response.py:632-635)"""
+
+    _fields_ = [("time", c_float), ("objectId", c_int32)]
 
 
 @dataclass
@@ -303,7 +316,7 @@ class HistogramHitResponse(HitResponse):
     def __init__(self, response: ValueResponse, *, nBins: int = 100, t0: float = 0.0 * u.ns,
                  binSize: float = 1.0 * u.ns, normalization: float | None = None, retrieve: bool = True,
                  reduceBlockSize: int = 128, updateResponse: bool = True, useSharedMemory: bool = True) -> None:
-        super().__init__({"ResponseParams": self.Params}, {"normalization"}, nRNGSamples=response.nRNGSamples)
+        HitResponse.__init__(self, {"ResponseParams": self.Params}, {"normalization"}, nRNGSamples=response.nRNGSamples)
         if response._kind != _abi.VALUE_UNIFORM:
             raise ValueError("this build offers UniformValueResponse only (user GLSL cannot be honoured)")
         self._response = response
@@ -386,7 +399,7 @@ class HistogramHitResponse(HitResponse):
             self._reducer = self._initReducer()
         p = self._block("ResponseParams", i)
         r = _abi.Response()
-        r.kind = _abi.RESPONSE_HISTOGRAM
+        r.kind = self._kind
         r.value_kind = self.response._kind
         r.hist.t0 = p.t0
         r.hist.binSize = p.binSize
@@ -411,6 +424,237 @@ class HistogramHitResponse(HitResponse):
         if self._reducer is None:
             self._reducer = self._initReducer()
         return self._reducer.run(i)
+
+
+class KernelHistogramHitResponse(HistogramHitResponse):
+    """
+    Histogram in which every hit is smeared by a Gaussian kernel of width ``kernelBandwidth``
+    over the bins within ``kernelSupport`` of its time: a binned kernel density estimate
+    (src/theia/response.py:1424-1673, sh/response.histogram.kernel.glsl). Partial histograms and
+    their reduction work as for ``HistogramHitResponse``.
+    """
+
+    name = "Kernel Histogram Hit Response"
+    _kind = _abi.RESPONSE_KERNEL_HISTOGRAM
+
+    class Params(Structure):
+        _fields_ = [("t0", c_float), ("binSize", c_float), ("kernelBandwidth", c_float), ("kernelSupport", c_float)]
+
+    def __init__(self, response: ValueResponse, *, nBins: int = 100, t0: float = 0.0 * u.ns,
+                 binSize: float = 1.0 * u.ns, kernelBandwidth: float = 1.0 * u.ns, kernelSupport: float = 3.0 * u.ns,
+                 normalization: float | None = None, retrieve: bool = True, reduceBlockSize: int = 128,
+                 updateResponse: bool = True, useSharedMemory: bool = True) -> None:
+        super().__init__(response, nBins=nBins, t0=t0, binSize=binSize, normalization=normalization, retrieve=retrieve,
+                         reduceBlockSize=reduceBlockSize, updateResponse=updateResponse,
+                         useSharedMemory=useSharedMemory)
+        self.setParams(kernelBandwidth=kernelBandwidth, kernelSupport=kernelSupport)
+
+    def _abiResponse(self, i: int, nBlocks: int) -> _abi.Response:
+        r = super()._abiResponse(i, nBlocks)
+        p = self._block("ResponseParams", i)
+        r.kernel_bandwidth = p.kernelBandwidth
+        r.kernel_support = p.kernelSupport
+        return r
+
+
+class StoreTimeHitResponse(HitResponse):
+    """
+    Keeps a hit with the probability its value response assigns to it and stores its arrival time
+    and, optionally, the id of the object it hit (src/theia/response.py:656-797,
+    sh/response.time.store.glsl). Meant for single photon tracing, where the value models the
+    detection probability. Consumes one random number per hit. ``capacity`` = 0 sizes the queue
+    from what the tracer reports. ``result(i)`` is a queue view with ``count``, ``time`` and
+    ``objectId``.
+    """
+
+    name = "Store Time Hit Response"
+    _kind = _abi.RESPONSE_STORE_TIME
+
+    def __init__(self, response: ValueResponse, *, capacity: int = 0, retrieve: bool = True,
+                 storeObjectId: bool = True, updateResponse: bool = True) -> None:
+        super().__init__(nRNGSamples=response.nRNGSamples + 1)
+        if response._kind != _abi.VALUE_UNIFORM:
+            raise ValueError("this build offers UniformValueResponse only (user GLSL cannot be honoured)")
+        self._response = response
+        self._capacity = capacity
+        self._retrieve = retrieve
+        self._storeObjectId = storeObjectId
+        self._updateResponse = updateResponse
+        self._queue = IOQueue(HitTimeAndIdItem if storeObjectId else HitTimeItem, mode="retrieve")
+        if capacity > 0:
+            self._queue.initialize(capacity)
+        self._tags = None
+
+    @property
+    def queue(self) -> IOQueue:
+        """Queue to be filled with the arrival times and optionally the object ids"""
+        return self._queue
+
+    @property
+    def capacity(self) -> int:
+        return self._capacity
+
+    @property
+    def response(self) -> ValueResponse:
+        return self._response
+
+    @property
+    def retrieve(self) -> bool:
+        return self._retrieve
+
+    @property
+    def storeObjectId(self) -> bool:
+        return self._storeObjectId
+
+    def result(self, i: int):
+        """The retrieved i-th queue; None if ``retrieve`` is False or nothing ran yet"""
+        if not self.retrieve or not self.queue.initialized:
+            return None
+        return self.queue.view(i)
+
+    def prepare(self, config: TraceConfig) -> None:
+        self.response.prepare(config)
+        maxHits = config.maxHitsPerThread * config.capacity
+        if self.queue.initialized and maxHits > self.capacity:
+            warn(f"The provided queue's capacity ({self.capacity}) is less than the max hit count reported by "
+                 f"the tracer ({maxHits}). Hits beyond the capacity are counted but not stored.")
+        elif not self.queue.initialized:
+            self._capacity = max(self._capacity, maxHits)
+
+    def enableTags(self) -> None:
+        """B200 extension (test seam): records which path and event produced each stored time."""
+        self._wantTags = True
+
+    def tags(self) -> tuple[NDArray, NDArray]:
+        return self._tags[0].cpu().numpy(), self._tags[1].cpu().numpy()
+
+    def _ensure(self) -> None:
+        if not self.queue.initialized:
+            if self.capacity <= 0:
+                raise RuntimeError(f"Cannot create a queue of size {self.capacity}")
+            self.queue.initialize(self.capacity)
+        if getattr(self, "_wantTags", False) and self._tags is None:
+            self._tags = [torch.zeros(self.capacity, dtype=torch.int32, device=self._device) for _ in range(2)]
+
+    def _abiResponse(self, i: int, nBlocks: int) -> _abi.Response:
+        self._ensure()
+        r = _abi.Response()
+        r.kind = _abi.RESPONSE_STORE_TIME
+        r.value_kind = self.response._kind
+        r.value_queue = self.queue.tensor.data_ptr()
+        r.value_capacity = self.capacity
+        r.store_object_id = int(self._storeObjectId)
+        if self._tags is not None:
+            r.tag_path = self._tags[0].data_ptr()
+            r.tag_event = self._tags[1].data_ptr()
+        return r
+
+    def update(self, i: int) -> None:
+        super().update(i)
+        if self._updateResponse:
+            self.response.update(i)
+
+    def run(self, i: int) -> list[Command]:
+        self._ensure()
+        return self.queue.run(i) if self.retrieve else []
+
+
+class ObjectHistogramHitResponse(HitResponse):
+    """
+    B200 extension: one time histogram per detector object, ``result(i)[objectId, bin]`` - the
+    per module light curves of a detector array (config C5), which the reference can only
+    obtain from ``HitRecorder`` plus binning on the host. Hits whose ``objectId`` lies outside
+    ``[0, nObjects)`` or whose time lies outside the histogram are dropped. Binning and value are
+    those of ``HistogramHitResponse`` (sh/response.histogram.glsl:59-68, sh/response.uniform.glsl);
+    lanes of a warp that hit the same (object, bin) are combined and issue one float atomic on
+    the ``[nObjects, nBins]`` array in HBM.
+    """
+
+    name = "Object Histogram Hit Response"
+    _kind = _abi.RESPONSE_OBJECT_HISTOGRAM
+
+    class Params(Structure):
+        _fields_ = [("t0", c_float), ("binSize", c_float)]
+
+    def __init__(self, response: ValueResponse, *, nObjects: int, nBins: int = 100, t0: float = 0.0 * u.ns,
+                 binSize: float = 1.0 * u.ns, normalization: float | None = None, retrieve: bool = True,
+                 updateResponse: bool = True) -> None:
+        super().__init__({"ResponseParams": self.Params}, {"normalization"}, nRNGSamples=response.nRNGSamples)
+        if response._kind != _abi.VALUE_UNIFORM:
+            raise ValueError("this build offers UniformValueResponse only (user GLSL cannot be honoured)")
+        if nObjects <= 0 or nBins <= 0:
+            raise ValueError("nObjects and nBins must be positive")
+        self._response = response
+        self._nObjects = nObjects
+        self._nBins = nBins
+        self.normalization = normalization
+        self._requestedNorm = 1.0
+        self._retrieve = retrieve
+        self._updateResponse = updateResponse
+        self.setParams(t0=t0, binSize=binSize)
+        n = nObjects * nBins
+        self._hist = _device.alloc(4 * n, self._device).view(torch.float32)[:n]
+        self._buffers = [_device.allocPinned(4 * n).view(torch.float32)[:n] for _ in range(2)] if retrieve else None
+
+    @property
+    def nObjects(self) -> int:
+        return self._nObjects
+
+    @property
+    def nBins(self) -> int:
+        return self._nBins
+
+    @property
+    def response(self) -> ValueResponse:
+        return self._response
+
+    @property
+    def retrieve(self) -> bool:
+        return self._retrieve
+
+    @property
+    def tensor(self) -> torch.Tensor:
+        """Device array ``[nObjects * nBins]`` the tracer accumulates into (un-normalised)"""
+        return self._hist
+
+    def result(self, i: int) -> NDArray | None:
+        if self._buffers is None:
+            return None
+        return self._buffers[i].numpy().reshape(self._nObjects, self._nBins)
+
+    def prepare(self, config: TraceConfig) -> None:
+        self.response.prepare(config)
+        self._requestedNorm = config.normalization
+
+    def updateConfig(self, config: TraceConfig) -> None:
+        self._requestedNorm = config.normalization
+
+    def _abiResponse(self, i: int, nBlocks: int) -> _abi.Response:
+        p = self._block("ResponseParams", i)
+        r = _abi.Response()
+        r.kind = _abi.RESPONSE_OBJECT_HISTOGRAM
+        r.value_kind = self.response._kind
+        r.hist.t0 = p.t0
+        r.hist.binSize = p.binSize
+        r.n_bins = self._nBins
+        r.object_hist = self._hist.data_ptr()
+        r.n_objects = self._nObjects
+        return r
+
+    def update(self, i: int) -> None:
+        super().update(i)
+        if self._updateResponse:
+            self.response.update(i)
+
+    def run(self, i: int) -> list[Command]:
+        def cmd() -> None:
+            norm = self.normalization if self.normalization is not None else self._requestedNorm
+            if self._buffers is not None:
+                if norm != 1.0:
+                    self._hist.mul_(norm)
+                self._buffers[i].copy_(self._hist, non_blocking=True)
+            self._hist.zero_()
+        return [cmd]
 
 
 def _maxGridBlocks() -> int:
