@@ -245,7 +245,11 @@ enum { THEIA_RESPONSE_EMPTY = 0, THEIA_RESPONSE_RECORD = 1, THEIA_RESPONSE_HISTO
        THEIA_RESPONSE_OBJECT_HISTOGRAM = 5  /* B200 extension: one time histogram per objectId */ };
 enum { THEIA_VALUE_UNIFORM = 1 };
 enum { THEIA_CALLBACK_EMPTY = 0, THEIA_CALLBACK_STAT = 1, THEIA_CALLBACK_TRACK = 2 };
-enum { THEIA_TRACER_VOLUME_FORWARD = 1, THEIA_TRACER_SCENE_FORWARD = 2 };
+enum { THEIA_TRACER_VOLUME_FORWARD = 1, THEIA_TRACER_SCENE_FORWARD = 2,
+       /* single photon tracers with absorption roulette: src/theia/trace.py:2657-2959 and 2370-2654,
+        * sh/tracer.volume.photon.*.glsl, sh/tracer.scene.photon.*.glsl. They take the TraceParams
+        * block of the matching forward tracer. */
+       THEIA_TRACER_VOLUME_PHOTON = 3, THEIA_TRACER_SCENE_PHOTON = 4 };
 
 /* A component = kind + flags + host pointer to its byte-identical parameter block. */
 typedef struct theia_component {
@@ -347,6 +351,12 @@ typedef struct theia_trace_launch {
      * which is meant for small batches. Contents need not be preserved between launches. */
     void *workspace;
     uint64_t workspace_bytes;
+    /* Photon tracers: path_length = nRuns * run_length scattering events in total. The reference
+     * dispatches one shader per run of run_length events and restarts the draw counter of run r
+     * at r * rng_per_run (Push.dim, src/theia/trace.py:2645-2650, 2946-2950); here a path simply
+     * continues and only its draw counter is set to that value at every run boundary. */
+    uint32_t run_length;  /* nScatteringPerRun (PATH_LENGTH of the photon shaders) */
+    uint32_t rng_per_run; /* _nRNGPerRun */
 } theia_trace_launch_t;
 
 /* ------------------------------------------------------------------ library */

@@ -137,7 +137,7 @@ def trace(tracer, i: int = 0, *, scene: OracleScene | None = None, threads: int 
         for _, stage in tracer.collectStages():
             stage.update(i)
     L, keep = tracer._launch(i)
-    if L.tracer == _abi.TRACER_SCENE_FORWARD:
+    if L.tracer in (_abi.TRACER_SCENE_FORWARD, _abi.TRACER_SCENE_PHOTON):
         if scene is None:
             scene = OracleScene(tracer.scene)
         L.tlas = scene.handle

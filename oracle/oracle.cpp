@@ -170,6 +170,8 @@ static HitItem loadHit(const uint32_t* queue, uint32_t cap, bool qpol, uint32_t 
 // counters[0] = segments (trace() executions), [1] = responses, [2..5] traversal statistics
 int orc_trace_forward(const theia_trace_launch_t* L, int nThreads, uint64_t* counters) {
     if (L->struct_size != sizeof(theia_trace_launch_t)) return -1;
+    if ((L->tracer == THEIA_TRACER_VOLUME_PHOTON || L->tracer == THEIA_TRACER_SCENE_PHOTON) &&
+        (L->run_length == 0 || L->path_length % L->run_length != 0)) return -4;
     const uint32_t bs = L->block_size ? L->block_size : 128;
     const uint32_t nChunks = (L->batch_size + bs - 1) / bs;
     const bool pol = L->polarized != 0;
@@ -189,13 +191,15 @@ int orc_trace_forward(const theia_trace_launch_t* L, int nThreads, uint64_t* cou
             Sink sink(L);
             uint32_t lo = (uint32_t)c * bs, hi = lo + bs;
             if (hi > L->batch_size) hi = L->batch_size;
-            if (L->tracer == THEIA_TRACER_VOLUME_FORWARD) {
+            if (L->tracer == THEIA_TRACER_VOLUME_FORWARD || L->tracer == THEIA_TRACER_VOLUME_PHOTON) {
                 VolumeTracer t{*L, *(const theia_volume_trace_params_t*)L->trace_params, sink, pol};
-                for (uint32_t k = lo; k < hi; ++k) t.traceMain(L->first_path + k);
+                if (L->tracer == THEIA_TRACER_VOLUME_FORWARD) for (uint32_t k = lo; k < hi; ++k) t.traceMain(L->first_path + k);
+                else for (uint32_t k = lo; k < hi; ++k) t.tracePhoton(L->first_path + k);
             } else {
                 SceneTracer t{*L, *(const theia_scene_trace_params_t*)L->trace_params, *(const Scene*)L->tlas,
                               sink, pol, counters ? ttrav : nullptr};
-                for (uint32_t k = lo; k < hi; ++k) t.traceMain(L->first_path + k);
+                if (L->tracer == THEIA_TRACER_SCENE_FORWARD) for (uint32_t k = lo; k < hi; ++k) t.traceMain(L->first_path + k);
+                else for (uint32_t k = lo; k < hi; ++k) t.tracePhoton(L->first_path + k);
             }
             if (Sink::hasHistogram(R.kind)) {
                 float* dst = R.hist_partials + (size_t)((uint32_t)c % R.hist_capacity) * R.n_bins;

@@ -88,6 +88,8 @@ struct SourceRay {  // sh/lightsource.common.glsl:12-26
 struct WavelengthSample { float wavelength, contrib; };  // sh/wavelengthsource.common.glsl:4-7
 
 // sh/ray.glsl:136-143
+// sh/ray.glsl:131-133
+static inline float getContrib(const Ray& r) { return r.lin_contrib * dm_exp(r.log_contrib); }
 static inline bool isRayBad(const Ray& r) {
     vec3 p = r.position, d = r.direction;
     return isnan_(p.x) || isnan_(p.y) || isnan_(p.z) || isinf_(p.x) || isinf_(p.y) || isinf_(p.z) ||

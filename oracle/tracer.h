@@ -140,6 +140,19 @@ static inline Ray sampleRay(const theia_trace_launch_t& L, uint64_t medium, Rng&
     return createRay(lightRay, medium, constants, photon);
 }
 
+// sh/tracer.scene.photon.init.glsl:90-106, sh/tracer.volume.photon.common.glsl:88-104
+static inline int photonRoulette(Ray& ray, Rng& rng, int result, bool pol) {
+    if (result < 0) return result;
+    if (pol) {
+        ray.lin_contrib *= ray.stokes.x;
+        ray.stokes = ray.stokes / ray.stokes.x;
+    }
+    if (getContrib(ray) <= rng.next()) return THEIA_RESULT_RAY_ABSORBED;
+    ray.lin_contrib = 1.0f;
+    ray.log_contrib = 0.0f;
+    return result;
+}
+
 // =================================================================== volume tracer
 struct VolumeTracer {
     const theia_trace_launch_t& L;
@@ -230,6 +243,46 @@ struct VolumeTracer {
             if (res < 0) return;
         }
         sink.onEvent(ray, THEIA_RESULT_MAX_ITER, idx, L.path_length + 2, pol);
+    }
+    // VolumePhotonTracer: sh/tracer.volume.photon.common.glsl:32-76
+    int tracePhotonStep(Ray& ray, Rng& rng) {
+        float u = rng.next();
+        float dist = sampleScatterLength(ray, P.propagation, u);
+        TargetSample hit = intersectTarget(L.target, ray.position, ray.direction);
+        bool hitValid = hit.valid && (hit.dist <= dist);
+        dist = min_(hit.dist, dist);
+        int result = propagateRay(ray, dist, P.propagation);
+        updateRayIS(ray, dist, P.propagation, hitValid);
+        if (result < 0) return result;
+        if (hitValid) {
+            alignRayToHit(ray, hit.normal, pol);
+            HitItem item = createHit(ray, hit.objPosition, hit.objNormal, P.objectId, hit.worldToObj, pol);
+            if (item.contrib > 0.0f) sink.response(item, rng);
+            return THEIA_RESULT_RAY_ABSORBED;
+        }
+        return THEIA_RESULT_RAY_SCATTERED;
+    }
+    // sh/tracer.volume.photon.init.glsl:30-62, traceLoop of sh/tracer.volume.photon.common.glsl:78-123 over
+    // all runs of sh/tracer.volume.photon.loop.glsl:20-31 (run r starts its draw counter at r * rng_per_run)
+    void tracePhoton(uint32_t idx) {
+        Rng rng{&L.rng, idx, 0};
+        Ray ray = sampleRay(L, P.medium, rng);
+        ray.lin_contrib = 1.0f;
+        ray.log_contrib = 0.0f;
+        sink.onEvent(ray, THEIA_RESULT_RAY_CREATED, idx, 0, pol);
+        if (isOccludedByTarget(L.target, ray.position)) {
+            sink.onEvent(ray, THEIA_ERROR_TRACE_ABORT, idx, 0, pol);
+            return;
+        }
+        for (uint32_t i = 1; i <= L.path_length; ++i) {
+            int result = tracePhotonStep(ray, rng);
+            scatterRay(ray, rng.next2(), pol);
+            result = photonRoulette(ray, rng, result, pol);
+            sink.onEvent(ray, result, idx, i, pol);
+            if (result < 0) return;
+            if (i < L.path_length && i % L.run_length == 0) rng.dim = (i / L.run_length) * L.rng_per_run;
+        }
+        sink.onEvent(ray, THEIA_RESULT_MAX_ITER, idx, L.path_length + 1, pol);
     }
 };
 
@@ -382,6 +435,26 @@ struct SceneTracer {
             if (result < 0) return;
             if (L.guide.kind != THEIA_GUIDE_NONE) allowResponse = result != THEIA_RESULT_RAY_SCATTERED;
             else allowResponse = true;
+        }
+        sink.onEvent(ray, THEIA_RESULT_MAX_ITER, idx, L.path_length + 1, pol);
+    }
+    // ScenePhotonTracer: sh/tracer.scene.photon.init.glsl:43-114 followed by the runs of
+    // sh/tracer.scene.photon.loop.glsl:38-99 (run r starts its draw counter at r * rng_per_run;
+    // what the queue between two runs carries is exactly the ray as it stands)
+    void tracePhoton(uint32_t idx) {
+        Rng rng{&L.rng, idx, 0};
+        Ray ray = sampleRay(L, P.sourceMedium, rng);
+        ray.lin_contrib = 1.0f;
+        ray.log_contrib = 0.0f;
+        sink.onEvent(ray, THEIA_RESULT_RAY_CREATED, idx, 0, pol);
+        for (uint32_t i = 1; i <= L.path_length; ++i) {
+            SurfaceHit hit;
+            int result = trace(ray, hit, rng, true);
+            if (result >= 0) result = processInteraction(ray, hit, rng, true, false);
+            result = photonRoulette(ray, rng, result, pol);
+            sink.onEvent(ray, result, idx, i, pol);
+            if (result < 0) return;
+            if (i < L.path_length && i % L.run_length == 0) rng.dim = (i / L.run_length) * L.rng_per_run;
         }
         sink.onEvent(ray, THEIA_RESULT_MAX_ITER, idx, L.path_length + 1, pol);
     }

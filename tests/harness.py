@@ -110,7 +110,7 @@ def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None,
                    polarized: bool = False, lightKind: str = "spherical", targetKind: str = "sphere",
                    wavelength: str = "const", water: bool = False, nScattering: int = 10, key: int = 42,
                    scatterCoefficient: float = 0.05, nBins: int = 100, binSize: float = 5.0, maxTime: float = 1000.0,
-                   respCapacity: int = 0):
+                   respCapacity: int = 0, photon=None):
     """Config C1 (examples/01 of the reference) and its flag variations (tests/test_trace.py:90-212)."""
     model = WaterTestModel() if water else HomogenousModel()
     med = model.createMedium()
@@ -140,10 +140,15 @@ def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None,
             wl = light.StreamingHostWavelengthSource(N, data=photons)
     r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize, capacity=respCapacity)
     rng = random.PhiloxRNG(key=key)
-    cb = makeCallback(callback, N, nScattering + 2, polarized)
-    tr = trace.VolumeForwardTracer(N, src, tgt, wl, r, rng, medium=store.media[med.name], nScattering=nScattering,
-                                   scatterCoefficient=scatterCoefficient, callback=cb, polarized=polarized,
-                                   disableDirectLighting=not direct, disableTargetSampling=not mis, maxTime=maxTime)
+    cb = makeCallback(callback, N, (photon[0] * photon[1] if photon else nScattering) + 2, polarized)
+    if photon:
+        # VolumePhotonTracer (examples of the reference's tests/test_trace.py:1605-1690): runs x events per run
+        tr = trace.VolumePhotonTracer(N, src, tgt, wl, r, rng, medium=store.media[med.name], nScatteringPerRun=photon[1],
+                                      nRuns=photon[0], callback=cb, polarized=polarized, maxTime=maxTime)
+    else:
+        tr = trace.VolumeForwardTracer(N, src, tgt, wl, r, rng, medium=store.media[med.name], nScattering=nScattering,
+                                       scatterCoefficient=scatterCoefficient, callback=cb, polarized=polarized,
+                                       disableDirectLighting=not direct, disableTargetSampling=not mis, maxTime=maxTime)
     rng.autoAdvance = tr.nRNGSamples
     return {"tracer": tr, "response": r, "callback": cb, "rng": rng, "store": store}
 
@@ -154,6 +159,13 @@ def _sceneCommon(N, instances, store, medium, src, wl, resp, callback, polarized
     r = makeResponse(resp, polarized=polarized, nBins=nBins, binSize=binSize, capacity=kw.pop("respCapacity", 0),
                      nObjects=len(instances))
     rng = random.PhiloxRNG(key=key)
+    photon = kw.pop("photon", None)
+    if photon:  # ScenePhotonTracer: (nRuns, nScatteringPerRun)
+        cb = makeCallback(callback, N, photon[0] * photon[1] + 1, polarized)
+        tr = trace.ScenePhotonTracer(N, src, wl, r, rng, sc, nRuns=photon[0], nScatteringPerRun=photon[1],
+                                     targetId=targetId, callback=cb, polarized=polarized, **kw)
+        rng.autoAdvance = tr.nRNGSamples
+        return {"tracer": tr, "response": r, "callback": cb, "rng": rng, "store": store, "scene": sc}
     cb = makeCallback(callback, N, maxPathLength + 1, polarized)
     tr = trace.SceneForwardTracer(N, src, wl, r, rng, sc, maxPathLength=maxPathLength, targetId=targetId,
                                   targetGuide=guide, callback=cb, polarized=polarized, **kw)

@@ -126,3 +126,26 @@ def test_plane_target_solid_angle(device, shape):
     tol = 4.0 * np.sqrt((1.0 - expected) / (expected * N)) + 3e-4
     print(f"{shape}: {total:.6f} vs {expected:.6f}")
     assert abs(total / expected - 1.0) < tol
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("builder,kw,budget", [(H.volumeScenario, dict(mis=False), 1e5),
+                                               (H.sceneC2, dict(lightKind="cone", polarized=False), 1e3),
+                                               (H.sceneC2, dict(lightKind="cone", polarized=True), 1e3)],
+                         ids=["volume", "c2", "c2-polarized"])
+def test_photon_tracer_estimates_the_forward_tracers_yield(device, builder, kw, budget):
+    # VolumePhotonTracer / ScenePhotonTracer (sh/tracer.*.photon.*.glsl): absorption roulette instead of
+    # weights. Summed over hits, both estimate the same detected fraction of the emitted light.
+    N = 1 << 17 if device == "cuda" else 1 << 16
+    with _device.useDevice(device):
+        fwd = builder(N, resp="record", **kw)
+        H.runAny(fwd)
+        a = H.hitView(fwd)["contrib"].astype(np.float64) / budget
+        pho = builder(N, resp="record", photon=(3, 4), **kw)
+        H.runAny(pho)
+        b = H.hitView(pho)["contrib"].astype(np.float64)
+    assert len(b) > 200 and b.max() <= 1.0 and b.min() > 0.0
+    ya, yb = a.sum() / N, b.sum() / N
+    err = np.sqrt((np.square(a).sum() + np.square(b).sum())) / N
+    print(f"forward {ya:.5f} photon {yb:.5f} +- {err:.5f}")
+    assert abs(ya - yb) < 4.5 * err

@@ -327,6 +327,61 @@ def test_object_histogram_matches_recorded_hits(cuda, orc):
     assert np.count_nonzero(hist.sum(1)) > 16  # many modules saw light
 
 
+PHOTON_CASES = [
+    (H.volumeScenario, dict(photon=(3, 4))),
+    (H.volumeScenario, dict(photon=(2, 5), polarized=True, water=True, lightKind="cone")),
+    (H.volumeScenario, dict(photon=(1, 12), targetKind="inner", wavelength="uniform", water=True)),
+    (H.sceneC2, dict(photon=(3, 4), lightKind="cone", mode="single")),
+    (H.sceneC2, dict(photon=(3, 4), lightKind="cone", mode="wavefront")),
+    (H.sceneC2, dict(photon=(2, 3), lightKind="cone", polarized=False, mode="wavefront", useRefractedHitDir=True)),
+    (H.sceneC3, dict(photon=(4, 3), guide=False, mode="single")),
+    (H.sceneC3, dict(photon=(4, 3), guide=False, mode="wavefront")),
+]
+
+
+@pytest.mark.parametrize("resp", ["record", "time"])
+@pytest.mark.parametrize("builder,kw", PHOTON_CASES, ids=lambda v: getattr(v, "__name__", None) or ",".join(
+    f"{a}={b}" for a, b in v.items()))
+def test_photon_tracers_bit_exact(cuda, orc, builder, kw, resp):
+    # VolumePhotonTracer / ScenePhotonTracer incl. the draw counter restart at every run boundary;
+    # with the store-time response the stored photons are the detected ones
+    N = 1 << 15
+    g, c = both(builder, N, resp=resp, **kw)
+    H.runGpu(g)
+    H.runOracle(c)
+    if resp == "record":
+        a, b = H.sortedHits(g), H.sortedHits(c)
+        assert b["count"] > 20
+        H.compareHits(a, b)
+    else:
+        a, b = H.sortedTimes(g), H.sortedTimes(c)
+        assert b["count"] > 20 and a["count"] == b["count"]
+        for f in ("path", "tag", "time", "objectId"):
+            assert np.array_equal(a[f], b[f]), f
+
+
+@pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict(photon=(2, 3), polarized=True, water=True)),
+                                        (H.sceneC2, dict(photon=(2, 3), lightKind="cone", mode="wavefront")),
+                                        (H.sceneC2, dict(photon=(2, 3), lightKind="cone", mode="single"))],
+                         ids=["volume", "c2-wavefront", "c2-single"])
+def test_photon_tracers_events_match(cuda, orc, builder, kw):
+    N = 1 << 12
+    for cb in ("stat", "track"):
+        g, c = both(builder, N, resp="empty", callback=cb, **kw)
+        H.runGpu(g)
+        H.runOracle(c)
+        if cb == "stat":
+            got, want = g["callback"]._read(), c["callback"]._read()
+            assert np.array_equal(got, want), f"{got} != {want}"
+            assert got[0] == N
+        else:
+            (ta, la, ca), (tb, lb, cbb) = g["callback"].result(0), c["callback"].result(0)
+            assert np.array_equal(la, lb) and np.array_equal(ca, cbb)
+            for k in range(N):
+                n = min(int(la[k]) + 1, ta.shape[1])
+                assert np.array_equal(ta[k, :n].view(np.uint32), tb[k, :n].view(np.uint32)), f"track {k}"
+
+
 def test_sharded_run_single_rank_matches_oracle(cuda, orc):
     from theia_b200 import distributed
     N, nBatches = 8192, 3

@@ -16,7 +16,7 @@ RESPONSE_EMPTY, RESPONSE_RECORD, RESPONSE_HISTOGRAM = 0, 1, 2
 RESPONSE_STORE_TIME, RESPONSE_KERNEL_HISTOGRAM, RESPONSE_OBJECT_HISTOGRAM = 3, 4, 5
 VALUE_UNIFORM = 1
 CALLBACK_EMPTY, CALLBACK_STAT, CALLBACK_TRACK = 0, 1, 2
-TRACER_VOLUME_FORWARD, TRACER_SCENE_FORWARD = 1, 2
+TRACER_VOLUME_FORWARD, TRACER_SCENE_FORWARD, TRACER_VOLUME_PHOTON, TRACER_SCENE_PHOTON = 1, 2, 3, 4
 
 
 class PhiloxParams(Structure):
@@ -108,6 +108,8 @@ class TraceLaunch(Structure):
         ("work_counters", c_void_p),
         ("workspace", c_void_p),
         ("workspace_bytes", c_uint64),
+        ("run_length", c_uint32),
+        ("rng_per_run", c_uint32),
     ]
 
 

@@ -293,7 +293,13 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
     D.hit_use_transmitted_dir = L->hit_use_transmitted_dir; D.path_length = L->path_length;
     D.batch_size = L->batch_size; D.first_path = L->first_path;
     D.rng = L->rng;
-    if (L->tracer == THEIA_TRACER_VOLUME_FORWARD) {
+    const bool photon = L->tracer == THEIA_TRACER_VOLUME_PHOTON || L->tracer == THEIA_TRACER_SCENE_PHOTON;
+    if (photon) {
+        if (L->run_length == 0 || L->path_length == 0 || L->path_length % L->run_length != 0) { setError("photon tracer: path_length must be a positive multiple of run_length"); return -1; }
+        if (L->guide.kind != THEIA_GUIDE_NONE) { setError("photon tracer: target guides are not used by the photon tracers"); return -1; }
+        D.photon = 1u; D.run_length = L->run_length; D.rng_per_run = L->rng_per_run;
+    }
+    if (L->tracer == THEIA_TRACER_VOLUME_FORWARD || L->tracer == THEIA_TRACER_VOLUME_PHOTON) {
         if (!L->trace_params || L->trace_params_size != sizeof(theia_volume_trace_params_t)) { setError("volume tracer: bad TraceParams block"); return -1; }
         theia_volume_trace_params_t p;
         memcpy(&p, L->trace_params, sizeof(p));
@@ -305,7 +311,7 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
         case THEIA_TARGET_DISK: if (copyBlock(L->target, D.target.p.disk, "disk target")) return -1; break;
         default: setError("volume tracer: unsupported target kind %u", L->target.kind); return -1;
         }
-    } else if (L->tracer == THEIA_TRACER_SCENE_FORWARD) {
+    } else if (L->tracer == THEIA_TRACER_SCENE_FORWARD || L->tracer == THEIA_TRACER_SCENE_PHOTON) {
         if (!L->trace_params || L->trace_params_size != sizeof(theia_scene_trace_params_t)) { setError("scene tracer: bad TraceParams block"); return -1; }
         theia_scene_trace_params_t p;
         memcpy(&p, L->trace_params, sizeof(p));
@@ -367,6 +373,8 @@ static int plan(const theia_trace_launch_t* L, const DeviceLaunch& D, KernelPlan
     size_t smem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
     if (L->tracer == THEIA_TRACER_VOLUME_FORWARD) {
         K.fn = pol ? (const void*)volumeForwardKernel<true> : (const void*)volumeForwardKernel<false>;
+    } else if (L->tracer == THEIA_TRACER_VOLUME_PHOTON) {
+        K.fn = pol ? (const void*)volumePhotonKernel<true> : (const void*)volumePhotonKernel<false>;
     } else {
         K.fn = pol ? (const void*)sceneForwardKernel<true> : (const void*)sceneForwardKernel<false>;
         smem += sizeof(WideNode) * THEIA_TOP_NODES;
@@ -408,7 +416,7 @@ static int persistentGrid(const void* fn, size_t smem, uint32_t* grid) {
 }
 
 static size_t workspaceBytes(const theia_trace_launch_t* L) {
-    if (L->tracer != THEIA_TRACER_SCENE_FORWARD) return 0;
+    if (L->tracer != THEIA_TRACER_SCENE_FORWARD && L->tracer != THEIA_TRACER_SCENE_PHOTON) return 0;
     return layoutWorkspace(nullptr, L->batch_size, L->polarized != 0, L->guide.kind != THEIA_GUIDE_NONE, nullptr);
 }
 
@@ -725,7 +733,7 @@ int theia_trace_grid_size(const theia_trace_launch_t* launch, uint32_t* n_blocks
     KernelPlan K;
     if (!n_blocks) { setError("theia_trace_grid_size: null argument"); return -1; }
     if (translate(launch, D)) return -1;
-    if (launch->tracer == THEIA_TRACER_SCENE_FORWARD && launch->workspace) {
+    if ((launch->tracer == THEIA_TRACER_SCENE_FORWARD || launch->tracer == THEIA_TRACER_SCENE_PHOTON) && launch->workspace) {
         // wavefront: the shading grids are the ones that write partial histograms
         const bool pol = launch->polarized != 0;
         const size_t smem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
@@ -757,11 +765,12 @@ int theia_trace_forward(const theia_trace_launch_t* launch) {
     KernelPlan K;
     if (translate(launch, D)) return -1;
     if (D.batch_size == 0) return 0;
-    if (launch->tracer == THEIA_TRACER_SCENE_FORWARD && launch->workspace) return launchWavefront(launch, D);
+    const bool sceneTracer = launch->tracer == THEIA_TRACER_SCENE_FORWARD || launch->tracer == THEIA_TRACER_SCENE_PHOTON;
+    if (sceneTracer && launch->workspace) return launchWavefront(launch, D);
     if (plan(launch, D, K)) return -1;
     void* args[] = {&D};
     {
-        Timed tm(launch->tracer == THEIA_TRACER_VOLUME_FORWARD ? KC_VOLUME : KC_SCENE, (cudaStream_t)launch->stream);
+        Timed tm(sceneTracer ? KC_SCENE : KC_VOLUME, (cudaStream_t)launch->stream);
         CUDA_TRY(cudaLaunchKernel(K.fn, dim3(K.grid), dim3(TRACE_THREADS), args, K.smem, (cudaStream_t)launch->stream));
     }
     countLaunches(1);

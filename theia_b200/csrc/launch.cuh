@@ -41,6 +41,7 @@ struct CallbackDev {
 struct DeviceLaunch {
     uint32_t disable_mis, disable_direct_lighting, disable_transmission, disable_volume_border;
     uint32_t hit_use_transmitted_dir, path_length, batch_size, first_path;
+    uint32_t photon, run_length, rng_per_run;  // photon tracers (absorption roulette, per run draw counters)
     theia_philox_params_t rng;
     // TraceParams of either tracer (trace.py:589-598, 1136-1145)
     uint64_t medium;   // volume: medium; scene: sourceMedium
@@ -280,6 +281,27 @@ TDEV void onEvent(const CallbackDev& cb, SinkShared* sh, bool has, const Ray& ra
             base[8 * plane + o] = pr.x; base[9 * plane + o] = pr.y; base[10 * plane + o] = pr.z;
         }
     }
+}
+
+// Photon tracers, end of an interaction (sh/tracer.scene.photon.init.glsl:90-106,
+// sh/tracer.volume.photon.common.glsl:88-104): the contribution is the survival probability so
+// far; play roulette on it and start over with one.
+template <bool POL>
+TDEV int photonRoulette(Ray& ray, Rng& rng, int result) {
+    if (result < 0) return result;
+    if (POL) {
+        ray.lin_contrib *= ray.stokes.x;
+        ray.stokes = ray.stokes / ray.stokes.x;
+    }
+    if (getContrib(ray) <= rng.next()) return THEIA_RESULT_RAY_ABSORBED;
+    ray.lin_contrib = 1.0f;
+    ray.log_contrib = 0.0f;
+    return result;
+}
+// The reference runs photon paths in shader dispatches of run_length events and starts the draw
+// counter of run r at r * rng_per_run: applied when event `it` (1 based) was the last of a run.
+TDEV void photonRunBoundary(const DeviceLaunch& P, Rng& rng, uint32_t it) {
+    if (P.run_length != 0 && it % P.run_length == 0) rng.dim = (it / P.run_length) * P.rng_per_run;
 }
 
 // CTA prologue / epilogue shared by both tracers.

@@ -97,6 +97,8 @@ struct SourceRay {  // sh/lightsource.common.glsl:12-26
 struct WavelengthSample { float wavelength, contrib; };
 
 // sh/ray.glsl:136-143
+// sh/ray.glsl:131-133
+TDEV float getContrib(const Ray& r) { return r.lin_contrib * dm_exp(r.log_contrib); }
 TDEV bool isRayBad(const Ray& r) {
     vec3 p = r.position, d = r.direction;
     return isnan_(p.x) || isnan_(p.y) || isnan_(p.z) || isinf_(p.x) || isinf_(p.y) || isinf_(p.z) ||

@@ -107,6 +107,7 @@ __global__ void __launch_bounds__(128, 4) sceneForwardKernel(const __grid_consta
         if (created) {
             rng = makeRng(&P.rng, idx);
             ray = sampleRay<POL>(P.wavelength, P.light, P.medium, rng);
+            if (P.photon) { ray.lin_contrib = 1.0f; ray.log_contrib = 0.0f; }  // sh/tracer.scene.photon.init.glsl:50-54
             allowResponse = P.disable_direct_lighting == 0;
             nPaths++;
         }
@@ -157,7 +158,7 @@ __global__ void __launch_bounds__(128, 4) sceneForwardKernel(const __grid_consta
 
         // ---- interaction (sh/scene.traverse.glsl:361-397)
         const bool interact = alive && result >= 0;
-        const bool last = it == PATH_LENGTH;
+        const bool last = P.photon ? false : it == PATH_LENGTH;  // the photon tracers always scatter
         bool wantMIS = false;
         float uResponse = 2.0f;
         if (interact && hit.valid) {
@@ -230,6 +231,7 @@ __global__ void __launch_bounds__(128, 4) sceneForwardKernel(const __grid_consta
         if (interact && !hit.valid && !last) scatterRay<POL>(ray, rng.next2());
 
         // ---- events and bookkeeping (sh/tracer.scene.forward.glsl:87-104)
+        if (P.photon && alive) result = photonRoulette<POL>(ray, rng, result);
         onEvent<POL>(P.callback, &sh, alive, ray, result, k, it);
         bool maxIter = false;
         if (alive) {
@@ -241,6 +243,7 @@ __global__ void __launch_bounds__(128, 4) sceneForwardKernel(const __grid_consta
                     maxIter = true;
                     alive = false;
                 } else {
+                    if (P.photon) photonRunBoundary(P, rng, it);
                     it++;
                 }
             }

@@ -177,4 +177,112 @@ __global__ void __launch_bounds__(128) volumeForwardKernel(const __grid_constant
     sinkFinish(P, &sh, sharedHist, nSegments, nResponses, 0, nPaths);
 }
 
+// ------------------------------------------------------------------ VolumePhotonTracer
+// sh/tracer.volume.photon.common.glsl:32-123 + sh/tracer.volume.photon.init.glsl:30-62: single
+// photons against the target: every event is trace (hit -> response, photon absorbed), scatter,
+// absorption roulette. Same persistent-warp form as the forward tracer: the state of a path
+// stays in registers, finished lanes take the next path of the warp's range.
+template <bool POL>
+__global__ void __launch_bounds__(128) volumePhotonKernel(const __grid_constant__ DeviceLaunch P) {
+    extern __shared__ float sharedHist[];
+    __shared__ SinkShared sh;
+    sinkInit(P, &sh, sharedHist);
+    float* hist = sinkHist(P, sharedHist);
+
+    const uint32_t warpsPerCta = blockDim.x >> 5;
+    const uint32_t nWarps = gridDim.x * warpsPerCta;
+    const uint32_t warp = blockIdx.x * warpsPerCta + (threadIdx.x >> 5);
+    const uint32_t perWarp = (P.batch_size + nWarps - 1) / nWarps;
+    uint32_t next = min(warp * perWarp, P.batch_size);
+    const uint32_t end = min(next + perWarp, P.batch_size);
+
+    bool alive = false;
+    uint32_t k = 0;   // path number inside the batch
+    uint32_t it = 1;  // event number, 1 .. path_length
+    Ray ray;
+    Rng rng;
+    uint32_t nSegments = 0, nResponses = 0, nPaths = 0;
+
+    while (true) {
+        uint32_t dead = __ballot_sync(FULL_MASK, !alive);
+        bool created = false;
+        if (dead) {
+            uint32_t avail = end - next;
+            uint32_t rank = __popc(dead & laneMaskLt());
+            if (!alive && rank < avail) {
+                alive = true;
+                created = true;
+                k = next + rank;
+                it = 1;
+            }
+            next += min((uint32_t)__popc(dead), avail);
+        }
+        if (!__any_sync(FULL_MASK, alive)) break;
+        const uint32_t idx = P.first_path + k;
+
+        // ---- create the path (init :30-62)
+        bool aborted = false;
+        if (created) {
+            rng = makeRng(&P.rng, idx);
+            ray = sampleRay<POL>(P.wavelength, P.light, P.medium, rng);
+            ray.lin_contrib = 1.0f;
+            ray.log_contrib = 0.0f;
+            nPaths++;
+            aborted = isOccludedByTarget(P.target, ray.position);
+        }
+        onEvent<POL>(P.callback, &sh, created, ray, THEIA_RESULT_RAY_CREATED, k, 0);
+        onEvent<POL>(P.callback, &sh, aborted, ray, THEIA_ERROR_TRACE_ABORT, k, 0);
+        if (aborted) alive = false;
+
+        // ---- trace (common :32-76)
+        HitItem item;
+        bool has = false;
+        int result = 0;
+        float uResponse = 2.0f;
+        if (alive) {
+            nSegments++;
+            float u = rng.next();
+            float dist = sampleScatterLength(ray, P.propagation, u);
+            TargetSample hit = intersectTarget(P.target, ray.position, ray.direction);
+            bool hitValid = hit.valid && (hit.dist <= dist);
+            dist = min_(hit.dist, dist);
+            result = propagateRay(ray, dist, P.propagation);
+            updateRayIS(ray, dist, P.propagation, hitValid);
+            if (result >= 0) {
+                if (hitValid) {
+                    alignRayToHit<POL>(ray, hit.normal);
+                    item = createHit<POL>(ray, hit.objPosition, hit.objNormal, P.objectId, targetWorldToObj(P.target));
+                    has = true;
+                    uResponse = responseDraw(P.response, rng, true, item);
+                    result = THEIA_RESULT_RAY_ABSORBED;  // never detect the same photon twice
+                } else {
+                    result = THEIA_RESULT_RAY_SCATTERED;
+                }
+            }
+        }
+        commitHit(P.response, hist, has, item, idx, it - 1u, nResponses, uResponse);
+
+        // ---- scatter, roulette, event (common :81-108)
+        if (alive) {
+            scatterRay<POL>(ray, rng.next2());
+            result = photonRoulette<POL>(ray, rng, result);
+        }
+        onEvent<POL>(P.callback, &sh, alive, ray, result, k, it);
+        bool maxIter = false;
+        if (alive) {
+            if (result < 0) {
+                alive = false;
+            } else if (it == P.path_length) {
+                maxIter = true;
+                alive = false;
+            } else {
+                photonRunBoundary(P, rng, it);
+                it++;
+            }
+        }
+        onEvent<POL>(P.callback, &sh, maxIter, ray, THEIA_RESULT_MAX_ITER, k, P.path_length + 1);
+    }
+    sinkFinish(P, &sh, sharedHist, nSegments, nResponses, 0, nPaths);
+}
+
 }  // namespace theia

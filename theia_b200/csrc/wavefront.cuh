@@ -359,13 +359,17 @@ TDEV void prepareQuery(const DeviceLaunch& P, float4* rayOut, const Ray& ray, Rn
 template <bool POL>
 TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* sh, bool active, uint32_t path, Ray& ray,
                         Rng& rng, int result, uint32_t it, bool GUIDE, uint32_t next, uint32_t& nSegments) {
+    if (P.photon && active) result = photonRoulette<POL>(ray, rng, result);
     onEvent<POL>(P.callback, sh, active, ray, result, path, it);
     bool cont = active && result >= 0;
     bool maxIter = false, allow = true;
     if (cont) {
         allow = GUIDE ? (result != THEIA_RESULT_RAY_SCATTERED) : true;
         if (it == P.path_length) { maxIter = true; cont = false; }
-        else it++;
+        else {
+            if (P.photon) photonRunBoundary(P, rng, it);
+            it++;
+        }
     }
     onEvent<POL>(P.callback, sh, maxIter, ray, THEIA_RESULT_MAX_ITER, path, P.path_length + 1);
     if (cont) nSegments++;
@@ -454,6 +458,7 @@ __global__ void __launch_bounds__(128, 4) wfGenerateKernel(const __grid_constant
             PreGamma pre = {false, 0.0f, 0u};
             if (PREGAMMA) pre = {true, u2f(ws.state[1][WF_PX * (size_t)ws.capacity + k]), ws.state[1][WF_DIM * (size_t)ws.capacity + k]};
             ray = sampleRay<POL>(P.wavelength, P.light, P.medium, rng, pre);
+            if (P.photon) { ray.lin_contrib = 1.0f; ray.log_contrib = 0.0f; }  // sh/tracer.scene.photon.init.glsl:50-54
             nPaths++;
             nSegments++;
         }
@@ -539,7 +544,7 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
         has = false;
 
         const bool interact = active && result >= 0;
-        const bool last = it == P.path_length;
+        const bool last = P.photon ? false : it == P.path_length;  // the photon tracers always scatter
         bool wantMIS = false;
         float uResponse = 2.0f;
         if (interact && hit.valid) {

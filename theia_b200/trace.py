@@ -29,8 +29,8 @@ from theia_b200.scene import RectBBox, Scene
 from theia_b200.target import Target, TargetGuide
 
 __all__ = [
-    "EmptyEventCallback", "EventResultCode", "EventStatisticCallback", "SceneForwardTracer", "Tracer",
-    "TraceEventCallback", "TrackRecordCallback", "VolumeForwardTracer",
+    "EmptyEventCallback", "EventResultCode", "EventStatisticCallback", "SceneForwardTracer", "ScenePhotonTracer",
+    "Tracer", "TraceEventCallback", "TrackRecordCallback", "VolumeForwardTracer", "VolumePhotonTracer",
 ]
 
 
@@ -640,3 +640,153 @@ class SceneForwardTracer(Tracer):
         if self._mode == "auto":
             return self.capacity >= 65536
         return self._mode == "wavefront"
+
+
+class VolumePhotonTracer(VolumeForwardTracer):
+    """
+    Traces single photons through a homogeneous medium towards a ``Target``: every scattering
+    event plays roulette on the survival probability instead of carrying a weight, and a photon
+    that reaches the target is handed to the response once and absorbed
+    (src/theia/trace.py:2657-2959, sh/tracer.volume.photon.*.glsl). Pair it with
+    ``StoreTimeHitResponse`` to obtain detected photons.
+
+    Parameters follow the reference: ``batchSize, source, target, wavelengthSource, response, rng,
+    *, medium, objectId=0, capacity=None, callback, nScatteringPerRun=10, nRuns=10, traceBBox,
+    maxTime=1 ms, polarized=False, blockSize=128``. The reference dispatches one shader per run
+    and hands the surviving photons over in a queue; here a photon simply lives on in the
+    registers of its lane, with the draw counter of run r starting at ``r * nRNGPerRun`` as in
+    the reference.
+    """
+
+    name = "Volume Photon Tracer"
+    _tracerKind = _abi.TRACER_VOLUME_PHOTON
+
+    def __init__(self, batchSize: int, source: LightSource, target: Target, wavelengthSource: WavelengthSource,
+                 response: HitResponse, rng: RNG, *, medium: int, objectId: int = 0, capacity: int | None = None,
+                 callback: TraceEventCallback | None = None, nScatteringPerRun: int = 10, nRuns: int = 10,
+                 traceBBox: RectBBox | None = None, maxTime: float = 1.0 * u.ms, polarized: bool = False,
+                 blockSize: int = 128, code: bytes | None = None) -> None:
+        if callback is None:
+            callback = EmptyEventCallback()
+        if traceBBox is None:
+            traceBBox = RectBBox((-1.0 * u.km,) * 3, (1.0 * u.km,) * 3)
+        if nScatteringPerRun <= 0 or nRuns <= 0:
+            raise ValueError("nScatteringPerRun and nRuns must be positive")
+        # budgets (trace.py:2784-2787)
+        nRNG = source.nRNGForward + wavelengthSource.nRNGSamples
+        nRNG += 4 * nRuns * nScatteringPerRun
+        nRNG += response.nRNGSamples
+        self._nRNGPerRun = 4 * nScatteringPerRun + response.nRNGSamples
+        Tracer.__init__(self, response, {"TraceParams": self.TraceParams}, batchSize=batchSize, blockSize=blockSize,
+                        capacity=capacity, nRNGSamples=nRNG, maxHitsPerThread=1, polarized=polarized)
+        self._source = source
+        self._wavelengthSource = wavelengthSource
+        self._rng = rng
+        self._target = target
+        self._callback = callback
+        self._nRuns = nRuns
+        self._nScatteringPerRun = nScatteringPerRun
+        self._nScattering = nRuns * nScatteringPerRun
+        self._pathLength = nRuns * nScatteringPerRun
+        self._directLightingDisabled = False
+        self._targetSamplingDisabled = True
+        self.setParams(scatterCoefficient=float("NaN"), medium=medium, objectId=objectId,
+                       lowerBBoxCorner=traceBBox.lowerCorner, upperBBoxCorner=traceBBox.upperCorner, maxTime=maxTime,
+                       _maxDist=traceBBox.diagonal)
+
+    @property
+    def nScatteringPerRun(self) -> int:
+        """Scattering events per run of the reference's loop shader"""
+        return self._nScatteringPerRun
+
+    @property
+    def nRuns(self) -> int:
+        return self._nRuns
+
+    @property
+    def maxPathLength(self) -> int:
+        return self._nRuns * self._nScatteringPerRun
+
+    @property
+    def code(self) -> bytes:
+        return repr((self.name, self.polarized, self._nRuns, self._nScatteringPerRun, self.blockSize)).encode()
+
+    def _fillLaunch(self, L: _abi.TraceLaunch, i: int, keep: list) -> None:
+        super()._fillLaunch(L, i, keep)
+        L.path_length = self.maxPathLength
+        L.run_length = self._nScatteringPerRun
+        L.rng_per_run = self._nRNGPerRun
+
+
+class ScenePhotonTracer(SceneForwardTracer):
+    """
+    Traces single photons through a meshed scene with absorption roulette after every
+    interaction (src/theia/trace.py:2370-2654, sh/tracer.scene.photon.*.glsl); no next event
+    estimation, every detector hit goes to the response. Parameters follow the reference:
+    ``batchSize, source, wavelengthSource, response, rng, scene, *, capacity=None, callback,
+    targetId=-1, sourceMedium=None, maxTime=1 ms, nScatteringPerRun=10, nRuns=10,
+    polarized=False, disableTransmission=False, disableVolumeBorder=False,
+    useRefractedHitDir=False, blockSize=128`` (+ ``mode`` as for ``SceneForwardTracer``).
+    """
+
+    name = "Scene Photon Tracer"
+    _tracerKind = _abi.TRACER_SCENE_PHOTON
+
+    def __init__(self, batchSize: int, source: LightSource, wavelengthSource: WavelengthSource,
+                 response: HitResponse, rng: RNG, scene: Scene, *, capacity: int | None = None,
+                 callback: TraceEventCallback | None = None, targetId: int = -1, sourceMedium: int | None = None,
+                 maxTime: float = 1.0 * u.ms, nScatteringPerRun: int = 10, nRuns: int = 10, polarized: bool = False,
+                 disableTransmission: bool = False, disableVolumeBorder: bool = False,
+                 useRefractedHitDir: bool = False, blockSize: int = 128, code: bytes | None = None,
+                 mode: str = "auto") -> None:
+        if callback is None:
+            callback = EmptyEventCallback()
+        if mode not in ("auto", "wavefront", "single"):
+            raise ValueError("mode must be 'auto', 'wavefront' or 'single'")
+        if nScatteringPerRun <= 0 or nRuns <= 0:
+            raise ValueError("nScatteringPerRun and nRuns must be positive")
+        self._mode = mode
+        self._workspace = None
+        # budgets (trace.py:2488-2491)
+        nRNG = source.nRNGForward + wavelengthSource.nRNGSamples
+        nRNG += 5 * nRuns * nScatteringPerRun
+        nRNG += response.nRNGSamples
+        self._nRNGPerRun = 5 * nScatteringPerRun + response.nRNGSamples
+        Tracer.__init__(self, response, {"TraceParams": self.TraceParams}, batchSize=batchSize, blockSize=blockSize,
+                        capacity=capacity, maxHitsPerThread=1, nRNGSamples=nRNG, polarized=polarized)
+        if sourceMedium is None:
+            sourceMedium = scene.medium
+        self._source = source
+        self._wavelengthSource = wavelengthSource
+        self._callback = callback
+        self._rng = rng
+        self._scene = scene
+        self._targetGuide = None
+        self._nRuns = nRuns
+        self._nScatteringPerRun = nScatteringPerRun
+        self._maxPathLength = nRuns * nScatteringPerRun
+        self._directLightingDisabled = False
+        self._transmissionDisabled = disableTransmission
+        self._volumeBorderDisabled = disableVolumeBorder
+        self._useRefractedHitDir = useRefractedHitDir
+        self.setParams(targetId=targetId, scatterCoefficient=float("NaN"), sourceMedium=sourceMedium,
+                       maxTime=maxTime, _lowerBBoxCorner=scene.bbox.lowerCorner,
+                       _upperBBoxCorner=scene.bbox.upperCorner, _maxDist=scene.bbox.diagonal)
+
+    @property
+    def nScatteringPerRun(self) -> int:
+        return self._nScatteringPerRun
+
+    @property
+    def nRuns(self) -> int:
+        return self._nRuns
+
+    @property
+    def code(self) -> bytes:
+        return repr((self.name, self.polarized, self._transmissionDisabled, self._volumeBorderDisabled,
+                     self._useRefractedHitDir, self._nRuns, self._nScatteringPerRun, self.blockSize)).encode()
+
+    def _fillLaunch(self, L: _abi.TraceLaunch, i: int, keep: list) -> None:
+        super()._fillLaunch(L, i, keep)
+        L.run_length = self._nScatteringPerRun
+        L.rng_per_run = self._nRNGPerRun
