@@ -34,17 +34,18 @@ METRIC = "photon path segments/s"
 UNIT = "segments/s"
 
 # declared algorithmic HBM bytes per unit of each kernel class: state words
-# (18 unpolarised / 25 polarised) + ray query (32 B) + result (16 B) + queue entry (4 B)
+# (19 unpolarised / 26 polarised incl. the path number; dense buffers, no queue of slots) + ray query
+# (32 B) + result (16 B)
 def algorithmicBytes(polarized: bool) -> dict:
-    state = 4 * (25 if polarized else 18)
+    state = 4 * (26 if polarized else 19)
     return {
         "volumeForwardKernel": 0,                                  # per segment: register resident
         "sceneForwardKernel": 0,
-        "wfGenerateKernel": state + 32 + 4,                       # per path: write state, ray, queue
-        "wfTraceKernel": 32 + 16 + 4,                             # per ray: read ray + queue, write result
-        "wfShadeKernel": 2 * state + 2 * 32 + 16 + 2 * 4,          # per segment: read+write state/ray/queue, read result
-        "wfTraceKernel(shadow)": 32 + 16 + 2,                     # per shadow ray (two rays share a queue entry)
-        "wfShadeShadowKernel": 2 * state + 2 * (32 + 16) + 32 + 2 * 4,  # per scatter event with guide
+        "wfGenerateKernel": state + 32,                           # per path: write state, ray
+        "wfTraceKernel": 32 + 16,                                 # per ray: read ray, write result
+        "wfShadeKernel": 2 * state + 2 * 32 + 16,                  # per segment: read+write state/ray, read result
+        "wfTraceKernel(shadow)": 32 + 16,                         # per shadow ray
+        "wfShadeShadowKernel": 2 * state + 2 * (32 + 16) + 32,     # per scatter event with guide
         "histReduceKernel": 0,
     }
 
