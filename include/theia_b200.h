@@ -143,6 +143,22 @@ typedef struct theia_light_muon {
     float b_angular;
 } theia_light_muon_t;
 
+/* src/theia/light.py:1215-1223 (CherenkovLightSource), sh/lightsource.cherenkov.simple.glsl:9-16 */
+typedef struct theia_light_cherenkov {
+    float trackStart[3];
+    float startTime;
+    float trackEnd[3];
+    float endTime;
+    float trackDir[3];
+    float trackDist;
+} theia_light_cherenkov_t;
+
+/* src/theia/light.py:1377-1378 (CherenkovTrackLightSource), sh/lightsource.cherenkov.track.glsl:9-21:
+ * track = dev address of { uint32 trackLength; { float x, y, z, t; } vertices[trackLength + 1]; } */
+typedef struct theia_light_cherenkov_track {
+    uint64_t track;
+} theia_light_cherenkov_track_t;
+
 /* src/theia/light.py:692-766 (HostLightSource), sh/lightsource.host.glsl:6-17 with the queue of
  * sh/lightsource.queue.glsl:11-33: field major float arrays of `capacity` entries each, NO count
  * word - posXYZ, dirXYZ, [stokes IQUV, polRef XYZ when polarized], startTime, contrib.
@@ -156,6 +172,13 @@ typedef struct theia_light_host {
 /* wavelength sources ---------------------------------------------------------- */
 /* src/theia/light.py:87-144 (HostWavelengthSource), sh/wavelengthsource.host.glsl:6-13 with the
  * queue of sh/wavelengthsource.queue.glsl:11-14: float wavelength[capacity], contrib[capacity] */
+/* src/theia/light.py:372-373 (FunctionWavelengthSource), sh/wavelengthsource.function.glsl:6-11:
+ * table = dev address of a Table1D { int32 nx; float samples[nx]; } holding the inverse CDF */
+typedef struct theia_wavelength_function {
+    uint64_t table;
+    float contrib;
+} theia_wavelength_function_t;
+
 typedef struct theia_wavelength_host {
     uint64_t queue; /* dev: float[2][capacity] */
     uint32_t capacity;
@@ -231,11 +254,14 @@ typedef struct theia_geometry {
 
 /* ------------------------------------------------------------------ component kinds */
 enum { THEIA_LIGHT_SPHERICAL = 1, THEIA_LIGHT_CONE = 2, THEIA_LIGHT_PENCIL = 3,
-       THEIA_LIGHT_CASCADE = 4, THEIA_LIGHT_MUON = 5, THEIA_LIGHT_HOST = 6 };
+       THEIA_LIGHT_CASCADE = 4, THEIA_LIGHT_MUON = 5, THEIA_LIGHT_HOST = 6, THEIA_LIGHT_CHERENKOV = 7,
+       THEIA_LIGHT_CHERENKOV_TRACK = 8 };
 /* light flags (reference: preamble macros of the light source snippets) */
 enum { THEIA_LIGHT_FLAG_POLARIZED = 1,     /* LIGHTSOURCE_POLARIZED, light.py:1009-1011 */
-       THEIA_LIGHT_FLAG_FRANK_TAMM_IS = 2  /* FRANK_TAMM_IS, light.py:1517-1519 */ };
-enum { THEIA_WAVELENGTH_CONST = 1, THEIA_WAVELENGTH_UNIFORM = 2, THEIA_WAVELENGTH_HOST = 3 };
+       THEIA_LIGHT_FLAG_FRANK_TAMM_IS = 2, /* FRANK_TAMM_IS, light.py:1517-1519 */
+       THEIA_LIGHT_FLAG_PHOTON_COUNT = 4   /* FRANK_TAMM_USE_PHOTON_COUNT, light.py:1258-1262 */ };
+enum { THEIA_WAVELENGTH_CONST = 1, THEIA_WAVELENGTH_UNIFORM = 2, THEIA_WAVELENGTH_HOST = 3,
+       THEIA_WAVELENGTH_FUNCTION = 4 };
 enum { THEIA_TARGET_NONE = 0, THEIA_TARGET_SPHERE = 1, THEIA_TARGET_INNER_SPHERE = 2, THEIA_TARGET_FLAT = 3,
        THEIA_TARGET_DISK = 4 };
 enum { THEIA_GUIDE_NONE = 0, THEIA_GUIDE_SPHERE = 1, THEIA_GUIDE_FLAT = 2, THEIA_GUIDE_DISK = 3 };

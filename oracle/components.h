@@ -22,6 +22,10 @@ static inline WavelengthSample sampleWavelength(const theia_component_t& c, Rng&
         if (k >= p->capacity) return {F_NAN, 0.0f};
         return {q[k], q[p->capacity + k]};
     }
+    if (c.kind == THEIA_WAVELENGTH_FUNCTION) {  // sh/wavelengthsource.function.glsl:13-16
+        const auto* p = (const theia_wavelength_function_t*)c.params;
+        return {lookUp(p->table, rng.next(), 0.0f), p->contrib};
+    }
     const auto* p = (const theia_wavelength_uniform_t*)c.params;
     float u = rng.next();
     float lam = mix_(p->lam_min, p->lam_max, u);
@@ -64,6 +68,56 @@ static inline float particle_sampleEmissionAngle(float n, float a, float b, floa
     u = u * (int_upper + int_lower) - int_lower;
     float x = dm_pow(-dm_log(1.0f - abs_(u)) / b, 1.0f / a);
     return cos_chev - sign_(u) * x;
+}
+
+// GLSL uint(floor(x)) for x >= 0 (NaN and negative values: 0)
+static inline uint32_t floorToUint(float x) { return x >= 1.0f ? (uint32_t)std::fmin(std::floor(x), 4294967040.0f) : 0u; }
+// sh/lightsource.cherenkov.common.glsl:13-17 (energy) and :31-35 (photon count)
+static inline float frank_tamm_cherenkov(float n, float lambda, bool photonCount) {
+    lambda *= 1e-3f;
+    float result = photonCount ? 7.2973525693f / (lambda * lambda) * (1.0f - (1.0f / (n * n)))
+                               : 9.04756408986352f / (lambda * lambda * lambda) * (1.0f - (1.0f / (n * n)));
+    return max_(result, 0.0f);
+}
+// sh/lightsource.cherenkov.simple.glsl:18-52 and sh/lightsource.cherenkov.track.glsl:23-66
+static inline SourceRay cherenkovSample(const theia_component_t& c, float wavelength, float n, float u, float v, bool polarized) {
+    const bool photonCount = (c.flags & THEIA_LIGHT_FLAG_PHOTON_COUNT) != 0;
+    vec3 pos, particleDir;
+    float time, contrib;
+    if (c.kind == THEIA_LIGHT_CHERENKOV) {
+        const auto* p = (const theia_light_cherenkov_t*)c.params;
+        vec3 s = v3(p->trackStart), e = v3(p->trackEnd);
+        pos = {mix_(s.x, e.x, u), mix_(s.y, e.y, u), mix_(s.z, e.z, u)};
+        time = mix_(p->startTime, p->endTime, u);
+        contrib = ORC_TWO_PI * frank_tamm_cherenkov(n, wavelength, photonCount) * p->trackDist;
+        particleDir = v3(p->trackDir);
+    } else {
+        const auto* p = (const theia_light_cherenkov_track_t*)c.params;
+        const uint32_t* track = (const uint32_t*)(uintptr_t)p->track;
+        const uint32_t trackLength = track[0];
+        u *= (float)trackLength;
+        uint32_t vertexIdx = std::min(floorToUint(u), trackLength - 1u);
+        u = u - std::floor(u);
+        const float* a = (const float*)(track + 1) + 4 * (size_t)vertexIdx;
+        vec3 s = {a[0], a[1], a[2]}, e = {a[4], a[5], a[6]};
+        pos = {mix_(s.x, e.x, u), mix_(s.y, e.y, u), mix_(s.z, e.z, u)};
+        time = mix_(a[3], a[7], u);
+        particleDir = normalize(e - s);
+        float segmentLength = distance(s, e);
+        contrib = ORC_TWO_PI * (float)trackLength * segmentLength;
+        contrib *= frank_tamm_cherenkov(n, wavelength, photonCount);
+    }
+    float cos_theta = 1.0f / n;
+    float sin_theta = std::sqrt(max_(1.0f - cos_theta * cos_theta, 0.0f));
+    float phi = ORC_TWO_PI * v;
+    float sp, cp;
+    dm_sincos(phi, &sp, &cp);
+    vec3 rayDir = createLocalCOSY(particleDir) * vec3{sin_theta * cp, sin_theta * sp, cos_theta};
+    if (polarized) {
+        vec3 polRef = normalize(cross(rayDir, particleDir));
+        return createSourceRay(pos, rayDir, vec4{1.0f, 1.0f, 0.0f, 0.0f}, polRef, time, contrib);
+    }
+    return createSourceRay(pos, rayDir, time, contrib, false);
 }
 
 // ------------------------------------------------------------------ light sources (forward)
@@ -133,6 +187,12 @@ static inline SourceRay sampleLight(const theia_component_t& c, float wavelength
         vec3 rayDir = createLocalCOSY(trackDir) * sphericalToCartessian(phi, cos_theta);
         if (!(c.flags & THEIA_LIGHT_FLAG_FRANK_TAMM_IS)) contrib *= frank_tamm(wavelength, medium.n);
         return createSourceRay(position, rayDir, startTime, contrib, polarized);
+    }
+    case THEIA_LIGHT_CHERENKOV:
+    case THEIA_LIGHT_CHERENKOV_TRACK: {
+        float u = rng.next();
+        float v = rng.next();
+        return cherenkovSample(c, wavelength, medium.n, u, v, polarized);
     }
     case THEIA_LIGHT_HOST: {  // sh/lightsource.host.glsl:10-17, LOAD_SAMPLE of sh/lightsource.queue.glsl:40-56
         const auto* p = (const theia_light_host_t*)c.params;

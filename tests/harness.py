@@ -100,6 +100,18 @@ def makeLight(kind: str, *, polarized: bool = False, position=(1.0, 0.0, 0.0), d
     if kind == "cascade":
         return light.ParticleCascadeLightSource(position, 2.0, direction, effectiveLength=5300.0, a_angular=0.54,
                                                 b_angular=3.3, a_long=4.6, b_long=0.58)
+    if kind == "cherenkov":
+        end = tuple(position[k] + 20.0 * direction[k] for k in range(3))
+        return light.CherenkovLightSource(trackStart=position, trackEnd=end, startTime=1.0,
+                                          endTime=1.0 + 20.0 / 0.299792458, usePhotonCount=True)
+    if kind == "cherenkovTrack":
+        d = np.asarray(direction, dtype=np.float64)
+        side = np.cross(d, (0.3, 0.5, 0.8))
+        pts = [np.asarray(position) + 5.0 * k * d + (0.4 * (k % 2)) * side for k in range(6)]
+        t = np.concatenate([[0.0], np.cumsum(np.linalg.norm(np.diff(pts, axis=0), axis=1))]) / 0.299792458
+        track = light.ParticleTrack(8)
+        track.setVertices(np.concatenate([np.array(pts), t[:, None]], 1))
+        return light.CherenkovTrackLightSource(track)
     if kind == "muon":
         end = tuple(position[k] + 30.0 * direction[k] for k in range(3))
         return light.MuonTrackLightSource(position, 1.0, end, 1.0 + 30.0 / 0.299792458, muonEnergy=1e3)
@@ -132,6 +144,9 @@ def volumeScenario(N: int, *, resp: str = "record", callback: str | None = None,
         src = makeLight(lightKind, polarized=polarized, position=(0.5, 0.2, -0.1), direction=(0.0, 0.6, 0.8))
     wl = light.ConstWavelengthSource(500.0) if wavelength == "const" else light.UniformWavelengthSource(
         lambdaRange=(400.0, 700.0))
+    if wavelength == "function":
+        wl = light.FunctionWavelengthSource(lambda lam: np.exp(-0.5 * ((lam - 480.0) / 60.0) ** 2) + 0.1,
+                                            lambdaRange=(350.0, 650.0), numSamples=256)
     if lightKind == "host":
         # two batches worth of host generated rays / photons, streamed batch by batch
         rays, photons = hostSourceData(2 * N, polarized=polarized)

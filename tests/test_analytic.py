@@ -149,3 +149,65 @@ def test_photon_tracer_estimates_the_forward_tracers_yield(device, builder, kw, 
     err = np.sqrt((np.square(a).sum() + np.square(b).sum())) / N
     print(f"forward {ya:.5f} photon {yb:.5f} +- {err:.5f}")
     assert abs(ya - yb) < 4.5 * err
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("kind", ["cherenkov", "cherenkovTrack"])
+def test_cherenkov_light_yield_and_cone(device, kind):
+    # sh/lightsource.cherenkov.{simple,track}.glsl: emission on the Cherenkov cone cos(theta) = 1 / n, and the
+    # light reaching a sphere around the track adds up to the Frank-Tamm yield 2 pi alpha / lambda^2 (1 - 1/n^2) L
+    from theia_b200 import light, material, random, response, target, trace
+    N, n, lam, L = 1 << 16, 1.33, 400.0, 12.0
+    with _device.useDevice(device):
+        med = H.EnergyModel(0.0, 0.005, 0.0, n=n, ng=n).createMedium()
+        store = material.MaterialStore([], media=[med])
+        if kind == "cherenkov":
+            src = light.CherenkovLightSource(trackStart=(1.0, 2.0, 3.0), trackEnd=(1.0, 2.0 + 0.6 * L, 3.0 + 0.8 * L),
+                                             startTime=5.0, endTime=5.0 + L / 0.299792458, usePhotonCount=True)
+        else:
+            pts = np.array([[1.0, 2.0, 3.0], [1.0, 2.0 + 0.6 * 4.0, 3.0 + 0.8 * 4.0],
+                            [1.0, 2.0 + 0.6 * 8.0, 3.0 + 0.8 * 8.0], [1.0, 2.0 + 0.6 * L, 3.0 + 0.8 * L]])
+            t = 5.0 + np.array([0.0, 4.0, 8.0, L]) / 0.299792458
+            track = light.ParticleTrack(4)
+            track.setVertices(np.concatenate([pts, t[:, None]], 1))
+            src = light.CherenkovTrackLightSource(track, usePhotonCount=True)
+        rec = response.HitRecorder()
+        rec.enableTags()
+        rng = random.PhiloxRNG(key=0xCE4E)
+        cb = trace.TrackRecordCallback(N, 4)
+        tgt = target.InnerSphereTarget(position=(1.0, 5.0, 7.0), radius=60.0)
+        tr = trace.VolumeForwardTracer(N, src, tgt, light.ConstWavelengthSource(lam), rec, rng, medium=store.media[med.name],
+                                       nScattering=10, callback=cb, maxTime=float("inf"))
+        cfg = {"tracer": tr, "response": rec, "callback": cb, "rng": rng, "store": store}
+        H.runAny(cfg)
+        total = float(H.hitView(cfg)["contrib"].astype(np.float64).sum()) / N
+        tracks, lengths, _ = cb.result(0)
+    ok = lengths >= 1
+    d = tracks[ok, 1, :3].astype(np.float64) - tracks[ok, 0, :3]
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    assert np.abs(d @ np.array([0.0, 0.6, 0.8]) - 1.0 / n).max() < 2e-4
+    s = (tracks[ok, 0, :3].astype(np.float64) - np.array([1.0, 2.0, 3.0])) @ np.array([0.0, 0.6, 0.8])
+    assert s.min() >= -1e-4 and s.max() <= L + 1e-4 and abs(s.mean() - L / 2) < 0.1
+    assert np.allclose(tracks[ok, 0, 3], 5.0 + s / 0.299792458, atol=1e-3)  # emitted when the particle passes
+    expected = 2.0 * np.pi * 7.2973525693 / (lam * 1e-3) ** 2 * (1.0 - 1.0 / n**2) * L
+    print(f"{kind}: {total:.3f} vs {expected:.3f}")
+    assert abs(total / expected - 1.0) < 0.01
+
+
+def test_function_wavelength_source_samples_the_function():
+    # sh/wavelengthsource.function.glsl: inverse CDF table; every sample carries the integral of fn
+    from scipy import integrate, stats
+    from theia_b200 import light
+    fn = lambda lam: np.exp(-0.5 * ((lam - 480.0) / 60.0) ** 2) + 0.1  # noqa: E731
+    lo, hi = 350.0, 650.0
+    with _device.useDevice("cpu"):
+        cfg = H.volumeScenario(1 << 14, lightKind="spherical", targetKind="inner", wavelength="function", resp="record")
+        H.runOracle(cfg)
+        lam = np.array(H.hitView(cfg)["wavelength"], dtype=np.float64)
+        p = cfg["tracer"].wavelengthSource._firstBlock(0)
+    assert p._contrib == pytest.approx(integrate.quad(fn, lo, hi)[0], rel=1e-5)
+    assert lam.min() >= lo and lam.max() <= hi
+    norm = integrate.quad(fn, lo, hi)[0]
+    cdf = np.vectorize(lambda x: integrate.quad(fn, lo, x)[0] / norm)
+    # one wavelength per path, many hits per path: test the distinct values
+    assert stats.kstest(np.unique(lam), cdf).pvalue > 1e-3

@@ -143,6 +143,19 @@ def test_ray_query_matches_brute_force(cuda, orc, builder, kw, box):
     assert stats[3] == n and stats[0] > 0
 
 
+def test_sweep_builder_option_gives_the_same_ray_queries(cuda):
+    # THEIA_BVH_BUILDER=sah (read once per process): the brute force comparison above in a child process
+    import os, subprocess, sys
+    if os.environ.get("THEIA_BVH_BUILDER") == "sah":
+        pytest.skip("already inside the child")
+    env = dict(os.environ, THEIA_BVH_BUILDER="sah")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-m", "gpu", "-x", "-k",
+                        "brute_force or (scene_tracer_hits and sceneC3 and wavefront)"], env=env, capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
+
+
 # ------------------------------------------------------------------ tracers, per path parity
 VOLUME_CASES = [
     dict(),
@@ -156,6 +169,10 @@ VOLUME_CASES = [
     dict(lightKind="muon", water=True, wavelength="uniform"),
     dict(targetKind="inner", mis=True),
     dict(targetKind="inner", mis=False, polarized=True, water=True),
+    dict(lightKind="cherenkov", water=True, wavelength="uniform"),
+    dict(lightKind="cherenkov", water=True, wavelength="function", polarized=True),
+    dict(lightKind="cherenkovTrack", water=True, wavelength="function", mis=False),
+    dict(lightKind="cherenkovTrack", water=True, wavelength="uniform", polarized=True),
     dict(lightKind="host"),
     dict(lightKind="host", wavelength="host", polarized=True, water=True, mis=False),
     dict(targetKind="flat"),

@@ -8,8 +8,9 @@ ABI_VERSION = 2
 
 # component kinds
 LIGHT_SPHERICAL, LIGHT_CONE, LIGHT_PENCIL, LIGHT_CASCADE, LIGHT_MUON, LIGHT_HOST = 1, 2, 3, 4, 5, 6
-LIGHT_FLAG_POLARIZED, LIGHT_FLAG_FRANK_TAMM_IS = 1, 2
-WAVELENGTH_CONST, WAVELENGTH_UNIFORM, WAVELENGTH_HOST = 1, 2, 3
+LIGHT_CHERENKOV, LIGHT_CHERENKOV_TRACK = 7, 8
+LIGHT_FLAG_POLARIZED, LIGHT_FLAG_FRANK_TAMM_IS, LIGHT_FLAG_PHOTON_COUNT = 1, 2, 4
+WAVELENGTH_CONST, WAVELENGTH_UNIFORM, WAVELENGTH_HOST, WAVELENGTH_FUNCTION = 1, 2, 3, 4
 TARGET_NONE, TARGET_SPHERE, TARGET_INNER_SPHERE, TARGET_FLAT, TARGET_DISK = 0, 1, 2, 3, 4
 GUIDE_NONE, GUIDE_SPHERE, GUIDE_FLAT, GUIDE_DISK = 0, 1, 2, 3
 RESPONSE_EMPTY, RESPONSE_RECORD, RESPONSE_HISTOGRAM = 0, 1, 2

@@ -338,6 +338,11 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
     case THEIA_LIGHT_PENCIL: if (copyBlock(L->light, D.light.p.pencil, "pencil light")) return -1; break;
     case THEIA_LIGHT_CASCADE: if (copyBlock(L->light, D.light.p.cascade, "cascade light")) return -1; break;
     case THEIA_LIGHT_MUON: if (copyBlock(L->light, D.light.p.muon, "muon light")) return -1; break;
+    case THEIA_LIGHT_CHERENKOV: if (copyBlock(L->light, D.light.p.cherenkov, "cherenkov light")) return -1; break;
+    case THEIA_LIGHT_CHERENKOV_TRACK:
+        if (copyBlock(L->light, D.light.p.track, "cherenkov track light")) return -1;
+        if (!D.light.p.track.track) { setError("cherenkov track light: no particle track"); return -1; }
+        break;
     case THEIA_LIGHT_HOST:
         if (copyBlock(L->light, D.light.p.host, "host light")) return -1;
         if (!D.light.p.host.queue || D.light.p.host.capacity < L->batch_size) { setError("host light: queue holds %u samples, batch needs %u", D.light.p.host.capacity, L->batch_size); return -1; }
@@ -348,6 +353,10 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
     switch (L->wavelength.kind) {
     case THEIA_WAVELENGTH_CONST: if (copyBlock(L->wavelength, D.wavelength.p.constant, "const wavelength")) return -1; break;
     case THEIA_WAVELENGTH_UNIFORM: if (copyBlock(L->wavelength, D.wavelength.p.uniform, "uniform wavelength")) return -1; break;
+    case THEIA_WAVELENGTH_FUNCTION:
+        if (copyBlock(L->wavelength, D.wavelength.p.function, "function wavelength")) return -1;
+        if (!D.wavelength.p.function.table) { setError("function wavelength: no table"); return -1; }
+        break;
     case THEIA_WAVELENGTH_HOST:
         if (copyBlock(L->wavelength, D.wavelength.p.host, "host wavelength")) return -1;
         if (!D.wavelength.p.host.queue || D.wavelength.p.host.capacity < L->batch_size) { setError("host wavelength: queue holds %u samples, batch needs %u", D.wavelength.p.host.capacity, L->batch_size); return -1; }

@@ -15,11 +15,14 @@ union LightBlock {
     theia_light_cascade_t cascade;
     theia_light_muon_t muon;
     theia_light_host_t host;
+    theia_light_cherenkov_t cherenkov;
+    theia_light_cherenkov_track_t track;
 };
 union WavelengthBlock {
     theia_wavelength_const_t constant;
     theia_wavelength_uniform_t uniform;
     theia_wavelength_host_t host;
+    theia_wavelength_function_t function;
 };
 // first = RNG stream of the first path of the launch: host queues are indexed by idx - first
 struct LightSel { uint32_t kind, flags, first; LightBlock p; };
@@ -47,6 +50,8 @@ TDEV WavelengthSample sampleWavelength(const WavelengthSel& c, Rng& rng) {
         if (k >= C) return {T_NAN, 0.0f};
         return {__ldg(q + k), __ldg(q + C + k)};
     }
+    if (c.kind == THEIA_WAVELENGTH_FUNCTION)  // sh/wavelengthsource.function.glsl:13-16
+        return {lookUp(c.p.function.table, rng.next(), 0.0f), c.p.function.contrib};
     float u = rng.next();
     float lam = mix_(c.p.uniform.lam_min, c.p.uniform.lam_max, u);
     return {lam, c.p.uniform.contrib};
@@ -106,6 +111,75 @@ TDEV bool gammaTrial(const GammaConsts& g, Rng& rng, float* X_out) {
 // Gamma variate sampled ahead of sampleLight (wavefront generate kernel): the value and the
 // draw counter after the rejection loop.
 struct PreGamma { bool valid; float value; uint32_t dimAfter; };
+
+// sh/lightsource.host.glsl:10-17, LOAD_SAMPLE of sh/lightsource.queue.glsl:40-56 (out of line: see
+// commitHitOther in launch.cuh)
+template <bool POL>
+static __device__ __noinline__ SourceRay hostLightSample(const theia_light_host_t& p, uint32_t k) {
+    const float* e = reinterpret_cast<const float*>(p.queue) + k;
+    const size_t C = p.capacity;
+    vec3 pos = {__ldg(e), __ldg(e + C), __ldg(e + 2 * C)};
+    vec3 dir = {__ldg(e + 3 * C), __ldg(e + 4 * C), __ldg(e + 5 * C)};
+    if (p.polarized) {
+        vec4 stokes = {__ldg(e + 6 * C), __ldg(e + 7 * C), __ldg(e + 8 * C), __ldg(e + 9 * C)};
+        vec3 polRef = {__ldg(e + 10 * C), __ldg(e + 11 * C), __ldg(e + 12 * C)};
+        return createSourceRay(pos, dir, stokes, polRef, __ldg(e + 13 * C), __ldg(e + 14 * C));
+    }
+    return createSourceRay<POL>(pos, dir, __ldg(e + 6 * C), __ldg(e + 7 * C));
+}
+
+// GLSL uint(floor(x)) for x >= 0 (NaN and negative values: 0)
+TDEV uint32_t floorToUint(float x) { return x >= 1.0f ? (uint32_t)fminf(floorf(x), 4294967040.0f) : 0u; }
+// sh/lightsource.cherenkov.common.glsl:13-17 (energy) and :31-35 (photon count)
+TDEV float frank_tamm_cherenkov(float n, float lambda, bool photonCount) {
+    lambda *= 1e-3f;
+    float result = photonCount ? 7.2973525693f / (lambda * lambda) * (1.0f - (1.0f / (n * n)))
+                               : 9.04756408986352f / (lambda * lambda * lambda) * (1.0f - (1.0f / (n * n)));
+    return max_(result, 0.0f);
+}
+// Cherenkov cone around a particle moving with beta = 1 from `start` to `end`; u, v are the two
+// draws. sh/lightsource.cherenkov.simple.glsl:18-52 (one segment, trackLength = 1) and
+// sh/lightsource.cherenkov.track.glsl:23-66 (segment picked by u). Out of line, see commitHitOther.
+template <bool POL>
+static __device__ __noinline__ SourceRay cherenkovSample(const LightSel& c, float wavelength, float n, float u, float v) {
+    const bool photonCount = (c.flags & THEIA_LIGHT_FLAG_PHOTON_COUNT) != 0;
+    vec3 pos, particleDir;
+    float time, contrib;
+    if (c.kind == THEIA_LIGHT_CHERENKOV) {
+        const theia_light_cherenkov_t& p = c.p.cherenkov;
+        vec3 s = v3(p.trackStart), e = v3(p.trackEnd);
+        pos = {mix_(s.x, e.x, u), mix_(s.y, e.y, u), mix_(s.z, e.z, u)};
+        time = mix_(p.startTime, p.endTime, u);
+        contrib = T_TWO_PI * frank_tamm_cherenkov(n, wavelength, photonCount) * p.trackDist;
+        particleDir = v3(p.trackDir);
+    } else {
+        const uint32_t* track = reinterpret_cast<const uint32_t*>(c.p.track.track);
+        const uint32_t trackLength = __ldg(track);
+        const float4* vertices = reinterpret_cast<const float4*>(track + 1);  // 4 byte aligned only
+        u *= (float)trackLength;
+        uint32_t vertexIdx = min(floorToUint(u), trackLength - 1u);
+        u = u - floorf(u);
+        const float* a = reinterpret_cast<const float*>(vertices) + 4 * (size_t)vertexIdx;
+        vec3 s = {__ldg(a), __ldg(a + 1), __ldg(a + 2)}, e = {__ldg(a + 4), __ldg(a + 5), __ldg(a + 6)};
+        pos = {mix_(s.x, e.x, u), mix_(s.y, e.y, u), mix_(s.z, e.z, u)};
+        time = mix_(__ldg(a + 3), __ldg(a + 7), u);
+        particleDir = normalize(e - s);
+        float segmentLength = distance(s, e);
+        contrib = T_TWO_PI * (float)trackLength * segmentLength;
+        contrib *= frank_tamm_cherenkov(n, wavelength, photonCount);
+    }
+    float cos_theta = 1.0f / n;
+    float sin_theta = sqrtf(max_(1.0f - cos_theta * cos_theta, 0.0f));
+    float phi = T_TWO_PI * v;
+    float sp, cp;
+    dm_sincos(phi, &sp, &cp);
+    vec3 rayDir = createLocalCOSY(particleDir) * vec3{sin_theta * cp, sin_theta * sp, cos_theta};
+    if (POL) {
+        vec3 polRef = normalize(cross(rayDir, particleDir));
+        return createSourceRay(pos, rayDir, vec4{1.0f, 1.0f, 0.0f, 0.0f}, polRef, time, contrib);
+    }
+    return createSourceRay<false>(pos, rayDir, time, contrib);
+}
 
 // ------------------------------------------------------------------ light sources (forward)
 template <bool POL>
@@ -179,21 +253,16 @@ TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants 
         if (!(c.flags & THEIA_LIGHT_FLAG_FRANK_TAMM_IS)) contrib *= frank_tamm(wavelength, medium.n);
         return createSourceRay<POL>(position, rayDir, startTime, contrib);
     }
-    case THEIA_LIGHT_HOST: {  // sh/lightsource.host.glsl:10-17, LOAD_SAMPLE of sh/lightsource.queue.glsl:40-56
-        const theia_light_host_t& p = c.p.host;
-        const float* q = reinterpret_cast<const float*>(p.queue);
-        const size_t C = p.capacity;
+    case THEIA_LIGHT_CHERENKOV:
+    case THEIA_LIGHT_CHERENKOV_TRACK: {
+        float u = rng.next();
+        float v = rng.next();
+        return cherenkovSample<POL>(c, wavelength, medium.n, u, v);
+    }
+    case THEIA_LIGHT_HOST: {
         const uint32_t k = rng.idx - c.first;
-        if (k >= p.capacity) break;
-        const float* e = q + k;
-        vec3 pos = {__ldg(e), __ldg(e + C), __ldg(e + 2 * C)};
-        vec3 dir = {__ldg(e + 3 * C), __ldg(e + 4 * C), __ldg(e + 5 * C)};
-        if (p.polarized) {
-            vec4 stokes = {__ldg(e + 6 * C), __ldg(e + 7 * C), __ldg(e + 8 * C), __ldg(e + 9 * C)};
-            vec3 polRef = {__ldg(e + 10 * C), __ldg(e + 11 * C), __ldg(e + 12 * C)};
-            return createSourceRay(pos, dir, stokes, polRef, __ldg(e + 13 * C), __ldg(e + 14 * C));
-        }
-        return createSourceRay<POL>(pos, dir, __ldg(e + 6 * C), __ldg(e + 7 * C));
+        if (k >= c.p.host.capacity) break;
+        return hostLightSample<POL>(c.p.host, k);
     }
     }
     SourceRay bad;  // sh/lightsource.common.glsl:28-37
@@ -285,19 +354,37 @@ TDEV PlaneHit planeIntersect(const float objToWorld[9], vec3 center, vec3 nrm, v
     return h;
 }
 
-// sh/target.sphere.glsl:18-43, sh/target.sphere.inner.glsl:18-36, flat / disk as above
-TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
+// flat / disk targets, out of line (see commitHitOther in launch.cuh): sh/target.flat.glsl:15-44,
+// sh/target.disk.glsl:15-40 (sample), sh/target.flat.glsl:46-74, sh/target.disk.glsl:42-68 (intersect)
+static __device__ __noinline__ TargetSample planeTargetSample(const TargetSel& c, vec3 observer, vec2 u) {
     if (c.kind == THEIA_TARGET_FLAT) {
         const theia_target_flat_t& p = c.p.flat;
-        vec2 u = rng.next2();
         vec3 localPos = {p.width * (u.x - 0.5f), p.length * (u.y - 0.5f), 0.0f};
         return planeSample(localPos, p.objToWorld, v3(p.position), v3(p.normal), p.prob, observer);
     }
-    if (c.kind == THEIA_TARGET_DISK) {
-        const theia_target_disk_t& p = c.p.disk;
-        vec3 localPos = p.radius * sampleUnitDisk(rng.next2());
-        return planeSample(localPos, p.objToWorld, v3(p.position), v3(p.normal), p.prob, observer);
-    }
+    const theia_target_disk_t& p = c.p.disk;
+    vec3 localPos = p.radius * sampleUnitDisk(u);
+    return planeSample(localPos, p.objToWorld, v3(p.position), v3(p.normal), p.prob, observer);
+}
+static __device__ __noinline__ TargetSample planeTargetIntersect(const TargetSel& c, vec3 observer, vec3 direction) {
+    TargetSample r;
+    const bool flat = c.kind == THEIA_TARGET_FLAT;
+    PlaneHit h = flat ? planeIntersect(c.p.flat.objToWorld, v3(c.p.flat.position), v3(c.p.flat.normal), observer, direction)
+                      : planeIntersect(c.p.disk.objToWorld, v3(c.p.disk.position), v3(c.p.disk.normal), observer, direction);
+    bool valid = h.t > 0.0f;
+    if (flat) valid = valid && 2.0f * abs_(h.localPos.x) <= c.p.flat.width && 2.0f * abs_(h.localPos.y) <= c.p.flat.length;
+    else valid = valid && length2(h.localPos.x, h.localPos.y) <= c.p.disk.radius;
+    r.position = h.pos; r.normal = h.normal; r.dist = h.t;
+    r.objPosition = h.localPos; r.objNormal = {0.0f, 0.0f, h.side};
+    r.prob = (flat ? c.p.flat.prob : c.p.disk.prob) * (valid ? 1.0f : 0.0f); r.valid = valid;
+    return r;
+}
+TDEV bool isPlaneTarget(uint32_t kind) { return kind == THEIA_TARGET_FLAT || kind == THEIA_TARGET_DISK; }
+
+// sh/target.sphere.glsl:18-43, sh/target.sphere.inner.glsl:18-36 (every shape draws one random2D)
+TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
+    const vec2 u = rng.next2();
+    if (isPlaneTarget(c.kind)) return planeTargetSample(c, observer, u);
     const theia_target_sphere_t& p = c.p.sphere;
     vec3 center = v3(p.position);
     TargetSample t;
@@ -305,7 +392,7 @@ TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
         vec3 dir = normalize(observer - center);
         float d = distance(observer, center);
         float cosOpening = p.radius / d;
-        vec3 normal = createLocalCOSY(dir) * sampleDirectionCone(cosOpening, rng.next2());
+        vec3 normal = createLocalCOSY(dir) * sampleDirectionCone(cosOpening, u);
         vec3 pos = normal * p.radius + center;
         float prob = p.prob / (1.0f - cosOpening);
         bool valid = !isinf_(prob);
@@ -313,7 +400,7 @@ TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
         t.position = pos; t.normal = normal; t.dist = distance(pos, observer);
         t.objPosition = normal; t.objNormal = normal; t.prob = prob; t.valid = valid;
     } else {
-        vec3 normal = sampleUnitSphere(rng.next2());
+        vec3 normal = sampleUnitSphere(u);
         vec3 pos = p.radius * normal + center;
         t.position = pos; t.normal = -normal; t.dist = distance(observer, pos);
         t.objPosition = normal; t.objNormal = -normal; t.prob = p.prob; t.valid = true;
@@ -322,19 +409,8 @@ TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
 }
 // sh/target.sphere.glsl:45-78, sh/target.sphere.inner.glsl:38-56, flat / disk as above
 TDEV TargetSample intersectTarget(const TargetSel& c, vec3 observer, vec3 direction) {
+    if (isPlaneTarget(c.kind)) return planeTargetIntersect(c, observer, direction);
     TargetSample r;
-    if (c.kind == THEIA_TARGET_FLAT || c.kind == THEIA_TARGET_DISK) {
-        const bool flat = c.kind == THEIA_TARGET_FLAT;
-        PlaneHit h = flat ? planeIntersect(c.p.flat.objToWorld, v3(c.p.flat.position), v3(c.p.flat.normal), observer, direction)
-                          : planeIntersect(c.p.disk.objToWorld, v3(c.p.disk.position), v3(c.p.disk.normal), observer, direction);
-        bool valid = h.t > 0.0f;
-        if (flat) valid = valid && 2.0f * abs_(h.localPos.x) <= c.p.flat.width && 2.0f * abs_(h.localPos.y) <= c.p.flat.length;
-        else valid = valid && length2(h.localPos.x, h.localPos.y) <= c.p.disk.radius;
-        r.position = h.pos; r.normal = h.normal; r.dist = h.t;
-        r.objPosition = h.localPos; r.objNormal = {0.0f, 0.0f, h.side};
-        r.prob = (flat ? c.p.flat.prob : c.p.disk.prob) * (valid ? 1.0f : 0.0f); r.valid = valid;
-        return r;
-    }
     const theia_target_sphere_t& p = c.p.sphere;
     vec3 center = v3(p.position);
     vec2 ts = intersectSphere(center, p.radius, observer, direction);
@@ -364,7 +440,7 @@ TDEV TargetSample intersectTarget(const TargetSel& c, vec3 observer, vec3 direct
 // sh/target.sphere.glsl:80-83, sh/target.sphere.inner.glsl:58-60, sh/target.flat.glsl:76-79,
 // sh/target.disk.glsl:70-73 (planes never occlude)
 TDEV bool isOccludedByTarget(const TargetSel& c, vec3 position) {
-    if (c.kind == THEIA_TARGET_FLAT || c.kind == THEIA_TARGET_DISK) return false;
+    if (isPlaneTarget(c.kind)) return false;
     float d = distance(position, v3(c.p.sphere.position));
     return c.kind == THEIA_TARGET_SPHERE ? d <= c.p.sphere.radius : d >= c.p.sphere.radius;
 }
@@ -405,44 +481,51 @@ TDEV void guideCone(const theia_guide_sphere_t& p, vec3 observer, float* d, vec3
     pr *= (*d > p.radius) ? 1.0f : 0.0f;
     *prob = pr;
 }
-// sh/target_guide.sphere.glsl:15-51, sh/target_guide.flat.glsl:15-26, sh/target_guide.disk.glsl:14-21
-TDEV TargetGuideSample sampleTargetGuide(const GuideSel& c, vec3 observer, Rng& rng) {
+// flat / disk guides, out of line: sh/target_guide.flat.glsl:15-26, sh/target_guide.disk.glsl:14-21 (sample),
+// sh/target_guide.flat.glsl:28-47, sh/target_guide.disk.glsl:23-43 (eval)
+static __device__ __noinline__ TargetGuideSample planeGuideSample(const GuideSel& c, vec3 observer, vec2 u) {
     if (c.kind == THEIA_GUIDE_FLAT) {
         const theia_target_flat_t& p = c.p.flat;
-        vec2 u = rng.next2();
         vec3 localPos = {p.width * (u.x - 0.5f), p.length * (u.y - 0.5f), 0.0f};
         vec3 pos = mat3Of(p.objToWorld) * localPos + v3(p.position);
         return guideSampleFromPoint(observer, pos, v3(p.normal), p.prob);
     }
-    if (c.kind == THEIA_GUIDE_DISK) {
-        const theia_target_disk_t& p = c.p.disk;
-        vec3 localPos = p.radius * sampleUnitDisk(rng.next2());
-        vec3 pos = mat3Of(p.objToWorld) * localPos + v3(p.position);
-        return guideSampleFromPoint(observer, pos, v3(p.normal), p.prob);
-    }
+    const theia_target_disk_t& p = c.p.disk;
+    vec3 localPos = p.radius * sampleUnitDisk(u);
+    vec3 pos = mat3Of(p.objToWorld) * localPos + v3(p.position);
+    return guideSampleFromPoint(observer, pos, v3(p.normal), p.prob);
+}
+static __device__ __noinline__ TargetGuideSample planeGuideEval(const GuideSel& c, vec3 observer, vec3 direction) {
+    const bool flat = c.kind == THEIA_GUIDE_FLAT;
+    PlaneHit h = flat ? planeIntersect(c.p.flat.objToWorld, v3(c.p.flat.position), v3(c.p.flat.normal), observer, direction)
+                      : planeIntersect(c.p.disk.objToWorld, v3(c.p.disk.position), v3(c.p.disk.normal), observer, direction);
+    bool valid = h.t > 0.0f && !isinf_(h.t) && !(h.t != h.t);
+    if (flat) valid = valid && 2.0f * abs_(h.localPos.x) <= c.p.flat.width && 2.0f * abs_(h.localPos.y) <= c.p.flat.length;
+    else valid = valid && length2(h.localPos.x, h.localPos.y) <= c.p.disk.radius;
+    float prob = (flat ? c.p.flat.prob : c.p.disk.prob) * (valid ? 1.0f : 0.0f);
+    return guideSampleFromDir(direction, h.t, flat ? v3(c.p.flat.normal) : v3(c.p.disk.normal), prob);
+}
+TDEV bool isPlaneGuide(uint32_t kind) { return kind == THEIA_GUIDE_FLAT || kind == THEIA_GUIDE_DISK; }
+
+// sh/target_guide.sphere.glsl:15-51 (every shape draws two numbers: random2D in the plane shapes, two
+// calls of random in the sphere, which address the same two counters)
+TDEV TargetGuideSample sampleTargetGuide(const GuideSel& c, vec3 observer, Rng& rng) {
+    const vec2 u = rng.next2();
+    if (isPlaneGuide(c.kind)) return planeGuideSample(c, observer, u);
     float d, cosMin, prob;
     vec3 viewDir;
     guideCone(c.p.sphere, observer, &d, &viewDir, &cosMin, &prob);
-    float cosTheta = 1.0f - cosMin * rng.next();
+    float cosTheta = 1.0f - cosMin * u.x;
     float sinTheta = sqrtf(max_(1.0f - cosTheta * cosTheta, 0.0f));
-    float phi = T_TWO_PI * rng.next();
+    float phi = T_TWO_PI * u.y;
     float sp, cp;
     dm_sincos(phi, &sp, &cp);
     vec3 dir = createLocalCOSY(viewDir) * vec3{sinTheta * sp, sinTheta * cp, cosTheta};
     return {dir, d + c.p.sphere.radius, prob};
 }
-// sh/target_guide.sphere.glsl:53-81, sh/target_guide.flat.glsl:28-47, sh/target_guide.disk.glsl:23-43
+// sh/target_guide.sphere.glsl:53-81
 TDEV TargetGuideSample evalTargetGuide(const GuideSel& c, vec3 observer, vec3 direction) {
-    if (c.kind == THEIA_GUIDE_FLAT || c.kind == THEIA_GUIDE_DISK) {
-        const bool flat = c.kind == THEIA_GUIDE_FLAT;
-        PlaneHit h = flat ? planeIntersect(c.p.flat.objToWorld, v3(c.p.flat.position), v3(c.p.flat.normal), observer, direction)
-                          : planeIntersect(c.p.disk.objToWorld, v3(c.p.disk.position), v3(c.p.disk.normal), observer, direction);
-        bool valid = h.t > 0.0f && !isinf_(h.t) && !(h.t != h.t);
-        if (flat) valid = valid && 2.0f * abs_(h.localPos.x) <= c.p.flat.width && 2.0f * abs_(h.localPos.y) <= c.p.flat.length;
-        else valid = valid && length2(h.localPos.x, h.localPos.y) <= c.p.disk.radius;
-        float prob = (flat ? c.p.flat.prob : c.p.disk.prob) * (valid ? 1.0f : 0.0f);
-        return guideSampleFromDir(direction, h.t, flat ? v3(c.p.flat.normal) : v3(c.p.disk.normal), prob);
-    }
+    if (isPlaneGuide(c.kind)) return planeGuideEval(c, observer, direction);
     float d, cosMin, prob;
     vec3 viewDir;
     guideCone(c.p.sphere, observer, &d, &viewDir, &cosMin, &prob);

@@ -129,31 +129,29 @@ TDEV float kernelCdf(float x) {
 // The store-time response consumes one number of the path's stream per hit; it has to be drawn
 // where the reference calls response() (other draws of the path may follow before the warp
 // reaches commitHit): responseDraw() at that point, its value handed to commitHit.
+static __device__ __noinline__ float randomOutOfLine(const theia_philox_params_t* p, PhiloxKey key, uint32_t dim) {
+    return random_s(*p, key, dim);  // a whole Philox block: not worth inlining at every response site
+}
 TDEV float responseDraw(const ResponseDev& r, Rng& rng, bool has, const HitItem& item) {
-    return (r.kind == THEIA_RESPONSE_STORE_TIME && has && item.contrib > 0.0f) ? rng.next() : 2.0f;
+    if (r.kind != THEIA_RESPONSE_STORE_TIME || !has || !(item.contrib > 0.0f)) return 2.0f;
+    float u = randomOutOfLine(rng.p, rng.key, rng.dim);
+    rng.dim += 1;
+    return u;
 }
-TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
-                        float u);
-// Returns whether the lane's hit reached the response (the call sites number a path's responses
-// inside an event with it: test tags).
-TDEV bool commitHit(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
-                    uint32_t& nResponses, float u) {
-    has = has && item.contrib > 0.0f;  // "if (hit.contrib > 0.0) response(hit)" at every call site
-    if (has) nResponses++;
-    commitHitImpl(r, hist, has, item, path, tag, u);
-    return has;
-}
-TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
-                        float u) {
+// Responses other than record / histogram live out of line: inlined at every call site they made
+// the tracing kernels (which already run at the limit of the instruction cache) 30 % larger and
+// measurably slower. Scalars only: handing over the hit by reference would pin it to local memory.
+static __device__ __noinline__ void commitHitOther(const ResponseDev& r, float* hist, bool has, float time, float contrib,
+                                                   int32_t objectId, uint32_t path, uint32_t tag, float u) {
     if (r.kind == THEIA_RESPONSE_KERNEL_HISTOGRAM) {  // sh/response.histogram.kernel.glsl:72-101
         if (!has) return;
-        const float value = item.contrib;  // sh/response.uniform.glsl:4-6
-        float t = item.time - r.t0;
+        const float value = contrib;  // sh/response.uniform.glsl:4-6
+        float t = time - r.t0;
         int32_t firstBin = floatToInt(floorf((t - r.kernel_support) / r.binSize));
         int32_t lastBin = floatToInt(ceilf((t + r.kernel_support) / r.binSize));
         firstBin = max(firstBin, 0);
         lastBin = min(lastBin, (int32_t)r.n_bins) - 1;
-        t = (float)firstBin * r.binSize + r.t0 - item.time;
+        t = (float)firstBin * r.binSize + r.t0 - time;
         const float h = 1.0f / r.kernel_bandwidth;
         float prev_cdf = kernelCdf(t * h);
         for (int32_t i = firstBin; i <= lastBin; ++i) {
@@ -165,7 +163,7 @@ TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitIt
         }
     } else if (r.kind == THEIA_RESPONSE_STORE_TIME) {  // sh/response.time.store.glsl:14-26
         bool keep = false;
-        if (has) keep = u < item.contrib;
+        if (has) keep = u < contrib;
         uint32_t act = __ballot_sync(FULL_MASK, keep);
         if (act == 0) return;
         uint32_t leader = __ffs(act) - 1;
@@ -175,26 +173,29 @@ TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitIt
         if (!keep) return;
         uint32_t slot = base + __popc(act & laneMaskLt());
         if (slot < r.value_capacity) {
-            reinterpret_cast<float*>(r.value_queue + 1)[slot] = item.time;
-            if (r.store_object_id) reinterpret_cast<int32_t*>(r.value_queue + 1)[(size_t)r.value_capacity + slot] = item.objectId;
+            reinterpret_cast<float*>(r.value_queue + 1)[slot] = time;
+            if (r.store_object_id) reinterpret_cast<int32_t*>(r.value_queue + 1)[(size_t)r.value_capacity + slot] = objectId;
             if (r.tag_path) r.tag_path[slot] = path;
             if (r.tag_event) r.tag_event[slot] = tag;
         }
     } else if (r.kind == THEIA_RESPONSE_OBJECT_HISTOGRAM) {
         uint32_t key = 0;
         if (has) {
-            uint32_t bin = histogramBin(r, item.time);
-            has = bin < r.n_bins && (uint32_t)item.objectId < r.n_objects;
-            key = (uint32_t)item.objectId * r.n_bins + bin;
+            uint32_t bin = histogramBin(r, time);
+            has = bin < r.n_bins && (uint32_t)objectId < r.n_objects;
+            key = (uint32_t)objectId * r.n_bins + bin;
         }
         uint32_t act = __ballot_sync(FULL_MASK, has);
         if (act == 0 || !has) return;
-        float value = item.contrib;
         uint32_t peers = __match_any_sync(act, key);
         float sum = 0.0f;
-        for (uint32_t m = peers; m; m &= m - 1) sum += __shfl_sync(peers, value, __ffs(m) - 1);
+        for (uint32_t m = peers; m; m &= m - 1) sum += __shfl_sync(peers, contrib, __ffs(m) - 1);
         if (laneId() == (uint32_t)(__ffs(peers) - 1)) atomicAdd(r.object_hist + key, sum);
-    } else if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
+    }
+}
+TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
+                        float u) {
+    if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
         uint32_t bin = 0;
         if (has) {
             bin = histogramBin(r, item.time);
@@ -222,9 +223,20 @@ TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitIt
             if (r.tag_path) r.tag_path[slot] = path;
             if (r.tag_event) r.tag_event[slot] = tag;
         }
+    } else if (r.kind != THEIA_RESPONSE_EMPTY) {
+        commitHitOther(r, hist, has, item.time, item.contrib, item.objectId, path, tag, u);
     }
 }
 
+// Returns whether the lane's hit reached the response (the call sites number a path's responses
+// inside an event with it: test tags).
+TDEV bool commitHit(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
+                    uint32_t& nResponses, float u) {
+    has = has && item.contrib > 0.0f;  // "if (hit.contrib > 0.0) response(hit)" at every call site
+    if (has) nResponses++;
+    commitHitImpl(r, hist, has, item, path, tag, u);
+    return has;
+}
 // sh/callback.stat.glsl:21-62: counter index of a result code (-1: not counted by name)
 TDEV int statIndex(int code) {
     switch (code) {

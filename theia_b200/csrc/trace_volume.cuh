@@ -39,7 +39,7 @@ TDEV bool volumeCreateResponse(const DeviceLaunch& P, Ray ray, const TargetSampl
 }
 
 template <bool POL>
-__global__ void __launch_bounds__(128) volumeForwardKernel(const __grid_constant__ DeviceLaunch P) {
+__global__ void __launch_bounds__(128, 4) volumeForwardKernel(const __grid_constant__ DeviceLaunch P) {
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
     sinkInit(P, &sh, sharedHist);
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(128) volumeForwardKernel(const __grid_constant
 // absorption roulette. Same persistent-warp form as the forward tracer: the state of a path
 // stays in registers, finished lanes take the next path of the warp's range.
 template <bool POL>
-__global__ void __launch_bounds__(128) volumePhotonKernel(const __grid_constant__ DeviceLaunch P) {
+__global__ void __launch_bounds__(128, 4) volumePhotonKernel(const __grid_constant__ DeviceLaunch P) {
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
     sinkInit(P, &sh, sharedHist);

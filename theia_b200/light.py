@@ -16,11 +16,12 @@ import numpy as np
 
 import theia_b200.units as u
 from theia_b200 import _abi
-from theia_b200.glsl import vec2, vec3, vec4
+from theia_b200.glsl import buffer_reference, vec2, vec3, vec4
 from theia_b200.pipeline import SourceCodeMixin
 
 __all__ = [
-    "ConeLightSource", "ConstWavelengthSource", "HostLightSource", "HostWavelengthSource", "LightSampleItem",
+    "CherenkovLightSource", "CherenkovTrackLightSource", "ConeLightSource", "ConstWavelengthSource",
+    "FunctionWavelengthSource", "HostLightSource", "HostWavelengthSource", "LightSampleItem", "ParticleTrack",
     "LightSource", "MuonTrackLightSource", "ParticleCascadeLightSource", "PencilLightSource",
     "PolarizedLightSampleItem", "SphericalLightSource", "StreamingHostLightSource",
     "StreamingHostWavelengthSource", "UniformWavelengthSource", "WavelengthSampleItem", "WavelengthSource",
@@ -156,6 +157,43 @@ class StreamingHostWavelengthSource(HostWavelengthSource):
     @staticmethod
     def _updateData(source: HostWavelengthSource, i: int) -> None:
         _streamInto(source, i, "StreamingHostWavelengthSource")
+
+
+class FunctionWavelengthSource(WavelengthSource):
+    """
+    Importance samples wavelengths from ``fn`` (nm -> density): the distribution is integrated
+    and inverted numerically on the host and uploaded as a look-up table of the inverse CDF
+    (src/theia/light.py:351-414, sh/wavelengthsource.function.glsl). The contribution of every
+    sample is the integral of ``fn`` over ``lambdaRange``.
+    """
+
+    name = "Function Wavelength Source"
+    _kind = _abi.WAVELENGTH_FUNCTION
+
+    class WavelengthParams(Structure):
+        _pack_ = 4
+        _fields_ = [("_table", c_uint64), ("_contrib", c_float)]
+
+    def __init__(self, fn: Callable[[float], float], *, lambdaRange: tuple[float, float] = (300.0, 700.0),
+                 numSamples: int = 1024) -> None:
+        super().__init__(nRNGSamples=1, params={"WavelengthParams": self.WavelengthParams})
+        self._updateFn(fn, lambdaRange, numSamples)
+
+    def _updateFn(self, fn, lambdaRange, numSamples: int) -> None:
+        from scipy.integrate import quad
+        from scipy.stats.sampling import NumericalInversePolynomial
+        from theia_b200.lookup import uploadTables
+
+        contrib, _ = quad(fn, *lambdaRange)
+
+        class Dist:
+            def pdf(self, x):
+                return fn(x)
+
+        inv_cdf = NumericalInversePolynomial(Dist(), domain=lambdaRange)
+        x = inv_cdf.ppf(np.linspace(0.0, 1.0, numSamples))
+        self._tableMemory, [adr] = uploadTables([x])
+        self.setParams(_table=adr, _contrib=contrib)
 
 
 class ConstWavelengthSource(WavelengthSource):
@@ -340,6 +378,134 @@ class StreamingHostLightSource(HostLightSource):
     @staticmethod
     def _updateData(source: HostLightSource, i: int) -> None:
         _streamInto(source, i, "StreamingHostLightSource")
+
+
+class CherenkovLightSource(LightSource):
+    """
+    Cherenkov light of a straight track between ``trackStart`` and ``trackEnd`` travelled at the
+    speed of light (beta = 1): emission points uniform along the track, directions on the
+    Cherenkov cone of the medium's refractive index at the sampled wavelength; polarised tracers
+    get linearly polarised light. The contribution is the Frank-Tamm yield in eV or, with
+    ``usePhotonCount``, in photons (src/theia/light.py:1183-1271,
+    sh/lightsource.cherenkov.simple.glsl). Forward sampling only in this build.
+    """
+
+    name = "Cherenkov Light Source"
+    _kind = _abi.LIGHT_CHERENKOV
+
+    class LightParams(Structure):
+        _fields_ = [("trackStart", vec3), ("startTime", c_float), ("trackEnd", vec3), ("endTime", c_float),
+                    ("_trackDir", vec3), ("_trackDist", c_float)]
+
+    def __init__(self, *, trackStart=(0.0, 0.0, 0.0), trackEnd=(100.0, 0.0, 0.0), startTime: float = 0.0 * u.ns,
+                 endTime: float = 100.0 * u.m / u.c, usePhotonCount: bool = False) -> None:
+        super().__init__(supportForward=True, supportBackward=True, nRNGForward=2, nRNGBackward=0,
+                         params={"LightParams": self.LightParams})
+        self._usePhotonCount = usePhotonCount
+        self.setParams(trackStart=trackStart, trackEnd=trackEnd, startTime=startTime, endTime=endTime)
+
+    @property
+    def usePhotonCount(self) -> bool:
+        """Whether to sample radiance in eV or #photons"""
+        return self._usePhotonCount
+
+    @property
+    def _flags(self) -> int:
+        return _abi.LIGHT_FLAG_PHOTON_COUNT if self._usePhotonCount else 0
+
+    def _finishParams(self, i: int) -> None:
+        d = np.array(self.getParam("trackEnd"), dtype=np.float64) - np.array(self.getParam("trackStart"), dtype=np.float64)
+        dist = np.sqrt(np.square(d).sum(-1))
+        self.setParams(_trackDir=d / dist, _trackDist=dist)
+
+
+class ParticleTrack:
+    """
+    Particle track on the device: ``uint32 length`` (number of segments) followed by ``capacity``
+    vertices ``(x, y, z, t)`` (src/theia/light.py:1274-1353). The reference maps one tensor into
+    host and device address space; here a host copy is edited and ``setVertices`` / ``flush``
+    push it to the device.
+    """
+
+    class Header(Structure):
+        _fields_ = [("length", c_uint32)]
+
+    class Vertex(Structure):
+        _fields_ = [("x", c_float), ("y", c_float), ("z", c_float), ("t", c_float)]
+
+    def __init__(self, capacity: int) -> None:
+        from theia_b200 import _device
+        self._capacity = capacity
+        self._host = np.zeros(1 + 4 * capacity, dtype=np.uint32)
+        self._tensor = _device.alloc(self._host.nbytes, _device.currentDevice())
+
+    @property
+    def capacity(self) -> int:
+        """Maximum number of vertices this track can store"""
+        return self._capacity
+
+    @property
+    def address(self) -> int:
+        """Device address of the track"""
+        return self._tensor.data_ptr()
+
+    @property
+    def length(self) -> int:
+        """Number of segments in the track, i.e. number of vertices - 1"""
+        return int(self._host[0])
+
+    @length.setter
+    def length(self, value: int) -> None:
+        if not 0 <= value <= self.capacity - 1:
+            raise ValueError("length must be between 0 and (capacity - 1)")
+        self._host[0] = value
+
+    def numpy(self, flat: bool = False) -> np.ndarray:
+        """Host copy of the vertices: structured, or ``(capacity, 4)`` floats if ``flat``"""
+        f = self._host[1:].view(np.float32).reshape(-1, 4)
+        return f if flat else f.view([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("t", "<f4")]).reshape(-1)
+
+    def flush(self) -> None:
+        """Copies the host copy to the device"""
+        import torch
+        self._tensor[: self._host.nbytes].copy_(torch.from_numpy(self._host.view(np.uint8)))
+
+    def setVertices(self, data) -> None:
+        """Copies vertices of shape (length + 1, 4) = (x[m], y[m], z[m], t[ns]) into the track"""
+        data = np.asarray(data, dtype=np.float32)
+        self.numpy(True)[: len(data)] = data
+        self.length = len(data) - 1
+        self.flush()
+
+
+class CherenkovTrackLightSource(LightSource):
+    """
+    Cherenkov light of a piecewise linear ``ParticleTrack`` (beta = 1): a segment is picked
+    uniformly, then sampled like ``CherenkovLightSource``
+    (src/theia/light.py:1356-1410, sh/lightsource.cherenkov.track.glsl).
+    """
+
+    name = "Cherenkov Track Light Source"
+    _kind = _abi.LIGHT_CHERENKOV_TRACK
+
+    class TrackParams(Structure):
+        _fields_ = [("track", buffer_reference)]
+
+    def __init__(self, track: "ParticleTrack | int | None" = None, *, usePhotonCount: bool = False) -> None:
+        super().__init__(supportForward=True, supportBackward=False, nRNGForward=2,
+                         params={"TrackParams": self.TrackParams})
+        self._usePhotonCount = usePhotonCount
+        self._trackObject = track if isinstance(track, ParticleTrack) else None
+        adr = track.address if isinstance(track, ParticleTrack) else (track if track is not None else 0)
+        self.setParams(track=adr)
+
+    @property
+    def usePhotonCount(self) -> bool:
+        return self._usePhotonCount
+
+    @property
+    def _flags(self) -> int:
+        return _abi.LIGHT_FLAG_PHOTON_COUNT if self._usePhotonCount else 0
 
 
 class ConeLightSource(LightSource):
