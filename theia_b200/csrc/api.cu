@@ -381,7 +381,11 @@ static int plan(const theia_trace_launch_t* L, const DeviceLaunch& D, KernelPlan
     const bool pol = L->polarized != 0;
     size_t smem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
     if (L->tracer == THEIA_TRACER_VOLUME_FORWARD) {
-        K.fn = pol ? (const void*)volumeForwardKernel<true> : (const void*)volumeForwardKernel<false>;
+        // the lean build of the kernel serves the components of the first round (see FULL in components.cuh)
+        const bool lean = D.light.kind <= THEIA_LIGHT_MUON && D.wavelength.kind <= THEIA_WAVELENGTH_UNIFORM &&
+                          D.target.kind <= THEIA_TARGET_INNER_SPHERE && D.response.kind <= THEIA_RESPONSE_HISTOGRAM;
+        if (lean) K.fn = pol ? (const void*)volumeForwardKernel<true, false> : (const void*)volumeForwardKernel<false, false>;
+        else K.fn = pol ? (const void*)volumeForwardKernel<true, true> : (const void*)volumeForwardKernel<false, true>;
     } else if (L->tracer == THEIA_TRACER_VOLUME_PHOTON) {
         K.fn = pol ? (const void*)volumePhotonKernel<true> : (const void*)volumePhotonKernel<false>;
     } else {

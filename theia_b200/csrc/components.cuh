@@ -42,8 +42,16 @@ struct GuideSel { uint32_t kind; GuideBlock p; };
 
 // ------------------------------------------------------------------ wavelength sources
 // sh/wavelengthsource.const.glsl:10-12, sh/wavelengthsource.uniform.glsl:12-16
+// FULL = false (here and below): the caller guarantees that none of the components that were added late
+// (host / function / Cherenkov sources, plane targets, responses beyond record and histogram) is in
+// use, and their code is left out: the volume kernel runs at the limit of the instruction cache.
+template <bool FULL = true>
 TDEV WavelengthSample sampleWavelength(const WavelengthSel& c, Rng& rng) {
     if (c.kind == THEIA_WAVELENGTH_CONST) return {c.p.constant.lambda, 1.0f};
+    if (!FULL) {
+        float u0 = rng.next();
+        return {mix_(c.p.uniform.lam_min, c.p.uniform.lam_max, u0), c.p.uniform.contrib};
+    }
     if (c.kind == THEIA_WAVELENGTH_HOST) {  // sh/wavelengthsource.host.glsl:10-13
         const float* q = reinterpret_cast<const float*>(c.p.host.queue);
         const uint32_t k = rng.idx - c.first, C = c.p.host.capacity;
@@ -182,7 +190,7 @@ static __device__ __noinline__ SourceRay cherenkovSample(const LightSel& c, floa
 }
 
 // ------------------------------------------------------------------ light sources (forward)
-template <bool POL>
+template <bool POL, bool FULL = true>
 TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants medium, Rng& rng,
                            PreGamma pre = PreGamma{false, 0.0f, 0u}) {
     switch (c.kind) {
@@ -255,11 +263,13 @@ TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants 
     }
     case THEIA_LIGHT_CHERENKOV:
     case THEIA_LIGHT_CHERENKOV_TRACK: {
+        if (!FULL) break;
         float u = rng.next();
         float v = rng.next();
         return cherenkovSample<POL>(c, wavelength, medium.n, u, v);
     }
     case THEIA_LIGHT_HOST: {
+        if (!FULL) break;
         const uint32_t k = rng.idx - c.first;
         if (k >= c.p.host.capacity) break;
         return hostLightSample<POL>(c.p.host, k);
@@ -273,12 +283,12 @@ TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants 
 }
 
 // sh/tracer.volume.forward.glsl:223-229, sh/tracer.scene.forward.glsl:50-56
-template <bool POL>
+template <bool POL, bool FULL = true>
 TDEV Ray sampleRay(const WavelengthSel& wl, const LightSel& light, uint64_t medium, Rng& rng,
                    PreGamma pre = PreGamma{false, 0.0f, 0u}) {
-    WavelengthSample photon = sampleWavelength(wl, rng);
+    WavelengthSample photon = sampleWavelength<FULL>(wl, rng);
     MediumConstants constants = lookUpMedium(medium, photon.wavelength);
-    SourceRay lightRay = sampleLight<POL>(light, photon.wavelength, constants, rng, pre);
+    SourceRay lightRay = sampleLight<POL, FULL>(light, photon.wavelength, constants, rng, pre);
     return createRay(lightRay, medium, constants, photon);
 }
 
@@ -302,7 +312,9 @@ TDEV TargetSample createTargetSampleMiss() {  // :77-91
 // GLSL column major mat3 of a parameter block; transposeOf = transpose(objToWorld)
 TDEV mat3 mat3Of(const float m[9]) { return {{m[0], m[1], m[2]}, {m[3], m[4], m[5]}, {m[6], m[7], m[8]}}; }
 TDEV mat3 transposeOf(const float m[9]) { return {{m[0], m[3], m[6]}, {m[1], m[4], m[7]}, {m[2], m[5], m[8]}}; }
+template <bool FULL = true>
 TDEV mat3 targetWorldToObj(const TargetSel& c) {
+    if (!FULL) return mat3_diag(c.p.sphere.invRad);
     switch (c.kind) {
     case THEIA_TARGET_FLAT: return transposeOf(c.p.flat.objToWorld);
     case THEIA_TARGET_DISK: return transposeOf(c.p.disk.objToWorld);
@@ -382,9 +394,10 @@ static __device__ __noinline__ TargetSample planeTargetIntersect(const TargetSel
 TDEV bool isPlaneTarget(uint32_t kind) { return kind == THEIA_TARGET_FLAT || kind == THEIA_TARGET_DISK; }
 
 // sh/target.sphere.glsl:18-43, sh/target.sphere.inner.glsl:18-36 (every shape draws one random2D)
+template <bool FULL = true>
 TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
     const vec2 u = rng.next2();
-    if (isPlaneTarget(c.kind)) return planeTargetSample(c, observer, u);
+    if (FULL && isPlaneTarget(c.kind)) return planeTargetSample(c, observer, u);
     const theia_target_sphere_t& p = c.p.sphere;
     vec3 center = v3(p.position);
     TargetSample t;
@@ -408,8 +421,9 @@ TDEV TargetSample sampleTarget(const TargetSel& c, vec3 observer, Rng& rng) {
     return t;
 }
 // sh/target.sphere.glsl:45-78, sh/target.sphere.inner.glsl:38-56, flat / disk as above
+template <bool FULL = true>
 TDEV TargetSample intersectTarget(const TargetSel& c, vec3 observer, vec3 direction) {
-    if (isPlaneTarget(c.kind)) return planeTargetIntersect(c, observer, direction);
+    if (FULL && isPlaneTarget(c.kind)) return planeTargetIntersect(c, observer, direction);
     TargetSample r;
     const theia_target_sphere_t& p = c.p.sphere;
     vec3 center = v3(p.position);
@@ -439,8 +453,9 @@ TDEV TargetSample intersectTarget(const TargetSel& c, vec3 observer, vec3 direct
 }
 // sh/target.sphere.glsl:80-83, sh/target.sphere.inner.glsl:58-60, sh/target.flat.glsl:76-79,
 // sh/target.disk.glsl:70-73 (planes never occlude)
+template <bool FULL = true>
 TDEV bool isOccludedByTarget(const TargetSel& c, vec3 position) {
-    if (isPlaneTarget(c.kind)) return false;
+    if (FULL && isPlaneTarget(c.kind)) return false;
     float d = distance(position, v3(c.p.sphere.position));
     return c.kind == THEIA_TARGET_SPHERE ? d <= c.p.sphere.radius : d >= c.p.sphere.radius;
 }

@@ -132,7 +132,9 @@ TDEV float kernelCdf(float x) {
 static __device__ __noinline__ float randomOutOfLine(const theia_philox_params_t* p, PhiloxKey key, uint32_t dim) {
     return random_s(*p, key, dim);  // a whole Philox block: not worth inlining at every response site
 }
+template <bool FULL = true>
 TDEV float responseDraw(const ResponseDev& r, Rng& rng, bool has, const HitItem& item) {
+    if (!FULL) return 2.0f;
     if (r.kind != THEIA_RESPONSE_STORE_TIME || !has || !(item.contrib > 0.0f)) return 2.0f;
     float u = randomOutOfLine(rng.p, rng.key, rng.dim);
     rng.dim += 1;
@@ -193,6 +195,7 @@ static __device__ __noinline__ void commitHitOther(const ResponseDev& r, float* 
         if (laneId() == (uint32_t)(__ffs(peers) - 1)) atomicAdd(r.object_hist + key, sum);
     }
 }
+template <bool FULL>
 TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
                         float u) {
     if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
@@ -223,18 +226,19 @@ TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitIt
             if (r.tag_path) r.tag_path[slot] = path;
             if (r.tag_event) r.tag_event[slot] = tag;
         }
-    } else if (r.kind != THEIA_RESPONSE_EMPTY) {
+    } else if (FULL && r.kind != THEIA_RESPONSE_EMPTY) {
         commitHitOther(r, hist, has, item.time, item.contrib, item.objectId, path, tag, u);
     }
 }
 
 // Returns whether the lane's hit reached the response (the call sites number a path's responses
 // inside an event with it: test tags).
+template <bool FULL = true>
 TDEV bool commitHit(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
                     uint32_t& nResponses, float u) {
     has = has && item.contrib > 0.0f;  // "if (hit.contrib > 0.0) response(hit)" at every call site
     if (has) nResponses++;
-    commitHitImpl(r, hist, has, item, path, tag, u);
+    commitHitImpl<FULL>(r, hist, has, item, path, tag, u);
     return has;
 }
 // sh/callback.stat.glsl:21-62: counter index of a result code (-1: not counted by name)

@@ -26,7 +26,7 @@ TDEV float jacobian_dAdW(vec3 obs, vec3 pos, vec3 nrm) {
 
 // sh/tracer.volume.forward.glsl:51-82. Works on a copy of the ray; returns whether a hit item
 // was produced (the contrib > 0 test happens in commitHit).
-template <bool POL>
+template <bool POL, bool FULL>
 TDEV bool volumeCreateResponse(const DeviceLaunch& P, Ray ray, const TargetSample& hit, vec3 dir, float weight,
                                bool scattered, HitItem& item) {
     if (!hit.valid) return false;
@@ -34,11 +34,11 @@ TDEV bool volumeCreateResponse(const DeviceLaunch& P, Ray ray, const TargetSampl
     int code = propagateRayToHit<POL>(ray, hit.position, hit.normal, P.propagation);
     if (code < 0) return false;
     ray.lin_contrib *= weight;
-    item = createHit<POL>(ray, hit.objPosition, hit.objNormal, P.objectId, targetWorldToObj(P.target));
+    item = createHit<POL>(ray, hit.objPosition, hit.objNormal, P.objectId, targetWorldToObj<FULL>(P.target));
     return true;
 }
 
-template <bool POL>
+template <bool POL, bool FULL>
 __global__ void __launch_bounds__(128, 4) volumeForwardKernel(const __grid_constant__ DeviceLaunch P) {
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
@@ -91,12 +91,12 @@ __global__ void __launch_bounds__(128, 4) volumeForwardKernel(const __grid_const
         bool aborted = false;
         if (created) {
             rng = makeRng(&P.rng, idx);
-            ray = sampleRay<POL>(P.wavelength, P.light, P.medium, rng);
+            ray = sampleRay<POL, FULL>(P.wavelength, P.light, P.medium, rng);
             nPaths++;
-            aborted = isOccludedByTarget(P.target, ray.position);
+            aborted = isOccludedByTarget<FULL>(P.target, ray.position);
             if (!aborted && MIS && DIRECT) {
-                TargetSample directHit = intersectTarget(P.target, ray.position, ray.direction);
-                has = volumeCreateResponse<POL>(P, ray, directHit, ray.direction, 1.0f, false, item);
+                TargetSample directHit = intersectTarget<FULL>(P.target, ray.position, ray.direction);
+                has = volumeCreateResponse<POL, FULL>(P, ray, directHit, ray.direction, 1.0f, false, item);
             }
         } else if (alive) {
             scatterRay<POL>(ray, rng.next2());
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(128, 4) volumeForwardKernel(const __grid_const
         onEvent<POL>(P.callback, &sh, created, ray, THEIA_RESULT_RAY_CREATED, k, 0);
         onEvent<POL>(P.callback, &sh, aborted, ray, THEIA_ERROR_TRACE_ABORT, k, 0);
         if (aborted) alive = false;
-        has = commitHit(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
+        has = commitHit<FULL>(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
 
         // ---- stage 2: trace (:153-208)
@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(128, 4) volumeForwardKernel(const __grid_const
             const bool allowResponse = seg == 0 ? DIRECT_LIGHTING : ALLOW_RESPONSE;
             float u = rng.next();
             float dist = sampleScatterLength(ray, P.propagation, u);
-            TargetSample hit = intersectTarget(P.target, ray.position, ray.direction);
+            TargetSample hit = intersectTarget<FULL>(P.target, ray.position, ray.direction);
             bool hitValid = hit.valid && (hit.dist <= dist);
             dist = min_(hit.dist, dist);
             result = propagateRay(ray, dist, P.propagation);
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(128, 4) volumeForwardKernel(const __grid_const
             if (result >= 0) {
                 if (hitValid && allowResponse) {
                     alignRayToHit<POL>(ray, hit.normal);
-                    item = createHit<POL>(ray, hit.objPosition, hit.objNormal, P.objectId, targetWorldToObj(P.target));
+                    item = createHit<POL>(ray, hit.objPosition, hit.objNormal, P.objectId, targetWorldToObj<FULL>(P.target));
                     has = true;
                     result = THEIA_RESULT_RAY_DETECTED;
                 } else if (hitValid) {
@@ -142,22 +142,22 @@ __global__ void __launch_bounds__(128, 4) volumeForwardKernel(const __grid_const
         if (wantMIS) {
             float pPP;
             vec3 dirPhase = scatter(P.medium, ray.direction, rng.next2(), &pPP);
-            TargetSample phaseHit = intersectTarget(P.target, ray.position, dirPhase);
-            targetHit = sampleTarget(P.target, ray.position, rng);
+            TargetSample phaseHit = intersectTarget<FULL>(P.target, ray.position, dirPhase);
+            targetHit = sampleTarget<FULL>(P.target, ray.position, rng);
             dirTarget = normalize(targetHit.position - ray.position);
             float pTT = targetHit.prob * jacobian_dAdW(ray.position, targetHit.position, targetHit.normal);
             float pPT = scatterProb(P.medium, ray.direction, dirTarget);
             float pTP = phaseHit.prob * jacobian_dAdW(ray.position, phaseHit.position, phaseHit.normal);
             wTarget = pTT * pPT / (pTT * pTT + pPT * pPT);
             float wPhase = pPP * pPP / (pPP * pPP + pTP * pTP);
-            has = volumeCreateResponse<POL>(P, ray, phaseHit, dirPhase, wPhase, true, item);
+            has = volumeCreateResponse<POL, FULL>(P, ray, phaseHit, dirPhase, wPhase, true, item);
         }
-        has = commitHit(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
+        has = commitHit<FULL>(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
         // ---- stage 4: MIS, target sample
         has = false;
-        if (wantMIS) has = volumeCreateResponse<POL>(P, ray, targetHit, dirTarget, wTarget, true, item);
-        has = commitHit(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
+        if (wantMIS) has = volumeCreateResponse<POL, FULL>(P, ray, targetHit, dirTarget, wTarget, true, item);
+        has = commitHit<FULL>(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
 
         // ---- events and path bookkeeping (:254-275)
         onEvent<POL>(P.callback, &sh, alive, ray, result, k, seg + 1);
