@@ -45,7 +45,9 @@ static_assert(sizeof(TriRec) == 48, "TriRec layout");
 
 #define THEIA_BLAS_MAGIC 0x534C4254u  // "TBLS"
 #define THEIA_TLAS_MAGIC 0x534C5454u  // "TTLS"
+#ifndef THEIA_LEAF_MAX
 #define THEIA_LEAF_MAX 4
+#endif
 #define THEIA_STACK_SIZE 128  // traversal stack entries per ray
 
 struct alignas(16) BlasHeader {  // 64 bytes, followed by nodes then triangles

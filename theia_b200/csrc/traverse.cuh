@@ -101,12 +101,18 @@ TDEV RayHit closestHit(const SceneView& sc, vec3 origin, vec3 dir, float tmax, T
         if (mask == 0) continue;
         const uint32_t imask = n.a.w >> 24;
 
-        // ---- leaves first (BLAS: triangles now; TLAS: instances are pushed like inner nodes)
+        // ---- leaves first (BLAS: triangles now; TLAS: instances are pushed like inner nodes), nearest
+        // leaf first (slot order along the node's widest axis), and a leaf whose box starts behind the
+        // closest hit so far is skipped
         uint32_t leafMask = mask & ~imask;
-        if (inBlas) {
+        if (inBlas && leafMask) {
+            const uint32_t axisL = (n.b.x >> 30);
+            const float idirL = axisL == 0 ? obj.ix : (axisL == 1 ? obj.iy : obj.iz);
+            const bool fwdL = idirL >= 0.0f;
             while (leafMask) {
-                const int i = __ffs(leafMask) - 1;
-                leafMask &= leafMask - 1;
+                const int i = fwdL ? (__ffs(leafMask) - 1) : (31 - __clz(leafMask));
+                leafMask &= ~(1u << i);
+                if (best.valid && tmin[i] > best.t) continue;
                 const uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, i & 3);
                 const uint32_t count = meta & 7u, first = n.b.y + (meta >> 3);
                 for (uint32_t k = 0; k < count; ++k) {
