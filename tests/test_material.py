@@ -107,3 +107,41 @@ def test_medium_tables_and_store_layout():
         assert rec[:8].view(np.uint64)[0] == store.media[med.name] and rec[8:16].view(np.uint64)[0] == 0
         fl = rec[16:24].view(np.uint32)
         assert fl[0] == int(material.parseMaterialFlags("TR")) and fl[1] == int(material.parseMaterialFlags("B"))
+
+
+def test_material_archive_round_trip(tmp_path):
+    # src/theia/material.py:715-881: material.json + media/<name> (npz), as a directory or a zip file
+    import json
+    from zipfile import ZipFile
+    import pytest
+    from theia_b200 import material
+    from theia_b200.testing import WaterTestModel
+    water = WaterTestModel().createMedium()
+    glass = material.BK7Model().createMedium()
+    mats = [material.Material("lens", glass, water, flags=("TR", "T")), material.Material("det", None, water, flags="DB")]
+    for target in (tmp_path / "mats.zip", tmp_path / "dir"):
+        if target.suffix != ".zip":
+            target.mkdir()
+        material.saveMaterials(target, mats)
+        if target.suffix == ".zip":
+            with ZipFile(target) as z:
+                assert sorted(z.namelist()) == ["material.json", f"media/{glass.name}", f"media/{water.name}"]
+                assert {e["name"] for e in json.loads(z.read("material.json"))} == {"lens", "det"}
+        else:
+            assert (target / "material.json").is_file() and (target / "media" / water.name).is_file()
+        got, media = material.loadMaterials(target)
+        assert set(got) == {"lens", "det"} and set(media) == {water.name, glass.name}
+        assert got["lens"].flagsInward == mats[0].flagsInward and got["lens"].flagsOutward == mats[0].flagsOutward
+        assert got["det"].inside is None and got["det"].outside.name == water.name
+        for name, m in ((water.name, water), (glass.name, glass)):
+            assert media[name].lambda_min == m.lambda_min and media[name].lambda_max == m.lambda_max
+            for prop in material.Medium._PROPS:
+                a, b = getattr(media[name], prop), getattr(m, prop)
+                assert (a is None) == (b is None) and (a is None or np.array_equal(a, b))
+        # the loaded materials build the same device tables
+        s1, s2 = material.MaterialStore(mats), material.MaterialStore(list(got.values()))
+        assert bytes(s1._tensor.cpu().numpy()[:64]) != b"" and s1._tensor.numel() == s2._tensor.numel()
+    with pytest.raises(ValueError):
+        material.saveMaterials(tmp_path / "bad.zip", [material.Material("m", "nowhere", None, flags="T")])
+    with pytest.raises(ValueError):
+        material.loadMaterials(tmp_path / "missing")

@@ -406,6 +406,21 @@ static int plan(const theia_trace_launch_t* L, const DeviceLaunch& D, KernelPlan
     return 0;
 }
 
+// The wavefront kernels exist in a lean instantiation without the components that were added late
+// (see FULL in components.cuh); which one a launch needs:
+static bool leanLaunch(const DeviceLaunch& D) {
+    return D.light.kind <= THEIA_LIGHT_MUON && D.wavelength.kind <= THEIA_WAVELENGTH_UNIFORM &&
+           D.guide.kind <= THEIA_GUIDE_SPHERE && D.response.kind <= THEIA_RESPONSE_HISTOGRAM && D.photon == 0;
+}
+struct WavefrontKernels { const void *gen, *shade, *shadow; };
+static WavefrontKernels wavefrontKernels(bool pol, bool lean) {
+    if (lean)
+        return pol ? WavefrontKernels{(const void*)wfGenerateKernel<true, false>, (const void*)wfShadeKernel<true, false>, (const void*)wfShadeShadowKernel<true, false>}
+                   : WavefrontKernels{(const void*)wfGenerateKernel<false, false>, (const void*)wfShadeKernel<false, false>, (const void*)wfShadeShadowKernel<false, false>};
+    return pol ? WavefrontKernels{(const void*)wfGenerateKernel<true, true>, (const void*)wfShadeKernel<true, true>, (const void*)wfShadeShadowKernel<true, true>}
+               : WavefrontKernels{(const void*)wfGenerateKernel<false, true>, (const void*)wfShadeKernel<false, true>, (const void*)wfShadeShadowKernel<false, true>};
+}
+
 // zeroes the wavefront counters selected by mask
 __global__ void wfResetKernel(uint32_t* counters, uint32_t mask) {
     if (threadIdx.x < WF_NCOUNTERS && ((mask >> threadIdx.x) & 1u)) counters[threadIdx.x] = 0u;
@@ -509,9 +524,8 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         return -1;
     }
     const size_t histSmem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
-    const void* genFn = pol ? (const void*)wfGenerateKernel<true> : (const void*)wfGenerateKernel<false>;
-    const void* shadeFn = pol ? (const void*)wfShadeKernel<true> : (const void*)wfShadeKernel<false>;
-    const void* shadowFn = pol ? (const void*)wfShadeShadowKernel<true> : (const void*)wfShadeShadowKernel<false>;
+    const WavefrontKernels wk = wavefrontKernels(pol, leanLaunch(D));
+    const void *genFn = wk.gen, *shadeFn = wk.shade, *shadowFn = wk.shadow;
     uint32_t gGen, gShade, gShadow, gTrace;
     if (persistentGrid(genFn, 0, &gGen) || persistentGrid(shadeFn, histSmem, &gShade) ||
         persistentGrid(shadowFn, histSmem, &gShadow) || persistentGrid((const void*)wfTraceKernel, 0, &gTrace))
@@ -751,8 +765,8 @@ int theia_trace_grid_size(const theia_trace_launch_t* launch, uint32_t* n_blocks
         const bool pol = launch->polarized != 0;
         const size_t smem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
         uint32_t gShade = 0, gShadow = 0;
-        if (persistentGrid(pol ? (const void*)wfShadeKernel<true> : (const void*)wfShadeKernel<false>, smem, &gShade) ||
-            persistentGrid(pol ? (const void*)wfShadeShadowKernel<true> : (const void*)wfShadeShadowKernel<false>, smem, &gShadow))
+        const WavefrontKernels wk = wavefrontKernels(pol, leanLaunch(D));
+        if (persistentGrid(wk.shade, smem, &gShade) || persistentGrid(wk.shadow, smem, &gShadow))
             return -1;
         const uint32_t need = blocksFor(D.batch_size, TRACE_THREADS);
         uint32_t g = gShade > gShadow ? gShade : gShadow;

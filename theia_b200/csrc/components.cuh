@@ -524,9 +524,10 @@ TDEV bool isPlaneGuide(uint32_t kind) { return kind == THEIA_GUIDE_FLAT || kind 
 
 // sh/target_guide.sphere.glsl:15-51 (every shape draws two numbers: random2D in the plane shapes, two
 // calls of random in the sphere, which address the same two counters)
+template <bool FULL = true>
 TDEV TargetGuideSample sampleTargetGuide(const GuideSel& c, vec3 observer, Rng& rng) {
     const vec2 u = rng.next2();
-    if (isPlaneGuide(c.kind)) return planeGuideSample(c, observer, u);
+    if (FULL && isPlaneGuide(c.kind)) return planeGuideSample(c, observer, u);
     float d, cosMin, prob;
     vec3 viewDir;
     guideCone(c.p.sphere, observer, &d, &viewDir, &cosMin, &prob);
@@ -539,8 +540,9 @@ TDEV TargetGuideSample sampleTargetGuide(const GuideSel& c, vec3 observer, Rng& 
     return {dir, d + c.p.sphere.radius, prob};
 }
 // sh/target_guide.sphere.glsl:53-81
+template <bool FULL = true>
 TDEV TargetGuideSample evalTargetGuide(const GuideSel& c, vec3 observer, vec3 direction) {
-    if (isPlaneGuide(c.kind)) return planeGuideEval(c, observer, direction);
+    if (FULL && isPlaneGuide(c.kind)) return planeGuideEval(c, observer, direction);
     float d, cosMin, prob;
     vec3 viewDir;
     guideCone(c.p.sphere, observer, &d, &viewDir, &cosMin, &prob);

@@ -334,7 +334,7 @@ enum : uint32_t { WF_SEQ1 = 1u << 18 };  // one response was already committed i
 // the target guide; writes the ray query to `rayOut` (the entry the path was given in the
 // output buffer). The health check of :285 (isRayBad) is done by the caller, which needs its
 // outcome to allocate the entry.
-template <bool POL>
+template <bool POL, bool FULL>
 TDEV void prepareQuery(const DeviceLaunch& P, float4* rayOut, const Ray& ray, Rng& rng, bool allowResponse, bool GUIDE,
                        bool& misTarget) {
     misTarget = false;
@@ -342,7 +342,7 @@ TDEV void prepareQuery(const DeviceLaunch& P, float4* rayOut, const Ray& ray, Rn
     float dist = sampleScatterLength(ray, P.propagation, rng.next());
     float sampledDist = dist;
     if (GUIDE) {
-        TargetGuideSample guideSample = evalTargetGuide(P.guide, ray.position, dir);
+        TargetGuideSample guideSample = evalTargetGuide<FULL>(P.guide, ray.position, dir);
         bool mis = allowResponse && guideSample.prob > 0.0f;
         if (mis) {
             mis = guideSample.dist > dist;
@@ -356,10 +356,10 @@ TDEV void prepareQuery(const DeviceLaunch& P, float4* rayOut, const Ray& ray, Rn
 
 // End of a segment (sh/tracer.scene.forward.glsl:87-104): event callback, stop conditions,
 // then the next ray query, appended to the output buffer. MUST be called by all 32 lanes.
-template <bool POL>
+template <bool POL, bool FULL>
 TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* sh, bool active, uint32_t path, Ray& ray,
                         Rng& rng, int result, uint32_t it, bool GUIDE, uint32_t next, uint32_t& nSegments) {
-    if (P.photon && active) result = photonRoulette<POL>(ray, rng, result);
+    if (FULL && P.photon && active) result = photonRoulette<POL>(ray, rng, result);
     onEvent<POL>(P.callback, sh, active, ray, result, path, it);
     bool cont = active && result >= 0;
     bool maxIter = false, allow = true;
@@ -367,7 +367,7 @@ TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* 
         allow = GUIDE ? (result != THEIA_RESULT_RAY_SCATTERED) : true;
         if (it == P.path_length) { maxIter = true; cont = false; }
         else {
-            if (P.photon) photonRunBoundary(P, rng, it);
+            if (FULL && P.photon) photonRunBoundary(P, rng, it);
             it++;
         }
     }
@@ -378,7 +378,7 @@ TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* 
     const uint32_t j = denseAlloc(ws.counters + (next ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0), ok);
     if (ok) {
         bool mis;
-        prepareQuery<POL>(P, ws.ray[next] + 2 * (size_t)j, ray, rng, allow, GUIDE, mis);
+        prepareQuery<POL, FULL>(P, ws.ray[next] + 2 * (size_t)j, ray, rng, allow, GUIDE, mis);
         storeState<POL>(ws.state[next], ws.capacity, j, ray, rng.dim, it | (allow ? WF_ALLOW : 0u) | (mis ? WF_MIS_TARGET : 0u), path);
     }
 }
@@ -433,7 +433,7 @@ TDEV void pregenerateGamma(const DeviceLaunch& P, const Workspace& ws, uint32_t 
 }
 
 // generate: sh/tracer.scene.forward.glsl:50-66. Each warp owns a contiguous range of paths.
-template <bool POL>
+template <bool POL, bool FULL>
 __global__ void __launch_bounds__(128, 4) wfGenerateKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws) {
     __shared__ SinkShared sh;
     sinkInit(P, &sh, nullptr);
@@ -457,8 +457,8 @@ __global__ void __launch_bounds__(128, 4) wfGenerateKernel(const __grid_constant
         if (active) {
             PreGamma pre = {false, 0.0f, 0u};
             if (PREGAMMA) pre = {true, u2f(ws.state[1][WF_PX * (size_t)ws.capacity + k]), ws.state[1][WF_DIM * (size_t)ws.capacity + k]};
-            ray = sampleRay<POL>(P.wavelength, P.light, P.medium, rng, pre);
-            if (P.photon) { ray.lin_contrib = 1.0f; ray.log_contrib = 0.0f; }  // sh/tracer.scene.photon.init.glsl:50-54
+            ray = sampleRay<POL, FULL>(P.wavelength, P.light, P.medium, rng, pre);
+            if (FULL && P.photon) { ray.lin_contrib = 1.0f; ray.log_contrib = 0.0f; }  // sh/tracer.scene.photon.init.glsl:50-54
             nPaths++;
             nSegments++;
         }
@@ -468,7 +468,7 @@ __global__ void __launch_bounds__(128, 4) wfGenerateKernel(const __grid_constant
         const uint32_t j = denseAlloc(ws.counters + WF_CNT_QUEUE0, ok);
         if (ok) {
             bool mis;
-            prepareQuery<POL>(P, ws.ray[0] + 2 * (size_t)j, ray, rng, allow, GUIDE, mis);
+            prepareQuery<POL, FULL>(P, ws.ray[0] + 2 * (size_t)j, ray, rng, allow, GUIDE, mis);
             storeState<POL>(ws.state[0], ws.capacity, j, ray, rng.dim, 1u | (allow ? WF_ALLOW : 0u) | (mis ? WF_MIS_TARGET : 0u), k);
         }
     }
@@ -483,7 +483,7 @@ TDEV RayHit resultToHit(uint4 r) {
 }
 
 // shade: second half of trace() (sh/scene.traverse.glsl:324-352) + processInteraction (:361-397)
-template <bool POL>
+template <bool POL, bool FULL>
 __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
                                                          uint32_t cur) {
     extern __shared__ float sharedHist[];
@@ -539,12 +539,12 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
             updateRayIS(ray, dist, P.propagation, hit.valid);
             result = queryResult <= THEIA_ERROR_MAX_VALUE ? queryResult : propResult;
         }
-        has = commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
+        has = commitHit<FULL>(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
         has = false;
 
         const bool interact = active && result >= 0;
-        const bool last = P.photon ? false : it == P.path_length;  // the photon tracers always scatter
+        const bool last = (FULL && P.photon) ? false : it == P.path_length;  // the photon tracers always scatter
         bool wantMIS = false;
         float uResponse = 2.0f;
         if (interact && hit.valid) {
@@ -561,7 +561,7 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
                 if (allowResponse && isTarget && (P.objectId < 0 || hit.customId == P.objectId)) {
                     sceneCreateResponse<POL>(P, ray, hit, surface, isAbs, item);
                     has = true;
-                    uResponse = responseDraw(P.response, rng, true, item);  // before the reflect / transmit draw
+                    uResponse = responseDraw<FULL>(P.response, rng, true, item);  // before the reflect / transmit draw
                     result = THEIA_RESULT_RAY_DETECTED;
                 }
                 if (isAbs) {
@@ -590,7 +590,7 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
             result = THEIA_RESULT_RAY_SCATTERED;
             wantMIS = GUIDE && !last;
         }
-        has = commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, uResponse);
+        has = commitHit<FULL>(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, uResponse);
 
         // paths that wait for shadow rays are parked in the shadow buffer (warp collective)
         uint32_t js = 0u;
@@ -599,9 +599,9 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
             // sampleTargetMIS (:234-269): the two shadow rays are traced by the next trace pass
             float pPP;
             vec3 dirPhase = scatter(ray.medium, ray.direction, rng.next2(), &pPP);
-            TargetGuideSample targetSample = sampleTargetGuide(P.guide, ray.position, rng);
+            TargetGuideSample targetSample = sampleTargetGuide<FULL>(P.guide, ray.position, rng);
             float pTT = targetSample.prob;
-            TargetGuideSample phaseSample = evalTargetGuide(P.guide, ray.position, dirPhase);
+            TargetGuideSample phaseSample = evalTargetGuide<FULL>(P.guide, ray.position, dirPhase);
             float pTP = phaseSample.prob;
             float pPT = scatterProb(ray.medium, ray.direction, targetSample.dir);
             float wTarget = pTT * pPT / (pTT * pTT + pPT * pPT);
@@ -616,14 +616,14 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
         } else if (interact && !hit.valid && !last) {
             scatterRay<POL>(ray, rng.next2());  // volume scatter (:386-393)
         }
-        finishSegment<POL>(P, ws, &sh, active && !wantMIS, path, ray, rng, result, it, GUIDE, next, nSegments);
+        finishSegment<POL, FULL>(P, ws, &sh, active && !wantMIS, path, ray, rng, result, it, GUIDE, next, nSegments);
     }
     sinkFinish(P, &sh, sharedHist, nSegments, nResponses, nShadow, 0);
 }
 
 // second shading pass (target guide only): shadow ray results -> responses
 // (traceShadowRay, sh/scene.traverse.glsl:185-214), then the deferred volume scatter
-template <bool POL>
+template <bool POL, bool FULL>
 __global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
                                                                uint32_t cur) {
     extern __shared__ float sharedHist[];
@@ -663,11 +663,11 @@ __global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_const
                     has = processShadowRay<POL>(P, r2, hit, item);
                 }
             }
-            has = commitHit(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw(P.response, rng, has, item));
+            has = commitHit<FULL>(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
             hitSeq += has ? 1u : 0u;
         }
         if (active) scatterRay<POL>(ray, rng.next2());
-        finishSegment<POL>(P, ws, &sh, active, path, ray, rng, THEIA_RESULT_RAY_SCATTERED, it, true, next, nSegments);
+        finishSegment<POL, FULL>(P, ws, &sh, active, path, ray, rng, THEIA_RESULT_RAY_SCATTERED, it, true, next, nSegments);
     }
     sinkFinish(P, &sh, sharedHist, nSegments, nResponses, 0, 0);
 }

@@ -350,56 +350,101 @@ class MaterialStore:
 # ------------------------------------------------------------------ persistence
 def saveMaterials(path, material: Iterable[Material], *, media: Iterable[Medium] = []) -> None:
     """
-    Saves materials and all referenced media (src/theia/material.py:715-800): a directory or
-    ``.zip`` holding ``materials.json`` and one ``<medium>.npz`` per medium.
+    Stores materials and all media they reference in the archive layout of the reference
+    (src/theia/material.py:715-794): ``material.json`` (name, inside, outside, flagsInward,
+    flagsOutward) next to ``media/<name>`` (numpy ``.npz`` content, see ``Medium.save``), in a
+    directory if ``path`` is one, else packed into a zip file.
     """
-    material, media = list(material), {m.name: m for m in media}
+    material = list(material)
+    mediaDict = {m.name: m for m in media}
     for mat in material:
         for m in (mat.inside, mat.outside):
             if isinstance(m, Medium):
-                media.setdefault(m.name, m)
+                mediaDict.setdefault(m.name, m)
+    for mat in material:
+        for m in (mat.inside, mat.outside):
+            if type(m) is str and m not in mediaDict:
+                raise ValueError(f"Material '{mat.name}' references an unknown medium '{m}'!")
     entries = [
         {"name": mat.name, "inside": _mediumName(mat.inside), "outside": _mediumName(mat.outside),
          "flagsInward": int(mat.flagsInward), "flagsOutward": int(mat.flagsOutward)}
         for mat in material
     ]
     path = Path(path)
-    if path.suffix == ".zip":
-        with ZipFile(path, "w") as z:
-            z.writestr("materials.json", json.dumps(entries))
-            for name, m in media.items():
-                with z.open(f"{name}.npz", "w") as f:
-                    m.save(f)
-    else:
-        path.mkdir(parents=True, exist_ok=True)
-        (path / "materials.json").write_text(json.dumps(entries))
-        for name, m in media.items():
-            with open(path / f"{name}.npz", "wb") as f:
+    if path.is_dir():
+        (path / "media").mkdir(exist_ok=True)
+        for name, m in mediaDict.items():
+            with open(path / "media" / name, "wb") as f:
                 m.save(f)
+        (path / "material.json").write_text(json.dumps(entries))
+    elif path.exists():
+        raise ValueError("Invalid path!")
+    else:
+        with ZipFile(path, "w") as z:
+            for name, m in mediaDict.items():
+                with z.open(f"media/{name}", "w") as f:
+                    m.save(f)
+            z.writestr("material.json", json.dumps(entries))
 
 
-def loadMaterials(path) -> tuple[list[Material], dict[str, Medium]]:
-    """Inverse of ``saveMaterials``; returns the materials and the media by name."""
+def loadMaterials(path, *, skipValidation: bool = False) -> tuple[dict[str, Material], dict[str, Medium]]:
+    """
+    Inverse of ``saveMaterials`` (src/theia/material.py:797-881): reads an archive written by this
+    package or by the reference and returns the materials and the media by name.
+    """
+    import io
     path = Path(path)
     media: dict[str, Medium] = {}
-    if path.is_file() and is_zipfile(path):
+    if path.is_file():
+        if not is_zipfile(path):
+            raise ValueError("Unexpected file format!")
         with ZipFile(path) as z:
-            entries = json.loads(z.read("materials.json"))
-            for n in z.namelist():
-                if n.endswith(".npz"):
-                    with z.open(n) as f:
-                        media[n[:-4]] = Medium.load(f, name=n[:-4])
+            names = [n for n in z.namelist() if n.startswith("media/") and not n.endswith("/")]
+            if not names and not any(n.startswith("media") for n in z.namelist()):
+                raise ValueError('Subdirectory "media" is missing!')
+            for n in names:
+                stem = Path(n).stem
+                try:
+                    media[stem] = Medium.load(io.BytesIO(z.read(n)), name=stem)
+                except Exception:
+                    raise ValueError(f"Failed to load media file: {n}")
+            if "material.json" not in z.namelist():
+                raise ValueError('Missing file: "material.json"!')
+            raw = z.read("material.json").decode()
+    elif path.is_dir():
+        mediaDir = path / "media"
+        if not mediaDir.is_dir():
+            raise ValueError('Subdirectory "media" is missing!')
+        for f in sorted(mediaDir.iterdir()):
+            try:
+                with open(f, "rb") as fh:
+                    media[f.stem] = Medium.load(fh, name=f.stem)
+            except Exception:
+                raise ValueError(f"Failed to load media file: {f.absolute()}")
+        if not (path / "material.json").is_file():
+            raise ValueError('Missing file: "material.json"!')
+        raw = (path / "material.json").read_text()
     else:
-        entries = json.loads((path / "materials.json").read_text())
-        for f in path.glob("*.npz"):
-            media[f.stem] = Medium.load(open(f, "rb"), name=f.stem)
+        raise ValueError("Incompatible path!")
+    try:
+        entries = json.loads(raw)
+    except Exception:
+        raise ValueError('Invalid material description file: "material.json"!')
     required = {"name", "inside", "outside", "flagsInward", "flagsOutward"}
-    mats = []
+    mats: dict[str, Material] = {}
     for e in entries:
-        if set(e) != required:
-            raise ValueError("malformed materials.json")
-        mats.append(Material(e["name"], media.get(e["inside"], e["inside"]), media.get(e["outside"], e["outside"]),
-                             flags=(MaterialFlags(e["flagsInward"]), MaterialFlags(e["flagsOutward"]))))
+        if not skipValidation and (not isinstance(e, dict) or set(e) != required):
+            raise ValueError('Invalid material description file: "material.json"!')
+        name = e["name"]
+        if name in mats:
+            raise ValueError(f"Duplicate material '{name}'!")
+        sides = []
+        for med in (e["inside"], e["outside"]):
+            if med is not None and med not in media:
+                raise ValueError(f"Material '{name}' references unknown medium: '{med}'!")
+            sides.append(None if med is None else media[med])
+        mats[name] = Material(name, sides[0], sides[1],
+                              flags=(MaterialFlags(e["flagsInward"]), MaterialFlags(e["flagsOutward"])))
     return mats, media
 
 

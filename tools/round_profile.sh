@@ -26,4 +26,6 @@ for r in wfshade_c2 wftrace_c2 wftrace_shadow_c3; do
     ncu -i $out/${tag}_$r.ncu-rep --page raw --metrics $METRICS > $out/${tag}_$r.txt 2>&1
   fi
 done
+python tools/ncu_lines.py $out/${tag}_wfshade_c2.ncu-rep wfShadeKernelILb1ELb0 --top 45 > $out/${tag}_wfshade_c2_lines.txt 2>&1
+python tools/ncu_lines.py $out/${tag}_wftrace_c2.ncu-rep wfTraceSimpleKernel --top 30 > $out/${tag}_wftrace_c2_lines.txt 2>&1
 ls -la $out | tail -40
