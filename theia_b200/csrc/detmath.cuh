@@ -41,7 +41,13 @@ TDEV float signBit(float f) { return u2f((f2u(f) & 0x80000000u) | 0x3F800000u); 
 
 // ---------------------------------------------------------------- deterministic math
 // sin/cos: Cody-Waite reduction by pi/2 in three fma steps, degree 7/8 minimax kernels.
-TDEV void dm_sincos(float x, float* s_out, float* c_out) {
+// Experiment switch THEIA_MATH_OUTLINE: one out-of-line copy of exp / log / sincos per kernel.
+#ifdef THEIA_MATH_OUTLINE
+#define TMATH static __device__ __noinline__
+#else
+#define TMATH TDEV
+#endif
+TDEV void dm_sincos_inl(float x, float* s_out, float* c_out) {
     const float TWO_OVER_PI = 0.636619772367581343f;
     const float MAGIC = 12582912.0f;  // 1.5 * 2^23
     const float PIO2_HI = 1.57079637050628662109375f;
@@ -69,7 +75,22 @@ TDEV void dm_sincos(float x, float* s_out, float* c_out) {
 }
 
 // exp: n = round(x log2 e), two step reduction, degree 6 polynomial, two step scaling.
-TDEV float dm_exp(float x) {
+#ifdef THEIA_MATH_OUTLINE
+static __device__ __noinline__ float2 dm_sincos2(float x) {
+    float2 r;
+    dm_sincos_inl(x, &r.x, &r.y);
+    return r;
+}
+TDEV void dm_sincos(float x, float* s_out, float* c_out) {
+    float2 r = dm_sincos2(x);
+    *s_out = r.x;
+    *c_out = r.y;
+}
+#else
+TDEV void dm_sincos(float x, float* s_out, float* c_out) { dm_sincos_inl(x, s_out, c_out); }
+#endif
+
+TMATH float dm_exp(float x) {
     if (isnan_(x)) return x;
     if (x > 88.7228394f) return T_INF;
     if (x < -103.972084f) return 0.0f;
@@ -118,7 +139,7 @@ TDEV float dm_atan(float x) {
 }
 
 // log: mantissa/exponent split at sqrt(1/2), degree 9 polynomial.
-TDEV float dm_log(float x) {
+TMATH float dm_log(float x) {
     if (isnan_(x)) return x;
     if (x < 0.0f) return T_NAN;
     if (x == 0.0f) return -T_INF;

@@ -68,15 +68,25 @@ TDEV float random_s(const theia_philox_params_t& p, PhiloxKey key, uint32_t i) {
     return normalizeUint(v);
 }
 
+// Experiment switch: one out-of-line copy of the Philox block per kernel instead of one per draw site.
+#ifdef THEIA_PHILOX_OUTLINE
+static __device__ __noinline__ float randomCall(const theia_philox_params_t* p, uint32_t k0, uint32_t k1, uint32_t i) {
+    return random_s(*p, PhiloxKey{k0, k1}, i);
+}
+#define THEIA_DRAW(p, key, i) randomCall(p, (key).k0, (key).k1, i)
+#else
+#define THEIA_DRAW(p, key, i) random_s(*(p), key, i)
+#endif
+
 // RNG handle carried by every sampling function: stream key + running draw counter "dim"
 struct Rng {
     const theia_philox_params_t* p;
     PhiloxKey key;
     uint32_t idx;
     uint32_t dim;
-    TDEV float next() { float r = random_s(*p, key, dim); dim += 1; return r; }
+    TDEV float next() { float r = THEIA_DRAW(p, key, dim); dim += 1; return r; }
     TDEV vec2 next2() {
-        vec2 r = {random_s(*p, key, dim), random_s(*p, key, dim + 1)};
+        vec2 r = {THEIA_DRAW(p, key, dim), THEIA_DRAW(p, key, dim + 1)};
         dim += 2;
         return r;
     }
