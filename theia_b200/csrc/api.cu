@@ -561,10 +561,10 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         const bool timed = timeIt && tuner && tuner->choice[cls] < 0 && g_optTraceKernel[cls] < 0;
         if (timed) { e0 = profEvent(); e1 = profEvent(); cudaEventRecord(e0, st); }
         if (kernelOf[cls] == TRACE_SIMPLE)
-            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, rpe);
+            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, rpe, D.batch_size);
         else
             wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, ws.counters + WF_CNT_CURSOR, rpe,
-                                                            minNodeLanes);
+                                                            minNodeLanes, D.batch_size);
         if (timed) { cudaEventRecord(e1, st); tuner->pending[cls].push_back({e0, e1}); }
     };
 
@@ -736,7 +736,7 @@ int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, in
         {
             Timed tm(KC_TRACE, st);
             wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
-                                                            counters, counters + 1, 1u, 16u);
+                                                            counters, counters + 1, 1u, 16u, 0u);
         }
         wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
         CUDA_TRY(cudaFreeAsync(counters, st));

@@ -47,8 +47,10 @@ struct Workspace {
     float4* ray[2];         // ping-pong, [capacity][2]: (origin, tmax), (direction, sampledDist)
     uint4* result;          // [capacity]: instance slot (0xFFFFFFFF = miss), primitive, u, v
     uint32_t* shadowState;  // [nFields][capacity]: paths with a pending pair of shadow rays, dense
-    float4* shadowRay;      // [2 * capacity][2]: (origin, tmax), (direction, weight)
-    uint4* shadowResult;    // [2 * capacity]
+    // shadow rays in two planes of `capacity` entries: [0] phase function samples, [1] guide samples (rays
+    // of a kind are neighbours: the first kind mostly misses the scene at once, the second crosses it)
+    float4* shadowRay;      // [2][capacity][2]: (origin, tmax), (direction, weight)
+    uint4* shadowResult;    // [2][capacity]
 };
 
 static inline size_t wfAlign(size_t v) { return (v + 255) & ~size_t(255); }
@@ -128,7 +130,9 @@ TDEV uint32_t denseAlloc(uint32_t* counter, bool push) {
 }
 
 // ------------------------------------------------------------------ trace kernel
-// Ray queries of a dense buffer: rays[2 r], rays[2 r + 1] hold ray r < *countPtr * raysPerEntry;
+// Ray queries of a dense buffer: rays[2 r], rays[2 r + 1] hold ray r. With raysPerEntry = 1 r < *countPtr;
+// with raysPerEntry = 2 (shadow rays) the rays live in two planes, r < *countPtr and planeStride <= r <
+// planeStride + *countPtr, which are walked one after the other;
 // results[r] receives (instance slot | ~0, primitive, u, v).
 //
 // Persistent warps, three phases per round so that the lanes of a warp do the same kind of
@@ -145,13 +149,14 @@ enum : uint32_t { WE_TLAS = 0u, WE_INST = 1u, WE_BLAS = 2u, WE_LEAF = 3u };
 __global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                          uint4* __restrict__ results,
                                                          const uint32_t* __restrict__ countPtr, uint32_t* cursor,
-                                                         uint32_t raysPerEntry, uint32_t minNodeLanes) {
+                                                         uint32_t raysPerEntry, uint32_t minNodeLanes, uint32_t planeStride) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
     const uint32_t nTop = stageTopNodes(tlas, sharedTop);
     __syncthreads();
     const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
-    const uint32_t total = *countPtr * raysPerEntry;
+    const uint32_t count = *countPtr;
+    const uint32_t total = count * raysPerEntry;
     // rays a lane takes per fetch: 4 while there is plenty of work (fewer atomics), 1 once the
     // queue is short, so that the tail is spread over all lanes instead of queued up in a few
     const uint32_t lanes = gridDim.x * blockDim.x;
@@ -199,7 +204,7 @@ __global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__
             if (i >= total) {
                 done = true;
             } else {
-                rid = i;
+                rid = i < count ? i : i - count + planeStride;
                 const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
                 ox = a.x; oy = a.y; oz = a.z; tmax = a.w; dx = b.x; dy = b.y; dz = b.z;
                 world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
@@ -311,16 +316,18 @@ __global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__
 // every workload for every threshold and was dropped.)
 __global__ void __launch_bounds__(128, 6) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                                uint4* __restrict__ results,
-                                                               const uint32_t* __restrict__ countPtr, uint32_t raysPerEntry) {
+                                                               const uint32_t* __restrict__ countPtr, uint32_t raysPerEntry,
+                                                               uint32_t planeStride) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
-    const uint32_t total = *countPtr * raysPerEntry;
+    const uint32_t count = *countPtr;
+    const uint32_t total = count * raysPerEntry;
     if (blockIdx.x * blockDim.x >= total) return;
     const uint32_t nTop = stageTopNodes(tlas, sharedTop);
     __syncthreads();
     const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const uint32_t rid = i;
+        const uint32_t rid = i < count ? i : i - count + planeStride;
         const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
         const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr);
         results[rid] = make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v));
@@ -606,11 +613,12 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
             float pPT = scatterProb(ray.medium, ray.direction, targetSample.dir);
             float wTarget = pTT * pPT / (pTT * pTT + pPT * pPT);
             float wPhase = pPP * pPP / (pPP * pPP + pTP * pTP);
-            float4* sr = ws.shadowRay + 4 * (size_t)js;
+            float4* sr = ws.shadowRay + 2 * (size_t)js;
+            float4* st = sr + 2 * (size_t)ws.capacity;
             sr[0] = make_float4(ray.position.x, ray.position.y, ray.position.z, phaseSample.dist);
             sr[1] = make_float4(dirPhase.x, dirPhase.y, dirPhase.z, wPhase);
-            sr[2] = make_float4(ray.position.x, ray.position.y, ray.position.z, targetSample.dist);
-            sr[3] = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, wTarget);
+            st[0] = make_float4(ray.position.x, ray.position.y, ray.position.z, targetSample.dist);
+            st[1] = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, wTarget);
             nShadow += 2;
             storeState<POL>(ws.shadowState, ws.capacity, js, ray, rng.dim, it | (hitSeq ? WF_SEQ1 : 0u), path);
         } else if (interact && !hit.valid && !last) {
@@ -653,8 +661,9 @@ __global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_const
             HitItem item;
             bool has = false;
             if (active) {
-                const float4 a = ws.shadowRay[4 * (size_t)slot + 2 * j], b = ws.shadowRay[4 * (size_t)slot + 2 * j + 1];
-                const RayHit q = resultToHit(ws.shadowResult[2 * (size_t)slot + j]);
+                const size_t r = (size_t)j * ws.capacity + slot;
+                const float4 a = ws.shadowRay[2 * r], b = ws.shadowRay[2 * r + 1];
+                const RayHit q = resultToHit(ws.shadowResult[r]);
                 Ray r2 = ray;
                 scatterRayIS<POL>(r2, vec3{b.x, b.y, b.z});
                 SurfaceHit hit;
