@@ -101,5 +101,29 @@ xf = [T.TRS(scale=0.8, translate=(3.0, 0.0, 0.0)),
       T.TRS(scale=(1.0, 2.0, 3.0), rotate=(1.0, 2.0, -0.5, 33.0), translate=(-4.0, 5.5, 0.25))]
 out["transform.trs"] = np.stack([np.asarray(t.numpy(), np.float64) for t in xf])
 
+# theia.cascades: particle -> light source parameters (host side tables and formulas)
+import theia.cascades as tc  # noqa: E402
+
+CASC_TYPES = [22, -11, 11, 111, 211, -211, 130, 2112, 2212, -2212]
+CASC_ENERGIES = [0.5, 1.0, 7.5, 100.0, 3.3e4]
+rows = []
+for t in CASC_TYPES:
+    for E in CASC_ENERGIES:
+        c = tc.createCascadeParameters(tc.getCascadeParamsFromParticleType(tc.ParticleType(t)), E)
+        c2 = tc.createCascadeParameters(tc.getCascadeParamsFromParticleType(tc.ParticleType(t)), E, tc.X0_ice, tc.rho_ice)
+        rows.append([c.a_long, c.b_long, c.effectiveLength, c.effectiveLengthStd, c.a_angular, c.b_angular,
+                     c2.b_long, c2.effectiveLength])
+out["cascades.parameters"] = np.array(rows, np.float64)
+rows = []
+for t, E, uRand in [(11, 50.0, None), (211, 800.0, 0.8), (22, 3.0, 0.1), (13, 120.0, None), (-15, 2e3, 0.35)]:
+    p = tc.Particle(tc.ParticleType(t), (1.0, -2.0, 3.5), (0.3, -0.4, 1.2), E, startTime=12.5, length=75.0)
+    cls, params, ly = tc.createParamsFromParticle(p, lightSourceName="src", uRand=uRand)
+    flat = []
+    for k in sorted(params):
+        flat += list(np.atleast_1d(np.asarray(params[k], np.float64)))
+    rows.append(([1.0] if cls is tc.MuonTrackLightSource else [0.0]) + flat + [ly.effectiveLength, ly.effectiveLengthStd] +
+                [0.0] * 8)
+out["cascades.from_particle"] = np.array([r[:16] for r in rows], np.float64)
+
 np.savez_compressed(OUT, **out)
 print(f"wrote {OUT}: {len(out)} arrays, {os.path.getsize(OUT)} bytes")

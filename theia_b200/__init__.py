@@ -3,9 +3,8 @@ theia_b200 - B200-native implementation of the forward photon tracing path of
 tkerscher/theia behind theia's own Python component API.
 
 Submodules mirror the reference's module names (src/theia/__init__.py:21-36):
-light, lookup, material, random, response, scene, target, task, testing, trace, units
-(theia.cascades, the particle parametrisations feeding the cascade / track light sources, is a
-"next" row of DESIGN.md), plus distributed (multi-GPU sharding).
+cascades, light, lookup, material, random, response, scene, target, task, testing, trace, units,
+plus distributed (multi-GPU sharding).
 All device work goes through the C-ABI library built from theia_b200/csrc
 (include/theia_b200.h); there is no CPU fallback.
 """
@@ -13,7 +12,7 @@ All device work goes through the C-ABI library built from theia_b200/csrc
 import importlib
 
 __all__ = [
-    "distributed", "light", "lookup", "material", "pipeline", "random", "response", "scene",
+    "cascades", "distributed", "light", "lookup", "material", "pipeline", "random", "response", "scene",
     "target", "task", "testing", "trace", "units",
 ]
 
