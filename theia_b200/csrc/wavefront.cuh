@@ -649,7 +649,16 @@ __global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_const
         const uint32_t slot = i;
         Ray ray;
         uint32_t dim = 0, flags = 1u, path = 0;
-        if (active) loadState<POL>(ws.shadowState, ws.capacity, i, ray, dim, flags, path);
+        // both shadow rays (direction + weight) and their results are requested together with the state
+        float4 dirW[2] = {make_float4(0, 0, 1, 0), make_float4(0, 0, 1, 0)};
+        uint4 res[2] = {make_uint4(0xFFFFFFFFu, 0u, 0u, 0u), make_uint4(0xFFFFFFFFu, 0u, 0u, 0u)};
+        if (active) {
+            dirW[0] = ws.shadowRay[2 * (size_t)slot + 1];
+            dirW[1] = ws.shadowRay[2 * ((size_t)ws.capacity + slot) + 1];
+            res[0] = ws.shadowResult[slot];
+            res[1] = ws.shadowResult[(size_t)ws.capacity + slot];
+            loadState<POL>(ws.shadowState, ws.capacity, i, ray, dim, flags, path);
+        }
         const uint32_t idx = P.first_path + path;
         Rng rng = makeRng(&P.rng, idx);
         rng.dim = dim;
@@ -661,9 +670,8 @@ __global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_const
             HitItem item;
             bool has = false;
             if (active) {
-                const size_t r = (size_t)j * ws.capacity + slot;
-                const float4 a = ws.shadowRay[2 * r], b = ws.shadowRay[2 * r + 1];
-                const RayHit q = resultToHit(ws.shadowResult[r]);
+                const float4 b = j == 0 ? dirW[0] : dirW[1];
+                const RayHit q = resultToHit(j == 0 ? res[0] : res[1]);
                 Ray r2 = ray;
                 scatterRayIS<POL>(r2, vec3{b.x, b.y, b.z});
                 SurfaceHit hit;
