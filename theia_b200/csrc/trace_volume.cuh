@@ -38,8 +38,11 @@ TDEV bool volumeCreateResponse(const DeviceLaunch& P, Ray ray, const TargetSampl
     return true;
 }
 
+#ifndef THEIA_VOLUME_CTAS
+#define THEIA_VOLUME_CTAS 6
+#endif
 template <bool POL, bool FULL>
-__global__ void __launch_bounds__(128, 4) volumeForwardKernel(const __grid_constant__ DeviceLaunch P) {
+__global__ void __launch_bounds__(128, THEIA_VOLUME_CTAS) volumeForwardKernel(const __grid_constant__ DeviceLaunch P) {
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
     sinkInit(P, &sh, sharedHist);

@@ -335,6 +335,18 @@ __global__ void __launch_bounds__(128, 6) wfTraceSimpleKernel(const void* __rest
 }
 
 // ------------------------------------------------------------------ shading side
+// Resident CTAs per SM of the shading kernels. They wait on chains of dependent loads, so more warps
+// are worth the spills of a smaller register budget: wfShadeKernel at 3 / 4 / 5 / 6 / 7 / 8 CTAs per SM
+// takes 0.237 / 0.201 / 0.195 / 0.191 / 0.182 / 0.182 ms per launch on C2 (profiles/r1h_shade_occupancy_ab.txt).
+#ifndef THEIA_SHADE_CTAS
+#define THEIA_SHADE_CTAS 7
+#endif
+#ifndef THEIA_SHADOW_CTAS
+#define THEIA_SHADOW_CTAS 4
+#endif
+#ifndef THEIA_GEN_CTAS
+#define THEIA_GEN_CTAS 4
+#endif
 enum : uint32_t { WF_SEQ1 = 1u << 18 };  // one response was already committed in this event
 
 // First half of trace() (sh/scene.traverse.glsl:280-323): free path sample, extension towards
@@ -441,7 +453,7 @@ TDEV void pregenerateGamma(const DeviceLaunch& P, const Workspace& ws, uint32_t 
 
 // generate: sh/tracer.scene.forward.glsl:50-66. Each warp owns a contiguous range of paths.
 template <bool POL, bool FULL>
-__global__ void __launch_bounds__(128, 4) wfGenerateKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws) {
+__global__ void __launch_bounds__(128, THEIA_GEN_CTAS) wfGenerateKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws) {
     __shared__ SinkShared sh;
     sinkInit(P, &sh, nullptr);
     const bool GUIDE = P.guide.kind != THEIA_GUIDE_NONE;
@@ -491,7 +503,7 @@ TDEV RayHit resultToHit(uint4 r) {
 
 // shade: second half of trace() (sh/scene.traverse.glsl:324-352) + processInteraction (:361-397)
 template <bool POL, bool FULL>
-__global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
+__global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
                                                          uint32_t cur) {
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
@@ -632,7 +644,7 @@ __global__ void __launch_bounds__(128, 4) wfShadeKernel(const __grid_constant__ 
 // second shading pass (target guide only): shadow ray results -> responses
 // (traceShadowRay, sh/scene.traverse.glsl:185-214), then the deferred volume scatter
 template <bool POL, bool FULL>
-__global__ void __launch_bounds__(128, 4) wfShadeShadowKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
+__global__ void __launch_bounds__(128, THEIA_SHADOW_CTAS) wfShadeShadowKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
                                                                uint32_t cur) {
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
