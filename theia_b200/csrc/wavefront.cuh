@@ -314,7 +314,10 @@ __global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__
 // per tracer and ray class from timings of the first batches. (A third form, persistent lanes
 // around this traversal step with Aila & Laine's refill threshold, lay between the two on
 // every workload for every threshold and was dropped.)
-__global__ void __launch_bounds__(128, 6) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
+#ifndef THEIA_SIMPLE_CTAS
+#define THEIA_SIMPLE_CTAS 6
+#endif
+__global__ void __launch_bounds__(128, THEIA_SIMPLE_CTAS) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                                uint4* __restrict__ results,
                                                                const uint32_t* __restrict__ countPtr, uint32_t raysPerEntry,
                                                                uint32_t planeStride) {
