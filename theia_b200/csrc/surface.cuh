@@ -26,6 +26,13 @@ TDEV vec3 ldVertex(uint64_t vertices, int32_t index, uint32_t offset) {
     return {__ldg(p), __ldg(p + 1), __ldg(p + 2)};
 }
 
+TDEV void ldVertex6(uint64_t vertices, int32_t index, vec3& pos, vec3& nrm) {
+    const float2* p = reinterpret_cast<const float2*>(reinterpret_cast<const float*>(vertices) + 6 * (size_t)index);
+    const float2 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    pos = {a.x, a.y, b.x};
+    nrm = {b.y, c.x, c.y};
+}
+
 // sh/scene.intersect.glsl:23-99
 TDEV int processRayQuery(const SceneView& sc, const Ray& ray, const RayHit& q, SurfaceHit& hit) {
     hit.valid = q.valid;
@@ -36,8 +43,11 @@ TDEV int processRayQuery(const SceneView& sc, const Ray& ray, const RayHit& q, S
     const uint64_t vertices = __ldg(&in->vertices);
     const int32_t* index = reinterpret_cast<const int32_t*>(__ldg(&in->indices)) + 3 * (size_t)q.prim;
     const int32_t i0 = __ldg(index), i1 = __ldg(index + 1), i2 = __ldg(index + 2);
-    vec3 v0 = ldVertex(vertices, i0, 0), v1 = ldVertex(vertices, i1, 0), v2 = ldVertex(vertices, i2, 0);
-    vec3 n0 = ldVertex(vertices, i0, 3), nn1 = ldVertex(vertices, i1, 3), nn2 = ldVertex(vertices, i2, 3);
+    // a vertex = {position, normal} = 24 bytes, 8 byte aligned: three 64 bit loads each
+    vec3 v0, v1, v2, n0, nn1, nn2;
+    ldVertex6(vertices, i0, v0, n0);
+    ldVertex6(vertices, i1, v1, nn1);
+    ldVertex6(vertices, i2, v2, nn2);
     vec3 e1 = v1 - v0, e2 = v2 - v0;
     float bx = q.u, by = q.v;
     // precise: v0 + fma(vec3(b.x), e1, b.y * e2)
