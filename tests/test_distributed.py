@@ -27,9 +27,13 @@ def freePort() -> int:
         return s.getsockname()[1]
 
 
-def makeRun(group=None):
+def makeRun(group=None, perObject: bool = False):
     with _device.useDevice("cpu"):
-        cfg = H.volumeScenario(N_PATHS, resp="hist", callback="stat")
+        if perObject:  # C5 style: one light curve per detector module
+            cfg = H.sceneC5(N_PATHS, resp="objhist", callback="stat", lattice=(3, 3, 3), pitch=(3.0, 3.0, 3.0), nBins=40,
+                            binSize=2.5)
+        else:
+            cfg = H.volumeScenario(N_PATHS, resp="hist", callback="stat")
     tr = cfg["tracer"]
 
     def launcher(i: int) -> None:  # stands in for Pipeline.run: same stages, executed by the oracle
@@ -38,12 +42,12 @@ def makeRun(group=None):
     return cfg, distributed.ShardedRun(tr, offset0=7, group=group, launcher=launcher)
 
 
-def worker(rank: int, world: int, port: int, outDir: str) -> None:
+def worker(rank: int, world: int, port: int, outDir: str, perObject: bool = False) -> None:
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        cfg, run = makeRun()
+        cfg, run = makeRun(perObject=perObject)
         res = run.run(N_BATCHES)
         assert res.localBatches == list(range(rank, N_BATCHES, world))
         np.save(os.path.join(outDir, f"curve{rank}.npy"), res.lightCurve)
@@ -77,3 +81,15 @@ def test_two_ranks_reproduce_the_single_process_run(tmp_path, orc):
     assert np.array_equal(counters[0], counters[1])
     assert np.array_equal(counters[0], np.array(list(single.counters.values()), np.int64))
     assert single.counters["created"] == N_BATCHES * N_PATHS
+
+
+def test_two_ranks_reduce_per_object_light_curves(tmp_path, orc):
+    # config C5: [module][time] histograms, one all-reduce of the whole array
+    cfg, run = makeRun(perObject=True)
+    single = run.run(N_BATCHES)
+    assert single.lightCurve.shape == (27, 40) and single.lightCurve.sum() > 0
+    port = freePort()
+    mp.spawn(worker, args=(2, port, str(tmp_path), True), nprocs=2, join=True)
+    curves = [np.load(tmp_path / f"curve{r}.npy") for r in range(2)]
+    assert np.array_equal(curves[0], curves[1])
+    assert np.allclose(curves[0], single.lightCurve, rtol=1e-5, atol=1e-9 * single.lightCurve.max())

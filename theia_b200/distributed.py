@@ -43,7 +43,8 @@ def batchOffset(offset0: int, batch: int, nRNGSamples: int) -> int:
 
 @dataclass
 class ShardResult:
-    #: mean over all batches of the per-batch light curves, float64[nBins] (None without histogram)
+    #: mean over all batches of the per-batch light curves, float64[nBins], or float64[nObjects, nBins] for
+    #: the per object response (None without histogram)
     lightCurve: np.ndarray | None
     #: total number of batches over all ranks
     nBatches: int
@@ -62,7 +63,8 @@ class ShardedRun:
     Parameters
     ----------
     tracer: theia_b200.trace.Tracer
-        tracer whose response is a ``HistogramHitResponse`` and / or ``HitRecorder``
+        tracer whose response is a histogram (``HistogramHitResponse``, ``KernelHistogramHitResponse``,
+        ``ObjectHistogramHitResponse``) and / or a ``HitRecorder``
     offset0: int
         Philox offset of batch 0
     group: torch.distributed.ProcessGroup | None
@@ -114,7 +116,8 @@ class ShardedRun:
         nRNG = tr.nRNGSamples
         dev = self._reduceDevice()
         nBins = getattr(resp, "nBins", 0)
-        acc = torch.zeros(max(nBins, 1), dtype=torch.float64, device=dev)
+        shape = (resp.nObjects, nBins) if hasattr(resp, "nObjects") else (max(nBins, 1),)
+        acc = torch.zeros(shape, dtype=torch.float64, device=dev)
         res = ShardResult(None, nBatches)
         stat = getattr(cb, "Statistic", None)  # EventStatisticCallback
         counterNames = [f[0] for f in stat._fields_] if stat is not None else []
