@@ -24,7 +24,11 @@ def both(builder, N, **kw):
 
 
 @pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict()), (H.sceneC2, dict(lightKind="cone", mode="single")),
-                                        (H.sceneC2, dict(lightKind="cone", mode="wavefront"))])
+                                        (H.sceneC2, dict(lightKind="cone", mode="wavefront")),
+                                        (H.sceneC3, dict(mode="wavefront")),
+                                        (H.sceneC3, dict(mode="wavefront", guide="disk", polarized=True)),
+                                        (H.sceneC2, dict(lightKind="cone", mode="wavefront", photon=(2, 3)))],
+                         ids=["volume", "c2-single", "c2-wavefront", "c3-guide", "c3-disk-guide", "c2-photon"])
 @pytest.mark.parametrize("batch", [1, 31, 33, 127, 1000, 4097])
 def test_ragged_batches(cuda, orc, builder, kw, batch):
     # batchSize below capacity and not a multiple of the warp / CTA size (src/theia/trace.py:399-408)
