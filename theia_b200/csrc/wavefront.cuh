@@ -146,7 +146,10 @@ TDEV uint32_t denseAlloc(uint32_t* counter, bool push) {
 #define WF_FETCH 4u
 enum : uint32_t { WE_TLAS = 0u, WE_INST = 1u, WE_BLAS = 2u, WE_LEAF = 3u };
 
-__global__ void __launch_bounds__(128, 5) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
+#ifndef THEIA_PHASED_CTAS
+#define THEIA_PHASED_CTAS 5
+#endif
+__global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                          uint4* __restrict__ results,
                                                          const uint32_t* __restrict__ countPtr, uint32_t* cursor,
                                                          uint32_t raysPerEntry, uint32_t minNodeLanes, uint32_t planeStride) {
