@@ -490,6 +490,68 @@ int theia_hit_replay(const uint32_t *queue_dev, uint32_t capacity, uint32_t pola
 int theia_math_eval(uint32_t fn, const float *x_dev, const float *y_dev, uint32_t n,
                     float *out_dev, void *stream);
 
+/* ------------------------------------------------------------------ component / shader unit seam
+ * One function of the path evaluated for n independent inputs: the counterpart of the reference's
+ * per-function test programs (tests/shader/<unit>.test.glsl, driven by tests/test_scatter.py,
+ * test_polarization.py, test_ray.py, test_math.py, test_random.py, test_light.py:721-836) and of
+ * its sampler stages (LightSampler src/theia/light.py:492-690 + sh/lightsource.sample.glsl,
+ * theia.testing.TargetSampler / TargetGuideSampler src/theia/testing.py:429-638 +
+ * sh/target.sample.glsl, sh/target_guide.sample.glsl).
+ * in_dev: float[n][in_width] (uint fields as raw bits), out_dev: float[n][out_width], row major;
+ * element i draws from Philox stream first + i starting at draw base_count.
+ *
+ * unit                      in row                              out row
+ * SCATTER_DIR               inDir3, cos_theta, phi              dir3               (sh/scatter.volume.glsl:7-26)
+ * REFLECTANCE  [material]   dir3, normal3, wavelength           r_s, r_p, n_tr     (sh/scatter.surface.glsl:21-51)
+ * VOLUME_SCATTER [rng]      dir3, medium lo, medium hi          dir3, prob         (sh/scatter.volume.glsl:28-58)
+ * SCATTER_PROB              inDir3, outDir3, medium lo, hi      prob               (sh/scatter.volume.glsl:60-65)
+ * ROTATE_PHI                stokes4, phi                        stokes4            (sh/polarization.glsl:7-21)
+ * ALIGN_POLREF [rng]        -                                   mat4 (column major): alignPolRef o rotatePolRef
+ * ROTATE_DIR                stokes4, dir3, ref3, phi, theta     stokes4, ref3      (sh/polarization.glsl:44-75)
+ * PHASE_MATRIX [medium]     stokes4, cos_theta                  stokes4            (sh/polarization.glsl:84-104)
+ * SURFACE [rng, material, params = normal3, lam_min, lam_max; polarized]
+ *                           -                                   wavelength, dir3, contrib, refl pos3, dir3, contrib,
+ *                                                               trans pos3, dir3, contrib, refl polRef3, trans polRef3,
+ *                                                               refl stokes4, trans stokes4  (tests/shader/ray.surface.test.glsl, FORWARD)
+ * SIGN_BIT                  x                                   signBit(x)         (sh/math.glsl:18-20)
+ * GAMMA [rng, params = alpha, lambda]   -                       sampleGamma        (sh/random.gamma.glsl:9-33)
+ * EMISSION_ANGLE [params = n, a, b]     u                       cos_theta          (sh/lightsource.particles.common.glsl:52-97)
+ * TARGET_SAMPLE [rng, target, params = min3, max3]   -          observer3, direction3, sample {pos3, nrm3, prob, valid, error},
+ *                                                               hit {pos3, nrm3, prob, valid, error}, occluded   (29 words)
+ * GUIDE_SAMPLE [rng, guide, params = min3, max3]     -          observer3, sample {dir3, dist, prob}, eval {dir3, dist, prob}
+ * LIGHT_SAMPLE [rng, wavelength, light, medium; polarized]: writes the reference's queues instead of rows:
+ *     light_queue_dev = uint32 count + field major LightSourceQueue (sh/lightsource.queue.glsl) of `capacity`
+ *     entries, wavelength_queue_dev likewise (sh/wavelengthsource.queue.glsl); count := n. */
+enum theia_unit {
+    THEIA_UNIT_SCATTER_DIR = 1, THEIA_UNIT_REFLECTANCE, THEIA_UNIT_VOLUME_SCATTER, THEIA_UNIT_SCATTER_PROB,
+    THEIA_UNIT_ROTATE_PHI, THEIA_UNIT_ALIGN_POLREF, THEIA_UNIT_ROTATE_DIR, THEIA_UNIT_PHASE_MATRIX,
+    THEIA_UNIT_SURFACE, THEIA_UNIT_SIGN_BIT, THEIA_UNIT_GAMMA, THEIA_UNIT_EMISSION_ANGLE,
+    THEIA_UNIT_TARGET_SAMPLE, THEIA_UNIT_GUIDE_SAMPLE, THEIA_UNIT_LIGHT_SAMPLE, THEIA_UNIT_COUNT
+};
+typedef struct theia_unit_args {
+    uint32_t struct_size; /* sizeof(theia_unit_args_t) */
+    uint32_t unit;
+    uint32_t n;
+    uint32_t polarized;
+    const float *in;      /* dev, may be NULL for units without input row */
+    float *out;           /* dev */
+    theia_philox_params_t rng;
+    uint32_t first;       /* stream / idx of element 0 */
+    uint32_t base_count;  /* first draw (dim) */
+    uint64_t medium;      /* dev address of a medium (0 = vacuum) */
+    uint64_t material;    /* dev address of a material */
+    float params[8];
+    theia_component_t light, wavelength, target, guide;
+    uint32_t *light_queue;      /* dev, LIGHT_SAMPLE only */
+    uint32_t *wavelength_queue; /* dev, LIGHT_SAMPLE only */
+    uint32_t capacity;          /* of both queues */
+    uint32_t _pad;
+    void *stream;
+} theia_unit_args_t;
+/* Row widths (in floats) of a unit; LIGHT_SAMPLE reports 0 / 0. */
+int theia_unit_widths(uint32_t unit, uint32_t polarized, uint32_t *in_width, uint32_t *out_width);
+int theia_unit_eval(const theia_unit_args_t *args);
+
 #ifdef __cplusplus
 }
 #endif

@@ -206,3 +206,55 @@ def guideEval(guide, observer: np.ndarray, direction: np.ndarray) -> dict:
     out = np.zeros((len(obs), 5), np.float32)
     lib().orc_guide_eval(ctypes.byref(comp), _ptr(obs), _ptr(d), len(obs), _ptr(out))
     return _unpack(out, _GUIDE_FIELDS)
+
+
+# ------------------------------------------------------------------ unit seam (mirror of theia_unit_eval)
+def evalUnit(unit: int, rows: np.ndarray | None, n: int | None = None, **kw) -> np.ndarray:
+    """
+    The oracle's evaluation of one unit (oracle/units.h): same arguments as
+    ``theia_b200._units.evalUnit``, components built under ``useDevice("cpu")``.
+    """
+    from theia_b200 import _units
+    l = lib()
+    l.orc_unit_eval.argtypes = [POINTER(_abi.UnitArgs)]
+    wi, wo = _units.WIDTHS[unit]
+    if rows is not None:
+        rows = np.ascontiguousarray(rows, dtype=np.float32).reshape(-1, wi)
+        n = len(rows)
+    A = _units.unitArgs(unit, int(n), **kw)
+    out = np.zeros((int(n), wo), dtype=np.float32)
+    A.in_ = _ptr(rows) if rows is not None else None
+    A.out = _ptr(out)
+    rc = l.orc_unit_eval(byref(A))
+    if rc != 0:
+        raise RuntimeError(f"oracle unit error {rc}")
+    return out
+
+
+def runSampler(sampler, i: int = 0) -> None:
+    """
+    Runs a sampler stage (``light.LightSampler``, ``testing.TargetSampler``, ``testing.TargetGuideSampler``)
+    built on the cpu device on the oracle: updates its stages, evaluates, and fills the host buffers the
+    stage's accessors (``lightQueue.view(i)``, ``getResults(i)``) read.
+    """
+    l = lib()
+    l.orc_unit_eval.argtypes = [POINTER(_abi.UnitArgs)]
+    if sampler._device != "cpu":
+        raise ValueError("the oracle needs a sampler built under useDevice('cpu')")
+    stages = sampler.collectStages()
+    for s in stages:
+        s.update(i)
+    for s in stages[:-1]:  # host sources copy their queues "to the device"
+        for cmd in s.run(i):
+            cmd()
+    A = sampler._unitArgs(i)
+    rc = l.orc_unit_eval(byref(A))
+    if rc != 0:
+        raise RuntimeError(f"oracle unit error {rc}")
+    if A.unit == _abi.UNIT_LIGHT_SAMPLE:
+        for q in (sampler.lightQueue, sampler.wavelengthQueue):
+            for cmd in q.run(i):
+                cmd()
+    else:
+        nbytes = 4 * sampler.batchSize * sampler._width
+        sampler._buffer[i][:nbytes].view(sampler._tensor.dtype).copy_(sampler._tensor)

@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include "tracer.h"
+#include "units.h"
 
 using namespace orc;
 
@@ -99,6 +100,12 @@ int orc_guide_eval(const theia_component_t* c, const float* observer, const floa
     }
     return 0;
 }
+
+// ---- unit seam (mirror of theia_unit_eval / theia_unit_widths, host pointers)
+int orc_unit_widths(uint32_t unit, uint32_t polarized, uint32_t* in_width, uint32_t* out_width) {
+    return unitWidths(unit, polarized, in_width, out_width);
+}
+int orc_unit_eval(const theia_unit_args_t* args) { return unitEval(*args); }
 
 // ---- scene
 void* orc_scene_create(const theia_instance_desc_t* desc, uint32_t n, const uint32_t* nVerts, const uint32_t* nTris,

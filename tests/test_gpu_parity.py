@@ -114,12 +114,13 @@ def _randomRays(rng, n, lo, hi, tmax):
     return rays
 
 
+@pytest.mark.parametrize("queryKernel", [0, 1, 2], ids=["direct", "phased", "queued"])
 @pytest.mark.parametrize("builder,kw,box", [
     (H.sceneC2, {}, (-2.0, 8.0)),
     (H.sceneC3, {}, (-4.0, 4.0)),
     (H.sceneC5, {"lattice": (6, 6, 6), "pitch": (2.0, 2.0, 2.0), "resp": "record"}, (-8.0, 8.0)),
 ])
-def test_ray_query_matches_brute_force(cuda, orc, builder, kw, box):
+def test_ray_query_matches_brute_force(cuda, orc, builder, kw, box, queryKernel):
     g, c = both(builder, 256, **kw)
     rng = np.random.default_rng(3)
     n = 200000
@@ -132,15 +133,21 @@ def test_ray_query_matches_brute_force(cuda, orc, builder, kw, box):
     ids = torch.zeros(n, 4, dtype=torch.int32, device="cuda")
     tuv = torch.zeros(n, 4, dtype=torch.float32, device="cuda")
     st = torch.zeros(4, dtype=torch.int64, device="cuda")
-    _lib.check(_lib.load().theia_tlas_query(g["scene"].tlas.data_ptr(), rd.data_ptr(), n, ids.data_ptr(), tuv.data_ptr(),
-                                            st.data_ptr(), 0))
-    torch.cuda.synchronize()
+    lib = _lib.load()
+    # the same queries through the one-thread-per-ray traversal and through both wavefront ray query kernels
+    _lib.check(lib.theia_set_option(b"query_kernel", queryKernel))
+    try:
+        _lib.check(lib.theia_tlas_query(g["scene"].tlas.data_ptr(), rd.data_ptr(), n, ids.data_ptr(), tuv.data_ptr(),
+                                        st.data_ptr(), 0))
+        torch.cuda.synchronize()
+    finally:
+        lib.theia_set_option(b"query_kernel", 0)
     ids_g, tuv_g = ids.cpu().numpy(), tuv.cpu().numpy()
     assert np.count_nonzero(ids_w[:, 0] >= 0) > n // 100
     assert np.array_equal(ids_g, ids_w), f"{np.count_nonzero((ids_g != ids_w).any(1))} rays hit a different triangle"
     assert np.array_equal(tuv_g.view(np.uint32), tuv_w.view(np.uint32))
     stats = st.cpu().numpy()
-    assert stats[3] == n and stats[0] > 0
+    assert queryKernel != 0 or (stats[3] == n and stats[0] > 0)
 
 
 def test_sweep_builder_option_gives_the_same_ray_queries(cuda):
@@ -208,7 +215,7 @@ SCENE_CASES = [
 ]
 
 
-@pytest.mark.parametrize("mode", ["single", "wavefront", "wavefront-simple"])
+@pytest.mark.parametrize("mode", ["single", "wavefront", "wavefront-simple", "wavefront-queued"])
 @pytest.mark.parametrize("builder,kw", SCENE_CASES, ids=lambda v: getattr(v, "__name__", None) or ",".join(
     f"{a}={b}" for a, b in v.items()) or "default")
 def test_scene_tracer_hits_bit_exact(cuda, orc, builder, kw, mode):
@@ -218,7 +225,7 @@ def test_scene_tracer_hits_bit_exact(cuda, orc, builder, kw, mode):
     kw["mode"] = mode.split("-")[0]
     # both ray query kernels of the wavefront tracer (normally picked by timing) are covered
     lib = _lib.load()
-    forced = 1 if mode.endswith("simple") else 0
+    forced = {"simple": 1, "queued": 2}.get(mode.split("-")[-1], 0)
     lib.theia_set_option(b"wf_trace_kernel", forced)
     lib.theia_set_option(b"wf_shadow_trace_kernel", forced)
     try:

@@ -127,3 +127,35 @@ class InstanceDesc(Structure):
         ("custom_index", c_int32),
         ("_pad", c_uint32),
     ]
+
+
+# unit seam (theia_unit_eval)
+(UNIT_SCATTER_DIR, UNIT_REFLECTANCE, UNIT_VOLUME_SCATTER, UNIT_SCATTER_PROB, UNIT_ROTATE_PHI, UNIT_ALIGN_POLREF,
+ UNIT_ROTATE_DIR, UNIT_PHASE_MATRIX, UNIT_SURFACE, UNIT_SIGN_BIT, UNIT_GAMMA, UNIT_EMISSION_ANGLE,
+ UNIT_TARGET_SAMPLE, UNIT_GUIDE_SAMPLE, UNIT_LIGHT_SAMPLE) = range(1, 16)
+
+
+class UnitArgs(Structure):
+    _fields_ = [
+        ("struct_size", c_uint32),
+        ("unit", c_uint32),
+        ("n", c_uint32),
+        ("polarized", c_uint32),
+        ("in_", c_void_p),
+        ("out", c_void_p),
+        ("rng", PhiloxParams),
+        ("first", c_uint32),
+        ("base_count", c_uint32),
+        ("medium", c_uint64),
+        ("material", c_uint64),
+        ("params", c_float * 8),
+        ("light", Component),
+        ("wavelength", Component),
+        ("target", Component),
+        ("guide", Component),
+        ("light_queue", c_void_p),
+        ("wavelength_queue", c_void_p),
+        ("capacity", c_uint32),
+        ("_pad", c_uint32),
+        ("stream", c_void_p),
+    ]

@@ -11,6 +11,8 @@
 #include <vector>
 #include "trace_volume.cuh"
 #include "wavefront.cuh"
+#include "trace_queue.cuh"
+#include "units.cuh"
 
 namespace theia {
 
@@ -285,6 +287,65 @@ static int copyBlock(const theia_component_t& c, T& dst, const char* what) {
     return 0;
 }
 
+// component description (kind + parameter block as the reference's ctypes structure) -> device selector
+static int fillTarget(const theia_component_t& c, TargetSel& d) {
+    d.kind = c.kind;
+    switch (c.kind) {
+    case THEIA_TARGET_SPHERE: case THEIA_TARGET_INNER_SPHERE: return copyBlock(c, d.p.sphere, "sphere target");
+    case THEIA_TARGET_FLAT: return copyBlock(c, d.p.flat, "flat target");
+    case THEIA_TARGET_DISK: return copyBlock(c, d.p.disk, "disk target");
+    default: setError("unsupported target kind %u", c.kind); return -1;
+    }
+}
+static int fillGuide(const theia_component_t& c, GuideSel& d) {
+    d.kind = c.kind;
+    switch (c.kind) {
+    case THEIA_GUIDE_NONE: return 0;
+    case THEIA_GUIDE_SPHERE: return copyBlock(c, d.p.sphere, "sphere target guide");
+    case THEIA_GUIDE_FLAT: return copyBlock(c, d.p.flat, "flat target guide");
+    case THEIA_GUIDE_DISK: return copyBlock(c, d.p.disk, "disk target guide");
+    default: setError("unsupported guide kind %u", c.kind); return -1;
+    }
+}
+static int fillLight(const theia_component_t& c, uint32_t first, uint32_t n, LightSel& d) {
+    d.kind = c.kind; d.flags = c.flags; d.first = first;
+    switch (c.kind) {
+    case THEIA_LIGHT_SPHERICAL: if (copyBlock(c, d.p.spherical, "spherical light")) return -1; break;
+    case THEIA_LIGHT_CONE: if (copyBlock(c, d.p.cone, "cone light")) return -1; break;
+    case THEIA_LIGHT_PENCIL: if (copyBlock(c, d.p.pencil, "pencil light")) return -1; break;
+    case THEIA_LIGHT_CASCADE: if (copyBlock(c, d.p.cascade, "cascade light")) return -1; break;
+    case THEIA_LIGHT_MUON: if (copyBlock(c, d.p.muon, "muon light")) return -1; break;
+    case THEIA_LIGHT_CHERENKOV: if (copyBlock(c, d.p.cherenkov, "cherenkov light")) return -1; break;
+    case THEIA_LIGHT_CHERENKOV_TRACK:
+        if (copyBlock(c, d.p.track, "cherenkov track light")) return -1;
+        if (!d.p.track.track) { setError("cherenkov track light: no particle track"); return -1; }
+        break;
+    case THEIA_LIGHT_HOST:
+        if (copyBlock(c, d.p.host, "host light")) return -1;
+        if (!d.p.host.queue || d.p.host.capacity < n) { setError("host light: queue holds %u samples, batch needs %u", d.p.host.capacity, n); return -1; }
+        break;
+    default: setError("unsupported light source kind %u", c.kind); return -1;
+    }
+    return 0;
+}
+static int fillWavelength(const theia_component_t& c, uint32_t first, uint32_t n, WavelengthSel& d) {
+    d.kind = c.kind; d.first = first;
+    switch (c.kind) {
+    case THEIA_WAVELENGTH_CONST: if (copyBlock(c, d.p.constant, "const wavelength")) return -1; break;
+    case THEIA_WAVELENGTH_UNIFORM: if (copyBlock(c, d.p.uniform, "uniform wavelength")) return -1; break;
+    case THEIA_WAVELENGTH_FUNCTION:
+        if (copyBlock(c, d.p.function, "function wavelength")) return -1;
+        if (!d.p.function.table) { setError("function wavelength: no table"); return -1; }
+        break;
+    case THEIA_WAVELENGTH_HOST:
+        if (copyBlock(c, d.p.host, "host wavelength")) return -1;
+        if (!d.p.host.queue || d.p.host.capacity < n) { setError("host wavelength: queue holds %u samples, batch needs %u", d.p.host.capacity, n); return -1; }
+        break;
+    default: setError("unsupported wavelength source kind %u", c.kind); return -1;
+    }
+    return 0;
+}
+
 static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
     if (!L || L->struct_size != sizeof(theia_trace_launch_t)) { setError("launch: struct_size mismatch (ABI version?)"); return -1; }
     memset(&D, 0, sizeof(D));
@@ -304,13 +365,7 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
         theia_volume_trace_params_t p;
         memcpy(&p, L->trace_params, sizeof(p));
         D.medium = p.medium; D.objectId = p.objectId; D.propagation = p.propagation;
-        D.target.kind = L->target.kind;
-        switch (L->target.kind) {
-        case THEIA_TARGET_SPHERE: case THEIA_TARGET_INNER_SPHERE: if (copyBlock(L->target, D.target.p.sphere, "sphere target")) return -1; break;
-        case THEIA_TARGET_FLAT: if (copyBlock(L->target, D.target.p.flat, "flat target")) return -1; break;
-        case THEIA_TARGET_DISK: if (copyBlock(L->target, D.target.p.disk, "disk target")) return -1; break;
-        default: setError("volume tracer: unsupported target kind %u", L->target.kind); return -1;
-        }
+        if (fillTarget(L->target, D.target)) return -1;
     } else if (L->tracer == THEIA_TRACER_SCENE_FORWARD || L->tracer == THEIA_TRACER_SCENE_PHOTON) {
         if (!L->trace_params || L->trace_params_size != sizeof(theia_scene_trace_params_t)) { setError("scene tracer: bad TraceParams block"); return -1; }
         theia_scene_trace_params_t p;
@@ -319,50 +374,12 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
         if (!L->tlas) { setError("scene tracer: no acceleration structure"); return -1; }
         if (L->path_length == 0) { setError("scene tracer: path_length must be at least 1"); return -1; }
         D.tlas = L->tlas;
-        D.guide.kind = L->guide.kind;
-        switch (L->guide.kind) {
-        case THEIA_GUIDE_NONE: break;
-        case THEIA_GUIDE_SPHERE: if (copyBlock(L->guide, D.guide.p.sphere, "sphere target guide")) return -1; break;
-        case THEIA_GUIDE_FLAT: if (copyBlock(L->guide, D.guide.p.flat, "flat target guide")) return -1; break;
-        case THEIA_GUIDE_DISK: if (copyBlock(L->guide, D.guide.p.disk, "disk target guide")) return -1; break;
-        default: setError("scene tracer: unsupported guide kind %u", L->guide.kind); return -1;
-        }
+        if (fillGuide(L->guide, D.guide)) return -1;
     } else {
         setError("unknown tracer kind %u", L->tracer);
         return -1;
     }
-    D.light.kind = L->light.kind; D.light.flags = L->light.flags; D.light.first = L->first_path;
-    switch (L->light.kind) {
-    case THEIA_LIGHT_SPHERICAL: if (copyBlock(L->light, D.light.p.spherical, "spherical light")) return -1; break;
-    case THEIA_LIGHT_CONE: if (copyBlock(L->light, D.light.p.cone, "cone light")) return -1; break;
-    case THEIA_LIGHT_PENCIL: if (copyBlock(L->light, D.light.p.pencil, "pencil light")) return -1; break;
-    case THEIA_LIGHT_CASCADE: if (copyBlock(L->light, D.light.p.cascade, "cascade light")) return -1; break;
-    case THEIA_LIGHT_MUON: if (copyBlock(L->light, D.light.p.muon, "muon light")) return -1; break;
-    case THEIA_LIGHT_CHERENKOV: if (copyBlock(L->light, D.light.p.cherenkov, "cherenkov light")) return -1; break;
-    case THEIA_LIGHT_CHERENKOV_TRACK:
-        if (copyBlock(L->light, D.light.p.track, "cherenkov track light")) return -1;
-        if (!D.light.p.track.track) { setError("cherenkov track light: no particle track"); return -1; }
-        break;
-    case THEIA_LIGHT_HOST:
-        if (copyBlock(L->light, D.light.p.host, "host light")) return -1;
-        if (!D.light.p.host.queue || D.light.p.host.capacity < L->batch_size) { setError("host light: queue holds %u samples, batch needs %u", D.light.p.host.capacity, L->batch_size); return -1; }
-        break;
-    default: setError("unsupported light source kind %u", L->light.kind); return -1;
-    }
-    D.wavelength.kind = L->wavelength.kind; D.wavelength.first = L->first_path;
-    switch (L->wavelength.kind) {
-    case THEIA_WAVELENGTH_CONST: if (copyBlock(L->wavelength, D.wavelength.p.constant, "const wavelength")) return -1; break;
-    case THEIA_WAVELENGTH_UNIFORM: if (copyBlock(L->wavelength, D.wavelength.p.uniform, "uniform wavelength")) return -1; break;
-    case THEIA_WAVELENGTH_FUNCTION:
-        if (copyBlock(L->wavelength, D.wavelength.p.function, "function wavelength")) return -1;
-        if (!D.wavelength.p.function.table) { setError("function wavelength: no table"); return -1; }
-        break;
-    case THEIA_WAVELENGTH_HOST:
-        if (copyBlock(L->wavelength, D.wavelength.p.host, "host wavelength")) return -1;
-        if (!D.wavelength.p.host.queue || D.wavelength.p.host.capacity < L->batch_size) { setError("host wavelength: queue holds %u samples, batch needs %u", D.wavelength.p.host.capacity, L->batch_size); return -1; }
-        break;
-    default: setError("unsupported wavelength source kind %u", L->wavelength.kind); return -1;
-    }
+    if (fillLight(L->light, L->first_path, L->batch_size, D.light) || fillWavelength(L->wavelength, L->first_path, L->batch_size, D.wavelength)) return -1;
     if (fillResponse(L->response, D.response)) return -1;
     D.callback.kind = L->callback.kind; D.callback.track_polarized = L->callback.track_polarized;
     D.callback.stats = (unsigned long long*)L->callback.stats; D.callback.track_buffer = L->callback.track_buffer;
@@ -449,7 +466,7 @@ static size_t workspaceBytes(const theia_trace_launch_t* L) {
 }
 
 // ------------------------------------------------------------------ options, trace kernel selection
-enum : int { TRACE_PHASED = 0, TRACE_SIMPLE = 1 };
+enum : int { TRACE_PHASED = 0, TRACE_SIMPLE = 1, TRACE_QUEUED = 2 };
 static int envInt(const char* name, int fallback) {
     const char* e = getenv(name);
     return e ? atoi(e) : fallback;
@@ -457,6 +474,8 @@ static int envInt(const char* name, int fallback) {
 // per ray class (primary, shadow): -1 = pick by measurement; the environment sets the defaults
 static int g_optTraceKernel[2] = {envInt("THEIA_WF_TRACE_KERNEL", -1), envInt("THEIA_WF_SHADOW_TRACE_KERNEL", -1)};
 static int g_optMinNodeLanes = envInt("THEIA_WF_MIN_NODE_LANES", 16);
+static int g_optFlushWaiting = envInt("THEIA_WF_FLUSH_WAITING", 4 | (8 << 8) | (4 << 16));  // thresholds of the queued kernel: waiting lanes | instance lanes << 8 | refill lanes << 16
+static int g_optQueryKernel = envInt("THEIA_QUERY_KERNEL", getenv("THEIA_QUERY_WAVEFRONT") ? 1 : 0);  // theia_tlas_query: 0 direct, 1 phased, 2 queued
 static std::mutex g_tunerMutex;
 
 // Picks the trace kernel of a (scene, batch size) from the first six batches: even ones run the
@@ -526,9 +545,10 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     const size_t histSmem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
     const WavefrontKernels wk = wavefrontKernels(pol, leanLaunch(D));
     const void *genFn = wk.gen, *shadeFn = wk.shade, *shadowFn = wk.shadow;
-    uint32_t gGen, gShade, gShadow, gTrace;
+    uint32_t gGen, gShade, gShadow, gTrace, gQueued;
     if (persistentGrid(genFn, 0, &gGen) || persistentGrid(shadeFn, histSmem, &gShade) ||
-        persistentGrid(shadowFn, histSmem, &gShadow) || persistentGrid((const void*)wfTraceKernel, 0, &gTrace))
+        persistentGrid(shadowFn, histSmem, &gShadow) || persistentGrid((const void*)wfTraceKernel, 0, &gTrace) ||
+        persistentGrid((const void*)wfTraceQueuedKernel, 0, &gQueued))
         return -1;
     // partial histograms: one row per CTA of the shading grids
     uint32_t need128 = blocksFor(D.batch_size, TRACE_THREADS);
@@ -536,6 +556,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     if (gShade > need128) gShade = need128;
     if (gShadow > need128) gShadow = need128;
     if (gTrace > need128) gTrace = need128;
+    if (gQueued > need128) gQueued = need128;
     const uint32_t minNodeLanes = (uint32_t)g_optMinNodeLanes;
     const uint32_t gSimple = need128 > 0 ? need128 : 1u;
 
@@ -560,7 +581,10 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         const bool timed = timeIt && tuner && tuner->choice[cls] < 0 && g_optTraceKernel[cls] < 0;
         if (timed) { e0 = profEvent(); e1 = profEvent(); cudaEventRecord(e0, st); }
-        if (kernelOf[cls] == TRACE_SIMPLE)
+        if (kernelOf[cls] == TRACE_QUEUED)
+            wfTraceQueuedKernel<<<gQueued, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, ws.counters + WF_CNT_CURSOR, rpe,
+                                                                  D.batch_size, (uint32_t)g_optFlushWaiting);
+        else if (kernelOf[cls] == TRACE_SIMPLE)
             wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, rpe, D.batch_size);
         else
             wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, ws.counters + WF_CNT_CURSOR, rpe,
@@ -613,6 +637,8 @@ int theia_set_option(const char* name, int value) {
     if (!name) { setError("theia_set_option: null name"); return -1; }
     if (!strcmp(name, "wf_trace_kernel")) { g_optTraceKernel[0] = value; return 0; }
     if (!strcmp(name, "wf_shadow_trace_kernel")) { g_optTraceKernel[1] = value; return 0; }
+    if (!strcmp(name, "wf_flush_waiting")) { g_optFlushWaiting = value; return 0; }
+    if (!strcmp(name, "query_kernel")) { g_optQueryKernel = value; return 0; }
     if (!strcmp(name, "wf_min_node_lanes")) { g_optMinNodeLanes = value < 1 ? 1 : (value > 32 ? 32 : value); return 0; }
     setError("theia_set_option: unknown option '%s'", name);
     return -1;
@@ -720,8 +746,7 @@ int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, in
                      uint64_t* stats_dev, void* stream) {
     if (!tlas_dev || !rays_dev || !out_dev || !out_bary_dev) { setError("theia_tlas_query: null argument"); return -1; }
     if (n == 0) return 0;
-    static const bool viaWavefront = getenv("THEIA_QUERY_WAVEFRONT") != nullptr;
-    if (viaWavefront) {
+    if (g_optQueryKernel > 0) {
         // measurement seam: the ray queries of the wavefront tracer on a caller supplied ray list
         cudaStream_t st = (cudaStream_t)stream;
         uint32_t* counters = nullptr;
@@ -729,14 +754,19 @@ int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, in
         CUDA_TRY(cudaMallocAsync(&counters, 16, st));
         CUDA_TRY(cudaMallocAsync(&results, 16 * (size_t)n, st));
         uint32_t gTrace = 0;
-        if (persistentGrid((const void*)wfTraceKernel, 0, &gTrace)) return -1;
+        const bool queued = g_optQueryKernel == 2;
+        if (persistentGrid(queued ? (const void*)wfTraceQueuedKernel : (const void*)wfTraceKernel, 0, &gTrace)) return -1;
         const uint32_t need = blocksFor(n, TRACE_THREADS);
         if (gTrace > need) gTrace = need;
         wfQuerySetupKernel<<<1, 32, 0, st>>>(counters, n);
         {
             Timed tm(KC_TRACE, st);
-            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
-                                                            counters, counters + 1, 1u, 16u, 0u);
+            if (queued)
+                wfTraceQueuedKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
+                                                                      counters, counters + 1, 1u, 0u, (uint32_t)g_optFlushWaiting);
+            else
+                wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
+                                                                counters, counters + 1, 1u, 16u, 0u);
         }
         wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
         CUDA_TRY(cudaFreeAsync(counters, st));
@@ -801,6 +831,39 @@ int theia_trace_forward(const theia_trace_launch_t* launch) {
         CUDA_TRY(cudaLaunchKernel(K.fn, dim3(K.grid), dim3(TRACE_THREADS), args, K.smem, (cudaStream_t)launch->stream));
     }
     countLaunches(1);
+    return 0;
+}
+
+int theia_unit_widths(uint32_t unit, uint32_t polarized, uint32_t* in_width, uint32_t* out_width) {
+    (void)polarized;
+    if (!in_width || !out_width || unitWidths(unit, in_width, out_width)) { setError("theia_unit_widths: unknown unit %u", unit); return -1; }
+    return 0;
+}
+
+int theia_unit_eval(const theia_unit_args_t* args) {
+    if (!args || args->struct_size != sizeof(theia_unit_args_t)) { setError("theia_unit_eval: struct_size mismatch (ABI version?)"); return -1; }
+    UnitDev A;
+    memset(&A, 0, sizeof(A));
+    if (unitWidths(args->unit, &A.in_width, &A.out_width)) { setError("theia_unit_eval: unknown unit %u", args->unit); return -1; }
+    A.unit = args->unit; A.n = args->n; A.polarized = args->polarized; A.first = args->first; A.base_count = args->base_count;
+    A.in = args->in; A.out = args->out; A.rng = args->rng; A.medium = args->medium; A.material = args->material;
+    memcpy(A.params, args->params, sizeof(A.params));
+    if (A.n == 0) return 0;
+    const uint32_t u = args->unit;
+    if (u == THEIA_UNIT_LIGHT_SAMPLE) {
+        if (!args->light_queue || !args->wavelength_queue || args->n > args->capacity) { setError("light sampler: %u samples do not fit queues of %u", args->n, args->capacity); return -1; }
+        A.light_queue = args->light_queue; A.wavelength_queue = args->wavelength_queue; A.capacity = args->capacity;
+        if (fillWavelength(args->wavelength, args->first, args->n, A.wavelength)) return -1;
+    } else if (!A.out || (A.in_width && !A.in)) { setError("theia_unit_eval: null buffer"); return -1; }
+    if ((u == THEIA_UNIT_LIGHT_SAMPLE || u == THEIA_UNIT_SURFACE) && fillLight(args->light, args->first, args->n, A.light)) return -1;
+    if (u == THEIA_UNIT_TARGET_SAMPLE && fillTarget(args->target, A.target)) return -1;
+    if (u == THEIA_UNIT_GUIDE_SAMPLE && (args->guide.kind == THEIA_GUIDE_NONE || fillGuide(args->guide, A.guide))) { if (args->guide.kind == THEIA_GUIDE_NONE) setError("guide sampler: no target guide"); return -1; }
+    if ((u == THEIA_UNIT_REFLECTANCE || u == THEIA_UNIT_SURFACE) && !A.material) { setError("theia_unit_eval: unit %u needs a material", u); return -1; }
+    cudaStream_t st = (cudaStream_t)args->stream;
+    if (A.polarized) unitEvalKernel<true><<<blocksFor(A.n, 128), 128, 0, st>>>(A);
+    else unitEvalKernel<false><<<blocksFor(A.n, 128), 128, 0, st>>>(A);
+    countLaunches(1);
+    CUDA_TRY(cudaGetLastError());
     return 0;
 }
 

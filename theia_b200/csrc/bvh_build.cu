@@ -718,7 +718,7 @@ extern "C" int theia_tlas_build(const theia_instance_desc_t* instances, uint32_t
     const uint32_t n = n_instances, bs = 256;
     // BLAS headers (host copies, one per distinct BLAS)
     std::map<const void*, BlasHeader> blas;
-    uint32_t maxBlasDepth = 0;
+    uint32_t maxBlasDepth = 0, maxBlasTris = 0;
     for (uint32_t i = 0; i < n; ++i) {
         const void* b = instances[i].blas;
         if (!b) { setError("theia_tlas_build: instance %u has no BLAS", i); return -1; }
@@ -729,6 +729,7 @@ extern "C" int theia_tlas_build(const theia_instance_desc_t* instances, uint32_t
         if (h.magic != THEIA_BLAS_MAGIC) { setError("theia_tlas_build: instance %u: not a BLAS", i); return -1; }
         blas[b] = h;
         if (h.orderAxis > maxBlasDepth) maxBlasDepth = h.orderAxis;
+        if (h.nTris > maxBlasTris) maxBlasTris = h.nTris;
     }
     std::vector<InstanceRec> recs(n);
     for (uint32_t i = 0; i < n; ++i) {
@@ -753,6 +754,9 @@ extern "C" int theia_tlas_build(const theia_instance_desc_t* instances, uint32_t
     h.magic = THEIA_TLAS_MAGIC;
     h.nodesOffset = sizeof(TlasHeader);
     h.instancesOffset = sizeof(TlasHeader) + (uint64_t)n * sizeof(WideNode);
+    // stride of the 32 bit tie key (instance * stride + primitive) of the queued ray query kernel
+    // (trace_queue.cuh); 0 = the scene does not fit it and that kernel falls back to one thread per ray
+    h.pad[0] = ((uint64_t)n * maxBlasTris < 0xFFFFFFFFull && maxBlasTris < (1u << 25)) ? maxBlasTris : 0u;
     CUDA_OK(cudaMemcpyAsync(out, &h, sizeof(h), cudaMemcpyHostToDevice, st));
     initBuildKernel<<<blocksFor(n > 8 ? n : 8, bs), bs, 0, st>>>(s, n);
     instanceBoxKernel<<<blocksFor(n, bs), bs, 0, st>>>(s, instIn, n);

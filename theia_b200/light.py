@@ -17,12 +17,12 @@ import numpy as np
 import theia_b200.units as u
 from theia_b200 import _abi
 from theia_b200.glsl import buffer_reference, vec2, vec3, vec4
-from theia_b200.pipeline import SourceCodeMixin
+from theia_b200.pipeline import PipelineStage, SourceCodeMixin
 
 __all__ = [
     "CherenkovLightSource", "CherenkovTrackLightSource", "ConeLightSource", "ConstWavelengthSource",
     "FunctionWavelengthSource", "HostLightSource", "HostWavelengthSource", "LightSampleItem", "ParticleTrack",
-    "LightSource", "MuonTrackLightSource", "ParticleCascadeLightSource", "PencilLightSource",
+    "LightSampler", "LightSource", "MuonTrackLightSource", "ParticleCascadeLightSource", "PencilLightSource",
     "PolarizedLightSampleItem", "SphericalLightSource", "StreamingHostLightSource",
     "StreamingHostWavelengthSource", "UniformWavelengthSource", "WavelengthSampleItem", "WavelengthSource",
     "frankTamm",
@@ -282,6 +282,131 @@ class LightSampleItem(Structure):
 class PolarizedLightSampleItem(Structure):
     _fields_ = [("position", c_float * 3), ("direction", c_float * 3), ("stokes", c_float * 4),
                 ("polarizationRef", c_float * 3), ("startTime", c_float), ("contrib", c_float)]
+
+
+class LightSampler(PipelineStage):
+    """
+    Samples a ``LightSource`` (+ ``WavelengthSource``) into queues (src/theia/light.py:492-690,
+    sh/lightsource.sample.glsl): sample k of a run is stream ``baseCount + k`` of the generator, drawing
+    the wavelength first and the light ray second, exactly like path k of a tracer does.
+
+    Parameters: ``source, wavelengthSource, capacity``; keywords ``rng, medium, polarized, retrieve,
+    scene, batchSize``. Stage parameters: ``count`` (samples per run, at most ``capacity``),
+    ``baseCount`` (offset into the sampling stream), ``medium`` (address of the medium the source is
+    submerged in; vacuum if 0).
+    """
+
+    name = "Light Sampler"
+
+    class SampleParams(Structure):
+        _fields_ = [("count", c_uint32), ("baseCount", c_uint32), ("medium", buffer_reference)]
+
+    def __init__(self, source: LightSource, wavelengthSource: WavelengthSource, capacity: int, *, rng=None,
+                 medium: int | None = None, polarized: bool = False, retrieve: bool = True, scene=None,
+                 batchSize: int = 128, code: bytes | None = None) -> None:
+        from theia_b200.queue import IOQueue
+        needRNG = source.nRNGForward > 0 or wavelengthSource.nRNGSamples > 0
+        if needRNG and rng is None:
+            raise ValueError("Light source requires a RNG but none was given!")
+        if isinstance(source, HostLightSource) and source.polarized != polarized:
+            raise RuntimeError("mismatch in light queue definition")  # sh/lightsource.sample.glsl:25-29
+        super().__init__({"SampleParams": self.SampleParams})
+        if medium is None:
+            medium = 0 if scene is None else scene.medium
+        self._batchSize = batchSize
+        self._capacity = capacity
+        self._scene = scene
+        self._source = source
+        self._retrieve = retrieve
+        self._polarized = polarized
+        self._rng = rng
+        self._wavelengthSource = wavelengthSource
+        self._code = code or b""
+        self.setParams(count=capacity, baseCount=0, medium=medium)
+        self._lightQueue = IOQueue(PolarizedLightSampleItem if polarized else LightSampleItem, capacity, mode="retrieve")
+        self._lamQueue = IOQueue(WavelengthSampleItem, capacity, mode="retrieve")
+
+    @property
+    def batchSize(self) -> int:
+        """Number of samples drawn per work group"""
+        return self._batchSize
+
+    @property
+    def capacity(self) -> int:
+        """Maximum number of samples that can be drawn per run"""
+        return self._capacity
+
+    @property
+    def code(self) -> bytes:
+        return self._code
+
+    @property
+    def lightQueue(self):
+        """Queue storing the light samples"""
+        return self._lightQueue
+
+    @property
+    def polarized(self) -> bool:
+        return self._polarized
+
+    @property
+    def retrieve(self) -> bool:
+        return self._retrieve
+
+    @property
+    def rng(self):
+        return self._rng
+
+    @property
+    def scene(self):
+        return self._scene
+
+    @property
+    def source(self) -> LightSource:
+        return self._source
+
+    @property
+    def wavelengthSource(self) -> WavelengthSource:
+        return self._wavelengthSource
+
+    @property
+    def wavelengthQueue(self):
+        """Queue holding the sampled wavelengths"""
+        return self._lamQueue
+
+    def collectStages(self) -> list[PipelineStage]:
+        stages = [] if self.rng is None else [self.rng]
+        stages.extend([self.wavelengthSource, self.source, self])
+        return stages
+
+    def _unitArgs(self, i: int):
+        """Launch description of configuration i (theia_unit_eval, unit LIGHT_SAMPLE)"""
+        from theia_b200 import _units
+        p = self._block("SampleParams", i)
+        if p.count > self._capacity:
+            raise ValueError("count exceeds the capacity of the sampler")
+        A = _units.unitArgs(_abi.UNIT_LIGHT_SAMPLE, p.count, rng=self._rng, i=i, polarized=self._polarized,
+                            first=p.baseCount, medium=p.medium.value, light=self._source, wavelength=self._wavelengthSource)
+        A.light_queue = self._lightQueue.tensor.data_ptr()
+        A.wavelength_queue = self._lamQueue.tensor.data_ptr()
+        A.capacity = self._capacity
+        return A
+
+    def run(self, i: int):
+        from ctypes import byref
+        from theia_b200 import _device, _lib
+
+        def cmd() -> None:
+            if self._device != "cuda":
+                raise RuntimeError("LightSampler needs a CUDA device (no CPU fallback)")
+            A = self._unitArgs(i)
+            A.stream = _device.currentStream("cuda")
+            _lib.check(_lib.load().theia_unit_eval(byref(A)))
+
+        cmds = [cmd]
+        if self._retrieve:
+            cmds += [*self._lightQueue.run(i), *self._lamQueue.run(i)]
+        return cmds
 
 
 class HostLightSource(LightSource):
