@@ -132,8 +132,7 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
     uint32_t chunk = total / (2u * nWarps);
     chunk = chunk > 32u ? 32u : (chunk < 1u ? 1u : chunk);
 
-    uint32_t stackKey[THEIA_STACK_SIZE];
-    float stackT[THEIA_STACK_SIZE];
+    unsigned long long stack[THEIA_STACK_SIZE];  // entry distance bits << 32 | key: one load / store per entry
     int sp = 0;
     bool have = false;
     uint32_t task = WT_NONE, payload = 0u;  // the entry this lane works on next (popped, not yet done)
@@ -189,8 +188,9 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
         if (task == WT_NONE) {
             while (sp > 0) {
                 --sp;
-                if (stackT[sp] > lim) continue;
-                const uint32_t key = stackKey[sp];
+                const unsigned long long e = stack[sp];
+                if (u2f((uint32_t)(e >> 32)) > lim) continue;
+                const uint32_t key = (uint32_t)e;
                 payload = key & 0x3FFFFFFFu;
                 const uint32_t type = key >> 30;
                 task = type == WE_INST ? WT_INST : WT_NODE;
@@ -267,9 +267,13 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
                     uint32_t k;
                     if ((imask >> i) & 1u) k = ((inBlas ? WE_BLAS : WE_TLAS) << 30) | (childBase + meta - 1u);
                     else k = (WE_INST << 30) | (n.b.y + (meta >> 3));
-                    if (sp < THEIA_STACK_SIZE) {  // cannot fail: theia_tlas_build bounds the depth of the trees
-                        stackKey[sp] = k;
-                        stackT[sp] = tmin[i];
+                    if (mask == 0u) {
+                        // the nearest child is the lane's next entry: it stays in registers
+                        payload = k & 0x3FFFFFFFu;
+                        task = (k >> 30) == WE_INST ? WT_INST : WT_NODE;
+                        taskBlas = (k >> 30) == WE_BLAS;
+                    } else if (sp < THEIA_STACK_SIZE) {  // cannot fail: theia_tlas_build bounds the depth of the trees
+                        stack[sp] = ((unsigned long long)f2u(tmin[i]) << 32) | k;
                         ++sp;
                     }
                 }
