@@ -464,6 +464,17 @@ int theia_tlas_build(const theia_instance_desc_t *instances, uint32_t n_instance
 int theia_tlas_query(const void *tlas_dev, const float *rays_dev, uint32_t n, int32_t *out_dev,
                      float *out_bary_dev, uint64_t *stats_dev, void *stream);
 
+/* The same ray queries for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). No counterpart in the reference.
+ * It runs the queued wavefront ray query kernel with its scratch memory (ray counter, work cursor, one 16 byte
+ * result record per ray) in a static device array of the library, and calls no cudaMalloc / cudaFree / allocating
+ * routine. Limits: n <= 262144 rays per call (more is rejected with an error; split the rays over several calls);
+ * every GPU that loads the library holds the array (4 MiB + 256 B) until the process exits. All calls share the
+ * array: calls that overlap on the GPU (different streams, or graphs replayed concurrently) race; calls on one
+ * stream are safe, each call rewrites what it reads. Same outputs, bit for bit, as theia_tlas_query (no statistics). */
+int theia_tlas_query_static(const void *tlas_dev, const float *rays_dev, uint32_t n, int32_t *out_dev,
+                            float *out_bary_dev, void *stream);
+
 /* ------------------------------------------------------------------ tracers */
 /* Number of CTAs the launch will use = number of partial histograms it writes. */
 int theia_trace_grid_size(const theia_trace_launch_t *launch, uint32_t *n_blocks);

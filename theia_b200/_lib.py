@@ -38,6 +38,7 @@ SYMBOLS = {
     "theia_tlas_build": (c_int, [POINTER(_abi.InstanceDesc), c_uint32, c_void_p, c_uint64, c_void_p, c_uint64,
                                  c_void_p]),
     "theia_tlas_query": (c_int, [c_void_p, c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "theia_tlas_query_static": (c_int, [c_void_p, c_void_p, c_uint32, c_void_p, c_void_p, c_void_p]),
     "theia_trace_grid_size": (c_int, [POINTER(_abi.TraceLaunch), POINTER(c_uint32)]),
     "theia_trace_workspace_size": (c_int, [POINTER(_abi.TraceLaunch), POINTER(c_uint64)]),
     "theia_trace_forward": (c_int, [POINTER(_abi.TraceLaunch)]),

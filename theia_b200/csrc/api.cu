@@ -868,3 +868,57 @@ int theia_unit_eval(const theia_unit_args_t* args) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ ray queries without any allocation
+// theia_tlas_query_static: the ray query seam through the queued wavefront kernel (trace_queue.cuh), whose
+// scratch memory (ray counter, work cursor, one result record per ray) lives in a file-scope device array
+// instead of cudaMallocAsync memory, for callers that must not allocate (CUDA graph capture, serving loops).
+// Every GPU that loads the library holds the array (4 MiB + 256 B) until the process exits.
+#define THEIA_QUERY_STATIC_MAX_RAYS (1u << 18)
+static __device__ __align__(256) unsigned char g_queryScratch[256 + 16ull * THEIA_QUERY_STATIC_MAX_RAYS];
+
+// Device address of g_queryScratch on the current device. In host code the array's name is only a stand-in
+// for the symbol, not an address a kernel may use: the address is asked for once per device.
+static int queryScratchAddress(unsigned char** out) {
+    static std::mutex mutex;
+    static unsigned char* perDevice[64] = {};
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { setError("theia_tlas_query_static: device ordinal %d not supported", dev); return -1; }
+    std::lock_guard<std::mutex> lock(mutex);
+    if (!perDevice[dev]) {
+        unsigned char* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress((void**)&p, g_queryScratch));
+        if (!p) { setError("theia_tlas_query_static: no address for the scratch array"); return -1; }
+        perDevice[dev] = p;
+    }
+    *out = perDevice[dev];
+    return 0;
+}
+
+extern "C" int theia_tlas_query_static(const void* tlas_dev, const float* rays_dev, uint32_t n, int32_t* out_dev,
+                                       float* out_bary_dev, void* stream) {
+    if (!tlas_dev || !rays_dev || !out_dev || !out_bary_dev) { setError("theia_tlas_query_static: null argument"); return -1; }
+    if (n > THEIA_QUERY_STATIC_MAX_RAYS) {
+        setError("theia_tlas_query_static: %u rays exceed the static scratch array (at most %u per call)", n,
+                 THEIA_QUERY_STATIC_MAX_RAYS);
+        return -1;
+    }
+    if (n == 0) return 0;
+    unsigned char* scratch = nullptr;
+    if (queryScratchAddress(&scratch)) return -1;
+    uint32_t* counters = reinterpret_cast<uint32_t*>(scratch);          // [0] rays, [1] cursor: rewritten by every call
+    uint4* results = reinterpret_cast<uint4*>(scratch + 256);           // [n]: every entry < n is written before it is read
+    cudaStream_t st = (cudaStream_t)stream;
+    uint32_t grid = 0;
+    if (persistentGrid((const void*)wfTraceQueuedKernel, 0, &grid)) return -1;
+    const uint32_t need = blocksFor(n, TRACE_THREADS);
+    if (grid > need) grid = need;
+    wfQuerySetupKernel<<<1, 32, 0, st>>>(counters, n);
+    wfTraceQueuedKernel<<<grid, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results, counters,
+                                                        counters + 1, 1u, 0u, (uint32_t)g_optFlushWaiting);
+    wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
+    countLaunches(3);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
