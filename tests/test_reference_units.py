@@ -434,3 +434,316 @@ def test_particle_sampleEmissionAngle_full(backend, n, a, b):  # tests/test_ligh
     err = np.abs(hist - exp_hist) / exp_hist
     assert err[: peak_bin - 1].max() < 0.05
     assert err[peak_bin + 2:].max() < 0.05
+
+
+# ------------------------------------------------------------------ tests/test_target.py, tests/test_target_guide.py
+def test_innerSphereTarget(backend):  # tests/test_target.py:125-163
+    from theia_b200 import random, target
+    from theia_b200.scene import RectBBox
+    from theia_b200.testing import TargetSampler
+    N = 32 * 256
+    pos, radius = (8.0, -5.0, 3.2), 4.8
+    box = RectBBox((3.0, -10.0, -1.0), (13.0, 0.0, 8.0))
+    with device(backend):
+        tgt = target.InnerSphereTarget(position=pos, radius=radius)
+        philox = random.PhiloxRNG(key=0xC0FFEE)
+        sampler = TargetSampler(N, tgt, rng=philox, sampleBox=box)
+    runSampler(backend, sampler)
+    r = sampler.getResults(0)
+    od = np.sqrt(np.square(r["observer"] - pos).sum(-1))
+    assert np.all((od >= radius) == r["occluded"])
+    oclMask = r["occluded"] == 0
+    assert np.allclose(r["sampleProb"][oclMask], 1.0 / (4.0 * np.pi * radius**2))
+    assert np.all(r["sampleError"][oclMask] == 0)
+    assert (r["sampleValid"] != 0).sum() > 0
+    hitMask = oclMask & (r["hitValid"] != 0)
+    assert hitMask.sum() > 0
+    # Bit 3 of hitError (direction of hitPos - observer against the query direction, 1e-5) cannot hold in float32 for an
+    # observer closer than ~0.1 m to the sphere: hitPos carries ulp(10) = 1e-6 of rounding, i.e. 1e-6 / t of direction
+    # error. It is checked where it is well conditioned; the other bits (distance, object space position / normal) always.
+    near = np.sqrt(np.square(r["hitPos"] - r["observer"]).sum(-1)) < 0.2
+    assert np.all((r["hitError"][hitMask] & 7) == 0)
+    assert np.all(r["hitError"][hitMask & ~near] == 0)
+    assert (hitMask & near).sum() < 0.05 * hitMask.sum()
+    p = np.array(pos)
+    sd = np.sqrt(np.square(r["samplePos"][oclMask] - p).sum(-1))
+    assert np.allclose(sd, radius)
+    sn = (r["samplePos"][oclMask] - p) / sd[:, None]
+    assert np.allclose(-sn, r["sampleNrm"][oclMask], atol=1e-7)
+    hd = np.sqrt(np.square(r["hitPos"][hitMask] - p).sum(-1))
+    assert np.allclose(hd, radius)
+    hn = (r["hitPos"][hitMask] - p) / hd[:, None]
+    assert np.allclose(-hn, r["hitNrm"][hitMask])
+
+
+def test_sphereTarget(backend):  # tests/test_target.py:166-203
+    from theia_b200 import random, target
+    from theia_b200.testing import TargetSampler
+    N = 32 * 256
+    pos, radius = (12.0, -5.0, 3.2), 4.0
+    with device(backend):
+        tgt = target.SphereTarget(position=pos, radius=radius)
+        philox = random.PhiloxRNG(key=0xC0FFEE)
+        sampler = TargetSampler(N, tgt, rng=philox)
+    runSampler(backend, sampler)
+    r = sampler.getResults(0)
+    od = np.sqrt(np.square(r["observer"] - pos).sum(-1))
+    assert np.all((od <= radius) == r["occluded"])
+    oclMask = r["occluded"] == 0
+    expProb = 1.0 / (2.0 * np.pi * radius**2) / (1.0 - radius / od)
+    assert np.allclose(r["sampleProb"][oclMask], expProb[oclMask])
+    assert np.all(r["sampleError"][oclMask] == 0)
+    assert (r["sampleValid"] != 0).sum() == N
+    hitMask = oclMask & (r["hitValid"] != 0)
+    assert hitMask.sum() > 0
+    assert np.all(r["hitError"][hitMask] == 0)
+    p = np.array(pos)
+    sd = np.sqrt(np.square(r["samplePos"][oclMask] - p).sum(-1))
+    assert np.allclose(sd, radius)
+    sn = (r["samplePos"][oclMask] - p) / sd[:, None]
+    assert np.allclose(sn, r["sampleNrm"][oclMask], atol=3e-7)
+    hd = np.sqrt(np.square(r["hitPos"][hitMask] - p).sum(-1))
+    assert np.allclose(hd, radius)
+    hn = (r["hitPos"][hitMask] - p) / hd[:, None]
+    assert np.allclose(hn, r["hitNrm"][hitMask])
+
+
+def intersectSphere(center, rad, pos, dir):
+    """near hit, far hit, hit mask (tests/test_target_guide.py:13-26; Ray Tracing Gems ch. 7)"""
+    f = pos - center
+    b2 = np.multiply(f, dir).sum(-1)
+    fd = f - b2[:, None] * dir
+    discr = rad**2 - np.square(fd).sum(-1)
+    c = np.square(f).sum(-1) - rad**2
+    with np.errstate(invalid="ignore"):
+        q = -b2 - np.copysign(1.0, b2) * np.sqrt(discr)
+    return c / q, q, discr >= 0.0
+
+
+def test_sphereTargetGuide(backend):  # tests/test_target_guide.py:37-72
+    from theia_b200 import random, target
+    from theia_b200.testing import TargetGuideSampler
+    N = 32 * 256
+    pos, radius = (12.0, -5.0, 3.2), 4.0 * u.m
+    with device(backend):
+        guide = target.SphereTargetGuide(position=pos, radius=radius)
+        philox = random.PhiloxRNG(key=0xC0FFEE)
+        sampler = TargetGuideSampler(N, guide, rng=philox)
+    runSampler(backend, sampler)
+    r = sampler.getResults(0)
+    pos = np.array(pos)
+    d = np.sqrt(np.square(pos - r["observer"]).sum(-1))
+    valid = d > radius
+    assert np.all(r["sampleProb"][~valid] == 0.0)
+    assert np.all((r["sampleProb"] > 0.0) == valid)
+    t1, t2, hit = intersectSphere(pos, radius, r["observer"].astype(np.float64), r["sampleDir"].astype(np.float64))
+    assert np.all(r["sampleDist"][valid] >= t2[valid])
+    assert np.allclose(np.square(r["sampleDir"]).sum(-1), 1.0)
+    with np.errstate(invalid="ignore"):
+        cosMin = 1.0 - np.sqrt(1.0 - (radius / d) ** 2)
+    prob = 1.0 / (2.0 * np.pi * cosMin)
+    assert np.allclose(r["sampleProb"][valid], prob[valid])
+    assert np.allclose(np.square(r["evalDir"]).sum(-1), 1.0)
+    t1, t2, hit = intersectSphere(pos, radius, r["observer"].astype(np.float64), r["evalDir"].astype(np.float64))
+    valid = valid & (t2 >= 0.0)
+    assert np.all(r["evalProb"][~valid] == 0.0)
+    assert np.all((r["evalProb"] > 0.0) == valid)
+    assert np.all(r["evalDist"][valid] >= t2[valid])
+    assert np.allclose(r["evalProb"][valid], prob[valid])
+
+
+# ------------------------------------------------------------------ tests/test_light.py (forward samplers)
+def _lightSampler(backend, makeLight, makePhotons, N, *, key, polarized=False, medium=None):
+    from theia_b200 import light, random
+    with device(backend):
+        philox = random.PhiloxRNG(key=key)
+        photons, source = makePhotons(), makeLight()
+        sampler = light.LightSampler(source, photons, N, rng=philox, polarized=polarized,
+                                     medium=medium() if medium else None)
+    runSampler(backend, sampler)
+    return source, sampler.lightQueue.view(0), sampler.wavelengthQueue.view(0)
+
+
+def test_constWavelength(backend):  # tests/test_light.py:154-169
+    from theia_b200 import light
+    N, lam = 32 * 256, 450.0 * u.nm
+    _, _, result = _lightSampler(backend, lambda: light.PencilLightSource(timeRange=(0.0, 0.0)),
+                                 lambda: light.ConstWavelengthSource(lam), N, key=0xC0110FFC0FFEE)
+    assert np.all(result["contrib"] == 1.0)
+    assert np.all(result["wavelength"] == lam)
+
+
+@pytest.mark.parametrize("normalize", [True, False])
+def test_uniformWavelength(backend, normalize):  # tests/test_light.py:172-194
+    from theia_b200 import light
+    N = 32 * 256
+    lamRange, dLam = (350.0 * u.nm, 750.0 * u.nm), 400.0 * u.nm
+    contrib = 1.0 if normalize else dLam
+    _, _, result = _lightSampler(backend, lambda: light.PencilLightSource(timeRange=(0.0, 0.0)),
+                                 lambda: light.UniformWavelengthSource(lambdaRange=lamRange, normalize=normalize), N,
+                                 key=0xC0110FFC0FFEE)
+    assert np.all(result["contrib"] == contrib)
+    assert np.abs(np.min(result["wavelength"]) - lamRange[0]) < 1.0
+    assert np.abs(np.max(result["wavelength"]) - lamRange[1]) < 1.0
+
+
+@pytest.mark.parametrize("polarized", [True, False])
+def test_coneLightSource_fwd(backend, polarized):  # tests/test_light.py:233-278
+    from theia_b200 import light
+    N = 32 * 256
+    position, direction, opening = (14.0, -2.0, 3.0), (0.8, 0.36, 0.48), 0.33
+    stokes, polRefIn, budget = (1.0, 0.9, 0.1, -0.5), (0.0, 0.48, -0.36), 12.0
+    _, result, _ = _lightSampler(
+        backend, lambda: light.ConeLightSource(position=position, direction=direction, timeRange=(10.0 * u.ns, 10.0 * u.ns),
+                                               cosOpeningAngle=opening, budget=budget, stokes=stokes,
+                                               polarizationReference=polRefIn, polarized=polarized),
+        lambda: light.ConstWavelengthSource(wavelength=100.0 * u.nm), N, key=0xC0110FFC0FFEE, polarized=polarized)
+    assert result.count == N
+    assert np.allclose(result["position"], position)
+    assert (result["direction"] * direction).sum(-1).min() >= opening
+    assert np.abs(np.square(result["direction"]).sum(-1) - 1.0).max() < 1e-5
+    assert np.all(result["contrib"] == budget)
+    if polarized:
+        assert np.allclose(result["stokes"], stokes)
+        polRef = result["polarizationRef"]
+        assert np.abs(np.square(polRef).sum(-1) - 1.0).max() < 1e-5
+        # polRef was only straightened against the ray, not rotated about it (that would invalidate the Stokes vector)
+        vol = (np.cross(result["direction"], polRefIn) * polRef).sum(-1)
+        assert np.abs(vol).max() < 1e-5
+
+
+@pytest.mark.parametrize("polarized", [True, False])
+def test_pencilLightSource(backend, polarized):  # tests/test_light.py:339-372
+    from theia_b200 import light
+    N = 32 * 256
+    position, direction = (14.0, -2.0, 3.0), (0.8, 0.36, 0.48)
+    stokes, polRef, budget = (1.0, 0.9, 0.1, -0.5), (0.0, 0.48, -0.36), 12.0
+    _, result, _ = _lightSampler(
+        backend, lambda: light.PencilLightSource(position=position, direction=direction, timeRange=(10.0 * u.ns, 10.0 * u.ns),
+                                                 budget=budget, stokes=stokes, polarizationRef=polRef),
+        lambda: light.ConstWavelengthSource(wavelength=100.0 * u.nm), N, key=0xC0110FFC0FFEE, polarized=polarized)
+    assert result.count == N
+    assert np.allclose(result["position"], position)
+    assert np.allclose(result["direction"], direction)
+    assert np.all(result["contrib"] == budget)
+    if polarized:
+        assert np.allclose(result["stokes"], stokes)
+        assert np.allclose(result["polarizationRef"], polRef)
+
+
+@pytest.mark.parametrize("polarized", [True, False])
+def test_sphericalLightSource_fwd(backend, polarized):  # tests/test_light.py:375-411
+    from theia_b200 import light
+    N = 32 * 256
+    position, budget = (14.0, -2.0, 3.0), 12.0
+    _, result, _ = _lightSampler(
+        backend, lambda: light.SphericalLightSource(position=position, timeRange=(10.0 * u.ns, 10.0 * u.ns), budget=budget),
+        lambda: light.ConstWavelengthSource(wavelength=100.0 * u.nm), N, key=0xC0110FFC0FFEE, polarized=polarized)
+    assert result.count == N
+    assert np.all(result["position"] == np.array(position, dtype=np.float32))
+    assert np.allclose(np.sqrt(np.square(result["direction"]).sum(-1)), 1.0)
+    assert np.abs(np.mean(result["direction"], axis=0)).max() < 0.01
+    assert np.allclose(result["contrib"], budget)
+    if polarized:
+        assert np.allclose(result["stokes"], (1.0, 0.0, 0.0, 0.0))
+        polRef = result["polarizationRef"]
+        assert np.abs((polRef * result["direction"]).sum(-1)).max() < 1e-5
+        assert (np.square(polRef).sum(-1) - 1.0).max() < 1e-5
+
+
+def _phiUniform(result, direction, up):
+    from scipy import stats
+    cos_phi = np.multiply(result["direction"], up).sum(-1)
+    sin_phi = np.multiply(np.cross(result["direction"], up), direction).sum(-1)
+    phi = (np.arctan2(sin_phi, cos_phi) + np.pi) / (2.0 * np.pi)
+    return stats.kstest(phi[::100], "uniform").pvalue
+
+
+@pytest.mark.parametrize("applyFrankTamm", [False, True])
+def test_muonTrackLightSource_fwd(backend, applyFrankTamm):  # tests/test_light.py:839-909
+    from scipy import integrate
+    from theia_b200 import light, material
+    from theia_b200.testing import WaterTestModel
+    N = 256 * 1024
+    lam_range = (300.0 * u.nm, 500.0 * u.nm)
+    E_muon = 10.0 * u.TeV
+    startPos, startTime = np.array([1.0, 5.0, -2.0]) * u.m, 0.5 * u.us
+    direction, dist = np.array([0.36, 0.48, 0.8]), 100.0 * u.m
+    endPos, endTime = startPos + direction * dist, startTime + dist / u.c
+    up = np.array([0.8, -0.6, 0.0])
+    water = WaterTestModel()
+    store = {}
+
+    def medium():
+        store["s"] = material.MaterialStore([], media=[water.createMedium(*lam_range)])
+        return store["s"].media["water"]
+
+    src, result, photons = _lightSampler(
+        backend, lambda: light.MuonTrackLightSource(startPos, startTime, endPos, endTime, E_muon, applyFrankTamm=applyFrankTamm),
+        lambda: light.UniformWavelengthSource(lambdaRange=lam_range, normalize=False), N, key=0xC0FFEE, medium=medium)
+    distStart = np.sqrt(np.square(startPos - result["position"]).sum(-1))
+    distEnd = np.sqrt(np.square(endPos - result["position"]).sum(-1))
+    assert np.allclose(distStart + distEnd, dist)
+    assert np.allclose(result["startTime"], startTime + distStart / u.c)
+    assert distStart.min() < 0.05 and distEnd.min() < 0.05
+    assert np.allclose(np.square(result["direction"]).sum(-1), 1.0)
+    cos_theta = np.multiply(result["direction"], direction).sum(-1)
+    assert cos_theta.max() > 0.999 and cos_theta.min() < -0.999
+    assert _phiUniform(result, direction, up) > 0.05
+    # the Monte Carlo estimate converges to the number of Cherenkov photons produced along the track
+    energyScale = src.getParam("_energyScale")
+    if applyFrankTamm:
+        lam = np.linspace(*lam_range, 1025)
+        dlam = (lam_range[1] - lam_range[0]) / (len(lam) - 1)
+        ft = light.frankTamm(lam, water.refractive_index(lam))
+        nPhotons = integrate.romb(ft, dlam) * dist * energyScale
+        contrib = result["contrib"].astype(np.float64) * photons["contrib"]
+        assert np.abs(1.0 - contrib.mean() / nPhotons) < 5e-4
+    else:
+        assert np.allclose(result["contrib"], dist * energyScale)
+
+
+@pytest.mark.parametrize("applyFrankTamm", [False, True])
+@pytest.mark.parametrize("particle", ["e-", "pi+"])
+def test_particleCascadeLightSource_fwd(backend, applyFrankTamm, particle):  # tests/test_light.py:991-1065
+    from scipy import integrate
+    from theia_b200 import cascades, light, material
+    from theia_b200.testing import WaterTestModel
+    N = 256 * 1024
+    lam_range = (300.0 * u.nm, 500.0 * u.nm)
+    startPos, startTime = np.array([1.0, 5.0, -2.0]) * u.m, 0.5 * u.us
+    direction = np.array([0.36, 0.48, 0.8])
+    up = np.array([0.8, -0.6, 0.0])
+    primary = cascades.ParticleType.E_MINUS if particle == "e-" else cascades.ParticleType.PI_PLUS
+    p = cascades.Particle(primary, startPos, direction, 1.0 * u.TeV, startTime)
+    params = cascades.createParamsFromParticle(p, lightSourceName="")[1]
+    water = WaterTestModel()
+    store = {}
+
+    def medium():
+        store["s"] = material.MaterialStore([], media=[water.createMedium(*lam_range)])
+        return store["s"].media["water"]
+
+    _, result, photons = _lightSampler(
+        backend, lambda: light.ParticleCascadeLightSource(**params, applyFrankTamm=applyFrankTamm),
+        lambda: light.UniformWavelengthSource(lambdaRange=lam_range), N, key=0xC0FFEE, medium=medium)
+    dirPos = result["position"] - startPos
+    distPos = np.sqrt(np.square(dirPos).sum(-1))
+    dirPos = dirPos / distPos[:, None]
+    assert np.allclose(dirPos[distPos > 0.0], direction)
+    assert np.allclose(startTime + distPos / u.c, result["startTime"])
+    z_max = (params["a_long"] - 1) * params["b_long"]  # mode of the gamma distribution
+    assert distPos.min() < 0.1 * z_max
+    assert distPos.max() > 4.0 * z_max
+    assert np.allclose(np.square(result["direction"]).sum(-1), 1.0)
+    cos_theta = np.multiply(result["direction"], direction).sum(-1)
+    assert cos_theta.min() < -0.999 and cos_theta.max() > 0.999
+    assert _phiUniform(result, direction, up) > 0.05
+    est = result["contrib"].astype(np.float64).mean()
+    expEst = params["effectiveLength"]
+    if applyFrankTamm:
+        lam = np.linspace(*lam_range, 1025)
+        dlam = (lam_range[1] - lam_range[0]) / (len(lam) - 1)
+        dN_dx = integrate.romb(light.frankTamm(lam, water.refractive_index(lam)), dlam)
+        expEst = dN_dx * params["effectiveLength"] / (lam_range[1] - lam_range[0])
+    assert np.abs(1.0 - est / expEst) < 5e-4
