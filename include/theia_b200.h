@@ -393,8 +393,11 @@ uint64_t theia_kernel_launches(void);
 
 /* Tuning / test seam (no counterpart in the reference). Options:
  *   "wf_trace_kernel", "wf_shadow_trace_kernel": ray query kernel of the wavefront scene tracer for
- *       primary / shadow rays: -1 (default) = picked per scene from timings of the first six
- *       batches, 0 = phased persistent kernel, 1 = one thread per ray. Results do not depend on it.
+ *       primary / shadow rays: -1 (default) = picked per scene from timings of the first nine
+ *       batches, 0 = phased persistent kernel, 1 = one thread per ray, 2 = queued (a warp level queue of triangle
+ *       tests, trace_queue.cuh). Results do not depend on it.
+ *   "wf_flush_waiting": thresholds of the queued kernel (waiting lanes | instance lanes << 8 | refill lanes << 16).
+ *   "query_kernel": kernel behind theia_tlas_query: 0 = direct traversal (default), 1 = phased, 2 = queued.
  *   "wf_min_node_lanes": 1..32, node phase threshold of the phased kernel (default 16).
  * theia_get_trace_choice reports what was picked for a scene (-1 = still measuring). */
 int theia_set_option(const char *name, int value);
@@ -409,6 +412,15 @@ int theia_get_trace_choice(const void *tlas_dev, uint32_t batch_size, int guide,
 int theia_profile_enable(int on);
 int theia_profile_read(double *ms, uint64_t *launches, uint32_t n);
 const char *theia_profile_class_name(uint32_t cls);
+/* Measurement aids for the roofline block of bench.py (no counterpart in the reference).
+ * theia_trace_stats_enable(stats_dev): while stats_dev != NULL every ray query launch of the wavefront scene tracer is
+ *   preceded by an instrumented pass over the same rays that adds, for primary rays to stats_dev[0..3] and for shadow
+ *   rays to stats_dev[4..7], {nodes visited, triangles tested, instances entered, rays} of the one-thread-per-ray
+ *   traversal of the same structure (the algorithmic visit counts). NULL switches it off. Not thread safe.
+ * theia_l2_probe: reads a buffer of `bytes` (choose it well below the L2 size) `iters` times with 128 bit loads that
+ *   bypass L1; bytes * iters / elapsed time (CUDA events of the caller) is the L2 read bandwidth of the device. */
+int theia_trace_stats_enable(uint64_t *stats_dev);
+int theia_l2_probe(const void *buf_dev, uint64_t bytes, uint32_t iters, uint32_t *sink_dev, void *stream);
 /* Number of SMs etc. of the current device; used by the host to size buffers. */
 int theia_device_info(int *sm_count, int *cc_major, int *cc_minor);
 

@@ -246,7 +246,7 @@ def sceneC3(N: int, *, resp: str = "record", callback: str | None = None, polari
 
 def sceneC5(N: int, *, resp: str = "hist", callback: str | None = None, polarized: bool = False,
             lattice=(10, 10, 50), pitch=(60.0, 60.0, 10.0), lightKind: str = "cascade", key: int = 0x5EED,
-            nBins: int = 500, binSize: float = 10.0, maxPathLength: int = 10, **kw):
+            nBins: int = 500, binSize: float = 10.0, maxPathLength: int = 10, wavelength: str = "uniform", **kw):
     """Config C5: lattice of spherical optical modules (one shared BLAS) in sea water."""
     water = WaterTestModel().createMedium()
     glass = material.BK7Model().createMedium()
@@ -270,6 +270,8 @@ def sceneC5(N: int, *, resp: str = "hist", callback: str | None = None, polarize
     else:
         src = makeLight(lightKind, position=(3.0, 2.0, -100.0), direction=(0.0, 0.0, 1.0))
     wl = light.UniformWavelengthSource(lambdaRange=(300.0, 600.0))
+    if wavelength == "host":  # host generated photons ahead of a device light source (no draw for the wavelength)
+        wl = light.StreamingHostWavelengthSource(N, data=hostSourceData(2 * N, polarized=False)[1])
     return _sceneCommon(N, inst, store, store.media["water"], src, wl, resp, callback, polarized, maxPathLength, -1,
                         None, key, nBins, binSize, **kw)
 

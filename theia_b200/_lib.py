@@ -27,6 +27,8 @@ SYMBOLS = {
     "theia_profile_enable": (c_int, [c_int]),
     "theia_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_uint64), c_uint32]),
     "theia_profile_class_name": (c_char_p, [c_uint32]),
+    "theia_trace_stats_enable": (c_int, [c_void_p]),
+    "theia_l2_probe": (c_int, [c_void_p, c_uint64, c_uint32, c_void_p, c_void_p]),
     "theia_device_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "theia_philox_fill": (c_int, [POINTER(_abi.PhiloxParams), c_uint32, c_uint32, c_uint32, c_uint32, c_uint32,
                                   c_void_p, c_void_p]),

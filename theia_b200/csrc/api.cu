@@ -29,19 +29,34 @@ enum KernelClass : int { KC_VOLUME, KC_SCENE, KC_GENERATE, KC_TRACE, KC_SHADE, K
 static const char* const g_classNames[KC_COUNT] = {"volumeForwardKernel", "sceneForwardKernel", "wfGenerateKernel",
                                                    "wfTraceKernel", "wfShadeKernel", "wfTraceKernel(shadow)",
                                                    "wfShadeShadowKernel", "histReduceKernel"};
-struct PendingTiming { int cls; cudaEvent_t a, b; };
+struct PendingTiming { int cls, dev; cudaEvent_t a, b; };
+#define THEIA_MAX_DEVICES 64
+// Guards the profiler and the trace kernel tuners: the library may be driven by several host threads (two pipeline
+// schedulers) and for several devices (events are only ever reused on the device they were created on).
+static std::recursive_mutex g_stateMutex;
 static struct {
     bool on = false;
     std::vector<PendingTiming> pending;
-    std::vector<cudaEvent_t> pool;
+    std::vector<cudaEvent_t> pool[THEIA_MAX_DEVICES];
     double ms[KC_COUNT] = {};
     unsigned long long n[KC_COUNT] = {};
 } g_prof;
-static cudaEvent_t profEvent() {
+static int currentDeviceSlot() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) dev = 0;
+    return dev % THEIA_MAX_DEVICES;
+}
+static cudaEvent_t profEvent(int dev) {
+    std::lock_guard<std::recursive_mutex> lock(g_stateMutex);
     cudaEvent_t e = nullptr;
-    if (!g_prof.pool.empty()) { e = g_prof.pool.back(); g_prof.pool.pop_back(); }
+    auto& pool = g_prof.pool[dev];
+    if (!pool.empty()) { e = pool.back(); pool.pop_back(); }
     else cudaEventCreate(&e);
     return e;
+}
+static void profRecycle(int dev, cudaEvent_t e) {
+    std::lock_guard<std::recursive_mutex> lock(g_stateMutex);
+    g_prof.pool[dev].push_back(e);
 }
 struct Timed {
     PendingTiming t{};
@@ -49,22 +64,24 @@ struct Timed {
     bool active;
     Timed(int cls, cudaStream_t s) : st(s), active(g_prof.on) {
         if (!active) return;
-        t.cls = cls; t.a = profEvent(); t.b = profEvent();
+        t.cls = cls; t.dev = currentDeviceSlot(); t.a = profEvent(t.dev); t.b = profEvent(t.dev);
         cudaEventRecord(t.a, st);
     }
     ~Timed() {
         if (!active) return;
         cudaEventRecord(t.b, st);
+        std::lock_guard<std::recursive_mutex> lock(g_stateMutex);
         g_prof.pending.push_back(t);
     }
 };
 static void profCollect() {
+    std::lock_guard<std::recursive_mutex> lock(g_stateMutex);
     for (auto& t : g_prof.pending) {
         float ms = 0.0f;
         cudaEventSynchronize(t.b);
         if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) { g_prof.ms[t.cls] += ms; g_prof.n[t.cls] += 1; }
-        g_prof.pool.push_back(t.a);
-        g_prof.pool.push_back(t.b);
+        g_prof.pool[t.dev].push_back(t.a);
+        g_prof.pool[t.dev].push_back(t.b);
     }
     g_prof.pending.clear();
 }
@@ -238,6 +255,43 @@ __global__ void wfQueryConvertKernel(const void* tlas, const float* rays, const 
     outBary[4 * i + 1] = h.valid ? h.u : 0.0f;
     outBary[4 * i + 2] = h.valid ? h.v : 0.0f;
     outBary[4 * i + 3] = 0.0f;
+}
+
+// ------------------------------------------------------------------ measurement aids
+// Visit counts of the ray queries of a wavefront launch (theia_trace_stats_enable): walks the same rays with the
+// instrumented one-thread-per-ray traversal and sums nodes visited / triangles tested / instances entered / rays.
+__global__ void __launch_bounds__(128) wfTraceStatsKernel(const void* tlas, const float4* rays, const uint32_t* countPtr,
+                                                          uint32_t raysPerEntry, uint32_t planeStride, unsigned long long* stats) {
+    const SceneView sc = makeSceneView(tlas, nullptr, 0);
+    const uint32_t count = *countPtr, total = count * raysPerEntry;
+    unsigned long long nodes = 0, tris = 0, inst = 0, n = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const uint32_t r = i < count ? i : i - count + planeStride;
+        const float4 a = __ldg(rays + 2 * (size_t)r), b = __ldg(rays + 2 * (size_t)r + 1);
+        TraversalStats st = {0, 0, 0};
+        closestHit<true>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, &st);
+        nodes += st.nodes; tris += st.tris; inst += st.instances; n += 1;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        nodes += __shfl_down_sync(FULL_MASK, nodes, o); tris += __shfl_down_sync(FULL_MASK, tris, o);
+        inst += __shfl_down_sync(FULL_MASK, inst, o); n += __shfl_down_sync(FULL_MASK, n, o);
+    }
+    if (laneId() == 0 && n) { atomicAdd(stats + 0, nodes); atomicAdd(stats + 1, tris); atomicAdd(stats + 2, inst); atomicAdd(stats + 3, n); }
+}
+static unsigned long long* g_traceStats = nullptr;  // device uint64[2][4]: primary, shadow rays; null = off
+
+// L2 read bandwidth probe (theia_l2_probe): every thread streams 128 bit loads that bypass L1 over a buffer that fits
+// the L2 cache, `iters` times; the caller times it with events. The xor of everything read lands in *sink.
+__global__ void __launch_bounds__(256) l2ProbeKernel(const uint4* buf, uint64_t n16, uint32_t iters, uint32_t* sink) {
+    uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint32_t it = 0; it < iters; ++it)
+        for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+            const uint4 v = __ldcg(buf + i);
+            acc.x ^= v.x; acc.y ^= v.y; acc.z ^= v.z; acc.w ^= v.w;
+        }
+    const uint32_t x = acc.x ^ acc.y ^ acc.z ^ acc.w;
+    if (x == 0x9E3779B9u) atomicXor(sink, x);  // keeps the loads alive; practically never taken
 }
 
 // ------------------------------------------------------------------ launch translation
@@ -476,13 +530,16 @@ static int g_optTraceKernel[2] = {envInt("THEIA_WF_TRACE_KERNEL", -1), envInt("T
 static int g_optMinNodeLanes = envInt("THEIA_WF_MIN_NODE_LANES", 16);
 static int g_optFlushWaiting = envInt("THEIA_WF_FLUSH_WAITING", 4 | (8 << 8) | (4 << 16));  // thresholds of the queued kernel: waiting lanes | instance lanes << 8 | refill lanes << 16
 static int g_optQueryKernel = envInt("THEIA_QUERY_KERNEL", getenv("THEIA_QUERY_WAVEFRONT") ? 1 : 0);  // theia_tlas_query: 0 direct, 1 phased, 2 queued
-static std::mutex g_tunerMutex;
-
-// Picks the trace kernel of a (scene, batch size) from the first six batches: even ones run the
-// phased kernel, odd ones the one-thread-per-ray kernel, each trace launch bracketed by events;
-// once the events of a timed batch have completed (polled, never waited for) they are summed
-// per ray class, and after the sixth the sums of batches 2-5 are compared. Both kernels return identical results, so tuning is invisible.
+// Picks the trace kernel of a (device, scene, batch size) from its first nine batches: batch b runs candidate b mod 3
+// (phased, one thread per ray, queued), each trace launch bracketed by events; once the events of a timed batch have
+// completed (polled, never waited for) they are summed per ray class, and after the ninth the sums of batches 3-8 are
+// compared (the first round only warms up: clocks, caches, lazy module loading). All kernels return identical results,
+// so tuning is invisible. A scene is known by the address of its TLAS; theia_tlas_build forgets what was learnt about an
+// address it writes a new structure to. All of this state is guarded by g_stateMutex, which launchWavefront holds
+// while it uses a tuner.
+#define TRACE_CANDIDATES 3
 struct TraceTuner {
+    int dev;
     const void* tlas;
     uint32_t batch;
     bool guide;
@@ -491,23 +548,35 @@ struct TraceTuner {
     int candidate = 0;
     bool inFlight = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending[2];
-    double ms[2][2] = {{0, 0}, {0, 0}};
+    double ms[2][TRACE_CANDIDATES] = {};
 };
 static std::vector<TraceTuner*> g_tuners;
-static TraceTuner* tunerFor(const void* tlas, uint32_t batch, bool guide) {
+static void tunerRelease(TraceTuner* t) {
+    for (auto& v : t->pending)
+        for (auto& e : v) { profRecycle(t->dev, e.first); profRecycle(t->dev, e.second); }
+    delete t;
+}
+static TraceTuner* tunerFor(int dev, const void* tlas, uint32_t batch, bool guide) {
     for (TraceTuner* t : g_tuners)
-        if (t->tlas == tlas && t->batch == batch && t->guide == guide) return t;
-    if (g_tuners.size() >= 64) {  // scenes come and go: forget the oldest entry
-        for (auto& v : g_tuners.front()->pending)
-            for (auto& e : v) { g_prof.pool.push_back(e.first); g_prof.pool.push_back(e.second); }
-        delete g_tuners.front();
+        if (t->dev == dev && t->tlas == tlas && t->batch == batch && t->guide == guide) return t;
+    if (g_tuners.size() >= 64) {  // scenes come and go: forget the oldest entry (nobody holds it: the mutex is ours)
+        tunerRelease(g_tuners.front());
         g_tuners.erase(g_tuners.begin());
     }
     TraceTuner* t = new TraceTuner;
-    t->tlas = tlas; t->batch = batch; t->guide = guide;
+    t->dev = dev; t->tlas = tlas; t->batch = batch; t->guide = guide;
     if (!guide) t->choice[1] = TRACE_PHASED;  // no shadow rays to decide about
     g_tuners.push_back(t);
     return t;
+}
+// called by theia_tlas_build: a new structure at this address is a new scene
+void tunerForget(const void* tlas) {
+    std::lock_guard<std::recursive_mutex> lock(g_stateMutex);
+    const int dev = currentDeviceSlot();
+    for (size_t i = 0; i < g_tuners.size();) {
+        if (g_tuners[i]->dev == dev && g_tuners[i]->tlas == tlas) { tunerRelease(g_tuners[i]); g_tuners.erase(g_tuners.begin() + i); }
+        else ++i;
+    }
 }
 static void tunerPoll(TraceTuner* t) {
     if (!t->inFlight) return;
@@ -516,17 +585,21 @@ static void tunerPoll(TraceTuner* t) {
     for (int c = 0; c < 2; ++c) {
         for (auto& e : t->pending[c]) {
             float ms = 0.0f;
-            // the first pair of batches only warms up (clocks, caches, lazy module loading)
-            if (t->step >= 2 && cudaEventElapsedTime(&ms, e.first, e.second) == cudaSuccess) t->ms[c][t->candidate] += ms;
-            g_prof.pool.push_back(e.first);
-            g_prof.pool.push_back(e.second);
+            if (t->step >= TRACE_CANDIDATES && cudaEventElapsedTime(&ms, e.first, e.second) == cudaSuccess) t->ms[c][t->candidate] += ms;
+            profRecycle(t->dev, e.first);
+            profRecycle(t->dev, e.second);
         }
         t->pending[c].clear();
     }
     t->inFlight = false;
-    if (++t->step >= 6)
+    if (++t->step >= 3 * TRACE_CANDIDATES)
         for (int c = 0; c < 2; ++c)
-            if (t->choice[c] < 0) t->choice[c] = t->ms[c][TRACE_SIMPLE] < t->ms[c][TRACE_PHASED] ? TRACE_SIMPLE : TRACE_PHASED;
+            if (t->choice[c] < 0) {
+                int best = 0;
+                for (int k = 1; k < TRACE_CANDIDATES; ++k)
+                    if (t->ms[c][k] < t->ms[c][best]) best = k;
+                t->choice[c] = best;
+            }
 }
 
 // Scene tracer, wavefront form: generate, then per segment trace + shade (+ shadow trace +
@@ -535,6 +608,8 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     const bool pol = L->polarized != 0, guide = D.guide.kind != THEIA_GUIDE_NONE;
     cudaStream_t st = (cudaStream_t)L->stream;
     if (((uintptr_t)L->workspace & 255u) != 0) { setError("workspace must be 256 byte aligned"); return -1; }
+    // the wavefront state keeps the segment number in 16 bits next to its flags (WF_FLAGS)
+    if (D.path_length > 0xFFFFu) { setError("scene tracer (wavefront): path_length %u exceeds 65535", D.path_length); return -1; }
     Workspace ws;
     size_t need = layoutWorkspace(L->workspace, D.batch_size, pol, guide, &ws);
     if (L->workspace_bytes < need) {
@@ -564,23 +639,32 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     TraceTuner* tuner = nullptr;
     int kernelOf[2] = {g_optTraceKernel[0], g_optTraceKernel[1]};
     bool timeIt = false;
+    // held to the end of this function while a tuner is in use: its events are recorded below
+    std::unique_lock<std::recursive_mutex> tunerLock(g_stateMutex, std::defer_lock);
+    const int devSlot = currentDeviceSlot();
     if (kernelOf[0] < 0 || kernelOf[1] < 0) {
-        std::lock_guard<std::mutex> lock(g_tunerMutex);
-        tuner = tunerFor(D.tlas, D.batch_size, guide);
+        tunerLock.lock();
+        tuner = tunerFor(devSlot, D.tlas, D.batch_size, guide);
         tunerPoll(tuner);
         for (int c = 0; c < 2; ++c) {
             if (kernelOf[c] >= 0) continue;
             if (tuner->choice[c] >= 0) kernelOf[c] = tuner->choice[c];
-            else if (!tuner->inFlight) { kernelOf[c] = tuner->step & 1; timeIt = true; }
+            else if (!tuner->inFlight) { kernelOf[c] = tuner->step % TRACE_CANDIDATES; timeIt = true; }
             else kernelOf[c] = TRACE_PHASED;  // a timed batch is still running: do not queue up events
         }
-        if (timeIt) { tuner->inFlight = true; tuner->candidate = tuner->step & 1; }
+        if (timeIt) { tuner->inFlight = true; tuner->candidate = tuner->step % TRACE_CANDIDATES; }
+        else tunerLock.unlock();  // decided (or busy): nothing of the tuner is touched below
     }
     auto launchTrace = [&](int cls, const float4* rays, uint4* results, const uint32_t* countPtr, uint32_t rpe) {
+        if (g_traceStats) {  // instrumented pass (measurement only, outside the timed launches)
+            wfTraceStatsKernel<<<gSimple < 1184u ? gSimple : 1184u, TRACE_THREADS, 0, st>>>(D.tlas, rays, countPtr, rpe, D.batch_size,
+                                                                                             g_traceStats + 4 * cls);
+            countLaunches(1);
+        }
         Timed tm(cls == 0 ? KC_TRACE : KC_SHADOW_TRACE, st);
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         const bool timed = timeIt && tuner && tuner->choice[cls] < 0 && g_optTraceKernel[cls] < 0;
-        if (timed) { e0 = profEvent(); e1 = profEvent(); cudaEventRecord(e0, st); }
+        if (timed) { e0 = profEvent(devSlot); e1 = profEvent(devSlot); cudaEventRecord(e0, st); }
         if (kernelOf[cls] == TRACE_QUEUED)
             wfTraceQueuedKernel<<<gQueued, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, ws.counters + WF_CNT_CURSOR, rpe,
                                                                   D.batch_size, (uint32_t)g_optFlushWaiting);
@@ -644,9 +728,10 @@ int theia_set_option(const char* name, int value) {
     return -1;
 }
 int theia_get_trace_choice(const void* tlas_dev, uint32_t batch_size, int guide, int* primary, int* shadow) {
-    std::lock_guard<std::mutex> lock(g_tunerMutex);
+    std::lock_guard<std::recursive_mutex> lock(g_stateMutex);
+    const int dev = currentDeviceSlot();
     for (TraceTuner* t : g_tuners)
-        if (t->tlas == tlas_dev && t->batch == batch_size && t->guide == (guide != 0)) {
+        if (t->dev == dev && t->tlas == tlas_dev && t->batch == batch_size && t->guide == (guide != 0)) {
             if (primary) *primary = t->choice[0];
             if (shadow) *shadow = t->choice[1];
             return 0;
@@ -657,6 +742,7 @@ int theia_get_trace_choice(const void* tlas_dev, uint32_t batch_size, int guide,
 }
 
 int theia_profile_enable(int on) {
+    std::lock_guard<std::recursive_mutex> lock(g_stateMutex);
     profCollect();
     if (on) { for (int k = 0; k < KC_COUNT; ++k) { g_prof.ms[k] = 0.0; g_prof.n[k] = 0; } }
     g_prof.on = on != 0;
@@ -664,6 +750,7 @@ int theia_profile_enable(int on) {
 }
 int theia_profile_read(double* ms, uint64_t* launches, uint32_t n) {
     if (!ms || !launches) { setError("theia_profile_read: null argument"); return -1; }
+    std::lock_guard<std::recursive_mutex> lock(g_stateMutex);
     profCollect();
     for (uint32_t k = 0; k < n; ++k) {
         ms[k] = k < KC_COUNT ? g_prof.ms[k] : 0.0;
@@ -831,6 +918,22 @@ int theia_trace_forward(const theia_trace_launch_t* launch) {
         CUDA_TRY(cudaLaunchKernel(K.fn, dim3(K.grid), dim3(TRACE_THREADS), args, K.smem, (cudaStream_t)launch->stream));
     }
     countLaunches(1);
+    return 0;
+}
+
+int theia_trace_stats_enable(uint64_t* stats_dev) {
+    g_traceStats = (unsigned long long*)stats_dev;
+    return 0;
+}
+
+int theia_l2_probe(const void* buf_dev, uint64_t bytes, uint32_t iters, uint32_t* sink_dev, void* stream) {
+    if (!buf_dev || !sink_dev || bytes < 16 || ((uintptr_t)buf_dev & 15u)) { setError("theia_l2_probe: bad argument"); return -1; }
+    int dev = 0, sms = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    l2ProbeKernel<<<(uint32_t)sms * 8u, 256, 0, (cudaStream_t)stream>>>((const uint4*)buf_dev, bytes / 16, iters, sink_dev);
+    countLaunches(1);
+    CUDA_TRY(cudaGetLastError());
     return 0;
 }
 

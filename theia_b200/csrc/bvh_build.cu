@@ -31,6 +31,7 @@ namespace theia {
 
 void setError(const char* fmt, ...);  // api.cu
 void countLaunches(unsigned n);      // api.cu
+void tunerForget(const void* tlas);  // api.cu
 
 // ------------------------------------------------------------------ scratch layout
 struct BuildScratch {
@@ -716,6 +717,7 @@ extern "C" int theia_tlas_build(const theia_instance_desc_t* instances, uint32_t
     }
     cudaStream_t st = (cudaStream_t)stream;
     const uint32_t n = n_instances, bs = 256;
+    tunerForget(result_dev);  // what the ray query kernel tuner learnt about this address belongs to another scene
     // BLAS headers (host copies, one per distinct BLAS)
     std::map<const void*, BlasHeader> blas;
     uint32_t maxBlasDepth = 0, maxBlasTris = 0;

@@ -225,8 +225,10 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
         // at most half of the lanes that entered may be dropped this way, or a warp with few
         // busy lanes would leave after every node)
         const uint32_t nodeLimit = min(minNodeLanes, ((uint32_t)__popc(__ballot_sync(FULL_MASK, sp > 0)) + 1u) >> 1);
+        bool firstNode = true;  // the first iteration always runs: progress does not rest on what __activemask reports
         while (sp > 0) {
-            if ((uint32_t)__popc(__activemask()) < nodeLimit) break;  // the first iteration always runs
+            if (!firstNode && (uint32_t)__popc(__activemask()) < nodeLimit) break;
+            firstNode = false;
             // pop until an entry that is still in front of the closest hit
             const float lim = bestValid ? bestT : tmax;
             uint32_t key;
@@ -424,14 +426,23 @@ TDEV void pregenerateGamma(const DeviceLaunch& P, const Workspace& ws, uint32_t 
     const float alpha0 = P.light.p.cascade.a_long;
     const bool rescale = alpha0 < 1.0f;
     const GammaConsts g = gammaConsts(rescale ? alpha0 + 1.0f : alpha0);
-    const uint32_t skip = P.wavelength.kind == THEIA_WAVELENGTH_CONST ? 0u : 1u;  // draws of sampleWavelength
+    // draws of sampleWavelength ahead of the light source: the const and host sources take none
+    // (sh/wavelengthsource.const.glsl, sh/wavelengthsource.host.glsl), uniform and function one
+    const uint32_t skip = (P.wavelength.kind == THEIA_WAVELENGTH_CONST || P.wavelength.kind == THEIA_WAVELENGTH_HOST) ? 0u : 1u;
     const size_t C = ws.capacity;
     uint32_t next = first;
     bool busy = false;
     uint32_t k = 0;
     float scale = 1.0f;
     Rng rng = makeRng(&P.rng, 0);
-    for (uint32_t guard = 0; guard < 100000000u; ++guard) {
+    for (uint32_t guard = 0;; ++guard) {
+        if (guard == 100000000u) {
+            // a parameter set whose rejection loop never accepts: the paths still waiting get a NaN depth and a defined
+            // draw counter, so they end with ERROR_CODE_RAY_BAD instead of reading stale workspace contents
+            if (busy) { ws.state[1][WF_PX * C + k] = f2u(T_NAN); ws.state[1][WF_DIM * C + k] = rng.dim; }
+            for (uint32_t j = next + laneId(); j < end; j += 32u) { ws.state[1][WF_PX * C + j] = f2u(T_NAN); ws.state[1][WF_DIM * C + j] = skip; }
+            break;
+        }
         uint32_t idle = __ballot_sync(FULL_MASK, !busy);
         if (idle) {
             uint32_t avail = end - next, rank = __popc(idle & laneMaskLt());

@@ -19,9 +19,10 @@ for combo in itertools.product(*[v for _, v in sweeps]) if sweeps else [()]:
     env = dict(os.environ)
     env.update({k: v for (k, _), v in zip(sweeps, combo)})
     for w in workloads:
-        cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", w, "--steps", "5", "--warmup", "3", "--no-cpu", *extra]
+        cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", w, "--steps", "5", "--warmup", "3", "--no-cpu",
+               "--secondary", "", "--e2e-small-batch", "0", *extra]
         try:
-            r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=120)
+            r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=240)
             d = json.loads(r.stdout.strip().splitlines()[-1])
             print(" ".join(f"{k}={v}" for (k, _), v in zip(sweeps, combo)), w, f"{d['value']:.4g} seg/s", f"{d['ms_per_step']:.3f} ms/step",
                   f"e2e {d['e2e']['value']:.4g}",
