@@ -258,3 +258,33 @@ def runSampler(sampler, i: int = 0) -> None:
     else:
         nbytes = 4 * sampler.batchSize * sampler._width
         sampler._buffer[i][:nbytes].view(sampler._tensor.dtype).copy_(sampler._tensor)
+
+
+def runReplay(replay, i: int = 0) -> None:
+    """
+    Runs a ``response.HitReplay`` stage built on the cpu device on the oracle (sh/response.replay.glsl:35-50):
+    feeds the hits of its host queue to its response and fills the response's host side results.
+    """
+    if replay._device != "cpu":
+        raise ValueError("the oracle needs a replay stage built under useDevice('cpu')")
+    stages = replay.collectStages()
+    for s in stages:
+        s.update(i)
+    for cmd in replay.queue.run(i):  # host copy -> "device" copy of the queue
+        cmd()
+    nBlocks = -(replay.capacity // -replay.blockSize)
+    r = replay.response._abiResponse(i, nBlocks)
+    rc = lib().orc_hit_replay(replay.queue.tensor.data_ptr(), replay.capacity, int(replay.polarized), byref(r),
+                              replay.blockSize)
+    if rc != 0:
+        raise RuntimeError(f"oracle replay error {rc}")
+    resp = replay.response
+    red = getattr(resp, "_reducer", None)
+    if red is not None:
+        p = red._block("Params", i)
+        parts = red.histIn.numpy().reshape(-1, resp.nBins)
+        red._buffer[i].numpy()[:] = histReduce(parts, p.normalization, clear=True)
+        red.histIn.zero_()
+    else:
+        for cmd in resp.run(i):
+            cmd()

@@ -747,3 +747,71 @@ def test_particleCascadeLightSource_fwd(backend, applyFrankTamm, particle):  # t
         dN_dx = integrate.romb(light.frankTamm(lam, water.refractive_index(lam)), dlam)
         expEst = dN_dx * params["effectiveLength"] / (lam_range[1] - lam_range[0])
     assert np.abs(1.0 - est / expEst) < 5e-4
+
+
+# ------------------------------------------------------------------ tests/test_response.py (replay seam)
+def runReplay(backend, replay, i=0):
+    if backend == "oracle":
+        import oracle
+        oracle.runReplay(replay, i)
+    else:
+        import torch
+        from theia_b200.pipeline import runPipeline
+        runPipeline(replay.collectStages(), i)
+        torch.cuda.synchronize()
+
+
+def _fillHits(samples, rng, N, polarized, *, tMax=100.0 * u.ns, contrib=None):
+    samples["position"] = (10.0 * rng.random((N, 3)) - 5.0) * u.m
+    samples["direction"] = rng.random((N, 3))
+    samples["normal"] = rng.random((N, 3))
+    samples["wavelength"] = (rng.random((N,)) * 100.0 + 400.0) * u.nm
+    samples["time"] = rng.random((N,)) * tMax
+    samples["contrib"] = np.arange(N).astype(np.float32) if contrib is None else contrib
+    if polarized:
+        samples["stokes"] = rng.random((N, 4))
+        samples["polarizationRef"] = rng.random((N, 3))
+
+
+@pytest.mark.parametrize("polarized", [True, False])
+def test_record(backend, rng, polarized):  # tests/test_response.py:17-50
+    from theia_b200 import response
+    N = 8192
+    with device(backend):
+        record = response.HitRecorder(polarized=polarized)
+        replay = response.HitReplay(N, record, polarized=polarized)
+    samples = replay.queue.view(0)
+    _fillHits(samples, rng, N, polarized)  # contrib encodes the ordering (the device scrambles the items)
+    runReplay(backend, replay)
+    results = record.queue.view(0)
+    assert results.count == N
+    results = results[np.argsort(results["contrib"])]
+    fields = ["position", "direction", "normal", "wavelength", "time", "contrib"]
+    for f in fields + (["stokes", "polarizationRef"] if polarized else []):
+        assert np.all(samples[f] == results[f]), f
+
+
+def test_hitPolarizationMismatch(backend):  # tests/test_response.py:53-59
+    from theia_b200 import response
+    with device(backend):
+        with pytest.raises(RuntimeError):
+            response.HitReplay(128, response.HitRecorder(polarized=True), polarized=False)
+        with pytest.raises(RuntimeError):
+            response.HitReplay(128, response.HitRecorder(polarized=False), polarized=True)
+
+
+def test_histogramResponse(backend, rng):  # tests/test_response.py:62-99
+    from theia_b200 import response
+    N, N_BINS, BIN_SIZE, T0, NORM = 256 * 1024, 50, 4.0 * u.ns, 20.0 * u.ns, 1e-5
+    T1 = T0 + N_BINS * BIN_SIZE
+    with device(backend):
+        resp = response.HistogramHitResponse(response.UniformValueResponse(), nBins=N_BINS, t0=T0, binSize=BIN_SIZE,
+                                             normalization=NORM)
+        replay = response.HitReplay(N, resp, blockSize=128)
+    samples = replay.queue.view(0)
+    _fillHits(samples, rng, N, False, tMax=T1, contrib=rng.random((N,)) * 10.0)
+    runReplay(backend, replay)
+    result = resp.result(0)
+    bin_edge = np.arange(N_BINS + 1) * BIN_SIZE + T0
+    exp_hist, _ = np.histogram(samples["time"], bin_edge, weights=samples["contrib"])
+    assert np.allclose(result, exp_hist * NORM, rtol=1e-4)
