@@ -159,49 +159,10 @@ static inline float dm_log(float x) {
     return r;
 }
 
-// pow(x, y) for x >= 0 through double precision exp(y*log(x)); only + - * / in double.
-static inline double dm_logd(double x) {  // x > 0, finite, normal
-    uint64_t ix = d2u(x);
-    int64_t e = (int64_t)(ix >> 52) - 1023;
-    double m = u2d((ix & 0x000FFFFFFFFFFFFFull) | 0x3FF0000000000000ull);  // [1, 2)
-    if (m > 1.4142135623730951) { m = m * 0.5; e += 1; }
-    double s = (m - 1.0) / (m + 1.0);
-    double s2 = s * s;
-    double p = 1.0 / 23.0;
-    p = p * s2 + 1.0 / 21.0;
-    p = p * s2 + 1.0 / 19.0;
-    p = p * s2 + 1.0 / 17.0;
-    p = p * s2 + 1.0 / 15.0;
-    p = p * s2 + 1.0 / 13.0;
-    p = p * s2 + 1.0 / 11.0;
-    p = p * s2 + 1.0 / 9.0;
-    p = p * s2 + 1.0 / 7.0;
-    p = p * s2 + 1.0 / 5.0;
-    p = p * s2 + 1.0 / 3.0;
-    p = p * s2 + 1.0;
-    return 2.0 * s * p + (double)e * 0.6931471805599453;
-}
-static inline double dm_expd(double x) {  // |x| < 700
-    double n = std::floor(x * 1.4426950408889634 + 0.5);
-    double r = (x - n * 0.693147180369123816490) - n * 1.90821492927058770002e-10;
-    double p = 1.0 / 6227020800.0;  // 1/13!
-    p = p * r + 1.0 / 479001600.0;
-    p = p * r + 1.0 / 39916800.0;
-    p = p * r + 1.0 / 3628800.0;
-    p = p * r + 1.0 / 362880.0;
-    p = p * r + 1.0 / 40320.0;
-    p = p * r + 1.0 / 5040.0;
-    p = p * r + 1.0 / 720.0;
-    p = p * r + 1.0 / 120.0;
-    p = p * r + 1.0 / 24.0;
-    p = p * r + 1.0 / 6.0;
-    p = p * r + 0.5;
-    p = p * r + 1.0;
-    p = p * r + 1.0;
-    int64_t ni = (int64_t)n;
-    double sc = u2d((uint64_t)(ni + 1023) << 52);
-    return p * sc;
-}
+// pow(x, y), x >= 0: exp(y log x) with log x carried as an unevaluated sum of two floats (H + L, ~2^-40 relative),
+// so that the result stays within ~2 ulp for |y log x| up to the range of exp. Float operations only (fma, +, -, *,
+// /): the first form went through double precision, which cost the cascade / muon light sources a third of their
+// generate kernel on a GPU with few FP64 units.
 static inline float dm_pow(float x, float y) {
     if (isnan_(x) || isnan_(y)) return F_NAN;
     if (y == 0.0f) return 1.0f;
@@ -213,12 +174,44 @@ static inline float dm_pow(float x, float y) {
         bool big = x > 1.0f;
         return ((y > 0.0f) == big) ? F_INF : 0.0f;
     }
-    double xd = (double)x;
-    if (x < 1.17549435e-38f) xd = xd;  // denormal floats are normal doubles
-    double t = (double)y * dm_logd(xd);
-    if (t > 89.0) return F_INF;
-    if (t < -104.0) return 0.0f;
-    return (float)dm_expd(t);
+    // ---- log x = e ln 2 + log m, m in (sqrt(1/2), sqrt(2)], log m = 2 atanh(s), s = (m - 1) / (m + 1)
+    int32_t e = 0;
+    if (x < 1.17549435e-38f) { x *= 8388608.0f; e = -23; }
+    uint32_t ix = f2u(x);
+    e += (int32_t)(ix >> 23) - 127;
+    float m = u2f((ix & 0x007FFFFFu) | 0x3F800000u);
+    if (m > 1.41421354f) { m *= 0.5f; e += 1; }
+    float f = m - 1.0f;                 // exact
+    float g = m + 1.0f;                 // rounded: m + 1 = g + gl exactly
+    float gl = m - (g - 1.0f);
+    float sh = f / g;
+    float r = fmaf(-sh, g, f);          // f - sh g, exact
+    r = fmaf(-sh, gl, r);
+    float sl = r / g;                   // s = sh + sl
+    float z = sh * sh;
+    float p = fmaf(1.5384615385e-1f, z, 1.8181818182e-1f);  // 2/13, 2/11, 2/9, 2/7, 2/5, 2/3
+    p = fmaf(p, z, 2.2222222222e-1f);
+    p = fmaf(p, z, 2.8571428571e-1f);
+    p = fmaf(p, z, 4.0e-1f);
+    p = fmaf(p, z, 6.6666666667e-1f);
+    float lh = sh + sh;
+    float ll = fmaf(sh * z, p, (sl + sl) * fmaf(z, 1.0f + z, 1.0f));  // d/ds 2 atanh(s) = 2 / (1 - s^2)
+    float fe = (float)e;
+    float a = fe * 0.693359375f;        // exact (ln 2 split as in dm_log)
+    float H = a + lh;                   // two-sum
+    float bv = H - a;
+    float L = (a - (H - bv)) + (lh - bv);
+    L += fmaf(fe, -2.12194440e-4f, ll);
+    float H2 = H + L;
+    L = L - (H2 - H);
+    H = H2;
+    // ---- t = y (H + L) as th + tl
+    float th = y * H;
+    float tl = fmaf(y, H, -th) + y * L;
+    if (th > 89.0f) return F_INF;
+    if (th < -104.0f) return 0.0f;
+    float q = dm_exp(th);
+    return fmaf(q, tl, q);
 }
 
 // ---------------------------------------------------------------- vectors

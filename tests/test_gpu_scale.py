@@ -31,27 +31,30 @@ def tlasNodes(sc) -> int:
 def test_full_c5_lattice_hits_bit_exact_with_every_ray_query_kernel(cuda, orc):
     # the 10 x 10 x 50 lattice of the bench scene: its TLAS does not fit the shared memory staging, so the global
     # memory branch of the node fetch is the one under test
-    N = 1 << 16
+    N = 1 << 19  # the modules are sparse (0.43 m spheres on a 60 m x 60 m x 10 m pitch): about one path in a thousand hits
     g, c = both(H.sceneC5, N, resp="record", mode="wavefront")
     assert len(g["scene"].instances) == 5000
     assert tlasNodes(g["scene"]) > TOP_NODES
     H.runOracle(c)
     want = H.sortedHits(c)
-    assert want["count"] > 100
+    assert want["count"] > 200
     lib = _lib.load()
     try:
         for kernel in (0, 1, 2):
             lib.theia_set_option(b"wf_trace_kernel", kernel)
+            g["rng"].setParam("offset", 0)  # the generator advances with every run: repeat the same batch
             H.runGpu(g)
             H.compareHits(H.sortedHits(g), want)
     finally:
         lib.theia_set_option(b"wf_trace_kernel", -1)
     # the same rays through the ray query seam against brute force over all 6.4 M triangles (a sample)
     rng = np.random.default_rng(5)
-    n = 4096
+    n = 2048  # (brute force over 6.4 M triangles per ray: keep it short) rays aimed at modules, so that half of them hit
     rays = np.zeros((n, 8), np.float32)
-    rays[:, :3] = rng.uniform(-30.0, 30.0, (n, 3)) * (1.0, 1.0, 8.0)
-    d = rng.normal(size=(n, 3))
+    rays[:, :3] = rng.uniform(-30.0, 30.0, (n, 3)) * (9.0, 9.0, 8.0)
+    module = np.stack([(rng.integers(0, 10, n) - 4.5) * 60.0, (rng.integers(0, 10, n) - 4.5) * 60.0,
+                       (rng.integers(0, 50, n) - 24.5) * 10.0], 1)
+    d = module + rng.normal(size=(n, 3)) * 0.15 - rays[:, :3]
     rays[:, 4:7] = d / np.linalg.norm(d, axis=1, keepdims=True)
     rays[:, 3] = 1000.0
     ids_w, tuv_w = orc.OracleScene(c["scene"], bruteForce=True).query(rays)
@@ -65,7 +68,7 @@ def test_full_c5_lattice_hits_bit_exact_with_every_ray_query_kernel(cuda, orc):
             torch.cuda.synchronize()
         finally:
             lib.theia_set_option(b"query_kernel", 0)
-        assert np.count_nonzero(ids_w[:, 0] >= 0) > 20
+        assert np.count_nonzero(ids_w[:, 0] >= 0) > n // 4
         assert np.array_equal(ids.cpu().numpy(), ids_w)
         assert np.array_equal(tuv.cpu().numpy().view(np.uint32), tuv_w.view(np.uint32))
 

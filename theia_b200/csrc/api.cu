@@ -484,12 +484,30 @@ static bool leanLaunch(const DeviceLaunch& D) {
            D.guide.kind <= THEIA_GUIDE_SPHERE && D.response.kind <= THEIA_RESPONSE_HISTOGRAM && D.photon == 0;
 }
 struct WavefrontKernels { const void *gen, *shade, *shadow; };
-static WavefrontKernels wavefrontKernels(bool pol, bool lean) {
-    if (lean)
-        return pol ? WavefrontKernels{(const void*)wfGenerateKernel<true, false>, (const void*)wfShadeKernel<true, false>, (const void*)wfShadeShadowKernel<true, false>}
-                   : WavefrontKernels{(const void*)wfGenerateKernel<false, false>, (const void*)wfShadeKernel<false, false>, (const void*)wfShadeShadowKernel<false, false>};
-    return pol ? WavefrontKernels{(const void*)wfGenerateKernel<true, true>, (const void*)wfShadeKernel<true, true>, (const void*)wfShadeShadowKernel<true, true>}
-               : WavefrontKernels{(const void*)wfGenerateKernel<false, true>, (const void*)wfShadeKernel<false, true>, (const void*)wfShadeShadowKernel<false, true>};
+// Variant tables of the shading kernels (wavefront.cuh, VK_*): lean launches get the instantiation that knows their
+// guide / response / callback at compile time, everything else the generic one.
+template <bool POL, uint32_t V>
+static const void* shadeFn() { return (const void*)wfShadeKernel<POL, V>; }
+template <bool POL, uint32_t V>
+static const void* shadowFn() { return (const void*)wfShadeShadowKernel<POL, V>; }
+template <bool POL>
+static WavefrontKernels wavefrontKernelsOf(const DeviceLaunch& D) {
+    if (!leanLaunch(D))
+        return {(const void*)wfGenerateKernel<POL, true>, shadeFn<POL, VK_FULL>(), shadowFn<POL, VK_FULL>()};
+    const bool guide = D.guide.kind != THEIA_GUIDE_NONE, hist = D.response.kind == THEIA_RESPONSE_HISTOGRAM,
+               nocb = D.callback.kind == THEIA_CALLBACK_EMPTY;
+    const uint32_t key = (guide ? 4u : 0u) | (hist ? 2u : 0u) | (nocb ? 1u : 0u);
+    static const void* const shade[8] = {
+        shadeFn<POL, 0u>(), shadeFn<POL, VK_NOCB>(), shadeFn<POL, VK_HIST>(), shadeFn<POL, VK_HIST | VK_NOCB>(),
+        shadeFn<POL, VK_GUIDE>(), shadeFn<POL, VK_GUIDE | VK_NOCB>(), shadeFn<POL, VK_GUIDE | VK_HIST>(),
+        shadeFn<POL, VK_GUIDE | VK_HIST | VK_NOCB>()};
+    static const void* const shadow[4] = {
+        shadowFn<POL, VK_GUIDE>(), shadowFn<POL, VK_GUIDE | VK_NOCB>(), shadowFn<POL, VK_GUIDE | VK_HIST>(),
+        shadowFn<POL, VK_GUIDE | VK_HIST | VK_NOCB>()};
+    return {(const void*)wfGenerateKernel<POL, false>, shade[key], shadow[key & 3u]};
+}
+static WavefrontKernels wavefrontKernels(bool pol, const DeviceLaunch& D) {
+    return pol ? wavefrontKernelsOf<true>(D) : wavefrontKernelsOf<false>(D);
 }
 
 // zeroes the wavefront counters selected by mask
@@ -618,7 +636,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         return -1;
     }
     const size_t histSmem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
-    const WavefrontKernels wk = wavefrontKernels(pol, leanLaunch(D));
+    const WavefrontKernels wk = wavefrontKernels(pol, D);
     const void *genFn = wk.gen, *shadeFn = wk.shade, *shadowFn = wk.shadow;
     uint32_t gGen, gShade, gShadow, gTrace, gQueued;
     if (persistentGrid(genFn, 0, &gGen) || persistentGrid(shadeFn, histSmem, &gShade) ||
@@ -882,7 +900,7 @@ int theia_trace_grid_size(const theia_trace_launch_t* launch, uint32_t* n_blocks
         const bool pol = launch->polarized != 0;
         const size_t smem = (responseHasHistogram(D.response.kind) && D.response.hist_shared) ? (size_t)D.response.n_bins * 4 : 0;
         uint32_t gShade = 0, gShadow = 0;
-        const WavefrontKernels wk = wavefrontKernels(pol, leanLaunch(D));
+        const WavefrontKernels wk = wavefrontKernels(pol, D);
         if (persistentGrid(wk.shade, smem, &gShade) || persistentGrid(wk.shadow, smem, &gShadow))
             return -1;
         const uint32_t need = blocksFor(D.batch_size, TRACE_THREADS);

@@ -195,10 +195,11 @@ static __device__ __noinline__ void commitHitOther(const ResponseDev& r, float* 
         if (laneId() == (uint32_t)(__ffs(peers) - 1)) atomicAdd(r.object_hist + key, sum);
     }
 }
-template <bool FULL>
+// HIST: the launch's response is known to be the plain histogram (compile time variant of the wavefront kernels)
+template <bool FULL, bool HIST = false>
 TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
                         float u) {
-    if (r.kind == THEIA_RESPONSE_HISTOGRAM) {
+    if (HIST || r.kind == THEIA_RESPONSE_HISTOGRAM) {
         uint32_t bin = 0;
         if (has) {
             bin = histogramBin(r, item.time);
@@ -212,7 +213,7 @@ TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitIt
         float sum = 0.0f;
         for (uint32_t m = peers; m; m &= m - 1) sum += __shfl_sync(peers, value, __ffs(m) - 1);
         if (laneId() == leader) atomicAdd(hist + bin, sum);
-    } else if (r.kind == THEIA_RESPONSE_RECORD) {
+    } else if (!HIST && r.kind == THEIA_RESPONSE_RECORD) {
         uint32_t act = __ballot_sync(FULL_MASK, has);
         if (act == 0) return;
         uint32_t leader = __ffs(act) - 1;
@@ -226,19 +227,19 @@ TDEV void commitHitImpl(const ResponseDev& r, float* hist, bool has, const HitIt
             if (r.tag_path) r.tag_path[slot] = path;
             if (r.tag_event) r.tag_event[slot] = tag;
         }
-    } else if (FULL && r.kind != THEIA_RESPONSE_EMPTY) {
+    } else if (!HIST && FULL && r.kind != THEIA_RESPONSE_EMPTY) {
         commitHitOther(r, hist, has, item.time, item.contrib, item.objectId, path, tag, u);
     }
 }
 
 // Returns whether the lane's hit reached the response (the call sites number a path's responses
 // inside an event with it: test tags).
-template <bool FULL = true>
+template <bool FULL = true, bool HIST = false>
 TDEV bool commitHit(const ResponseDev& r, float* hist, bool has, const HitItem& item, uint32_t path, uint32_t tag,
                     uint32_t& nResponses, float u) {
     has = has && item.contrib > 0.0f;  // "if (hit.contrib > 0.0) response(hit)" at every call site
     if (has) nResponses++;
-    commitHitImpl<FULL>(r, hist, has, item, path, tag, u);
+    commitHitImpl<FULL, HIST>(r, hist, has, item, path, tag, u);
     return has;
 }
 // sh/callback.stat.glsl:21-62: counter index of a result code (-1: not counted by name)
@@ -261,8 +262,10 @@ TDEV int statIndex(int code) {
 
 // onEvent(ray, code, idx, i). The statistic part is warp aggregated and MUST be called by
 // all 32 lanes (has = false for lanes without an event); the track part is a plain store.
-template <bool POL>
+// NOCB: the launch is known to have no callback (compile time variant of the wavefront kernels)
+template <bool POL, bool NOCB = false>
 TDEV void onEvent(const CallbackDev& cb, SinkShared* sh, bool has, const Ray& ray, int code, uint32_t k, uint32_t i) {
+    if (NOCB) return;
     if (cb.kind == THEIA_CALLBACK_STAT) {
         uint32_t act = __ballot_sync(FULL_MASK, has);
         if (act == 0 || !has) return;

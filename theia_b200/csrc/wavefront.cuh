@@ -357,6 +357,21 @@ __global__ void __launch_bounds__(128, THEIA_SIMPLE_CTAS) wfTraceSimpleKernel(co
 #endif
 enum : uint32_t { WF_SEQ1 = 1u << 18 };  // one response was already committed in this event
 
+// Compile time variant key of the shading kernels (the reference compiles one shader per configuration,
+// src/theia/util.py:102-115, src/theia/trace.py:666-685; here the configurations of BASELINE.json get their own
+// instantiations and everything else runs the generic ones). The kernels are 110-160 KB of SASS when every
+// component kind is a run time switch and starve on instruction fetch (profiles/r1i_wfshade_c2.txt).
+//   VK_FULL    all components, everything decided at run time (responses / guides / sources added late, photon tracers)
+//   VK_RTGUIDE lean components, guide decided at run time (generate kernel)
+//   VK_GUIDE   a sphere target guide is set        VK_HIST  the response is the plain histogram
+//   VK_NOCB    no callback
+enum : uint32_t { VK_FULL = 1u, VK_RTGUIDE = 2u, VK_GUIDE = 4u, VK_HIST = 8u, VK_NOCB = 16u };
+template <uint32_t V>
+TDEV bool variantGuide(const DeviceLaunch& P) {
+    if (V & (VK_FULL | VK_RTGUIDE)) return P.guide.kind != THEIA_GUIDE_NONE;
+    return (V & VK_GUIDE) != 0;
+}
+
 // First half of trace() (sh/scene.traverse.glsl:280-323): free path sample, extension towards
 // the target guide; writes the ray query to `rayOut` (the entry the path was given in the
 // output buffer). The health check of :285 (isRayBad) is done by the caller, which needs its
@@ -383,11 +398,12 @@ TDEV void prepareQuery(const DeviceLaunch& P, float4* rayOut, const Ray& ray, Rn
 
 // End of a segment (sh/tracer.scene.forward.glsl:87-104): event callback, stop conditions,
 // then the next ray query, appended to the output buffer. MUST be called by all 32 lanes.
-template <bool POL, bool FULL>
+template <bool POL, uint32_t V>
 TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* sh, bool active, uint32_t path, Ray& ray,
                         Rng& rng, int result, uint32_t it, bool GUIDE, uint32_t next, uint32_t& nSegments) {
+    constexpr bool FULL = (V & VK_FULL) != 0, NOCB = (V & VK_NOCB) != 0;
     if (FULL && P.photon && active) result = photonRoulette<POL>(ray, rng, result);
-    onEvent<POL>(P.callback, sh, active, ray, result, path, it);
+    onEvent<POL, NOCB>(P.callback, sh, active, ray, result, path, it);
     bool cont = active && result >= 0;
     bool maxIter = false, allow = true;
     if (cont) {
@@ -398,10 +414,10 @@ TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* 
             it++;
         }
     }
-    onEvent<POL>(P.callback, sh, maxIter, ray, THEIA_RESULT_MAX_ITER, path, P.path_length + 1);
+    onEvent<POL, NOCB>(P.callback, sh, maxIter, ray, THEIA_RESULT_MAX_ITER, path, P.path_length + 1);
     if (cont) nSegments++;
     const bool ok = cont && !isRayBad(ray);
-    onEvent<POL>(P.callback, sh, cont && !ok, ray, THEIA_ERROR_RAY_BAD, path, it);
+    onEvent<POL, NOCB>(P.callback, sh, cont && !ok, ray, THEIA_ERROR_RAY_BAD, path, it);
     const uint32_t j = denseAlloc(ws.counters + (next ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0), ok);
     if (ok) {
         bool mis;
@@ -519,15 +535,16 @@ TDEV RayHit resultToHit(uint4 r) {
 }
 
 // shade: second half of trace() (sh/scene.traverse.glsl:324-352) + processInteraction (:361-397)
-template <bool POL, bool FULL>
+template <bool POL, uint32_t V>
 __global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
                                                          uint32_t cur) {
+    constexpr bool FULL = (V & VK_FULL) != 0, HIST = (V & VK_HIST) != 0;
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
     sinkInit(P, &sh, sharedHist);
     float* hist = sinkHist(P, sharedHist);
     const SceneView sc = makeSceneView(P.tlas, nullptr, 0);
-    const bool GUIDE = P.guide.kind != THEIA_GUIDE_NONE;
+    const bool GUIDE = variantGuide<V>(P);
     const uint32_t count = ws.counters[cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0];
     const uint32_t next = cur ^ 1u;
     const uint32_t* stateIn = ws.state[cur];
@@ -575,7 +592,7 @@ __global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __g
             updateRayIS(ray, dist, P.propagation, hit.valid);
             result = queryResult <= THEIA_ERROR_MAX_VALUE ? queryResult : propResult;
         }
-        has = commitHit<FULL>(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
+        has = commitHit<FULL, HIST>(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
         has = false;
 
@@ -626,7 +643,7 @@ __global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __g
             result = THEIA_RESULT_RAY_SCATTERED;
             wantMIS = GUIDE && !last;
         }
-        has = commitHit<FULL>(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, uResponse);
+        has = commitHit<FULL, HIST>(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, uResponse);
 
         // paths that wait for shadow rays are parked in the shadow buffer (warp collective)
         uint32_t js = 0u;
@@ -653,16 +670,17 @@ __global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __g
         } else if (interact && !hit.valid && !last) {
             scatterRay<POL>(ray, rng.next2());  // volume scatter (:386-393)
         }
-        finishSegment<POL, FULL>(P, ws, &sh, active && !wantMIS, path, ray, rng, result, it, GUIDE, next, nSegments);
+        finishSegment<POL, V>(P, ws, &sh, active && !wantMIS, path, ray, rng, result, it, GUIDE, next, nSegments);
     }
     sinkFinish(P, &sh, sharedHist, nSegments, nResponses, nShadow, 0);
 }
 
 // second shading pass (target guide only): shadow ray results -> responses
 // (traceShadowRay, sh/scene.traverse.glsl:185-214), then the deferred volume scatter
-template <bool POL, bool FULL>
+template <bool POL, uint32_t V>
 __global__ void __launch_bounds__(128, THEIA_SHADOW_CTAS) wfShadeShadowKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws,
                                                                uint32_t cur) {
+    constexpr bool FULL = (V & VK_FULL) != 0, HIST = (V & VK_HIST) != 0;
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
     sinkInit(P, &sh, sharedHist);
@@ -709,11 +727,11 @@ __global__ void __launch_bounds__(128, THEIA_SHADOW_CTAS) wfShadeShadowKernel(co
                     has = processShadowRay<POL>(P, r2, hit, item);
                 }
             }
-            has = commitHit<FULL>(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
+            has = commitHit<FULL, HIST>(P.response, hist, has, item, idx, tagEvent | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
             hitSeq += has ? 1u : 0u;
         }
         if (active) scatterRay<POL>(ray, rng.next2());
-        finishSegment<POL, FULL>(P, ws, &sh, active, path, ray, rng, THEIA_RESULT_RAY_SCATTERED, it, true, next, nSegments);
+        finishSegment<POL, V>(P, ws, &sh, active, path, ray, rng, THEIA_RESULT_RAY_SCATTERED, it, true, next, nSegments);
     }
     sinkFinish(P, &sh, sharedHist, nSegments, nResponses, 0, 0);
 }
