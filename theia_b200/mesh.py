@@ -16,7 +16,7 @@ from pathlib import Path
 import numpy as np
 from numpy.typing import NDArray
 
-__all__ = ["Mesh", "loadMesh", "icosphere", "box", "torus"]
+__all__ = ["Mesh", "SceneFile", "loadMesh", "loadSceneFile", "icosphere", "box", "torus"]
 
 
 class Mesh:
@@ -232,3 +232,171 @@ def torus(major: float = 1.0, minor: float = 0.25, nu: int = 48, nv: int = 16) -
     f = np.concatenate([np.stack([j0[0], j1[0], j1[1]], -1).reshape(-1, 3),
                         np.stack([j0[0], j1[1], j0[1]], -1).reshape(-1, 3)])
     return fromTriangles(p.reshape(-1, 3).astype(np.float32), f, n.reshape(-1, 3))
+
+
+# ------------------------------------------------------------------ scene files (SceneTemplate)
+class SceneFile:
+    """
+    What ``trimesh.load(file, force="scene")`` provides to the reference's ``SceneTemplate``
+    (src/theia/scene.py:757-806): the meshes of a file by name, the material name of each mesh, and the
+    instances of the scene graph (name, mesh name, 3x4 transformation to the base frame).
+    """
+
+    def __init__(self) -> None:
+        self.meshes: dict[str, Mesh] = {}
+        self.materials: dict[str, str] = {}   # mesh name -> material name ("" = none assigned)
+        self.instances: list[tuple[str, str, NDArray]] = []  # (instance name, mesh name, float64[3, 4])
+
+
+_GLTF_TYPES = {5120: np.int8, 5121: np.uint8, 5122: np.int16, 5123: np.uint16, 5125: np.uint32, 5126: np.float32}
+_GLTF_WIDTH = {"SCALAR": 1, "VEC2": 2, "VEC3": 3, "VEC4": 4, "MAT4": 16}
+
+
+def _quatMatrix(q) -> NDArray:
+    x, y, z, w = (float(v) for v in q)
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                     [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                     [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+
+
+def _loadGLTF(path: Path) -> SceneFile:
+    """glTF 2.0 (.gltf with external / base64 buffers, or binary .glb): triangle primitives, node hierarchy."""
+    import base64
+    import json
+    raw = path.read_bytes()
+    binChunk = None
+    if raw[:4] == b"glTF":
+        length = struct.unpack("<I", raw[8:12])[0]
+        at, doc = 12, None
+        while at < length:
+            n, kind = struct.unpack("<II", raw[at:at + 8])
+            chunk = raw[at + 8:at + 8 + n]
+            if kind == 0x4E4F534A:
+                doc = json.loads(chunk.decode())
+            elif kind == 0x004E4942 and binChunk is None:
+                binChunk = chunk
+            at += 8 + n + (-n % 4)
+        if doc is None:
+            raise ValueError(f"{path}: GLB file without JSON chunk")
+    else:
+        doc = json.loads(raw.decode())
+    buffers = []
+    for b in doc.get("buffers", []):
+        uri = b.get("uri")
+        if uri is None:
+            buffers.append(binChunk)
+        elif uri.startswith("data:"):
+            buffers.append(base64.b64decode(uri.split(",", 1)[1]))
+        else:
+            buffers.append((path.parent / uri).read_bytes())
+
+    def accessor(i: int) -> NDArray:
+        a = doc["accessors"][i]
+        view = doc["bufferViews"][a["bufferView"]]
+        dt, w = np.dtype(_GLTF_TYPES[a["componentType"]]), _GLTF_WIDTH[a["type"]]
+        start = view.get("byteOffset", 0) + a.get("byteOffset", 0)
+        stride = view.get("byteStride", 0) or dt.itemsize * w
+        data = np.frombuffer(buffers[view["buffer"]], dtype=np.uint8, count=(a["count"] - 1) * stride + dt.itemsize * w, offset=start)
+        rows = np.lib.stride_tricks.as_strided(data, shape=(a["count"], dt.itemsize * w), strides=(stride, 1))
+        return np.ascontiguousarray(rows).view(dt).reshape(a["count"], w)
+
+    out = SceneFile()
+    matNames = [m.get("name", "") for m in doc.get("materials", [])]
+    meshParts: list[list[str]] = []
+    for k, m in enumerate(doc.get("meshes", [])):
+        base = m.get("name") or f"mesh_{k}"
+        parts = []
+        for p, prim in enumerate(m["primitives"]):
+            if prim.get("mode", 4) != 4:
+                continue  # triangles only
+            pos = accessor(prim["attributes"]["POSITION"]).astype(np.float32)
+            idx = accessor(prim["indices"]).reshape(-1, 3) if "indices" in prim else np.arange(len(pos)).reshape(-1, 3)
+            nrm = accessor(prim["attributes"]["NORMAL"]).astype(np.float32) if "NORMAL" in prim["attributes"] else None
+            if nrm is None:
+                pos, idx = weld(pos, idx.astype(np.int64))
+            name = base if len(m["primitives"]) == 1 else f"{base}_{p}"
+            while name in out.meshes:
+                name += "_"
+            out.meshes[name] = fromTriangles(pos, idx, nrm)
+            out.materials[name] = matNames[prim["material"]] if "material" in prim else ""
+            parts.append(name)
+        meshParts.append(parts)
+
+    nodes = doc.get("nodes", [])
+
+    def local(n) -> NDArray:
+        if "matrix" in n:
+            return np.array(n["matrix"], dtype=np.float64).reshape(4, 4).T  # column major in the file
+        m = np.eye(4)
+        m[:3, :3] = _quatMatrix(n.get("rotation", (0, 0, 0, 1))) * np.array(n.get("scale", (1, 1, 1)), dtype=np.float64)[None, :]
+        m[:3, 3] = n.get("translation", (0, 0, 0))
+        return m
+
+    def walk(i: int, parent: NDArray) -> None:
+        n = nodes[i]
+        world = parent @ local(n)
+        if "mesh" in n:
+            for part in meshParts[n["mesh"]]:
+                name = n.get("name") or f"node_{i}"
+                if len(meshParts[n["mesh"]]) > 1:
+                    name = f"{name}/{part}"
+                while any(name == inst[0] for inst in out.instances):
+                    name += "_"
+                out.instances.append((name, part, world[:3, :].copy()))
+        for c in n.get("children", []):
+            walk(c, world)
+
+    scenes = doc.get("scenes") or [{"nodes": list(range(len(nodes)))}]
+    for root in scenes[doc.get("scene", 0)]["nodes"]:
+        walk(root, np.eye(4))
+    return out
+
+
+def _loadOBJ(path: Path) -> SceneFile:
+    """Wavefront OBJ: every object / group is one mesh and one instance (identity transformation), ``usemtl`` names its material."""
+    verts: list[list[float]] = []
+    groups: dict[str, list[list[int]]] = {}
+    mats: dict[str, str] = {}
+    cur, curMat = "default", ""
+    for line in path.read_text(errors="ignore").splitlines():
+        t = line.split()
+        if not t or t[0].startswith("#"):
+            continue
+        if t[0] == "v":
+            verts.append([float(x) for x in t[1:4]])
+        elif t[0] in ("o", "g"):
+            cur = " ".join(t[1:]) or "default"
+        elif t[0] == "usemtl":
+            curMat = " ".join(t[1:])
+        elif t[0] == "f":
+            idx = [int(x.split("/")[0]) for x in t[1:]]
+            idx = [i - 1 if i > 0 else len(verts) + i for i in idx]
+            faces = groups.setdefault(cur, [])
+            mats.setdefault(cur, curMat)
+            for k in range(1, len(idx) - 1):  # fan triangulation
+                faces.append([idx[0], idx[k], idx[k + 1]])
+    out = SceneFile()
+    allVerts = np.array(verts, dtype=np.float32).reshape(-1, 3)
+    for name, faces in groups.items():
+        f = np.array(faces, dtype=np.int64)
+        used, inverse = np.unique(f.reshape(-1), return_inverse=True)
+        pos, f = weld(allVerts[used], inverse.reshape(-1, 3))
+        out.meshes[name] = fromTriangles(pos, f)
+        out.materials[name] = mats.get(name, "")
+        out.instances.append((name, name, np.eye(4)[:3, :].copy()))
+    return out
+
+
+def loadSceneFile(filepath: str | Path) -> SceneFile:
+    """Loads a scene file (glTF 2.0 ``.gltf`` / ``.glb``, Wavefront ``.obj``); a plain mesh file becomes a scene of one instance."""
+    path = Path(filepath)
+    ext = path.suffix.lower()
+    if ext in (".gltf", ".glb"):
+        return _loadGLTF(path)
+    if ext == ".obj":
+        return _loadOBJ(path)
+    out = SceneFile()
+    out.meshes[path.stem] = loadMesh(path)
+    out.materials[path.stem] = ""
+    out.instances.append((path.stem, path.stem, np.eye(4)[:3, :].copy()))
+    return out

@@ -26,7 +26,7 @@ from theia_b200.glsl import vec3
 from theia_b200.material import MaterialStore
 from theia_b200.mesh import Mesh, loadMesh
 
-__all__ = ["loadMesh", "Mesh", "MeshInstance", "MeshStore", "RectBBox", "Scene", "SphereBBox", "Transform"]
+__all__ = ["loadMesh", "Mesh", "MeshInstance", "MeshStore", "RectBBox", "Scene", "SceneTemplate", "SphereBBox", "Transform"]
 
 
 class Transform:
@@ -447,3 +447,131 @@ class Scene:
     def tlas(self) -> torch.Tensor | None:
         """Buffer holding the top level acceleration structure"""
         return self._tlas
+
+
+class SceneTemplate:
+    """
+    Template for creating scenes: loads meshes and a partial scene (instances with their transformations and material
+    names) from a file and creates complete scenes from copies of it (src/theia/scene.py:713-935). The reference reads the
+    file with ``trimesh``; here ``theia_b200.mesh.loadSceneFile`` reads glTF 2.0 (``.gltf`` / ``.glb``) and Wavefront
+    ``.obj`` itself.
+
+    Parameters
+    ----------
+    file: path of the scene file
+    materials: MaterialStore | Mapping[str, int] | None
+        material map used when creating scenes; if None it must be passed to ``createScene``
+    sceneMedium: device address of the medium the template is embedded within
+    templateTransform: optional transformation applied to the loaded template
+    detectorIdMap: optional map instance name -> detectorId (others get 0); if None every instance gets a unique id from 1
+    detectorMaterial: if given (and no detectorIdMap), only instances with one of these materials get a unique id
+    """
+
+    from dataclasses import dataclass as _dataclass
+
+    @_dataclass(frozen=True)
+    class InstanceInfo:
+        name: str            #: instance name
+        meshName: str        #: name of the referenced mesh
+        transform: Transform  #: base transformation from mesh to template
+        material: str        #: name of the referenced material
+        detectorId: int      #: detector id assigned to the instance when creating a scene
+
+    def __init__(self, file: str | Path, *, materials: MaterialStore | Mapping[str, int] | None = None, sceneMedium: int = 0,
+                 templateTransform: Transform | None = None, detectorIdMap: Mapping[str, int] | None = None,
+                 detectorMaterial: set[str] | None = None) -> None:
+        from types import MappingProxyType
+        from theia_b200.mesh import loadSceneFile
+        sceneFile = loadSceneFile(file)
+        for meshName, mat in sceneFile.materials.items():
+            if mat == "" or mat == "material_0":  # second: trimesh's default name, kept for files written by it
+                raise ValueError(f'Mesh "{meshName}" has no material assigned!')
+        self._store = MeshStore(dict(sceneFile.meshes))
+        instances: dict[str, SceneTemplate.InstanceInfo] = {}
+        nextId = 1
+        for instanceName, meshName, matrix in sceneFile.instances:
+            trafo = Transform(np.asarray(matrix, dtype=np.float64)[:3, :])
+            if templateTransform is not None:
+                trafo @= templateTransform
+            trafo.freeze()
+            mat = sceneFile.materials[meshName]
+            detId = 0
+            if detectorIdMap is not None:
+                detId = detectorIdMap.get(instanceName, 0)
+            elif detectorMaterial is not None:
+                if mat in detectorMaterial:
+                    detId = nextId
+                    nextId += 1
+            else:
+                detId = nextId
+                nextId += 1
+            instances[instanceName] = self.InstanceInfo(instanceName, meshName, trafo, mat, detId)
+        self._instances = MappingProxyType(instances)
+        self.materials = materials
+        self._sceneMedium = sceneMedium
+        self._idStride = nextId - 1
+
+    @property
+    def materials(self) -> Mapping[str, int] | None:
+        """Material map used when creating scenes from this template (None: pass it to ``createScene``)"""
+        return self._materials
+
+    @materials.setter
+    def materials(self, value: MaterialStore | Mapping[str, int] | None) -> None:
+        self._materialStore = value if isinstance(value, MaterialStore) else None
+        if isinstance(value, MaterialStore):
+            value = value.material
+        self._materials = value
+
+    @property
+    def meshStore(self) -> MeshStore:
+        """MeshStore containing the meshes used by this template"""
+        return self._store
+
+    @property
+    def instances(self):
+        return self._instances
+
+    @property
+    def sceneMedium(self) -> int:
+        """Device address of the medium the template is embedded within"""
+        return self._sceneMedium
+
+    @sceneMedium.setter
+    def sceneMedium(self, value: int) -> None:
+        self._sceneMedium = value
+
+    def createScene(self, tempInstance: Iterable[Transform] | None = None, *,
+                    materials: MaterialStore | Mapping[str, int] | None = None, sceneMedium: int = 0,
+                    sceneTransformation: Transform | None = None, sceneBBox: RectBBox | None = None,
+                    detectorIdStride: int | None = None) -> tuple[Scene, dict[tuple[str, int], int]]:
+        """
+        Creates a scene of one copy of the template per transformation in ``tempInstance`` (None: a single untransformed
+        copy). Returns the scene and the map (instance name, copy number) -> detectorId; copy ``i`` offsets the detector
+        ids of the template by ``i * detectorIdStride`` (default: the smallest stride that keeps them unique).
+        """
+        if materials is None:
+            materials = self._materialStore if self._materialStore is not None else self.materials
+        if materials is None:
+            raise ValueError("No material mapping was provided!")
+        if tempInstance is None:
+            tempInstance = [None]
+        if detectorIdStride is None:
+            detectorIdStride = self._idStride
+        sceneInst = []
+        detIdMap: dict[tuple[str, int], int] = {}
+        for i, trafo in enumerate(tempInstance):
+            offset = i * detectorIdStride
+            for tempInst in self.instances.values():
+                detId = tempInst.detectorId
+                if detId != 0:
+                    detId += offset
+                    detIdMap[(tempInst.name, i)] = detId
+                t = tempInst.transform.copy()
+                if trafo is not None:
+                    t @= trafo
+                if sceneTransformation is not None:
+                    t @= sceneTransformation
+                sceneInst.append(self.meshStore.createInstance(tempInst.meshName, tempInst.material, t, detectorId=detId))
+        kw = {} if sceneBBox is None else {"bbox": sceneBBox}
+        return Scene(sceneInst, materials, medium=sceneMedium, **kw), detIdMap
