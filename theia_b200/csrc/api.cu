@@ -510,11 +510,6 @@ static WavefrontKernels wavefrontKernels(bool pol, const DeviceLaunch& D) {
     return pol ? wavefrontKernelsOf<true>(D) : wavefrontKernelsOf<false>(D);
 }
 
-// zeroes the wavefront counters selected by mask
-__global__ void wfResetKernel(uint32_t* counters, uint32_t mask) {
-    if (threadIdx.x < WF_NCOUNTERS && ((mask >> threadIdx.x) & 1u)) counters[threadIdx.x] = 0u;
-}
-
 static int persistentGrid(const void* fn, size_t smem, uint32_t* grid) {
     // occupancy queries are not free: remember the answer per (device, kernel, shared memory)
     struct Entry { int dev; const void* fn; size_t smem; uint32_t grid; };
@@ -534,7 +529,7 @@ static int persistentGrid(const void* fn, size_t smem, uint32_t* grid) {
 
 static size_t workspaceBytes(const theia_trace_launch_t* L) {
     if (L->tracer != THEIA_TRACER_SCENE_FORWARD && L->tracer != THEIA_TRACER_SCENE_PHOTON) return 0;
-    return layoutWorkspace(nullptr, L->batch_size, L->polarized != 0, L->guide.kind != THEIA_GUIDE_NONE, nullptr);
+    return layoutWorkspace(nullptr, L->batch_size, L->polarized != 0, L->guide.kind != THEIA_GUIDE_NONE, L->path_length, nullptr);
 }
 
 // ------------------------------------------------------------------ options, trace kernel selection
@@ -629,7 +624,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     // the wavefront state keeps the segment number in 16 bits next to its flags (WF_FLAGS)
     if (D.path_length > 0xFFFFu) { setError("scene tracer (wavefront): path_length %u exceeds 65535", D.path_length); return -1; }
     Workspace ws;
-    size_t need = layoutWorkspace(L->workspace, D.batch_size, pol, guide, &ws);
+    size_t need = layoutWorkspace(L->workspace, D.batch_size, pol, guide, D.path_length, &ws);
     if (L->workspace_bytes < need) {
         setError("workspace too small: %llu bytes given, %llu needed", (unsigned long long)L->workspace_bytes,
                  (unsigned long long)need);
@@ -673,7 +668,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         if (timeIt) { tuner->inFlight = true; tuner->candidate = tuner->step % TRACE_CANDIDATES; }
         else tunerLock.unlock();  // decided (or busy): nothing of the tuner is touched below
     }
-    auto launchTrace = [&](int cls, const float4* rays, uint4* results, const uint32_t* countPtr, uint32_t rpe) {
+    auto launchTrace = [&](int cls, const float4* rays, uint4* results, const uint32_t* countPtr, uint32_t* cursor, uint32_t rpe) {
         if (g_traceStats) {  // instrumented pass (measurement only, outside the timed launches)
             wfTraceStatsKernel<<<gSimple < 1184u ? gSimple : 1184u, TRACE_THREADS, 0, st>>>(D.tlas, rays, countPtr, rpe, D.batch_size,
                                                                                              g_traceStats + 4 * cls);
@@ -684,37 +679,38 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         const bool timed = timeIt && tuner && tuner->choice[cls] < 0 && g_optTraceKernel[cls] < 0;
         if (timed) { e0 = profEvent(devSlot); e1 = profEvent(devSlot); cudaEventRecord(e0, st); }
         if (kernelOf[cls] == TRACE_QUEUED)
-            wfTraceQueuedKernel<<<gQueued, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, ws.counters + WF_CNT_CURSOR, rpe,
+            wfTraceQueuedKernel<<<gQueued, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, rpe,
                                                                   D.batch_size, (uint32_t)g_optFlushWaiting);
         else if (kernelOf[cls] == TRACE_SIMPLE)
             wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, rpe, D.batch_size);
         else
-            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, ws.counters + WF_CNT_CURSOR, rpe,
+            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, rpe,
                                                             minNodeLanes, D.batch_size);
         if (timed) { cudaEventRecord(e1, st); tuner->pending[cls].push_back({e0, e1}); }
     };
 
-    wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 0xFFu);
+    // all counters of the batch are cleared here, once (one slot per segment generation: wavefront.cuh)
+    CUDA_TRY(cudaMemsetAsync(ws.counters, 0, 4 * WF_SLOT * ((size_t)D.path_length + 1), st));
+    auto slot = [&](uint32_t s) { return ws.counters + (size_t)WF_SLOT * s; };
     {
         Timed tm(KC_GENERATE, st);
+        ws.cntIn = nullptr; ws.cntOut = slot(0) + WF_CNT_QUEUE; ws.cntShadow = nullptr;
         void* args[] = {(void*)&D, (void*)&ws};
         CUDA_TRY(cudaLaunchKernel(genFn, dim3(gGen), dim3(TRACE_THREADS), args, 0, st));
     }
     uint32_t cur = 0;
-    countLaunches(2);
+    countLaunches(1);
     for (uint32_t it = 1; it <= D.path_length; ++it) {
-        countLaunches((guide && it < D.path_length) ? 6 : 3);
-        const uint32_t nextBit = cur ? (1u << WF_CNT_QUEUE0) : (1u << WF_CNT_QUEUE1);
-        wfResetKernel<<<1, 32, 0, st>>>(ws.counters, nextBit | (1u << WF_CNT_SHADOW) | (1u << WF_CNT_CURSOR));
-        launchTrace(0, ws.ray[cur], ws.result, ws.counters + (cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0), 1u);
+        countLaunches((guide && it < D.path_length) ? 4 : 2);
+        ws.cntIn = slot(it - 1) + WF_CNT_QUEUE; ws.cntOut = slot(it) + WF_CNT_QUEUE; ws.cntShadow = slot(it) + WF_CNT_SHADOW;
+        launchTrace(0, ws.ray[cur], ws.result, ws.cntIn, slot(it) + WF_CNT_CURSOR, 1u);
         {
             Timed tm(KC_SHADE, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadeFn, dim3(gShade), dim3(TRACE_THREADS), args, histSmem, st));
         }
         if (guide && it < D.path_length) {
-            wfResetKernel<<<1, 32, 0, st>>>(ws.counters, 1u << WF_CNT_CURSOR);
-            launchTrace(1, ws.shadowRay, ws.shadowResult, ws.counters + WF_CNT_SHADOW, 2u);
+            launchTrace(1, ws.shadowRay, ws.shadowResult, ws.cntShadow, slot(it) + WF_CNT_SHADOW_CURSOR, 2u);
             Timed tm(KC_SHADE_SHADOW, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadowFn, dim3(gShadow), dim3(TRACE_THREADS), args, histSmem, st));

@@ -38,11 +38,18 @@ enum : uint32_t {
 };
 // WF_FLAGS: bits 0-15 segment number "it", bit 16 allowResponse, bit 17 mis_target
 enum : uint32_t { WF_ALLOW = 1u << 16, WF_MIS_TARGET = 1u << 17 };
-enum : uint32_t { WF_CNT_QUEUE0 = 0, WF_CNT_QUEUE1 = 1, WF_CNT_SHADOW = 2, WF_CNT_CURSOR = 3, WF_NCOUNTERS = 8 };
+// Counters: one slot of four words per segment generation s = 0 .. pathLength, cleared ONCE per batch (a memset), so
+// no launch in between has to reset anything: [0] live entries produced by generation s (s = 0: the generate kernel),
+// [1] paths of generation s waiting for shadow rays, [2] / [3] work cursors of the primary / shadow ray query launch.
+enum : uint32_t { WF_CNT_QUEUE = 0, WF_CNT_SHADOW = 1, WF_CNT_CURSOR = 2, WF_CNT_SHADOW_CURSOR = 3, WF_SLOT = 4 };
 
 struct Workspace {
     uint32_t capacity;      // paths per batch
-    uint32_t* counters;     // [WF_NCOUNTERS]: live entries of buffer 0 / 1, of the shadow buffer, trace cursor
+    uint32_t* counters;     // [pathLength + 1][WF_SLOT], see above
+    // the counters of the launch at hand (set by the host per launch): entries to read, entries produced, shadow entries
+    const uint32_t* cntIn;
+    uint32_t* cntOut;
+    uint32_t* cntShadow;
     uint32_t* state[2];     // ping-pong, [nFields][capacity] words, dense
     float4* ray[2];         // ping-pong, [capacity][2]: (origin, tmax), (direction, sampledDist)
     uint4* result;          // [capacity]: instance slot (0xFFFFFFFF = miss), primitive, u, v
@@ -56,7 +63,7 @@ struct Workspace {
 static inline size_t wfAlign(size_t v) { return (v + 255) & ~size_t(255); }
 
 // Carves the workspace out of a caller supplied buffer (base may be null to get the size).
-static inline size_t layoutWorkspace(void* base, uint32_t capacity, bool polarized, bool guide, Workspace* ws) {
+static inline size_t layoutWorkspace(void* base, uint32_t capacity, bool polarized, bool guide, uint32_t pathLength, Workspace* ws) {
     size_t off = 0;
     char* b = (char*)base;
     auto take = [&](size_t bytes) { void* p = b ? b + off : nullptr; off += wfAlign(bytes); return p; };
@@ -64,7 +71,8 @@ static inline size_t layoutWorkspace(void* base, uint32_t capacity, bool polariz
     const size_t nFields = polarized ? WF_NFIELDS_POL : WF_NFIELDS_UNPOL;
     Workspace w;
     w.capacity = capacity;
-    w.counters = (uint32_t*)take(4 * WF_NCOUNTERS);
+    w.counters = (uint32_t*)take(4 * WF_SLOT * ((size_t)pathLength + 1));
+    w.cntIn = nullptr; w.cntOut = nullptr; w.cntShadow = nullptr;
     w.state[0] = (uint32_t*)take(4 * nFields * C);
     w.state[1] = (uint32_t*)take(4 * nFields * C);
     w.ray[0] = (float4*)take(32 * C);
@@ -418,7 +426,7 @@ TDEV void finishSegment(const DeviceLaunch& P, const Workspace& ws, SinkShared* 
     if (cont) nSegments++;
     const bool ok = cont && !isRayBad(ray);
     onEvent<POL, NOCB>(P.callback, sh, cont && !ok, ray, THEIA_ERROR_RAY_BAD, path, it);
-    const uint32_t j = denseAlloc(ws.counters + (next ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0), ok);
+    const uint32_t j = denseAlloc(ws.cntOut, ok);
     if (ok) {
         bool mis;
         prepareQuery<POL, FULL>(P, ws.ray[next] + 2 * (size_t)j, ray, rng, allow, GUIDE, mis);
@@ -517,7 +525,7 @@ __global__ void __launch_bounds__(128, THEIA_GEN_CTAS) wfGenerateKernel(const __
         onEvent<POL>(P.callback, &sh, active, ray, THEIA_RESULT_RAY_CREATED, k, 0);
         const bool ok = active && !isRayBad(ray);
         onEvent<POL>(P.callback, &sh, active && !ok, ray, THEIA_ERROR_RAY_BAD, k, 1);
-        const uint32_t j = denseAlloc(ws.counters + WF_CNT_QUEUE0, ok);
+        const uint32_t j = denseAlloc(ws.cntOut, ok);
         if (ok) {
             bool mis;
             prepareQuery<POL, FULL>(P, ws.ray[0] + 2 * (size_t)j, ray, rng, allow, GUIDE, mis);
@@ -545,7 +553,7 @@ __global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __g
     float* hist = sinkHist(P, sharedHist);
     const SceneView sc = makeSceneView(P.tlas, nullptr, 0);
     const bool GUIDE = variantGuide<V>(P);
-    const uint32_t count = ws.counters[cur ? WF_CNT_QUEUE1 : WF_CNT_QUEUE0];
+    const uint32_t count = *ws.cntIn;
     const uint32_t next = cur ^ 1u;
     const uint32_t* stateIn = ws.state[cur];
     const float4* rayIn = ws.ray[cur];
@@ -647,7 +655,7 @@ __global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __g
 
         // paths that wait for shadow rays are parked in the shadow buffer (warp collective)
         uint32_t js = 0u;
-        if (GUIDE) js = denseAlloc(ws.counters + WF_CNT_SHADOW, wantMIS);
+        if (GUIDE) js = denseAlloc(ws.cntShadow, wantMIS);
         if (wantMIS) {
             // sampleTargetMIS (:234-269): the two shadow rays are traced by the next trace pass
             float pPP;
@@ -686,7 +694,7 @@ __global__ void __launch_bounds__(128, THEIA_SHADOW_CTAS) wfShadeShadowKernel(co
     sinkInit(P, &sh, sharedHist);
     float* hist = sinkHist(P, sharedHist);
     const SceneView sc = makeSceneView(P.tlas, nullptr, 0);
-    const uint32_t count = ws.counters[WF_CNT_SHADOW];
+    const uint32_t count = *ws.cntShadow;
     const uint32_t next = cur ^ 1u;
     uint32_t nSegments = 0, nResponses = 0, stride;
 
