@@ -93,7 +93,7 @@ TDEV void wqProcess(WarpQueue& q, uint32_t head, uint32_t n) {
 }
 
 #ifndef THEIA_QUEUED_CTAS
-#define THEIA_QUEUED_CTAS 5
+#define THEIA_QUEUED_CTAS 6
 #endif
 enum : uint32_t { WT_NONE = 0u, WT_NODE = 1u, WT_INST = 2u };
 // rays[2 r], rays[2 r + 1]: ray r; results[r] = (instance slot | ~0, primitive, u, v). Rays 0 .. *countPtr - 1 and,
