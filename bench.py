@@ -522,7 +522,8 @@ def summary(m: dict, args, world: int) -> dict:
             "hits_per_s": m["hits"] / sec, "shadow_rays_per_s": m["shadow"] / sec, "paths_per_s": m["paths"] / sec,
             "segments_per_path": m["segs"] / max(m["paths"], 1),
             "e2e": {"value": m["e2e_segs"] / m["e2e_sec"], "unit": UNIT, "h2d_bytes_per_step": m["h2d"],
-                    "d2h_bytes_per_step": m["d2h"], "ms_per_step": m["e2e_sec"] * 1e3 / m["steps"]},
+                    "d2h_bytes_per_step": m["d2h"], "ms_per_step": m["e2e_sec"] * 1e3 / m["steps"],
+                    "small_batch": m.get("e2e_small")},
             "clocks": m["clocks"], "gpu_launches": m["launches"], "grid_ctas": m["grid"],
             "ray_query_kernel": None if tc is None else {"primary": KERNEL_NAMES.get(tc[0]),
                                                          "shadow": KERNEL_NAMES.get(tc[1]) if m["guide"] else None},
@@ -582,8 +583,6 @@ def runB200(args) -> None:
         "light_curve_sum": head["light_curve_sum"],
         "secondary": secondary,
     }
-    if "e2e_small" in m:
-        line["e2e"]["small_batch"] = m["e2e_small"]
     if not args.no_cpu and world == 1:
         try:
             paths_cpu = args.cpu_paths or cpuSamplePaths(args.workload, 1, 12.0, args.batch)
