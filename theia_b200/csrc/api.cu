@@ -179,7 +179,6 @@ __global__ void __launch_bounds__(128) hitReplayKernel(const uint32_t* queue, ui
     if (responseHasHistogram(r.kind))
         hist = r.hist_shared ? sharedHist : r.hist_partials + (size_t)(blockIdx.x % r.hist_capacity) * r.n_bins;
     uint32_t count = min(queue[0], capacity);
-    uint32_t nResp = 0;
     // grid-stride over warps so that all 32 lanes reach commitHit together
     for (uint32_t base = blockIdx.x * blockDim.x; base < capacity; base += gridDim.x * blockDim.x) {
         uint32_t k = base + threadIdx.x;
@@ -187,7 +186,8 @@ __global__ void __launch_bounds__(128) hitReplayKernel(const uint32_t* queue, ui
         HitItem item;
         item.contrib = 0.0f; item.time = 0.0f;
         if (has) item = loadHit(queue, capacity, polarized != 0, k);
-        commitHit(r, hist, has, item, k, 0u, nResp, 2.0f);
+        // response(hit) without the "contrib > 0" test of the tracers' call sites (sh/response.replay.glsl:46-47)
+        commitHitImpl<true, false>(r, hist, has, item, k, 0u, 2.0f);
     }
     __syncthreads();
     if (responseHasHistogram(r.kind) && r.hist_shared) {
