@@ -100,6 +100,27 @@ TDEV NodeRegs loadNodeShared(const WideNode* n) {
     return r;
 }
 
+// Rays and results stream through once: keep them out of L1, which holds the nodes and triangles that are read again.
+#ifndef THEIA_STREAM_RAYS
+#define THEIA_STREAM_RAYS 1
+#endif
+TDEV float4 loadStream(const float4* p) {
+#if THEIA_STREAM_RAYS
+    float4 v;
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+TDEV void storeStream(uint4* p, uint4 v) {
+#if THEIA_STREAM_RAYS
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+#else
+    *p = v;
+#endif
+}
+
 // (feeds the conservative box tests only: the 1 ulp of rcp.approx is inside their slack)
 TDEV float safeInv(float d) {
     float inv;

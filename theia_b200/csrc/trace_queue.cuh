@@ -93,7 +93,7 @@ TDEV void wqProcess(WarpQueue& q, uint32_t head, uint32_t n) {
 }
 
 #ifndef THEIA_QUEUED_CTAS
-#define THEIA_QUEUED_CTAS 6
+#define THEIA_QUEUED_CTAS 7
 #endif
 enum : uint32_t { WT_NONE = 0u, WT_NODE = 1u, WT_INST = 2u };
 // rays[2 r], rays[2 r + 1]: ray r; results[r] = (instance slot | ~0, primitive, u, v). Rays 0 .. *countPtr - 1 and,
@@ -120,9 +120,9 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
     if (keyStride == 0u) {
         for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
             const uint32_t r = i < count ? i : i - count + planeStride;
-            const float4 a = __ldg(rays + 2 * (size_t)r), b = __ldg(rays + 2 * (size_t)r + 1);
+            const float4 a = loadStream(rays + 2 * (size_t)r), b = loadStream(rays + 2 * (size_t)r + 1);
             const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr);
-            results[r] = make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v));
+            storeStream(results + r, make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v)));
         }
         return;
     }
@@ -152,8 +152,8 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
         if (have && task == WT_NONE && sp == 0 && clear) {
             const unsigned long long b = q.best[lane];
             const bool valid = (uint32_t)b != 0xFFFFFFFFu;
-            results[rid] = make_uint4(valid ? q.bslot[lane] : 0xFFFFFFFFu, valid ? q.bprim[lane] : 0xFFFFFFFFu,
-                                      f2u(valid ? q.bu[lane] : 0.0f), f2u(valid ? q.bv[lane] : 0.0f));
+            storeStream(results + rid, make_uint4(valid ? q.bslot[lane] : 0xFFFFFFFFu, valid ? q.bprim[lane] : 0xFFFFFFFFu,
+                                      f2u(valid ? q.bu[lane] : 0.0f), f2u(valid ? q.bv[lane] : 0.0f)));
             have = false;
         }
         const uint32_t needMask = __ballot_sync(FULL_MASK, !have);
@@ -168,7 +168,7 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
             const uint32_t i = wNext + (uint32_t)__popc(needMask & laneMaskLt());
             if (!have && i < wEnd) {
                 rid = i < count ? i : i - count + planeStride;
-                const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
+                const float4 a = loadStream(rays + 2 * (size_t)rid), b = loadStream(rays + 2 * (size_t)rid + 1);
                 ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z;
                 world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
                 q.best[lane] = ((unsigned long long)f2u(a.w) << 32) | 0xFFFFFFFFull;
@@ -260,21 +260,31 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
                         ++pos;
                     }
                 }
-                while (mask) {
-                    const int i = forward ? (31 - __clz(mask)) : (__ffs(mask) - 1);  // farthest slot first
-                    mask &= ~(1u << i);
-                    const uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, i & 3);
-                    uint32_t k;
-                    if ((imask >> i) & 1u) k = ((inBlas ? WE_BLAS : WE_TLAS) << 30) | (childBase + meta - 1u);
-                    else k = (WE_INST << 30) | (n.b.y + (meta >> 3));
-                    if (mask == 0u) {
-                        // the nearest child is the lane's next entry: it stays in registers
-                        payload = k & 0x3FFFFFFFu;
-                        task = (k >> 30) == WE_INST ? WT_INST : WT_NODE;
-                        taskBlas = (k >> 30) == WE_BLAS;
-                    } else if (sp < THEIA_STACK_SIZE) {  // cannot fail: theia_tlas_build bounds the depth of the trees
-                        stack[sp] = ((unsigned long long)f2u(tmin[i]) << 32) | k;
-                        ++sp;
+                if (mask) {
+                    // inner children / instances that were hit. The nearest one in slot order along the node's axis is
+                    // the lane's next entry and stays in registers; the others go to the stack, nearer ones on top, by
+                    // straight line code over the eight slots (entry distances stay in registers, no loop over bits).
+                    const uint32_t innerKey = ((inBlas ? WE_BLAS : WE_TLAS) << 30) | (childBase - 1u);
+                    const uint32_t instKey = (WE_INST << 30) | n.b.y;
+                    const int i0 = forward ? (__ffs(mask) - 1) : (31 - __clz(mask));
+                    const uint32_t meta0 = byteOf(i0 < 4 ? n.b.z : n.b.w, i0 & 3);
+                    if ((imask >> i0) & 1u) { payload = childBase + meta0 - 1u; task = WT_NODE; taskBlas = inBlas; }
+                    else { payload = n.b.y + (meta0 >> 3); task = WT_INST; taskBlas = false; }
+                    const uint32_t rest = mask & ~(1u << i0);
+                    if (rest) {  // (cannot overflow: theia_tlas_build bounds the depth of the trees to the stack size)
+                        const int nRest = __popc(rest);
+                        int pos = forward ? sp + nRest - 1 : sp;
+                        const int step = forward ? -1 : 1;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            if ((rest >> i) & 1u) {
+                                const uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, i & 3);
+                                const uint32_t k = ((imask >> i) & 1u) ? innerKey + meta : instKey + (meta >> 3);
+                                stack[pos] = ((unsigned long long)f2u(tmin[i]) << 32) | k;
+                                pos += step;
+                            }
+                        }
+                        sp += nRest;
                     }
                 }
             }

@@ -4,7 +4,9 @@
 
 namespace theia {
 
+#ifndef THEIA_TOP_NODES
 #define THEIA_TOP_NODES 72  // TLAS nodes staged in shared memory per CTA (breadth first prefix)
+#endif
 
 enum : uint32_t { ENTRY_TLAS = 0u, ENTRY_INST = 1u << 30, ENTRY_BLAS = 2u << 30, ENTRY_TYPE = 3u << 30 };
 

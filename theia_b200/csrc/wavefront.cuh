@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
         // ---- phase F
         const bool idle = sp == 0 && !done;
         if (idle && have) {
-            results[rid] = make_uint4(bestValid ? (uint32_t)bestSlot : 0xFFFFFFFFu, (uint32_t)bestPrim, f2u(bestU), f2u(bestV));
+            storeStream(results + rid, make_uint4(bestValid ? (uint32_t)bestSlot : 0xFFFFFFFFu, (uint32_t)bestPrim, f2u(bestU), f2u(bestV)));
             have = false;
         }
         const uint32_t needChunk = __ballot_sync(FULL_MASK, idle && chunkNext == chunkEnd);
@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
                 done = true;
             } else {
                 rid = i < count ? i : i - count + planeStride;
-                const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
+                const float4 a = loadStream(rays + 2 * (size_t)rid), b = loadStream(rays + 2 * (size_t)rid + 1);
                 ox = a.x; oy = a.y; oz = a.z; tmax = a.w; dx = b.x; dy = b.y; dz = b.z;
                 world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
                 bestValid = false; bestInst = -1; bestSlot = -1; bestPrim = -1; bestT = 0.0f; bestU = 0.0f; bestV = 0.0f;
@@ -344,9 +344,9 @@ __global__ void __launch_bounds__(128, THEIA_SIMPLE_CTAS) wfTraceSimpleKernel(co
     const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const uint32_t rid = i < count ? i : i - count + planeStride;
-        const float4 a = __ldg(rays + 2 * (size_t)rid), b = __ldg(rays + 2 * (size_t)rid + 1);
+        const float4 a = loadStream(rays + 2 * (size_t)rid), b = loadStream(rays + 2 * (size_t)rid + 1);
         const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr);
-        results[rid] = make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v));
+        storeStream(results + rid, make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v)));
     }
 }
 
