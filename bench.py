@@ -184,7 +184,7 @@ def cpuBaseline(workload: str, paths: int, steps: int = 1, warmup: int = 0):
 
 def cpuSamplePaths(workload: str, nSteps: int, budgetSeconds: float, limit: int) -> int:
     """Paths per step so that nSteps steps of the CPU arm take about budgetSeconds (from a pilot of 2^15 paths)."""
-    pilot = 1 << 15
+    pilot = 1 << 17
     _, _, _, sec, _ = cpuBaseline(workload, pilot, steps=1, warmup=0)
     n = int(pilot * budgetSeconds / max(nSteps, 1) / max(sec, 1e-4))
     p = 1 << 14
@@ -226,7 +226,7 @@ def l2PeakGBs(lib) -> float:
     buf = torch.zeros(32 << 20, dtype=torch.uint8, device="cuda")
     sink = torch.zeros(4, dtype=torch.int32, device="cuda")
     best = 0.0
-    for it in range(4):
+    for it in range(9):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         _lib.check(lib.theia_l2_probe(buf.data_ptr(), buf.numel(), 64, sink.data_ptr(), _device.currentStream("cuda")))
@@ -398,11 +398,16 @@ def measure(name: str, args, steps: int, lib, *, detail: bool, batch: int | None
         if wavefront:
             stats = torch.zeros(8, dtype=torch.int64, device="cuda")
             _lib.check(lib.theia_trace_stats_enable(stats.data_ptr()))
+            counters.zero_()
             deviceStep(step * world + rank)
             step += 1
             torch.cuda.synchronize()
             _lib.check(lib.theia_trace_stats_enable(None))
             out["visits"] = [int(x) for x in stats.cpu().numpy()]
+            # shadow rays the path tracing algorithm asks for (two per MIS event) vs those that had to be traced
+            # (the others cannot reach the target: wfTargetBoxKernel), both of the instrumented step
+            issued = int(counters.cpu().numpy()[2])
+            out["shadow_traced_fraction"] = (out["visits"][7] / issued) if issued else 1.0
 
     # ---------------- the reference's own batch size (2^20 paths, examples/01) end to end, for the launch overhead
     if detail and args.e2e_small_batch and args.e2e_small_batch < batch:
@@ -435,6 +440,7 @@ def rooflines(m: dict, peaks: dict, l2Peak: float, sms: int) -> dict:
     state = stateBytes(pol)
     physics = SEGMENT_INSTR[kind + ("_pol" if pol and kind == "volume_mis" else "")]
     events = shadow // 2
+    traced = int(round(shadow * m.get("shadow_traced_fraction", 1.0)))  # shadow rays that reached the ray query kernel
     # class -> (units, lane instructions, L2 bytes, HBM bytes) per unit
     model = {
         "volumeForwardKernel": (segs, physics, TABLE_BYTES, 0),
@@ -445,7 +451,7 @@ def rooflines(m: dict, peaks: dict, l2Peak: float, sms: int) -> dict:
                           NODE_BYTES * nodes[0] + TRI_BYTES * tris[0] + INST_BYTES * inst[0], 32 + 16),
         # (every segment is charged a committed hit on the L2 side: an upper bound of the declared figure)
         "wfShadeKernel": (segs, physics, TABLE_BYTES + HIT_BYTES, 2 * state + 2 * 32 + 16),
-        "wfTraceKernel(shadow)": (shadow, NODE_INSTR * nodes[1] + TRI_INSTR * tris[1] + INST_INSTR * inst[1],
+        "wfTraceKernel(shadow)": (traced, NODE_INSTR * nodes[1] + TRI_INSTR * tris[1] + INST_INSTR * inst[1],
                                   NODE_BYTES * nodes[1] + TRI_BYTES * tris[1] + INST_BYTES * inst[1], 32 + 16),
         "wfShadeShadowKernel": (events, GUIDE_EVENT_INSTR, 2 * HIT_BYTES + TABLE_BYTES, 2 * state + 2 * (32 + 16) + 32),
         "histReduceKernel": (0, 0, 0, 0),
@@ -489,6 +495,7 @@ def rooflines(m: dict, peaks: dict, l2Peak: float, sms: int) -> dict:
                       "hbm_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)"},
             "visits_per_ray": {"primary": {"nodes": nodes[0], "triangles": tris[0], "instances": inst[0]},
                                "shadow": {"nodes": nodes[1], "triangles": tris[1], "instances": inst[1]}},
+            "shadow_rays_traced_fraction": m.get("shadow_traced_fraction", 1.0),
             "kernels": kernels,
             "note": "achieved = algorithmic work (declared per-unit constants x counts of this run, visit counts from an "
                     "instrumented step) / live CUDA-event time of the dominant kernel; bound = the largest of the issue / "
@@ -585,7 +592,7 @@ def runB200(args) -> None:
     }
     if not args.no_cpu and world == 1:
         try:
-            paths_cpu = args.cpu_paths or cpuSamplePaths(args.workload, 1, 12.0, args.batch)
+            paths_cpu = args.cpu_paths or cpuSamplePaths(args.workload, 1, 20.0, args.batch)
             segps, hitps, cores, secStep, _ = cpuBaseline(args.workload, paths_cpu, steps=1, warmup=0)
             line["cpu_baseline"] = {"value": segps, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"{paths_cpu} paths of workload {args.workload} ({secStep:.1f} s; CPU oracle, "

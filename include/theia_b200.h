@@ -397,6 +397,8 @@ uint64_t theia_kernel_launches(void);
  *       batches, 0 = phased persistent kernel, 1 = one thread per ray, 2 = queued (a warp level queue of triangle
  *       tests, trace_queue.cuh). Results do not depend on it.
  *   "wf_flush_waiting": thresholds of the queued kernel (waiting lanes | instance lanes << 8 | refill lanes << 16).
+ *   "wf_shadow_cull": 1 (default): shadow rays of the target guide that cannot reach the box around the instances the
+ *       target id selects are not traced (they cannot create a response; results are identical); 0: all are traced.
  *   "query_kernel": kernel behind theia_tlas_query: 0 = direct traversal (default), 1 = phased, 2 = queued.
  *   "wf_min_node_lanes": 1..32, node phase threshold of the phased kernel (default 16).
  * theia_get_trace_choice reports what was picked for a scene (-1 = still measuring). */

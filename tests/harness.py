@@ -232,12 +232,15 @@ def sceneC3(N: int, *, resp: str = "record", callback: str | None = None, polari
     ]
     src = light.SphericalLightSource(position=(0.0, -6.0, 0.0), timeRange=(0.0, 5.0), budget=1e5)
     wl = light.ConstWavelengthSource(450.0)
-    # guide: True / "sphere", "flat", "disk" (planes facing the light source at y = -6), or False
+    # guide: True / "sphere", "small", "flat", "disk" (planes facing the light source at y = -6), or False
     if guide == "flat":
         g = target.FlatTargetGuide(width=3.0, height=3.0, position=(0.0, -1.2, 0.0), normal=(0.0, -1.0, 0.0),
                                    up=(0.0, 0.0, 1.0))
     elif guide == "disk":
         g = target.DiskTargetGuide(position=(0.0, -1.2, 0.0), radius=1.6, normal=(0.1, -1.0, 0.05))
+    elif guide == "small":
+        # much smaller than the detector and off centre: shadow rays outside its cone still reach the detector
+        g = target.SphereTargetGuide(position=(0.6, -0.2, 0.3), radius=0.4)
     else:
         g = target.SphereTargetGuide(position=(0.0, 0.0, 0.0), radius=1.5) if guide else None
     return _sceneCommon(N, inst, store, store.media[med.name], src, wl, resp, callback, polarized, 10, 1, g, key,

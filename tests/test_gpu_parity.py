@@ -211,6 +211,7 @@ SCENE_CASES = [
     (H.sceneC2, dict(lightKind="host")),
     (H.sceneC3, dict(guide="flat")),
     (H.sceneC3, dict(guide="disk", polarized=True)),
+    (H.sceneC3, dict(guide="small")),
     (H.sceneC5, dict(resp="record", lattice=(6, 6, 6), pitch=(4.0, 4.0, 4.0))),
     # host wavelength source (no draw) ahead of the cascade light, whose gamma variate the wavefront pregenerates
     (H.sceneC5, dict(resp="record", lattice=(6, 6, 6), pitch=(4.0, 4.0, 4.0), wavelength="host")),
@@ -240,6 +241,29 @@ def test_scene_tracer_hits_bit_exact(cuda, orc, builder, kw, mode):
     a, b = H.sortedHits(g), H.sortedHits(c)
     assert b["count"] > 0
     H.compareHits(a, b)
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(guide="small"), dict(guide="flat", polarized=True)],
+                         ids=lambda k: ",".join(f"{a}={b}" for a, b in k.items()) or "C3")
+def test_shadow_ray_culling_changes_nothing(cuda, kw):
+    """Shadow rays that cannot reach the target are not traced (wfTargetBoxKernel): same hits, same counts as with
+    every one of them traced."""
+    lib = _lib.load()
+    runs = []
+    for cull in (1, 0):
+        lib.theia_set_option(b"wf_shadow_cull", cull)
+        try:
+            with _device.useDevice("cuda"):
+                g = H.sceneC3(1 << 16, resp="record", **kw)
+            counters = g["tracer"].enableWorkCounters()
+            H.runGpu(g)
+            runs.append((H.sortedHits(g), counters.cpu().numpy().copy()))
+        finally:
+            lib.theia_set_option(b"wf_shadow_cull", 1)
+    (a, ca), (b, cb) = runs
+    assert a["count"] > 100
+    H.compareHits(a, b)
+    assert np.array_equal(ca, cb)
 
 
 @pytest.mark.parametrize("builder,kw", [(H.volumeScenario, dict()), (H.volumeScenario, dict(mis=False)),

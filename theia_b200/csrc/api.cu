@@ -261,15 +261,14 @@ __global__ void wfQueryConvertKernel(const void* tlas, const float* rays, const 
 // Visit counts of the ray queries of a wavefront launch (theia_trace_stats_enable): walks the same rays with the
 // instrumented one-thread-per-ray traversal and sums nodes visited / triangles tested / instances entered / rays.
 __global__ void __launch_bounds__(128) wfTraceStatsKernel(const void* tlas, const float4* rays, const uint32_t* countPtr,
-                                                          uint32_t raysPerEntry, uint32_t planeStride, unsigned long long* stats) {
+                                                          unsigned long long* stats, int32_t targetId) {
     const SceneView sc = makeSceneView(tlas, nullptr, 0);
-    const uint32_t count = *countPtr, total = count * raysPerEntry;
+    const uint32_t total = *countPtr;
     unsigned long long nodes = 0, tris = 0, inst = 0, n = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const uint32_t r = i < count ? i : i - count + planeStride;
-        const float4 a = __ldg(rays + 2 * (size_t)r), b = __ldg(rays + 2 * (size_t)r + 1);
+        const float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
         TraversalStats st = {0, 0, 0};
-        closestHit<true>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, &st);
+        closestHit<true>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, &st, targetId);
         nodes += st.nodes; tris += st.tris; inst += st.instances; n += 1;
     }
     for (int o = 16; o > 0; o >>= 1) {
@@ -541,6 +540,7 @@ static int envInt(const char* name, int fallback) {
 // per ray class (primary, shadow): -1 = pick by measurement; the environment sets the defaults
 static int g_optTraceKernel[2] = {envInt("THEIA_WF_TRACE_KERNEL", -1), envInt("THEIA_WF_SHADOW_TRACE_KERNEL", -1)};
 static int g_optMinNodeLanes = envInt("THEIA_WF_MIN_NODE_LANES", 16);
+static int g_optShadowCull = envInt("THEIA_WF_SHADOW_CULL", 1);  // 0: trace every shadow ray (A/B runs, tests)
 static int g_optFlushWaiting = envInt("THEIA_WF_FLUSH_WAITING", 4 | (8 << 8) | (4 << 16));  // thresholds of the queued kernel: waiting lanes | instance lanes << 8 | refill lanes << 16
 static int g_optQueryKernel = envInt("THEIA_QUERY_KERNEL", getenv("THEIA_QUERY_WAVEFRONT") ? 1 : 0);  // theia_tlas_query: 0 direct, 1 phased, 2 queued
 // Picks the trace kernel of a (device, scene, batch size) from its first nine batches: batch b runs candidate b mod 3
@@ -668,10 +668,12 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         if (timeIt) { tuner->inFlight = true; tuner->candidate = tuner->step % TRACE_CANDIDATES; }
         else tunerLock.unlock();  // decided (or busy): nothing of the tuner is touched below
     }
-    auto launchTrace = [&](int cls, const float4* rays, uint4* results, const uint32_t* countPtr, uint32_t* cursor, uint32_t rpe) {
+    // cls 1: shadow rays, a dense list of up to two per path whose results go where the rays say (indirect)
+    auto launchTrace = [&](int cls, const float4* rays, uint4* results, const uint32_t* countPtr, uint32_t* cursor) {
+        const uint32_t indirect = cls == 1 ? 1u : 0u, rpe = cls == 1 ? 2u : 1u;
+        const int32_t targetId = (cls == 1 && g_optShadowCull) ? D.objectId : -1;  // shadow rays: target first
         if (g_traceStats) {  // instrumented pass (measurement only, outside the timed launches)
-            wfTraceStatsKernel<<<gSimple < 1184u ? gSimple : 1184u, TRACE_THREADS, 0, st>>>(D.tlas, rays, countPtr, rpe, D.batch_size,
-                                                                                             g_traceStats + 4 * cls);
+            wfTraceStatsKernel<<<gSimple < 1184u ? gSimple : 1184u, TRACE_THREADS, 0, st>>>(D.tlas, rays, countPtr, g_traceStats + 4 * cls, targetId);
             countLaunches(1);
         }
         Timed tm(cls == 0 ? KC_TRACE : KC_SHADOW_TRACE, st);
@@ -679,22 +681,26 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         const bool timed = timeIt && tuner && tuner->choice[cls] < 0 && g_optTraceKernel[cls] < 0;
         if (timed) { e0 = profEvent(devSlot); e1 = profEvent(devSlot); cudaEventRecord(e0, st); }
         if (kernelOf[cls] == TRACE_QUEUED)
-            wfTraceQueuedKernel<<<gQueued, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, rpe,
-                                                                  D.batch_size, (uint32_t)g_optFlushWaiting);
+            wfTraceQueuedKernel<<<gQueued, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, indirect,
+                                                                  (uint32_t)g_optFlushWaiting, targetId);
         else if (kernelOf[cls] == TRACE_SIMPLE)
-            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, rpe, D.batch_size);
+            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, indirect, targetId);
         else
-            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, rpe,
-                                                            minNodeLanes, D.batch_size);
+            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, indirect, minNodeLanes);
         if (timed) { cudaEventRecord(e1, st); tuner->pending[cls].push_back({e0, e1}); }
     };
 
     // all counters of the batch are cleared here, once (one slot per segment generation: wavefront.cuh)
     CUDA_TRY(cudaMemsetAsync(ws.counters, 0, 4 * WF_SLOT * ((size_t)D.path_length + 1), st));
     auto slot = [&](uint32_t s) { return ws.counters + (size_t)WF_SLOT * s; };
+    ws.cullShadow = g_optShadowCull ? 1u : 0u;
+    if (guide && ws.cullShadow) {  // the box a shadow ray has to reach to matter (scene and target id may change per batch)
+        wfTargetBoxKernel<<<1, 256, 0, st>>>(D.tlas, D.objectId, ws.targetBox);
+        countLaunches(1);
+    }
     {
         Timed tm(KC_GENERATE, st);
-        ws.cntIn = nullptr; ws.cntOut = slot(0) + WF_CNT_QUEUE; ws.cntShadow = nullptr;
+        ws.cntIn = nullptr; ws.cntOut = slot(0) + WF_CNT_QUEUE; ws.cntShadow = nullptr; ws.cntShadowRays = nullptr;
         void* args[] = {(void*)&D, (void*)&ws};
         CUDA_TRY(cudaLaunchKernel(genFn, dim3(gGen), dim3(TRACE_THREADS), args, 0, st));
     }
@@ -703,14 +709,15 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     for (uint32_t it = 1; it <= D.path_length; ++it) {
         countLaunches((guide && it < D.path_length) ? 4 : 2);
         ws.cntIn = slot(it - 1) + WF_CNT_QUEUE; ws.cntOut = slot(it) + WF_CNT_QUEUE; ws.cntShadow = slot(it) + WF_CNT_SHADOW;
-        launchTrace(0, ws.ray[cur], ws.result, ws.cntIn, slot(it) + WF_CNT_CURSOR, 1u);
+        ws.cntShadowRays = slot(it) + WF_CNT_SHADOW_RAYS;
+        launchTrace(0, ws.ray[cur], ws.result, ws.cntIn, slot(it) + WF_CNT_CURSOR);
         {
             Timed tm(KC_SHADE, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadeFn, dim3(gShade), dim3(TRACE_THREADS), args, histSmem, st));
         }
         if (guide && it < D.path_length) {
-            launchTrace(1, ws.shadowRay, ws.shadowResult, ws.cntShadow, slot(it) + WF_CNT_SHADOW_CURSOR, 2u);
+            launchTrace(1, ws.shadowLive, ws.shadowResult, ws.cntShadowRays, slot(it) + WF_CNT_SHADOW_CURSOR);
             Timed tm(KC_SHADE_SHADOW, st);
             void* args[] = {(void*)&D, (void*)&ws, (void*)&cur};
             CUDA_TRY(cudaLaunchKernel(shadowFn, dim3(gShadow), dim3(TRACE_THREADS), args, histSmem, st));
@@ -736,6 +743,7 @@ int theia_set_option(const char* name, int value) {
     if (!strcmp(name, "wf_trace_kernel")) { g_optTraceKernel[0] = value; return 0; }
     if (!strcmp(name, "wf_shadow_trace_kernel")) { g_optTraceKernel[1] = value; return 0; }
     if (!strcmp(name, "wf_flush_waiting")) { g_optFlushWaiting = value; return 0; }
+    if (!strcmp(name, "wf_shadow_cull")) { g_optShadowCull = value != 0; return 0; }
     if (!strcmp(name, "query_kernel")) { g_optQueryKernel = value; return 0; }
     if (!strcmp(name, "wf_min_node_lanes")) { g_optMinNodeLanes = value < 1 ? 1 : (value > 32 ? 32 : value); return 0; }
     setError("theia_set_option: unknown option '%s'", name);
@@ -864,10 +872,10 @@ int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, in
             Timed tm(KC_TRACE, st);
             if (queued)
                 wfTraceQueuedKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
-                                                                      counters, counters + 1, 1u, 0u, (uint32_t)g_optFlushWaiting);
+                                                                      counters, counters + 1, 0u, (uint32_t)g_optFlushWaiting, -1);
             else
                 wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
-                                                                counters, counters + 1, 1u, 16u, 0u);
+                                                                counters, counters + 1, 0u, 16u);
         }
         wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
         CUDA_TRY(cudaFreeAsync(counters, st));
@@ -1033,7 +1041,7 @@ extern "C" int theia_tlas_query_static(const void* tlas_dev, const float* rays_d
     if (grid > need) grid = need;
     wfQuerySetupKernel<<<1, 32, 0, st>>>(counters, n);
     wfTraceQueuedKernel<<<grid, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results, counters,
-                                                        counters + 1, 1u, 0u, (uint32_t)g_optFlushWaiting);
+                                                        counters + 1, 0u, (uint32_t)g_optFlushWaiting, -1);
     wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
     countLaunches(3);
     CUDA_TRY(cudaGetLastError());

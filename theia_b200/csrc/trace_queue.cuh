@@ -96,15 +96,19 @@ TDEV void wqProcess(WarpQueue& q, uint32_t head, uint32_t n) {
 #define THEIA_QUEUED_CTAS 7
 #endif
 enum : uint32_t { WT_NONE = 0u, WT_NODE = 1u, WT_INST = 2u };
-// rays[2 r], rays[2 r + 1]: ray r; results[r] = (instance slot | ~0, primitive, u, v). Rays 0 .. *countPtr - 1 and,
-// with raysPerEntry = 2, planeStride .. planeStride + *countPtr - 1 (the two planes of shadow rays).
+// rays[2 r], rays[2 r + 1]: ray r < *countPtr; results[r] = (instance slot | ~0, primitive, u, v), or with indirect != 0
+// results[k], k = the bits of rays[2 r + 1].w (shadow rays).
+// targetId >= 0 (shadow rays: only a closest hit on an instance with this custom id matters, processShadowRay): a ray
+// is first traced against those instances alone and, if it hits one, against the others up to that hit, which may
+// replace it; the result is the closest hit of the scene whenever that is on such an instance, and unspecified
+// (a miss, or a hit elsewhere) when it is not.
 // keyStride (TlasHeader::pad[0]) == 0: (instance, primitive) does not fit the tie key: one thread per ray instead.
 // thresholds = flushWaiting | instLanes << 8 | refillLanes << 16: a kind of work runs once that many lanes want it
 // (or nothing else is left to do): run for a few lanes it costs the warp as many issue slots as for all of them.
 __global__ void __launch_bounds__(32 * WQ_WARPS, THEIA_QUEUED_CTAS)
 wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ rays, uint4* __restrict__ results,
-                    const uint32_t* __restrict__ countPtr, uint32_t* cursor, uint32_t raysPerEntry, uint32_t planeStride,
-                    uint32_t thresholds) {
+                    const uint32_t* __restrict__ countPtr, uint32_t* cursor, uint32_t indirect, uint32_t thresholds,
+                    int32_t targetId) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     __shared__ WarpQueue queues[WQ_WARPS];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
@@ -115,13 +119,12 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
     __syncthreads();
     const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
     const uint32_t keyStride = reinterpret_cast<const TlasHeader*>(tlas)->pad[0];
-    const uint32_t count = *countPtr;
-    const uint32_t total = count * raysPerEntry;
+    const uint32_t total = *countPtr;
     if (keyStride == 0u) {
         for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-            const uint32_t r = i < count ? i : i - count + planeStride;
-            const float4 a = loadStream(rays + 2 * (size_t)r), b = loadStream(rays + 2 * (size_t)r + 1);
-            const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr);
+            const float4 a = loadStream(rays + 2 * (size_t)i), b = loadStream(rays + 2 * (size_t)i + 1);
+            const uint32_t r = indirect ? f2u(b.w) : i;
+            const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr, targetId);
             storeStream(results + r, make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v)));
         }
         return;
@@ -145,10 +148,18 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
     const WideNode* blasNodes = nullptr;
     uint32_t head = 0u;  // ring position of the oldest item (uniform)
     bool idleRound = true;  // no node work in the last round (uniform): everything that waits may go ahead
+    const bool filtered = targetId >= 0;
+    bool second = false;  // filtered: the lane's ray is on its second pass (instances that do not belong to the target)
+    // an instance entry the lane's pass leaves out?
+    auto leftOut = [&](uint32_t slot) { return filtered && ((__ldg(&sc.instances[slot].customIndex) == targetId) == second); };
 
     while (true) {
         // ---- results and refill
         bool clear = (int32_t)(head - pendingEnd) >= 0;
+        if (have && task == WT_NONE && sp == 0 && clear && filtered && !second && (uint32_t)q.best[lane] != 0xFFFFFFFFu) {
+            second = true;  // a hit on the target: is anything of the rest of the scene in front of it?
+            task = WT_NODE; payload = 0u; taskBlas = false;
+        }
         if (have && task == WT_NONE && sp == 0 && clear) {
             const unsigned long long b = q.best[lane];
             const bool valid = (uint32_t)b != 0xFFFFFFFFu;
@@ -167,14 +178,15 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
             }
             const uint32_t i = wNext + (uint32_t)__popc(needMask & laneMaskLt());
             if (!have && i < wEnd) {
-                rid = i < count ? i : i - count + planeStride;
-                const float4 a = loadStream(rays + 2 * (size_t)rid), b = loadStream(rays + 2 * (size_t)rid + 1);
+                const float4 a = loadStream(rays + 2 * (size_t)i), b = loadStream(rays + 2 * (size_t)i + 1);
+                rid = indirect ? f2u(b.w) : i;
                 ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z;
                 world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
                 q.best[lane] = ((unsigned long long)f2u(a.w) << 32) | 0xFFFFFFFFull;
                 q.tmax[lane] = a.w;
                 sp = 0;
                 task = WT_NODE; payload = 0u; taskBlas = false;  // root of the TLAS
+                second = false;
                 have = true;
                 pendingEnd = head;
                 clear = true;
@@ -193,6 +205,7 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
                 const uint32_t key = (uint32_t)e;
                 payload = key & 0x3FFFFFFFu;
                 const uint32_t type = key >> 30;
+                if (type == WE_INST && leftOut(payload)) continue;
                 task = type == WE_INST ? WT_INST : WT_NODE;
                 taskBlas = type == WE_BLAS;
                 break;
@@ -269,7 +282,7 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
                     const int i0 = forward ? (__ffs(mask) - 1) : (31 - __clz(mask));
                     const uint32_t meta0 = byteOf(i0 < 4 ? n.b.z : n.b.w, i0 & 3);
                     if ((imask >> i0) & 1u) { payload = childBase + meta0 - 1u; task = WT_NODE; taskBlas = inBlas; }
-                    else { payload = n.b.y + (meta0 >> 3); task = WT_INST; taskBlas = false; }
+                    else { payload = n.b.y + (meta0 >> 3); task = leftOut(payload) ? WT_NONE : WT_INST; taskBlas = false; }
                     const uint32_t rest = mask & ~(1u << i0);
                     if (rest) {  // (cannot overflow: theia_tlas_build bounds the depth of the trees to the stack size)
                         const int nRest = __popc(rest);

@@ -40,8 +40,10 @@ TDEV uint32_t stageTopNodes(const void* tlas, WideNode* sharedTop) {
 // Closest hit over all instances. Per node: triangles of hit leaf children are tested right
 // away, inner children (and instances) are pushed far-to-near with their entry distance, so
 // entries that fall behind a closer hit are dropped when popped.
+// targetId >= 0 (shadow rays, see wfTraceQueuedKernel): two passes, first the instances with this custom id alone,
+// then, if one was hit, the others up to that hit; exact whenever the closest hit is on such an instance.
 template <bool STATS>
-TDEV RayHit closestHit(const SceneView& sc, vec3 origin, vec3 dir, float tmax, TraversalStats* st) {
+TDEV RayHit closestHit(const SceneView& sc, vec3 origin, vec3 dir, float tmax, TraversalStats* st, int32_t targetId = -1) {
     RayHit best;
     best.valid = false; best.instance = -1; best.prim = -1; best.slot = -1; best.t = 0.0f; best.u = 0.0f; best.v = 0.0f;
 
@@ -59,7 +61,15 @@ TDEV RayHit closestHit(const SceneView& sc, vec3 origin, vec3 dir, float tmax, T
     const WideNode* blasNodes = nullptr;
     const TriRec* blasTris = nullptr;
 
-    while (sp > 0) {
+    bool second = false;
+    while (true) {
+        if (sp == 0) {
+            if (targetId < 0 || second || !best.valid) break;
+            second = true;  // a hit on the target: is anything of the rest of the scene in front of it?
+            stackKey[0] = ENTRY_TLAS | 0u;
+            stackT[0] = 0.0f;
+            sp = 1;
+        }
         --sp;
         const uint32_t key = stackKey[sp];
         const float tEntry = stackT[sp];
@@ -71,6 +81,7 @@ TDEV RayHit closestHit(const SceneView& sc, vec3 origin, vec3 dir, float tmax, T
         if (type == ENTRY_INST) {
             // enter the instance: object space ray, watertight setup
             const InstanceRec* in = sc.instances + index;
+            if (targetId >= 0 && ((__ldg(&in->customIndex) == targetId) == second)) continue;
             const float4* q = reinterpret_cast<const float4*>(in);
             float4 r0 = __ldg(q), r1 = __ldg(q + 1), r2 = __ldg(q + 2);
             const float m[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};

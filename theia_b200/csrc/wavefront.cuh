@@ -40,8 +40,10 @@ enum : uint32_t {
 enum : uint32_t { WF_ALLOW = 1u << 16, WF_MIS_TARGET = 1u << 17 };
 // Counters: one slot of four words per segment generation s = 0 .. pathLength, cleared ONCE per batch (a memset), so
 // no launch in between has to reset anything: [0] live entries produced by generation s (s = 0: the generate kernel),
-// [1] paths of generation s waiting for shadow rays, [2] / [3] work cursors of the primary / shadow ray query launch.
-enum : uint32_t { WF_CNT_QUEUE = 0, WF_CNT_SHADOW = 1, WF_CNT_CURSOR = 2, WF_CNT_SHADOW_CURSOR = 3, WF_SLOT = 4 };
+// [1] paths of generation s waiting for shadow rays, [2] / [3] work cursors of the primary / shadow ray query launch,
+// [4] shadow rays of generation s that have to be traced (see targetBox).
+enum : uint32_t { WF_CNT_QUEUE = 0, WF_CNT_SHADOW = 1, WF_CNT_CURSOR = 2, WF_CNT_SHADOW_CURSOR = 3, WF_CNT_SHADOW_RAYS = 4,
+                  WF_SLOT = 8 };
 
 struct Workspace {
     uint32_t capacity;      // paths per batch
@@ -50,14 +52,19 @@ struct Workspace {
     const uint32_t* cntIn;
     uint32_t* cntOut;
     uint32_t* cntShadow;
+    uint32_t* cntShadowRays;
     uint32_t* state[2];     // ping-pong, [nFields][capacity] words, dense
     float4* ray[2];         // ping-pong, [capacity][2]: (origin, tmax), (direction, sampledDist)
     uint4* result;          // [capacity]: instance slot (0xFFFFFFFF = miss), primitive, u, v
     uint32_t* shadowState;  // [nFields][capacity]: paths with a pending pair of shadow rays, dense
-    // shadow rays in two planes of `capacity` entries: [0] phase function samples, [1] guide samples (rays
-    // of a kind are neighbours: the first kind mostly misses the scene at once, the second crosses it)
-    float4* shadowRay;      // [2][capacity][2]: (origin, tmax), (direction, weight)
-    uint4* shadowResult;    // [2][capacity]
+    // the two shadow rays of a parked path: plane [0] phase function sample, plane [1] guide sample
+    float4* shadowDir;      // [2][capacity]: (direction, weight)
+    uint4* shadowResult;    // [2][capacity], written for the rays that were traced (WF_LIVE0 / WF_LIVE1 of the path)
+    // Only a shadow ray whose closest hit is a target creates a response (processShadowRay), so one that misses the
+    // box around all instances the target id selects is not traced at all. The others, dense:
+    float4* shadowLive;     // [2 capacity][2]: (origin, tmax), (direction, plane * capacity + slot as bits)
+    float* targetBox;       // [8]: lo.xyz, hi.xyz of that box (padded), computed per batch by wfTargetBoxKernel
+    uint32_t cullShadow;    // 0: every shadow ray is traced (option wf_shadow_cull, for A/B runs and tests)
 };
 
 static inline size_t wfAlign(size_t v) { return (v + 255) & ~size_t(255); }
@@ -72,7 +79,7 @@ static inline size_t layoutWorkspace(void* base, uint32_t capacity, bool polariz
     Workspace w;
     w.capacity = capacity;
     w.counters = (uint32_t*)take(4 * WF_SLOT * ((size_t)pathLength + 1));
-    w.cntIn = nullptr; w.cntOut = nullptr; w.cntShadow = nullptr;
+    w.cntIn = nullptr; w.cntOut = nullptr; w.cntShadow = nullptr; w.cntShadowRays = nullptr;
     w.state[0] = (uint32_t*)take(4 * nFields * C);
     w.state[1] = (uint32_t*)take(4 * nFields * C);
     w.ray[0] = (float4*)take(32 * C);
@@ -80,11 +87,14 @@ static inline size_t layoutWorkspace(void* base, uint32_t capacity, bool polariz
     w.result = (uint4*)take(16 * C);
     if (guide) {
         w.shadowState = (uint32_t*)take(4 * nFields * C);
-        w.shadowRay = (float4*)take(64 * C);
+        w.shadowDir = (float4*)take(32 * C);
         w.shadowResult = (uint4*)take(32 * C);
+        w.shadowLive = (float4*)take(64 * C);
+        w.targetBox = (float*)take(32);
     } else {
-        w.shadowState = nullptr; w.shadowRay = nullptr; w.shadowResult = nullptr;
+        w.shadowState = nullptr; w.shadowDir = nullptr; w.shadowResult = nullptr; w.shadowLive = nullptr; w.targetBox = nullptr;
     }
+    w.cullShadow = 1u;
     if (ws) *ws = w;
     return off;
 }
@@ -137,11 +147,88 @@ TDEV uint32_t denseAlloc(uint32_t* counter, bool push) {
     return base + __popc(m & laneMaskLt());
 }
 
+// ------------------------------------------------------------------ shadow ray culling
+// Can a ray reach the box (lo = box[0..2], hi = box[3..5])? Errs on the side of yes: the box is padded by what the
+// coordinates can be off (wfTargetBoxKernel), and the distances get 2e-5 of slack for origins far away from it (the
+// ray queries carry the same kind of error: their object space rays are rounded, too).
+TDEV bool rayMayHitBox(const float* __restrict__ box, vec3 o, vec3 d, float tmax) {
+    const float lx = __ldg(box), ly = __ldg(box + 1), lz = __ldg(box + 2);
+    const float hx = __ldg(box + 3), hy = __ldg(box + 4), hz = __ldg(box + 5);
+    if (!(lx <= hx)) return false;  // no instance belongs to the target
+    const float ix = safeInv(d.x), iy = safeInv(d.y), iz = safeInv(d.z);
+    const float x0 = (lx - o.x) * ix, x1 = (hx - o.x) * ix;
+    const float y0 = (ly - o.y) * iy, y1 = (hy - o.y) * iy;
+    const float z0 = (lz - o.z) * iz, z1 = (hz - o.z) * iz;
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
+    return tn <= fmaf(2e-5f, tf, tf);
+}
+
+// World box around every instance a shadow ray may create a response on: custom id == targetId (any id if
+// targetId < 0) and a material with the detector flag on one of its sides (processShadowRay,
+// sh/scene.traverse.glsl:165-170). One CTA; box[6] = number of such instances.
+__global__ void __launch_bounds__(256) wfTargetBoxKernel(const void* __restrict__ tlas, int32_t targetId, float* __restrict__ box) {
+    const TlasHeader* h = reinterpret_cast<const TlasHeader*>(tlas);
+    const InstanceRec* inst = reinterpret_cast<const InstanceRec*>(reinterpret_cast<const char*>(tlas) + h->instancesOffset);
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    uint32_t count = 0;
+    for (uint32_t i = threadIdx.x; i < h->nInstances; i += blockDim.x) {
+        const InstanceRec& in = inst[i];
+        if (targetId >= 0 && in.customIndex != targetId) continue;
+        if (in.material != 0) {
+            const MaterialRec* m = reinterpret_cast<const MaterialRec*>(in.material);
+            if (((m->flagsInwards | m->flagsOutwards) & MATERIAL_DETECTOR_BIT) == 0) continue;
+        }
+        const BlasHeader* b = reinterpret_cast<const BlasHeader*>(reinterpret_cast<const char*>(in.blasNodes) - sizeof(BlasHeader));
+        float objMag = 0.0f, scale = 0.0f;
+        for (int a = 0; a < 3; ++a) {
+            objMag = fmaxf(objMag, fmaxf(fabsf(b->lo[a]), fabsf(b->hi[a])));
+            scale = fmaxf(scale, fabsf(in.o2w[4 * a]) + fabsf(in.o2w[4 * a + 1]) + fabsf(in.o2w[4 * a + 2]));
+        }
+        float l[3] = {INFINITY, INFINITY, INFINITY}, u[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (int c = 0; c < 8; ++c) {
+            const float p[3] = {(c & 1) ? b->hi[0] : b->lo[0], (c & 2) ? b->hi[1] : b->lo[1], (c & 4) ? b->hi[2] : b->lo[2]};
+            float w[3];
+            transformPoint(in.o2w, p, w);
+            for (int a = 0; a < 3; ++a) { l[a] = fminf(l[a], w[a]); u[a] = fmaxf(u[a], w[a]); }
+        }
+        for (int a = 0; a < 3; ++a) {
+            // 1e-4 of everything that sets the size of a rounding error: world and object coordinates, extent
+            const float pad = 1e-4f * (fmaxf(fabsf(l[a]), fabsf(u[a])) + (u[a] - l[a]) + scale * objMag) + 1e-30f;
+            lo[a] = fminf(lo[a], l[a] - pad);
+            hi[a] = fmaxf(hi[a], u[a] + pad);
+        }
+        ++count;
+    }
+    __shared__ float red[8][6];
+    __shared__ uint32_t redCount[8];
+    for (int a = 0; a < 3; ++a)
+        for (int d = 16; d > 0; d >>= 1) {
+            lo[a] = fminf(lo[a], __shfl_xor_sync(FULL_MASK, lo[a], d));
+            hi[a] = fmaxf(hi[a], __shfl_xor_sync(FULL_MASK, hi[a], d));
+        }
+    for (int d = 16; d > 0; d >>= 1) count += __shfl_xor_sync(FULL_MASK, count, d);
+    if (laneId() == 0) {
+        for (int a = 0; a < 3; ++a) { red[threadIdx.x >> 5][a] = lo[a]; red[threadIdx.x >> 5][3 + a] = hi[a]; }
+        redCount[threadIdx.x >> 5] = count;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t total = 0;
+        for (uint32_t w = 0; w < blockDim.x / 32; ++w) {
+            total += redCount[w];
+            for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], red[w][a]); hi[a] = fmaxf(hi[a], red[w][3 + a]); }
+        }
+        for (int a = 0; a < 3; ++a) { box[a] = lo[a]; box[3 + a] = hi[a]; }
+        box[6] = (float)total;
+        box[7] = 0.0f;
+    }
+}
+
 // ------------------------------------------------------------------ trace kernel
-// Ray queries of a dense buffer: rays[2 r], rays[2 r + 1] hold ray r. With raysPerEntry = 1 r < *countPtr;
-// with raysPerEntry = 2 (shadow rays) the rays live in two planes, r < *countPtr and planeStride <= r <
-// planeStride + *countPtr, which are walked one after the other;
-// results[r] receives (instance slot | ~0, primitive, u, v).
+// Ray queries of a dense buffer: rays[2 r], rays[2 r + 1] hold ray r < *countPtr; results[r] receives (instance slot | ~0,
+// primitive, u, v). With indirect != 0 (shadow rays) the result goes to results[k] instead, k = the bits of the fourth
+// component of rays[2 r + 1].
 //
 // Persistent warps, three phases per round so that the lanes of a warp do the same kind of
 // work at the same time (the traversal steps differ a lot in cost, and a mixed warp would
@@ -160,14 +247,13 @@ enum : uint32_t { WE_TLAS = 0u, WE_INST = 1u, WE_BLAS = 2u, WE_LEAF = 3u };
 __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                          uint4* __restrict__ results,
                                                          const uint32_t* __restrict__ countPtr, uint32_t* cursor,
-                                                         uint32_t raysPerEntry, uint32_t minNodeLanes, uint32_t planeStride) {
+                                                         uint32_t indirect, uint32_t minNodeLanes) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
     const uint32_t nTop = stageTopNodes(tlas, sharedTop);
     __syncthreads();
     const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
-    const uint32_t count = *countPtr;
-    const uint32_t total = count * raysPerEntry;
+    const uint32_t total = *countPtr;
     // rays a lane takes per fetch: 4 while there is plenty of work (fewer atomics), 1 once the
     // queue is short, so that the tail is spread over all lanes instead of queued up in a few
     const uint32_t lanes = gridDim.x * blockDim.x;
@@ -215,8 +301,8 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
             if (i >= total) {
                 done = true;
             } else {
-                rid = i < count ? i : i - count + planeStride;
-                const float4 a = loadStream(rays + 2 * (size_t)rid), b = loadStream(rays + 2 * (size_t)rid + 1);
+                const float4 a = loadStream(rays + 2 * (size_t)i), b = loadStream(rays + 2 * (size_t)i + 1);
+                rid = indirect ? f2u(b.w) : i;
                 ox = a.x; oy = a.y; oz = a.z; tmax = a.w; dx = b.x; dy = b.y; dz = b.z;
                 world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
                 bestValid = false; bestInst = -1; bestSlot = -1; bestPrim = -1; bestT = 0.0f; bestU = 0.0f; bestV = 0.0f;
@@ -332,20 +418,19 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
 #endif
 __global__ void __launch_bounds__(128, THEIA_SIMPLE_CTAS) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                                uint4* __restrict__ results,
-                                                               const uint32_t* __restrict__ countPtr, uint32_t raysPerEntry,
-                                                               uint32_t planeStride) {
+                                                               const uint32_t* __restrict__ countPtr, uint32_t indirect,
+                                                               int32_t targetId) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
-    const uint32_t count = *countPtr;
-    const uint32_t total = count * raysPerEntry;
+    const uint32_t total = *countPtr;
     if (blockIdx.x * blockDim.x >= total) return;
     const uint32_t nTop = stageTopNodes(tlas, sharedTop);
     __syncthreads();
     const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const uint32_t rid = i < count ? i : i - count + planeStride;
-        const float4 a = loadStream(rays + 2 * (size_t)rid), b = loadStream(rays + 2 * (size_t)rid + 1);
-        const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr);
+        const float4 a = loadStream(rays + 2 * (size_t)i), b = loadStream(rays + 2 * (size_t)i + 1);
+        const uint32_t rid = indirect ? f2u(b.w) : i;
+        const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr, targetId);
         storeStream(results + rid, make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v)));
     }
 }
@@ -364,6 +449,7 @@ __global__ void __launch_bounds__(128, THEIA_SIMPLE_CTAS) wfTraceSimpleKernel(co
 #define THEIA_GEN_CTAS 4
 #endif
 enum : uint32_t { WF_SEQ1 = 1u << 18 };  // one response was already committed in this event
+enum : uint32_t { WF_LIVE0 = 1u << 19, WF_LIVE1 = 1u << 20 };  // parked path: its phase / guide shadow ray is traced
 
 // Compile time variant key of the shading kernels (the reference compiles one shader per configuration,
 // src/theia/util.py:102-115, src/theia/trace.py:666-685; here the configurations of BASELINE.json get their own
@@ -656,6 +742,9 @@ __global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __g
         // paths that wait for shadow rays are parked in the shadow buffer (warp collective)
         uint32_t js = 0u;
         if (GUIDE) js = denseAlloc(ws.cntShadow, wantMIS);
+        bool live0 = false, live1 = false;
+        float4 srOrigin = make_float4(0, 0, 0, 0), srDir0 = make_float4(0, 0, 1, 0), srDir1 = make_float4(0, 0, 1, 0);
+        float srDist1 = 0.0f;
         if (wantMIS) {
             // sampleTargetMIS (:234-269): the two shadow rays are traced by the next trace pass
             float pPP;
@@ -667,16 +756,38 @@ __global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __g
             float pPT = scatterProb(ray.medium, ray.direction, targetSample.dir);
             float wTarget = pTT * pPT / (pTT * pTT + pPT * pPT);
             float wPhase = pPP * pPP / (pPP * pPP + pTP * pTP);
-            float4* sr = ws.shadowRay + 2 * (size_t)js;
-            float4* st = sr + 2 * (size_t)ws.capacity;
-            sr[0] = make_float4(ray.position.x, ray.position.y, ray.position.z, phaseSample.dist);
-            sr[1] = make_float4(dirPhase.x, dirPhase.y, dirPhase.z, wPhase);
-            st[0] = make_float4(ray.position.x, ray.position.y, ray.position.z, targetSample.dist);
-            st[1] = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, wTarget);
+            ws.shadowDir[js] = make_float4(dirPhase.x, dirPhase.y, dirPhase.z, wPhase);
+            ws.shadowDir[(size_t)ws.capacity + js] = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, wTarget);
+            // a shadow ray that cannot reach any instance of the target has no effect whatever it hits: not traced
+            live0 = !ws.cullShadow || rayMayHitBox(ws.targetBox, ray.position, dirPhase, phaseSample.dist);
+            live1 = !ws.cullShadow || rayMayHitBox(ws.targetBox, ray.position, targetSample.dir, targetSample.dist);
+            srOrigin = make_float4(ray.position.x, ray.position.y, ray.position.z, phaseSample.dist);
+            srDir0 = make_float4(dirPhase.x, dirPhase.y, dirPhase.z, u2f(js));
+            srDir1 = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, u2f(ws.capacity + js));
+            srDist1 = targetSample.dist;
             nShadow += 2;
-            storeState<POL>(ws.shadowState, ws.capacity, js, ray, rng.dim, it | (hitSeq ? WF_SEQ1 : 0u), path);
+            storeState<POL>(ws.shadowState, ws.capacity, js, ray, rng.dim,
+                            it | (hitSeq ? WF_SEQ1 : 0u) | (live0 ? WF_LIVE0 : 0u) | (live1 ? WF_LIVE1 : 0u), path);
         } else if (interact && !hit.valid && !last) {
             scatterRay<POL>(ray, rng.next2());  // volume scatter (:386-393)
+        }
+        if (GUIDE) {
+            // the rays to trace, dense: first the phase function samples of the warp, then its guide samples (rays of a
+            // kind are neighbours: the first kind mostly leaves the scene at once, the second crosses it)
+            const uint32_t m0 = __ballot_sync(FULL_MASK, live0), m1 = __ballot_sync(FULL_MASK, live1);
+            if (m0 | m1) {
+                uint32_t base = 0u;
+                if (laneId() == 0) base = atomicAdd(ws.cntShadowRays, (uint32_t)(__popc(m0) + __popc(m1)));
+                base = __shfl_sync(FULL_MASK, base, 0);
+                if (live0) {
+                    float4* r = ws.shadowLive + 2 * (size_t)(base + (uint32_t)__popc(m0 & laneMaskLt()));
+                    r[0] = srOrigin; r[1] = srDir0;
+                }
+                if (live1) {
+                    float4* r = ws.shadowLive + 2 * (size_t)(base + (uint32_t)__popc(m0) + (uint32_t)__popc(m1 & laneMaskLt()));
+                    r[0] = make_float4(srOrigin.x, srOrigin.y, srOrigin.z, srDist1); r[1] = srDir1;
+                }
+            }
         }
         finishSegment<POL, V>(P, ws, &sh, active && !wantMIS, path, ray, rng, result, it, GUIDE, next, nSegments);
     }
@@ -708,11 +819,10 @@ __global__ void __launch_bounds__(128, THEIA_SHADOW_CTAS) wfShadeShadowKernel(co
         float4 dirW[2] = {make_float4(0, 0, 1, 0), make_float4(0, 0, 1, 0)};
         uint4 res[2] = {make_uint4(0xFFFFFFFFu, 0u, 0u, 0u), make_uint4(0xFFFFFFFFu, 0u, 0u, 0u)};
         if (active) {
-            dirW[0] = ws.shadowRay[2 * (size_t)slot + 1];
-            dirW[1] = ws.shadowRay[2 * ((size_t)ws.capacity + slot) + 1];
-            res[0] = ws.shadowResult[slot];
-            res[1] = ws.shadowResult[(size_t)ws.capacity + slot];
             loadState<POL>(ws.shadowState, ws.capacity, i, ray, dim, flags, path);
+            // (a ray that was not traced has no result: it counts as a miss)
+            if (flags & WF_LIVE0) { dirW[0] = ws.shadowDir[slot]; res[0] = ws.shadowResult[slot]; }
+            if (flags & WF_LIVE1) { dirW[1] = ws.shadowDir[(size_t)ws.capacity + slot]; res[1] = ws.shadowResult[(size_t)ws.capacity + slot]; }
         }
         const uint32_t idx = P.first_path + path;
         Rng rng = makeRng(&P.rng, idx);
@@ -724,9 +834,9 @@ __global__ void __launch_bounds__(128, THEIA_SHADOW_CTAS) wfShadeShadowKernel(co
         for (uint32_t j = 0; j < 2; ++j) {
             HitItem item;
             bool has = false;
-            if (active) {
+            const RayHit q = resultToHit(j == 0 ? res[0] : res[1]);
+            if (active && q.valid) {  // (a miss has no effect: processShadowRay, sh/scene.traverse.glsl:168)
                 const float4 b = j == 0 ? dirW[0] : dirW[1];
-                const RayHit q = resultToHit(j == 0 ? res[0] : res[1]);
                 Ray r2 = ray;
                 scatterRayIS<POL>(r2, vec3{b.x, b.y, b.z});
                 SurfaceHit hit;
