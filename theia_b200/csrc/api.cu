@@ -261,14 +261,15 @@ __global__ void wfQueryConvertKernel(const void* tlas, const float* rays, const 
 // Visit counts of the ray queries of a wavefront launch (theia_trace_stats_enable): walks the same rays with the
 // instrumented one-thread-per-ray traversal and sums nodes visited / triangles tested / instances entered / rays.
 __global__ void __launch_bounds__(128) wfTraceStatsKernel(const void* tlas, const float4* rays, const uint32_t* countPtr,
-                                                          unsigned long long* stats, int32_t targetId) {
+                                                          unsigned long long* stats, int32_t targetId, const float* targetBox) {
     const SceneView sc = makeSceneView(tlas, nullptr, 0);
     const uint32_t total = *countPtr;
+    const uint32_t onlySlot = singleTargetSlot(targetBox, targetId);
     unsigned long long nodes = 0, tris = 0, inst = 0, n = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
         TraversalStats st = {0, 0, 0};
-        closestHit<true>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, &st, targetId);
+        closestHit<true>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, &st, targetId, onlySlot);
         nodes += st.nodes; tris += st.tris; inst += st.instances; n += 1;
     }
     for (int o = 16; o > 0; o >>= 1) {
@@ -672,8 +673,9 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     auto launchTrace = [&](int cls, const float4* rays, uint4* results, const uint32_t* countPtr, uint32_t* cursor) {
         const uint32_t indirect = cls == 1 ? 1u : 0u, rpe = cls == 1 ? 2u : 1u;
         const int32_t targetId = (cls == 1 && g_optShadowCull) ? D.objectId : -1;  // shadow rays: target first
+        const float* targetBox = targetId >= 0 ? ws.targetBox : nullptr;
         if (g_traceStats) {  // instrumented pass (measurement only, outside the timed launches)
-            wfTraceStatsKernel<<<gSimple < 1184u ? gSimple : 1184u, TRACE_THREADS, 0, st>>>(D.tlas, rays, countPtr, g_traceStats + 4 * cls, targetId);
+            wfTraceStatsKernel<<<gSimple < 1184u ? gSimple : 1184u, TRACE_THREADS, 0, st>>>(D.tlas, rays, countPtr, g_traceStats + 4 * cls, targetId, targetBox);
             countLaunches(1);
         }
         Timed tm(cls == 0 ? KC_TRACE : KC_SHADOW_TRACE, st);
@@ -682,11 +684,12 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         if (timed) { e0 = profEvent(devSlot); e1 = profEvent(devSlot); cudaEventRecord(e0, st); }
         if (kernelOf[cls] == TRACE_QUEUED)
             wfTraceQueuedKernel<<<gQueued, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, indirect,
-                                                                  (uint32_t)g_optFlushWaiting, targetId);
+                                                                  (uint32_t)g_optFlushWaiting, targetId, targetBox);
         else if (kernelOf[cls] == TRACE_SIMPLE)
-            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, indirect, targetId);
+            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, indirect, targetId, targetBox);
         else
-            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, indirect, minNodeLanes);
+            wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, indirect, minNodeLanes,
+                                                            targetId, targetBox);
         if (timed) { cudaEventRecord(e1, st); tuner->pending[cls].push_back({e0, e1}); }
     };
 
@@ -872,10 +875,10 @@ int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, in
             Timed tm(KC_TRACE, st);
             if (queued)
                 wfTraceQueuedKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
-                                                                      counters, counters + 1, 0u, (uint32_t)g_optFlushWaiting, -1);
+                                                                      counters, counters + 1, 0u, (uint32_t)g_optFlushWaiting, -1, nullptr);
             else
                 wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
-                                                                counters, counters + 1, 0u, 16u);
+                                                                counters, counters + 1, 0u, 16u, -1, nullptr);
         }
         wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
         CUDA_TRY(cudaFreeAsync(counters, st));
@@ -1041,7 +1044,7 @@ extern "C" int theia_tlas_query_static(const void* tlas_dev, const float* rays_d
     if (grid > need) grid = need;
     wfQuerySetupKernel<<<1, 32, 0, st>>>(counters, n);
     wfTraceQueuedKernel<<<grid, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results, counters,
-                                                        counters + 1, 0u, (uint32_t)g_optFlushWaiting, -1);
+                                                        counters + 1, 0u, (uint32_t)g_optFlushWaiting, -1, nullptr);
     wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
     countLaunches(3);
     CUDA_TRY(cudaGetLastError());

@@ -108,7 +108,7 @@ enum : uint32_t { WT_NONE = 0u, WT_NODE = 1u, WT_INST = 2u };
 __global__ void __launch_bounds__(32 * WQ_WARPS, THEIA_QUEUED_CTAS)
 wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ rays, uint4* __restrict__ results,
                     const uint32_t* __restrict__ countPtr, uint32_t* cursor, uint32_t indirect, uint32_t thresholds,
-                    int32_t targetId) {
+                    int32_t targetId, const float* __restrict__ targetBox) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     __shared__ WarpQueue queues[WQ_WARPS];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
@@ -124,7 +124,8 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
         for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
             const float4 a = loadStream(rays + 2 * (size_t)i), b = loadStream(rays + 2 * (size_t)i + 1);
             const uint32_t r = indirect ? f2u(b.w) : i;
-            const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr, targetId);
+            const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr, targetId,
+                                               singleTargetSlot(targetBox, targetId));
             storeStream(results + r, make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v)));
         }
         return;
@@ -149,6 +150,7 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
     uint32_t head = 0u;  // ring position of the oldest item (uniform)
     bool idleRound = true;  // no node work in the last round (uniform): everything that waits may go ahead
     const bool filtered = targetId >= 0;
+    const uint32_t onlySlot = singleTargetSlot(targetBox, targetId);  // the target's one instance: first passes start there
     bool second = false;  // filtered: the lane's ray is on its second pass (instances that do not belong to the target)
     // an instance entry the lane's pass leaves out?
     auto leftOut = [&](uint32_t slot) { return filtered && ((__ldg(&sc.instances[slot].customIndex) == targetId) == second); };
@@ -186,6 +188,7 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
                 q.tmax[lane] = a.w;
                 sp = 0;
                 task = WT_NODE; payload = 0u; taskBlas = false;  // root of the TLAS
+                if (onlySlot != 0xFFFFFFFFu) { task = WT_INST; payload = onlySlot; }
                 second = false;
                 have = true;
                 pendingEnd = head;

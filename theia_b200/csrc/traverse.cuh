@@ -37,20 +37,28 @@ TDEV uint32_t stageTopNodes(const void* tlas, WideNode* sharedTop) {
     return n;
 }
 
+// Slot of the one instance of the target, or ~0 (several, none, or no filter): the first pass of a filtered ray
+// query starts at that instance instead of the root of the TLAS.
+TDEV uint32_t singleTargetSlot(const float* __restrict__ targetBox, int32_t targetId) {
+    if (targetId < 0 || targetBox == nullptr || __ldg(targetBox + 6) != 1.0f) return 0xFFFFFFFFu;
+    return f2u(__ldg(targetBox + 7));
+}
+
 // Closest hit over all instances. Per node: triangles of hit leaf children are tested right
 // away, inner children (and instances) are pushed far-to-near with their entry distance, so
 // entries that fall behind a closer hit are dropped when popped.
 // targetId >= 0 (shadow rays, see wfTraceQueuedKernel): two passes, first the instances with this custom id alone,
 // then, if one was hit, the others up to that hit; exact whenever the closest hit is on such an instance.
 template <bool STATS>
-TDEV RayHit closestHit(const SceneView& sc, vec3 origin, vec3 dir, float tmax, TraversalStats* st, int32_t targetId = -1) {
+TDEV RayHit closestHit(const SceneView& sc, vec3 origin, vec3 dir, float tmax, TraversalStats* st, int32_t targetId = -1,
+                       uint32_t onlySlot = 0xFFFFFFFFu /* slot of the target's one instance: the first pass starts there */) {
     RayHit best;
     best.valid = false; best.instance = -1; best.prim = -1; best.slot = -1; best.t = 0.0f; best.u = 0.0f; best.v = 0.0f;
 
     uint32_t stackKey[THEIA_STACK_SIZE];
     float stackT[THEIA_STACK_SIZE];
     int sp = 0;
-    stackKey[0] = ENTRY_TLAS | 0u;
+    stackKey[0] = onlySlot != 0xFFFFFFFFu ? (ENTRY_INST | onlySlot) : (ENTRY_TLAS | 0u);
     stackT[0] = 0.0f;
     sp = 1;
 

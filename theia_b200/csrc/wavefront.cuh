@@ -166,15 +166,17 @@ TDEV bool rayMayHitBox(const float* __restrict__ box, vec3 o, vec3 d, float tmax
 
 // World box around every instance a shadow ray may create a response on: custom id == targetId (any id if
 // targetId < 0) and a material with the detector flag on one of its sides (processShadowRay,
-// sh/scene.traverse.glsl:165-170). One CTA; box[6] = number of such instances.
+// sh/scene.traverse.glsl:165-170). One CTA; box[6] = number of instances with that custom id, box[7] = (as bits) the
+// slot of the instance record if there is exactly one (the ray queries start there: singleTargetSlot).
 __global__ void __launch_bounds__(256) wfTargetBoxKernel(const void* __restrict__ tlas, int32_t targetId, float* __restrict__ box) {
     const TlasHeader* h = reinterpret_cast<const TlasHeader*>(tlas);
     const InstanceRec* inst = reinterpret_cast<const InstanceRec*>(reinterpret_cast<const char*>(tlas) + h->instancesOffset);
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    uint32_t count = 0;
+    uint32_t count = 0, slots = 0;
     for (uint32_t i = threadIdx.x; i < h->nInstances; i += blockDim.x) {
         const InstanceRec& in = inst[i];
         if (targetId >= 0 && in.customIndex != targetId) continue;
+        ++count; slots += i;
         if (in.material != 0) {
             const MaterialRec* m = reinterpret_cast<const MaterialRec*>(in.material);
             if (((m->flagsInwards | m->flagsOutwards) & MATERIAL_DETECTOR_BIT) == 0) continue;
@@ -198,37 +200,36 @@ __global__ void __launch_bounds__(256) wfTargetBoxKernel(const void* __restrict_
             lo[a] = fminf(lo[a], l[a] - pad);
             hi[a] = fmaxf(hi[a], u[a] + pad);
         }
-        ++count;
     }
     __shared__ float red[8][6];
-    __shared__ uint32_t redCount[8];
+    __shared__ uint32_t redCount[8], redSlots[8];
     for (int a = 0; a < 3; ++a)
         for (int d = 16; d > 0; d >>= 1) {
             lo[a] = fminf(lo[a], __shfl_xor_sync(FULL_MASK, lo[a], d));
             hi[a] = fmaxf(hi[a], __shfl_xor_sync(FULL_MASK, hi[a], d));
         }
-    for (int d = 16; d > 0; d >>= 1) count += __shfl_xor_sync(FULL_MASK, count, d);
+    for (int d = 16; d > 0; d >>= 1) { count += __shfl_xor_sync(FULL_MASK, count, d); slots += __shfl_xor_sync(FULL_MASK, slots, d); }
     if (laneId() == 0) {
         for (int a = 0; a < 3; ++a) { red[threadIdx.x >> 5][a] = lo[a]; red[threadIdx.x >> 5][3 + a] = hi[a]; }
-        redCount[threadIdx.x >> 5] = count;
+        redCount[threadIdx.x >> 5] = count; redSlots[threadIdx.x >> 5] = slots;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        uint32_t total = 0;
+        uint32_t total = 0, slot = 0;
         for (uint32_t w = 0; w < blockDim.x / 32; ++w) {
-            total += redCount[w];
+            total += redCount[w]; slot += redSlots[w];
             for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], red[w][a]); hi[a] = fmaxf(hi[a], red[w][3 + a]); }
         }
         for (int a = 0; a < 3; ++a) { box[a] = lo[a]; box[3 + a] = hi[a]; }
         box[6] = (float)total;
-        box[7] = 0.0f;
+        box[7] = u2f(total == 1u ? slot : 0xFFFFFFFFu);
     }
 }
 
 // ------------------------------------------------------------------ trace kernel
 // Ray queries of a dense buffer: rays[2 r], rays[2 r + 1] hold ray r < *countPtr; results[r] receives (instance slot | ~0,
 // primitive, u, v). With indirect != 0 (shadow rays) the result goes to results[k] instead, k = the bits of the fourth
-// component of rays[2 r + 1].
+// component of rays[2 r + 1]. targetId >= 0: two passes per ray, the target's instances first (see wfTraceQueuedKernel).
 //
 // Persistent warps, three phases per round so that the lanes of a warp do the same kind of
 // work at the same time (the traversal steps differ a lot in cost, and a mixed warp would
@@ -247,7 +248,8 @@ enum : uint32_t { WE_TLAS = 0u, WE_INST = 1u, WE_BLAS = 2u, WE_LEAF = 3u };
 __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                          uint4* __restrict__ results,
                                                          const uint32_t* __restrict__ countPtr, uint32_t* cursor,
-                                                         uint32_t indirect, uint32_t minNodeLanes) {
+                                                         uint32_t indirect, uint32_t minNodeLanes, int32_t targetId,
+                                                         const float* __restrict__ targetBox) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
     const uint32_t nTop = stageTopNodes(tlas, sharedTop);
@@ -278,8 +280,16 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
     int32_t bestInst = -1, bestSlot = -1, bestPrim = -1;
     float bestT = 0.0f, bestU = 0.0f, bestV = 0.0f;
 
+    const uint32_t onlySlot = singleTargetSlot(targetBox, targetId);
+    bool second = false;  // targetId >= 0: the ray is on its second pass (instances that do not belong to the target)
     while (true) {
         // ---- phase F
+        if (sp == 0 && have && targetId >= 0 && !second && bestValid) {
+            second = true;  // a hit on the target: is anything of the rest of the scene in front of it?
+            stackKey[0] = WE_TLAS << 30;
+            stackT[0] = 0.0f;
+            sp = 1;
+        }
         const bool idle = sp == 0 && !done;
         if (idle && have) {
             storeStream(results + rid, make_uint4(bestValid ? (uint32_t)bestSlot : 0xFFFFFFFFu, (uint32_t)bestPrim, f2u(bestU), f2u(bestV)));
@@ -306,9 +316,10 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
                 ox = a.x; oy = a.y; oz = a.z; tmax = a.w; dx = b.x; dy = b.y; dz = b.z;
                 world = {ox, oy, oz, safeInv(dx), safeInv(dy), safeInv(dz)};
                 bestValid = false; bestInst = -1; bestSlot = -1; bestPrim = -1; bestT = 0.0f; bestU = 0.0f; bestV = 0.0f;
-                stackKey[0] = WE_TLAS << 30;
+                stackKey[0] = onlySlot != 0xFFFFFFFFu ? ((WE_INST << 30) | onlySlot) : (WE_TLAS << 30);
                 stackT[0] = 0.0f;
                 sp = 1;
+                second = false;
                 have = true;
             }
         }
@@ -337,6 +348,7 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
             if (type == WE_LEAF) { pending = payload; break; }
             if (type == WE_INST) {
                 const InstanceRec* in = sc.instances + payload;
+                if (targetId >= 0 && ((__ldg(&in->customIndex) == targetId) == second)) continue;
                 const float4* q = reinterpret_cast<const float4*>(in);
                 const float4 r0 = __ldg(q), r1 = __ldg(q + 1), r2 = __ldg(q + 2);
                 const float m[12] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
@@ -419,7 +431,7 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
 __global__ void __launch_bounds__(128, THEIA_SIMPLE_CTAS) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                                uint4* __restrict__ results,
                                                                const uint32_t* __restrict__ countPtr, uint32_t indirect,
-                                                               int32_t targetId) {
+                                                               int32_t targetId, const float* __restrict__ targetBox) {
     __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
     const uint32_t total = *countPtr;
@@ -427,10 +439,11 @@ __global__ void __launch_bounds__(128, THEIA_SIMPLE_CTAS) wfTraceSimpleKernel(co
     const uint32_t nTop = stageTopNodes(tlas, sharedTop);
     __syncthreads();
     const SceneView sc = makeSceneView(tlas, sharedTop, nTop);
+    const uint32_t onlySlot = singleTargetSlot(targetBox, targetId);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const float4 a = loadStream(rays + 2 * (size_t)i), b = loadStream(rays + 2 * (size_t)i + 1);
         const uint32_t rid = indirect ? f2u(b.w) : i;
-        const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr, targetId);
+        const RayHit h = closestHit<false>(sc, vec3{a.x, a.y, a.z}, vec3{b.x, b.y, b.z}, a.w, nullptr, targetId, onlySlot);
         storeStream(results + rid, make_uint4(h.valid ? (uint32_t)h.slot : 0xFFFFFFFFu, (uint32_t)h.prim, f2u(h.u), f2u(h.v)));
     }
 }
@@ -756,11 +769,11 @@ __global__ void __launch_bounds__(128, THEIA_SHADE_CTAS) wfShadeKernel(const __g
             float pPT = scatterProb(ray.medium, ray.direction, targetSample.dir);
             float wTarget = pTT * pPT / (pTT * pTT + pPT * pPT);
             float wPhase = pPP * pPP / (pPP * pPP + pTP * pTP);
-            ws.shadowDir[js] = make_float4(dirPhase.x, dirPhase.y, dirPhase.z, wPhase);
-            ws.shadowDir[(size_t)ws.capacity + js] = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, wTarget);
             // a shadow ray that cannot reach any instance of the target has no effect whatever it hits: not traced
             live0 = !ws.cullShadow || rayMayHitBox(ws.targetBox, ray.position, dirPhase, phaseSample.dist);
             live1 = !ws.cullShadow || rayMayHitBox(ws.targetBox, ray.position, targetSample.dir, targetSample.dist);
+            if (live0) ws.shadowDir[js] = make_float4(dirPhase.x, dirPhase.y, dirPhase.z, wPhase);
+            if (live1) ws.shadowDir[(size_t)ws.capacity + js] = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, wTarget);
             srOrigin = make_float4(ray.position.x, ray.position.y, ray.position.z, phaseSample.dist);
             srDir0 = make_float4(dirPhase.x, dirPhase.y, dirPhase.z, u2f(js));
             srDir1 = make_float4(targetSample.dir.x, targetSample.dir.y, targetSample.dir.z, u2f(ws.capacity + js));
