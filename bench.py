@@ -183,9 +183,9 @@ def cpuBaseline(workload: str, paths: int, steps: int = 1, warmup: int = 0):
 
 
 def cpuSamplePaths(workload: str, nSteps: int, budgetSeconds: float, limit: int) -> int:
-    """Paths per step so that nSteps steps of the CPU arm take about budgetSeconds (from a pilot of 2^15 paths)."""
+    """Paths per step so that nSteps steps of the CPU arm take about budgetSeconds (from a warmed up pilot of 2^17 paths)."""
     pilot = 1 << 17
-    _, _, _, sec, _ = cpuBaseline(workload, pilot, steps=1, warmup=0)
+    _, _, _, sec, _ = cpuBaseline(workload, pilot, steps=1, warmup=1)
     n = int(pilot * budgetSeconds / max(nSteps, 1) / max(sec, 1e-4))
     p = 1 << 14
     while p * 2 <= min(n, limit):
@@ -358,24 +358,29 @@ def measure(name: str, args, steps: int, lib, *, detail: bool, batch: int | None
            "trace_choice": traceChoice()}
     out["segs"], out["hits"], out["shadow"], out["paths"] = (int(x) for x in counters.cpu().numpy().astype(np.int64))
 
-    # ---------------- end to end through the public API, host buffers
-    def e2eRun(pipeline, response, setB, n) -> tuple[float, int]:
+    # ---------------- end to end through the public API, host buffers: ShardedRun (theia_b200/distributed.py), the call a
+    # user of N GPUs makes. A step = one batch per rank: parameter update and launch assembly on the host, tracer,
+    # reduce kernel, device side accumulation, one all-reduce of the light curve (N > 1), D2H of the curve, synchronise.
+    from theia_b200.distributed import ShardedRun, batchOffset
+
+    def e2eRun(tracer, nRng, n) -> tuple[float, int]:
+        sharded = ShardedRun(tracer)
         counters.zero_()
         torch.cuda.synchronize()
-        s = step
+        if world > 1:
+            dist.barrier()
         t0 = time.perf_counter()
-        for _ in range(n):
-            setB(s * world + rank)
-            pipeline.run(0)  # update, launch assembly, tracer, reduce, D2H of the light curve, synchronise
-            response.result(0)
-            s += 1
+        for k in range(n):
+            sharded.offset0 = batchOffset(0, (step + k) * world, nRng, RNG_STRIDE)  # rank r runs batch (step + k) world + r
+            curve = sharded.run(world).lightCurve  # numpy, host
+            assert curve is not None
         dt = time.perf_counter() - t0
         return dt, int(counters.cpu().numpy()[0])
 
-    out["e2e_sec"], out["e2e_segs"] = e2eRun(pipe, resp, setBatch, steps)
+    out["e2e_sec"], out["e2e_segs"] = e2eRun(tr, nRNG, steps)
     step += steps
     out["h2d"] = ctypes.sizeof(launch0) + 512  # launch description + parameter blocks -> kernel argument space
-    out["d2h"] = resp.nBins * 4
+    out["d2h"] = resp.nBins * 8  # the float64 light curve ShardedRun hands back
 
     # ---------------- per kernel durations, live (CUDA events around every launch inside the library), then one
     # instrumented step for the visit counts of the ray queries
@@ -419,12 +424,11 @@ def measure(name: str, args, steps: int, lib, *, detail: bool, batch: int | None
         pipeS = pl.Pipeline(trS.collectStages())
         rngS.autoAdvance = 0
         nS = trS.nRNGSamples
-        setS = lambda b: rngS.setParam("offset", b * RNG_STRIDE * nS)  # noqa: E731
         for k in range(12):  # warm-up incl. the kernel choice for this batch size
-            setS(k)
+            rngS.setParam("offset", (k * world + rank) * RNG_STRIDE * nS)
             pipeS.run(0)
         counters = countersS
-        dt, segs = e2eRun(pipeS, respS, setS, 4 * steps)
+        dt, segs = e2eRun(trS, nS, 4 * steps)
         out["e2e_small"] = {"paths_per_step": args.e2e_small_batch, "value": segs / dt, "ms_per_step": dt * 1e3 / (4 * steps)}
     return out
 
@@ -592,7 +596,7 @@ def runB200(args) -> None:
     }
     if not args.no_cpu and world == 1:
         try:
-            paths_cpu = args.cpu_paths or cpuSamplePaths(args.workload, 1, 20.0, args.batch)
+            paths_cpu = args.cpu_paths or cpuSamplePaths(args.workload, 1, 20.0, 8 * args.batch)
             segps, hitps, cores, secStep, _ = cpuBaseline(args.workload, paths_cpu, steps=1, warmup=0)
             line["cpu_baseline"] = {"value": segps, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"{paths_cpu} paths of workload {args.workload} ({secStep:.1f} s; CPU oracle, "
