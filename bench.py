@@ -429,7 +429,9 @@ def measure(name: str, args, steps: int, lib, *, detail: bool, batch: int | None
             pipeS.run(0)
         counters = countersS
         dt, segs = e2eRun(trS, nS, 4 * steps)
-        out["e2e_small"] = {"paths_per_step": args.e2e_small_batch, "value": segs / dt, "ms_per_step": dt * 1e3 / (4 * steps)}
+        out["e2e_small"] = {"paths_per_step_per_gpu": args.e2e_small_batch, "value": segs / dt, "ms_per_step": dt * 1e3 / (4 * steps),
+                            "steps": 4 * steps}
+        out["e2e_small_segs"], out["e2e_small_sec"] = segs, dt
     return out
 
 
@@ -513,13 +515,16 @@ def reduceOverRanks(m: dict) -> dict:
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if world == 1:
         return m
-    keys = ["ms", "e2e_sec", "segs", "hits", "shadow", "paths", "e2e_segs"]
-    t = torch.tensor([float(m[k]) for k in keys], dtype=torch.float64, device="cuda")
+    keys = ["ms", "e2e_sec", "segs", "hits", "shadow", "paths", "e2e_segs", "e2e_small_segs", "e2e_small_sec"]
+    t = torch.tensor([float(m.get(k, 0.0)) for k in keys], dtype=torch.float64, device="cuda")
     mx, sm = t.clone(), t.clone()
     dist.all_reduce(mx, op=dist.ReduceOp.MAX)
     dist.all_reduce(sm, op=dist.ReduceOp.SUM)
     for i, k in enumerate(keys):
-        m[k] = float(mx[i]) if k in ("ms", "e2e_sec") else int(sm[i])
+        m[k] = float(mx[i]) if k in ("ms", "e2e_sec", "e2e_small_sec") else int(sm[i])
+    if "e2e_small" in m:  # whole job: segments of all ranks over the slowest rank's time
+        m["e2e_small"]["value"] = m["e2e_small_segs"] / m["e2e_small_sec"]
+        m["e2e_small"]["ms_per_step"] = m["e2e_small_sec"] * 1e3 / m["e2e_small"]["steps"]
     return m
 
 
