@@ -445,6 +445,7 @@ static int translate(const theia_trace_launch_t* L, DeviceLaunch& D) {
 }
 
 #define TRACE_THREADS 128u
+#define QUEUED_THREADS (32u * WQ_WARPS)  // CTA of wfTraceQueuedKernel
 
 struct KernelPlan { const void* fn; size_t smem; uint32_t grid; };
 
@@ -510,7 +511,7 @@ static WavefrontKernels wavefrontKernels(bool pol, const DeviceLaunch& D) {
     return pol ? wavefrontKernelsOf<true>(D) : wavefrontKernelsOf<false>(D);
 }
 
-static int persistentGrid(const void* fn, size_t smem, uint32_t* grid) {
+static int persistentGrid(const void* fn, size_t smem, uint32_t* grid, int threads = (int)TRACE_THREADS) {
     // occupancy queries are not free: remember the answer per (device, kernel, shared memory)
     struct Entry { int dev; const void* fn; size_t smem; uint32_t grid; };
     static thread_local Entry cache[16];
@@ -520,7 +521,7 @@ static int persistentGrid(const void* fn, size_t smem, uint32_t* grid) {
     for (int i = 0; i < nCache; ++i)
         if (cache[i].dev == dev && cache[i].fn == fn && cache[i].smem == smem) { *grid = cache[i].grid; return 0; }
     CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fn, (int)TRACE_THREADS, smem));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fn, threads, smem));
     if (perSm < 1) { setError("wavefront kernel does not fit on an SM"); return -1; }
     *grid = (uint32_t)sms * (uint32_t)perSm;
     if (nCache < 16) cache[nCache++] = Entry{dev, fn, smem, *grid};
@@ -637,7 +638,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     uint32_t gGen, gShade, gShadow, gTrace, gQueued;
     if (persistentGrid(genFn, 0, &gGen) || persistentGrid(shadeFn, histSmem, &gShade) ||
         persistentGrid(shadowFn, histSmem, &gShadow) || persistentGrid((const void*)wfTraceKernel, 0, &gTrace) ||
-        persistentGrid((const void*)wfTraceQueuedKernel, 0, &gQueued))
+        persistentGrid((const void*)wfTraceQueuedKernel, 0, &gQueued, QUEUED_THREADS))
         return -1;
     // partial histograms: one row per CTA of the shading grids
     uint32_t need128 = blocksFor(D.batch_size, TRACE_THREADS);
@@ -645,7 +646,7 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
     if (gShade > need128) gShade = need128;
     if (gShadow > need128) gShadow = need128;
     if (gTrace > need128) gTrace = need128;
-    if (gQueued > need128) gQueued = need128;
+    if (gQueued > need128 * (TRACE_THREADS / QUEUED_THREADS)) gQueued = need128 * (TRACE_THREADS / QUEUED_THREADS);
     const uint32_t minNodeLanes = (uint32_t)g_optMinNodeLanes;
     const uint32_t gSimple = need128 > 0 ? need128 : 1u;
 
@@ -683,10 +684,10 @@ static int launchWavefront(const theia_trace_launch_t* L, const DeviceLaunch& D)
         const bool timed = timeIt && tuner && tuner->choice[cls] < 0 && g_optTraceKernel[cls] < 0;
         if (timed) { e0 = profEvent(devSlot); e1 = profEvent(devSlot); cudaEventRecord(e0, st); }
         if (kernelOf[cls] == TRACE_QUEUED)
-            wfTraceQueuedKernel<<<gQueued, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, indirect,
+            wfTraceQueuedKernel<<<gQueued, QUEUED_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, indirect,
                                                                   (uint32_t)g_optFlushWaiting, targetId, targetBox);
         else if (kernelOf[cls] == TRACE_SIMPLE)
-            wfTraceSimpleKernel<<<rpe * gSimple, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, indirect, targetId, targetBox);
+            wfTraceSimpleKernel<<<rpe * gSimple * (TRACE_THREADS / THEIA_SIMPLE_THREADS), THEIA_SIMPLE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, indirect, targetId, targetBox);
         else
             wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(D.tlas, rays, results, countPtr, cursor, indirect, minNodeLanes,
                                                             targetId, targetBox);
@@ -867,14 +868,15 @@ int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, in
         CUDA_TRY(cudaMallocAsync(&results, 16 * (size_t)n, st));
         uint32_t gTrace = 0;
         const bool queued = g_optQueryKernel == 2;
-        if (persistentGrid(queued ? (const void*)wfTraceQueuedKernel : (const void*)wfTraceKernel, 0, &gTrace)) return -1;
-        const uint32_t need = blocksFor(n, TRACE_THREADS);
+        if (persistentGrid(queued ? (const void*)wfTraceQueuedKernel : (const void*)wfTraceKernel, 0, &gTrace,
+                           queued ? (int)QUEUED_THREADS : (int)TRACE_THREADS)) return -1;
+        const uint32_t need = blocksFor(n, queued ? QUEUED_THREADS : TRACE_THREADS);
         if (gTrace > need) gTrace = need;
         wfQuerySetupKernel<<<1, 32, 0, st>>>(counters, n);
         {
             Timed tm(KC_TRACE, st);
             if (queued)
-                wfTraceQueuedKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
+                wfTraceQueuedKernel<<<gTrace, QUEUED_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
                                                                       counters, counters + 1, 0u, (uint32_t)g_optFlushWaiting, -1, nullptr);
             else
                 wfTraceKernel<<<gTrace, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results,
@@ -1039,11 +1041,11 @@ extern "C" int theia_tlas_query_static(const void* tlas_dev, const float* rays_d
     uint4* results = reinterpret_cast<uint4*>(scratch + 256);           // [n]: every entry < n is written before it is read
     cudaStream_t st = (cudaStream_t)stream;
     uint32_t grid = 0;
-    if (persistentGrid((const void*)wfTraceQueuedKernel, 0, &grid)) return -1;
-    const uint32_t need = blocksFor(n, TRACE_THREADS);
+    if (persistentGrid((const void*)wfTraceQueuedKernel, 0, &grid, (int)QUEUED_THREADS)) return -1;
+    const uint32_t need = blocksFor(n, QUEUED_THREADS);
     if (grid > need) grid = need;
     wfQuerySetupKernel<<<1, 32, 0, st>>>(counters, n);
-    wfTraceQueuedKernel<<<grid, TRACE_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results, counters,
+    wfTraceQueuedKernel<<<grid, QUEUED_THREADS, 0, st>>>(tlas_dev, reinterpret_cast<const float4*>(rays_dev), results, counters,
                                                         counters + 1, 0u, (uint32_t)g_optFlushWaiting, -1, nullptr);
     wfQueryConvertKernel<<<blocksFor(n, 128), 128, 0, st>>>(tlas_dev, rays_dev, results, n, out_dev, out_bary_dev);
     countLaunches(3);

@@ -28,7 +28,13 @@
 namespace theia {
 
 #define WQ_CAP 512u  // ring entries per warp (power of two): < 32 left by a flush + at most 8 per lane and node step
-#define WQ_WARPS 4u  // warps per CTA of the queued kernel
+#ifndef WQ_WARPS
+// Warps per CTA of the queued kernel. One: the warp's queue sits at a fixed shared memory address, so none of its many
+// accesses needs address arithmetic or a base register (C3 shadow trace 1.159 -> 1.048 ms, C2 0.405 -> 0.367 ms against
+// four warps per CTA at the same number of warps per SM); only 8 nodes of the TLAS are staged per CTA then.
+#define WQ_WARPS 1u
+#endif
+#define WQ_TOP_NODES (WQ_WARPS == 1u ? 8u : (uint32_t)THEIA_TOP_NODES)  // TLAS nodes staged in shared memory per CTA
 
 struct WarpQueue {
     unsigned long long best[32];  // (t bits << 32) | tie key; low word 0xFFFFFFFF: no hit (t = tmax)
@@ -93,7 +99,7 @@ TDEV void wqProcess(WarpQueue& q, uint32_t head, uint32_t n) {
 }
 
 #ifndef THEIA_QUEUED_CTAS
-#define THEIA_QUEUED_CTAS 7
+#define THEIA_QUEUED_CTAS (28u / WQ_WARPS)  // 28 warps per SM (72 registers)
 #endif
 enum : uint32_t { WT_NONE = 0u, WT_NODE = 1u, WT_INST = 2u };
 // rays[2 r], rays[2 r + 1]: ray r < *countPtr; results[r] = (instance slot | ~0, primitive, u, v), or with indirect != 0
@@ -109,10 +115,10 @@ __global__ void __launch_bounds__(32 * WQ_WARPS, THEIA_QUEUED_CTAS)
 wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ rays, uint4* __restrict__ results,
                     const uint32_t* __restrict__ countPtr, uint32_t* cursor, uint32_t indirect, uint32_t thresholds,
                     int32_t targetId, const float* __restrict__ targetBox) {
-    __shared__ float4 sharedRaw[THEIA_TOP_NODES * 5];
+    __shared__ float4 sharedRaw[WQ_TOP_NODES * 5];
     __shared__ WarpQueue queues[WQ_WARPS];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
-    const uint32_t nTop = stageTopNodes(tlas, sharedTop);
+    const uint32_t nTop = stageTopNodes(tlas, sharedTop, WQ_TOP_NODES);
     const uint32_t lane = laneId();
     WarpQueue& q = queues[threadIdx.x >> 5];
     if (lane == 0) q.tail = 0u;

@@ -28,10 +28,10 @@ TDEV SceneView makeSceneView(const void* tlas, const WideNode* sharedTop, uint32
     return v;
 }
 // Cooperative copy of the top of the TLAS into shared memory (call with the whole CTA).
-TDEV uint32_t stageTopNodes(const void* tlas, WideNode* sharedTop) {
+TDEV uint32_t stageTopNodes(const void* tlas, WideNode* sharedTop, uint32_t cap = THEIA_TOP_NODES) {
     const TlasHeader* h = reinterpret_cast<const TlasHeader*>(tlas);
     const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(tlas) + h->nodesOffset);
-    uint32_t n = min(h->nNodes, (uint32_t)THEIA_TOP_NODES);
+    uint32_t n = min(h->nNodes, cap);
     uint4* dst = reinterpret_cast<uint4*>(sharedTop);
     for (uint32_t i = threadIdx.x; i < n * 5; i += blockDim.x) dst[i] = __ldg(src + i);
     return n;

@@ -428,7 +428,10 @@ __global__ void __launch_bounds__(128, THEIA_PHASED_CTAS) wfTraceKernel(const vo
 #ifndef THEIA_SIMPLE_CTAS
 #define THEIA_SIMPLE_CTAS 6
 #endif
-__global__ void __launch_bounds__(128, THEIA_SIMPLE_CTAS) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
+#ifndef THEIA_SIMPLE_THREADS
+#define THEIA_SIMPLE_THREADS 128
+#endif
+__global__ void __launch_bounds__(THEIA_SIMPLE_THREADS, THEIA_SIMPLE_CTAS) wfTraceSimpleKernel(const void* __restrict__ tlas, const float4* __restrict__ rays,
                                                                uint4* __restrict__ results,
                                                                const uint32_t* __restrict__ countPtr, uint32_t indirect,
                                                                int32_t targetId, const float* __restrict__ targetBox) {
