@@ -31,10 +31,16 @@ namespace theia {
 #ifndef WQ_WARPS
 // Warps per CTA of the queued kernel. One: the warp's queue sits at a fixed shared memory address, so none of its many
 // accesses needs address arithmetic or a base register (C3 shadow trace 1.159 -> 1.048 ms, C2 0.405 -> 0.367 ms against
-// four warps per CTA at the same number of warps per SM); only 8 nodes of the TLAS are staged per CTA then.
+// four warps per CTA at the same number of warps per SM); the top of the TLAS is not staged in shared memory then.
 #define WQ_WARPS 1u
 #endif
-#define WQ_TOP_NODES (WQ_WARPS == 1u ? 8u : (uint32_t)THEIA_TOP_NODES)  // TLAS nodes staged in shared memory per CTA
+#define WQ_TOP_NODES (WQ_WARPS == 1u ? 0u : (uint32_t)THEIA_TOP_NODES)  // TLAS nodes staged in shared memory per CTA
+// Entries of a lane's traversal stack that live in shared memory (the rest in local memory). The stack is read when a
+// lane runs out of hit children, with the node fetch waiting on it, and local memory mostly missed L1 there (77 % of
+// the sectors: the L1 is churned by nodes and triangles).
+#ifndef WQ_SSTACK
+#define WQ_SSTACK 6
+#endif
 
 struct WarpQueue {
     unsigned long long best[32];  // (t bits << 32) | tie key; low word 0xFFFFFFFF: no hit (t = tmax)
@@ -48,6 +54,8 @@ struct WarpQueue {
     uint32_t items[WQ_CAP];       // leaves: owner lane << 27 | (triangles - 1) << 25 | first triangle in the owner's BLAS
     uint8_t expand[128];          // triangle slot of a pass -> item lane << 2 | triangle within the leaf
     uint32_t tail;                // ring position behind the last item (free running; the head is warp uniform, in registers)
+    uint32_t pad_;
+    unsigned long long sstack[WQ_SSTACK > 0 ? WQ_SSTACK : 1][32];  // bottom of the lanes' stacks
 };
 
 // Tests the triangles of up to 32 queued leaves (n of them from `head`): the leaves are expanded into
@@ -115,10 +123,15 @@ __global__ void __launch_bounds__(32 * WQ_WARPS, THEIA_QUEUED_CTAS)
 wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ rays, uint4* __restrict__ results,
                     const uint32_t* __restrict__ countPtr, uint32_t* cursor, uint32_t indirect, uint32_t thresholds,
                     int32_t targetId, const float* __restrict__ targetBox) {
+#if WQ_WARPS == 1
+    WideNode* sharedTop = nullptr;
+    const uint32_t nTop = 0u;
+#else
     __shared__ float4 sharedRaw[WQ_TOP_NODES * 5];
-    __shared__ WarpQueue queues[WQ_WARPS];
     WideNode* sharedTop = reinterpret_cast<WideNode*>(sharedRaw);
     const uint32_t nTop = stageTopNodes(tlas, sharedTop, WQ_TOP_NODES);
+#endif
+    __shared__ WarpQueue queues[WQ_WARPS];
     const uint32_t lane = laneId();
     WarpQueue& q = queues[threadIdx.x >> 5];
     if (lane == 0) q.tail = 0u;
@@ -142,7 +155,8 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
     uint32_t chunk = total / (2u * nWarps);
     chunk = chunk > 32u ? 32u : (chunk < 1u ? 1u : chunk);
 
-    unsigned long long stack[THEIA_STACK_SIZE];  // entry distance bits << 32 | key: one load / store per entry
+    // entry distance bits << 32 | key: one load / store per entry; entries 0 .. WQ_SSTACK - 1 in shared memory
+    unsigned long long stack[THEIA_STACK_SIZE - WQ_SSTACK];
     int sp = 0;
     bool have = false;
     uint32_t task = WT_NONE, payload = 0u;  // the entry this lane works on next (popped, not yet done)
@@ -209,7 +223,7 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
         if (task == WT_NONE) {
             while (sp > 0) {
                 --sp;
-                const unsigned long long e = stack[sp];
+                const unsigned long long e = sp < WQ_SSTACK ? q.sstack[sp][lane] : stack[sp - WQ_SSTACK];
                 if (u2f((uint32_t)(e >> 32)) > lim) continue;
                 const uint32_t key = (uint32_t)e;
                 payload = key & 0x3FFFFFFFu;
@@ -260,7 +274,11 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
             const bool inBlas = taskBlas;
             const WideNode* np = inBlas ? blasNodes + payload
                                         : (payload < sc.nTop ? sc.topNodes + payload : sc.nodes + payload);
+#if WQ_WARPS == 1 && !defined(WQ_GENERIC_NODE_LOAD)
+            const NodeRegs n = loadNode(np);  // always global memory: the read-only path
+#else
             const NodeRegs n = loadNodeShared(np);
+#endif
             float tmin[8];
             uint32_t mask = testChildren(n, inBlas ? obj : world, lim, tmin);
             if (mask) {
@@ -302,7 +320,9 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
                             if ((rest >> i) & 1u) {
                                 const uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, i & 3);
                                 const uint32_t k = ((imask >> i) & 1u) ? innerKey + meta : instKey + (meta >> 3);
-                                stack[pos] = ((unsigned long long)f2u(tmin[i]) << 32) | k;
+                                const unsigned long long e = ((unsigned long long)f2u(tmin[i]) << 32) | k;
+                                if (pos < WQ_SSTACK) q.sstack[pos][lane] = e;
+                                else stack[pos - WQ_SSTACK] = e;
                                 pos += step;
                             }
                         }
