@@ -459,7 +459,7 @@ __global__ void __launch_bounds__(THEIA_SIMPLE_THREADS, THEIA_SIMPLE_CTAS) wfTra
 #define THEIA_SHADE_CTAS 7
 #endif
 #ifndef THEIA_SHADOW_CTAS
-#define THEIA_SHADOW_CTAS 4
+#define THEIA_SHADOW_CTAS 5  // 4 / 5 / 6 / 7 / 8: 0.366 / 0.322 / 0.321 / 0.324 / 0.318 ms per launch on C3 (profiles/r2_ab_shade_ctas.txt)
 #endif
 #ifndef THEIA_GEN_CTAS
 #define THEIA_GEN_CTAS 4
