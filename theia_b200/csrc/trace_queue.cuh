@@ -106,6 +106,16 @@ TDEV void wqProcess(WarpQueue& q, uint32_t head, uint32_t n) {
     }
 }
 
+// Byte i (0..7) of the eight child meta bytes of a node: one byte permute with the slot as its selector.
+TDEV uint32_t metaByte(const NodeRegs& n, int i) { return __byte_perm(n.b.z, n.b.w, (uint32_t)i) & 0xFFu; }
+// t[i] for a run time i out of eight registers (seven selects; an indexed array would be spilled to local memory)
+TDEV float pick8(const float t[8], int i) {
+    const bool b0 = (i & 1) != 0, b1 = (i & 2) != 0, b2 = (i & 4) != 0;
+    const float a0 = b0 ? t[1] : t[0], a1 = b0 ? t[3] : t[2], a2 = b0 ? t[5] : t[4], a3 = b0 ? t[7] : t[6];
+    const float c0 = b1 ? a1 : a0, c1 = b1 ? a3 : a2;
+    return b2 ? c1 : c0;
+}
+
 #ifndef THEIA_QUEUED_CTAS
 #define THEIA_QUEUED_CTAS (28u / WQ_WARPS)  // 28 warps per SM (72 registers)
 #endif
@@ -295,38 +305,34 @@ wfTraceQueuedKernel(const void* __restrict__ tlas, const float4* __restrict__ ra
                     while (leafMask) {
                         const int i = __ffs(leafMask) - 1;
                         leafMask &= leafMask - 1u;
-                        const uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, i & 3);
+                        const uint32_t meta = metaByte(n, i);
                         q.items[pos & (WQ_CAP - 1u)] = (lane << 27) | (((meta & 7u) - 1u) << 25) | (n.b.y + (meta >> 3));
                         ++pos;
                     }
                 }
                 if (mask) {
                     // inner children / instances that were hit. The nearest one in slot order along the node's axis is
-                    // the lane's next entry and stays in registers; the others go to the stack, nearer ones on top, by
-                    // straight line code over the eight slots (entry distances stay in registers, no loop over bits).
+                    // the lane's next entry and stays in registers; the others go to the stack, nearer ones on top. The
+                    // loop runs as often as the lane of the warp with the most of them needs (two or three times as a
+                    // rule), so an iteration has to be short: the entry distance comes out of the eight registers by
+                    // selects (an array indexed by i would live in local memory), the meta byte by one byte permute.
                     const uint32_t innerKey = ((inBlas ? WE_BLAS : WE_TLAS) << 30) | (childBase - 1u);
                     const uint32_t instKey = (WE_INST << 30) | n.b.y;
                     const int i0 = forward ? (__ffs(mask) - 1) : (31 - __clz(mask));
-                    const uint32_t meta0 = byteOf(i0 < 4 ? n.b.z : n.b.w, i0 & 3);
+                    const uint32_t meta0 = metaByte(n, i0);
                     if ((imask >> i0) & 1u) { payload = childBase + meta0 - 1u; task = WT_NODE; taskBlas = inBlas; }
                     else { payload = n.b.y + (meta0 >> 3); task = leftOut(payload) ? WT_NONE : WT_INST; taskBlas = false; }
-                    const uint32_t rest = mask & ~(1u << i0);
-                    if (rest) {  // (cannot overflow: theia_tlas_build bounds the depth of the trees to the stack size)
-                        const int nRest = __popc(rest);
-                        int pos = forward ? sp + nRest - 1 : sp;
-                        const int step = forward ? -1 : 1;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            if ((rest >> i) & 1u) {
-                                const uint32_t meta = byteOf(i < 4 ? n.b.z : n.b.w, i & 3);
-                                const uint32_t k = ((imask >> i) & 1u) ? innerKey + meta : instKey + (meta >> 3);
-                                const unsigned long long e = ((unsigned long long)f2u(tmin[i]) << 32) | k;
-                                if (pos < WQ_SSTACK) q.sstack[pos][lane] = e;
-                                else stack[pos - WQ_SSTACK] = e;
-                                pos += step;
-                            }
-                        }
-                        sp += nRest;
+                    uint32_t rest = mask & ~(1u << i0);
+                    // (the stack cannot overflow: theia_tlas_build bounds the depth of the trees to its size)
+                    while (rest) {
+                        const int i = forward ? (31 - __clz(rest)) : (__ffs(rest) - 1);  // farthest slot first
+                        rest &= ~(1u << i);
+                        const uint32_t meta = metaByte(n, i);
+                        const uint32_t k = ((imask >> i) & 1u) ? innerKey + meta : instKey + (meta >> 3);
+                        const unsigned long long e = ((unsigned long long)f2u(pick8(tmin, i)) << 32) | k;
+                        if (sp < WQ_SSTACK) q.sstack[sp][lane] = e;
+                        else stack[sp - WQ_SSTACK] = e;
+                        ++sp;
                     }
                 }
             }
