@@ -100,6 +100,16 @@ TDEV NodeRegs loadNodeShared(const WideNode* n) {
     return r;
 }
 
+// Byte i (0..7) of the eight child meta bytes of a node: one byte permute with the slot as its selector.
+TDEV uint32_t metaByte(const NodeRegs& n, int i) { return __byte_perm(n.b.z, n.b.w, (uint32_t)i) & 0xFFu; }
+// t[i] for a run time i out of eight registers (seven selects; an indexed array would be spilled to local memory)
+TDEV float pick8(const float t[8], int i) {
+    const bool b0 = (i & 1) != 0, b1 = (i & 2) != 0, b2 = (i & 4) != 0;
+    const float a0 = b0 ? t[1] : t[0], a1 = b0 ? t[3] : t[2], a2 = b0 ? t[5] : t[4], a3 = b0 ? t[7] : t[6];
+    const float c0 = b1 ? a1 : a0, c1 = b1 ? a3 : a2;
+    return b2 ? c1 : c0;
+}
+
 // Rays and results stream through once: keep them out of L1, which holds the nodes and triangles that are read again.
 #ifndef THEIA_STREAM_RAYS
 #define THEIA_STREAM_RAYS 1
