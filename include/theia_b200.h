@@ -508,6 +508,12 @@ int theia_hist_reduce(float *partials_dev, uint32_t n_hist, uint32_t n_bins, flo
  * queue (same SoA layout as theia_response_t.queue) to a response. */
 int theia_hit_replay(const uint32_t *queue_dev, uint32_t capacity, uint32_t polarized,
                      const theia_response_t *response, uint32_t block_size, void *stream);
+/* The same with the replay stage's optional random number generator (src/theia/response.py:278-422, HitReplay(rng=...)):
+ * hit k draws from stream k, first number first (sh/response.replay.glsl:37-38). rng may be NULL; the store time
+ * response needs one. */
+int theia_hit_replay_rng(const uint32_t *queue_dev, uint32_t capacity, uint32_t polarized,
+                         const theia_response_t *response, const theia_philox_params_t *rng,
+                         uint32_t block_size, void *stream);
 
 /* ------------------------------------------------------------------ device math test seam
  * Evaluates the library's deterministic float math on the device (fn: 0 sin, 1 cos, 2 exp,

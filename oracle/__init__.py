@@ -54,6 +54,7 @@ def lib() -> ctypes.CDLL:
         for fn in ("orc_target_intersect", "orc_guide_eval"):
             getattr(l, fn).argtypes = [POINTER(_abi.Component), c_void_p, c_void_p, c_uint32, c_void_p]
         l.orc_hit_replay.argtypes = [c_void_p, c_uint32, c_uint32, POINTER(_abi.Response), c_uint32]
+        l.orc_hit_replay_rng.argtypes = [c_void_p, c_uint32, c_uint32, POINTER(_abi.Response), c_void_p, c_uint32]
         _lib = l
     return _lib
 
@@ -274,8 +275,9 @@ def runReplay(replay, i: int = 0) -> None:
         cmd()
     nBlocks = -(replay.capacity // -replay.blockSize)
     r = replay.response._abiResponse(i, nBlocks)
-    rc = lib().orc_hit_replay(replay.queue.tensor.data_ptr(), replay.capacity, int(replay.polarized), byref(r),
-                              replay.blockSize)
+    rng = replay.rng._abiParams(i) if replay.rng is not None else None
+    rc = lib().orc_hit_replay_rng(replay.queue.tensor.data_ptr(), replay.capacity, int(replay.polarized), byref(r),
+                                  ctypes.addressof(rng) if rng is not None else None, replay.blockSize)
     if rc != 0:
         raise RuntimeError(f"oracle replay error {rc}")
     resp = replay.response

@@ -286,21 +286,25 @@ int orc_hist_reduce(float* partials, uint32_t nHist, uint32_t nBins, float norm,
 }
 
 // sh/response.replay.glsl:35-50
-int orc_hit_replay(const uint32_t* queue, uint32_t capacity, uint32_t polarized, const theia_response_t* response,
-                   uint32_t block_size) {
-    if (response->kind == THEIA_RESPONSE_STORE_TIME) return -3;
+// rng may be null ("optional RNG", :8-9): responses that draw (store time) need one. Hit k uses stream k from its
+// first draw (idx = gl_GlobalInvocationID.x, dim = 0, :37-38).
+int orc_hit_replay_rng(const uint32_t* queue, uint32_t capacity, uint32_t polarized, const theia_response_t* response,
+                       const theia_philox_params_t* rng, uint32_t block_size) {
+    if (response->kind == THEIA_RESPONSE_STORE_TIME && !rng) return -3;
     theia_trace_launch_t L{};
     L.response = *response;
     uint32_t count = queue[0] < capacity ? queue[0] : capacity;
     uint32_t bs = block_size ? block_size : 128;
     uint32_t nChunks = (capacity + bs - 1) / bs;
     std::vector<TaggedHit> all;
+    std::vector<Sink::TimeHit> times;
     for (uint32_t c = 0; c < nChunks; ++c) {
         Sink sink(&L);
         for (uint32_t k = c * bs; k < (c + 1) * bs && k < count; ++k) {
-            Rng none{nullptr, k, 0u};  // a replay has no random number stream
-            sink.response(loadHit(queue, capacity, polarized != 0, k), none);
+            Rng stream{rng, k, 0u};
+            sink.response(loadHit(queue, capacity, polarized != 0, k), stream);
         }
+        for (auto& t : sink.times) times.push_back(t);
         if (Sink::hasHistogram(response->kind)) {
             float* dst = response->hist_partials + (size_t)(c % response->hist_capacity) * response->n_bins;
             for (uint32_t b = 0; b < response->n_bins; ++b) dst[b] += sink.hist[b];
@@ -316,7 +320,24 @@ int orc_hit_replay(const uint32_t* queue, uint32_t capacity, uint32_t polarized,
         }
         response->queue[0] = n;
     }
+    if (response->kind == THEIA_RESPONSE_STORE_TIME) {  // sh/response.time.store.glsl:4-10 (count, time[], objectId[])
+        uint32_t n = response->value_queue[0];
+        float* time = (float*)(response->value_queue + 1);
+        int32_t* ids = (int32_t*)(response->value_queue + 1) + response->value_capacity;
+        for (auto& h : times) {
+            if (n < response->value_capacity) {
+                time[n] = h.time;
+                if (response->store_object_id) ids[n] = h.objectId;
+            }
+            ++n;
+        }
+        response->value_queue[0] = n;
+    }
     return 0;
+}
+int orc_hit_replay(const uint32_t* queue, uint32_t capacity, uint32_t polarized, const theia_response_t* response,
+                   uint32_t block_size) {
+    return orc_hit_replay_rng(queue, capacity, polarized, response, nullptr, block_size);
 }
 
 }  // extern "C"

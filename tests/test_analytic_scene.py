@@ -6,6 +6,8 @@ MIS with a target guide -> response), ported with its scenes, parameters and tol
   tests/test_trace_energy.py:187-337  test_SceneForwardTracer_Crosscheck    target guide (MIS) against brute force, 2 % / 1 %
   tests/test_trace_energy.py:479-568  test_SceneForwardTracer_MultiMedia    nested media, reflection + transmission, 0.61 %
   tests/test_trace.py:1122-1193       test_volumeBorder                     no refraction at a volume border, group index
+  tests/test_trace_energy.py:1341-1461 test_ScenePhotonTracer               photon counts against the forward tracer, 5 sigma
+  tests/test_trace_energy.py:1464-1580 test_VolumePhotonTracer              the same for the volume tracers
 
 Each runs on the CPU oracle (pinning the restatement; "not gpu" suite, reduced statistics with the tolerance widened
 by the statistics only where the reference's bound is a statistical one) and on the CUDA path (-m gpu, at the
@@ -205,3 +207,92 @@ def test_volumeBorder(device):
     n2_exp = material.speed_of_light / model.group_velocity(LAMBDA)
     assert np.abs(n1 - 1.0).max() < 5e-5
     assert np.abs(n2 - n2_exp).max() < 5e-5
+
+
+PHOTON_CASES = [(0.0, 0.05, 0.0, False), (0.05, 0.05, 0.0, False), (0.05, 0.01, -0.9, False), (0.05, 0.01, 0.9, False),
+                (0.05, 0.01, -0.9, True)]  # (the reference leaves (0.0, 0.05, 0.0, True) out: "polarization seems broken")
+
+
+def _photonAgainstForward(device, makeForward, makePhoton, mu_a, budget, batch_size, n_batches):
+    """The forward tracer's light curve, summed, is the number of photons the photon tracer must detect (5 sigma)."""
+    hist_tracer, hist_response, rng = makeForward()
+    rng.autoAdvance = hist_tracer.nRNGSamples
+    hists = []
+    runBatches(hist_tracer, n_batches, lambda i: hists.append(np.array(hist_response.result(i), dtype=np.float64)))
+    per_batch = np.array([h.sum() for h in hists])
+    exp_hits = per_batch.mean()
+    tracer, resp = makePhoton(rng)
+    H.runAny({"tracer": tracer, "response": resp, "callback": tracer.callback, "rng": rng})
+    hits = resp.result(0)
+    assert hits is not None
+    print(f"photon tracer {hits.count} hits, forward tracer expects {exp_hits:.1f}")
+    if mu_a != 0.0:
+        # the reference's bound; at the reduced statistics of the oracle run the error of the forward estimate itself
+        # (standard error over its batches) is not negligible next to it
+        slack = 0.0 if device == "cuda" else 4.0 * per_batch.std(ddof=1) / np.sqrt(len(per_batch))
+        assert np.abs(hits.count - exp_hits) < 5.0 * np.sqrt(exp_hits) + slack
+    else:
+        assert hits.count == int(budget)  # no absorption: every photon is recovered
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("mu_a,mu_s,g,polarized", PHOTON_CASES)
+def test_ScenePhotonTracer(device, mu_a, mu_s, g, polarized):
+    position, radius = (12.0, 15.0, 0.2), 60.0 * u.m
+    t0, lam = 10.0 * u.ns, 400.0 * u.nm
+    budget, batch_size, n_batches = (1e6, 1024 * 1024, 20) if device == "cuda" else (1e5, 32 * 1024, 8)
+    with _device.useDevice(device):
+        model = H.EnergyModel(mu_a, mu_s, g)
+        medium = model.createMedium()
+        matStore = material.MaterialStore([material.Material("det", medium, None, flags="DB")])
+        meshStore = scene.MeshStore({"sphere": SPHERE})
+        det = meshStore.createInstance("sphere", "det", scene.Transform.TRS(scale=radius, translate=position), detectorId=0)
+        sc = scene.Scene([det], matStore.material, medium=matStore.media[medium.name])
+        photons = light.UniformWavelengthSource(lambdaRange=(lam, lam))
+        src = light.SphericalLightSource(position=position, timeRange=(t0, t0), budget=budget)
+
+        def makeForward():
+            rng = random.PhiloxRNG(key=0xC01DC0FFEE)
+            hist = response.HistogramHitResponse(response.UniformValueResponse(), binSize=50.0 * u.ns, nBins=400)
+            tr = trace.SceneForwardTracer(batch_size, src, photons, hist, rng, sc, maxPathLength=80, scatterCoefficient=0.05,
+                                          maxTime=float("inf"), polarized=polarized)
+            return tr, hist, rng
+
+        def makePhoton(rng):
+            resp = response.StoreTimeHitResponse(response.UniformValueResponse())
+            tr = trace.ScenePhotonTracer(int(budget), src, photons, resp, rng, sc, nScatteringPerRun=5, nRuns=20,
+                                         maxTime=float("inf"), polarized=polarized, callback=trace.EventStatisticCallback())
+            return tr, resp
+
+        _photonAgainstForward(device, makeForward, makePhoton, mu_a, budget, batch_size, n_batches)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("mu_a,mu_s,g,polarized", PHOTON_CASES)
+def test_VolumePhotonTracer(device, mu_a, mu_s, g, polarized):
+    position, radius = (12.0, 15.0, 0.2), 60.0 * u.m
+    t0, lam = 10.0 * u.ns, 400.0 * u.nm
+    budget, batch_size, n_batches = (1e6, 1024 * 1024, 20) if device == "cuda" else (1e5, 32 * 1024, 8)
+    with _device.useDevice(device):
+        model = H.EnergyModel(mu_a, mu_s, g)
+        medium = model.createMedium()
+        store = material.MaterialStore([], media=[medium])
+        photons = light.UniformWavelengthSource(lambdaRange=(lam, lam))
+        src = light.SphericalLightSource(position=position, timeRange=(t0, t0), budget=budget)
+        tgt = target.InnerSphereTarget(position=position, radius=radius)
+
+        def makeForward():
+            rng = random.PhiloxRNG(key=0xC0FFEE)
+            hist = response.HistogramHitResponse(response.UniformValueResponse(), binSize=50.0 * u.ns, nBins=400)
+            tr = trace.VolumeForwardTracer(batch_size, src, tgt, photons, hist, rng, medium=store.media[medium.name],
+                                           maxTime=float("inf"), nScattering=80, scatterCoefficient=0.05, polarized=polarized)
+            return tr, hist, rng
+
+        def makePhoton(rng):
+            resp = response.StoreTimeHitResponse(response.UniformValueResponse())
+            tr = trace.VolumePhotonTracer(int(budget), src, tgt, photons, resp, rng, medium=store.media[medium.name],
+                                          nScatteringPerRun=5, nRuns=40, maxTime=float("inf"), polarized=polarized,
+                                          callback=trace.EventStatisticCallback())
+            return tr, resp
+
+        _photonAgainstForward(device, makeForward, makePhoton, mu_a, budget, batch_size, n_batches)

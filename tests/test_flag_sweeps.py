@@ -3,6 +3,9 @@ The flag sweeps of the reference's tracer tests, ported with their scenes and as
   tests/test_trace.py:82-212   test_VolumeForwardTracer       2^5 combinations
   tests/test_trace.py:335-457  test_SceneForwardTracer        2^7 combinations
   tests/test_trace.py:460-518  test_SceneForwardTracer_multiTarget
+  tests/test_trace.py:947-1046 test_EventStatisticCallback    every result code of a scene with all material kinds
+  tests/test_trace.py:1048-1119 test_TrackRecordCallback
+  tests/test_trace.py:1466-1561 test_ScenePhotonTracer, :1563-1654 test_VolumePhotonTracer
 Every combination runs on the CPU oracle ("not gpu" suite) and on the CUDA path (-m gpu).
 """
 
@@ -175,3 +178,139 @@ def test_SceneForwardTracer_multiTarget(device):
     assert np.all((r_hits <= 1.0 + 1e-6) & (r_hits >= R_SCALE - 1e-6))
     assert np.allclose(np.square(hits["normal"]).sum(-1), 1.0)
     assert (hits["objectId"] == 0).sum() > 0 and (hits["objectId"] == 1).sum() > 0
+
+
+@pytest.mark.parametrize("device", DEVICES)
+def test_EventStatisticCallback(device):
+    N, T0, T1 = 32 * 1024, 10.0 * u.ns, 20.0 * u.ns
+    with _device.useDevice(device):
+        water = WaterTestModel().createMedium()
+        glass = material.BK7Model().createMedium()
+        matStore = material.MaterialStore([material.Material("mat", glass, water, flags=("DR", "B")),
+                                           material.Material("vol", glass, water, flags="V"),
+                                           material.Material("abs", glass, water, flags="B")])
+        store = scene.MeshStore({"sphere": os.path.join(H.ASSETS, "sphere.stl")})
+        r = 20.0
+        inst = [store.createInstance("sphere", "mat", scene.Transform.TRS(scale=r, translate=(17.0, 17.0, 17.0)), detectorId=0),
+                store.createInstance("sphere", "mat", scene.Transform.TRS(scale=r, translate=(-17.0, -17.0, -17.0)), detectorId=1),
+                store.createInstance("sphere", "vol", scene.Transform.TRS(scale=r, translate=(17.0, 17.0, -17.0))),
+                store.createInstance("sphere", "abs", scene.Transform.TRS(scale=r, translate=(-17.0, 17.0, 17.0)))]
+        bbox = scene.RectBBox((-50.0,) * 3, (50.0,) * 3)
+        sc = scene.Scene(inst, matStore.material, medium=matStore.media["water"], bbox=bbox)
+        sc._keepAlive = (matStore, store)
+        rng = random.PhiloxRNG(key=0xC01DC0FFEE)
+        stats = trace.EventStatisticCallback()
+        tracer = trace.SceneForwardTracer(N, light.SphericalLightSource(timeRange=(T0, T1)), light.UniformWavelengthSource(),
+                                          response.EmptyResponse(), rng, callback=stats, scene=sc, targetId=1, maxPathLength=1,
+                                          scatterCoefficient=0.005 / u.m, maxTime=100.0 * u.ns)
+        names = ("created", "absorbed", "hit", "detected", "scattered", "lost", "decayed", "volume", "maxIter", "error", "mismatch")
+        assert all(getattr(stats, n) == 0 for n in names)  # starts empty
+        run(tracer)
+        assert stats.created == N
+        for n in ("absorbed", "hit", "detected", "scattered", "lost", "decayed", "volume", "maxIter"):
+            assert getattr(stats, n) > 0, n
+        assert stats.error == 0 and stats.mismatch == 0
+        total = stats.absorbed + stats.hit + stats.detected + stats.scattered + stats.lost + stats.decayed + stats.volume
+        assert total == N
+        stats.reset()
+        assert all(getattr(stats, n) == 0 for n in names)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("polarized", BOOL)
+@pytest.mark.parametrize("polarizedTrack", BOOL)
+def test_TrackRecordCallback(device, polarizedTrack, polarized):
+    N, N_SCATTER = 32 * 256, 6
+    LENGTH = N_SCATTER + 2  # one more than needed
+    T0, T1, T_MAX = 10.0 * u.ns, 20.0 * u.ns, 500.0 * u.ns
+    target_pos, target_radius = (5.0, 2.0, -8.0), 4.0 * u.m
+    light_pos, light_dir = (100.0, -50.0, 20.0), (1.0, 0.0, 0.0)
+    stokes, polRef = (1.0, 0.5, 0.1, 0.4), (0.0, 1.0, 0.0)
+    with _device.useDevice(device):
+        water = WaterTestModel().createMedium()
+        store = material.MaterialStore([], media=[water])
+        rng = random.PhiloxRNG(key=0xC01DC0FFEE)
+        source = light.PencilLightSource(position=light_pos, direction=light_dir, timeRange=(T0, T1), stokes=stokes,
+                                         polarizationRef=polRef)
+        track = trace.TrackRecordCallback(N, LENGTH, polarized=polarizedTrack)
+        tracer = trace.VolumeForwardTracer(N, source, target.SphereTarget(position=target_pos, radius=target_radius),
+                                           light.UniformWavelengthSource(), response.EmptyResponse(), rng, callback=track,
+                                           medium=store.media["water"], nScattering=N_SCATTER, scatterCoefficient=0.1,
+                                           maxTime=T_MAX, traceBBox=scene.RectBBox((-200.0 * u.m,) * 3, (200.0 * u.m,) * 3),
+                                           polarized=polarized)
+        run(tracer)
+        tracks, lengths, codes = track.result(0)
+    assert tracks.shape == (N, LENGTH, 11 if polarizedTrack else 4)
+    assert np.all(tracks[:, 0, :3] == light_pos)
+    assert tracks[:, 0, 3].min() >= T0 and tracks[:, 0, 3].max() <= T1
+    # pencil beam in x direction: y and z of the first scatter are still deterministic
+    assert np.all(tracks[:, 1, 1] == light_pos[1]) and np.all(tracks[:, 1, 2] == light_pos[2])
+    assert lengths.min() >= 1 and lengths.max() <= N_SCATTER
+    assert codes.min() >= min(c.value for c in trace.EventResultCode)
+    assert codes.max() <= max(c.value for c in trace.EventResultCode)
+    if polarizedTrack and polarized:
+        assert np.isclose(tracks[:, 0, 4:8], stokes).all()  # only the first state is known
+        assert np.isclose(tracks[:, 0, 8:], polRef).all()
+    elif polarizedTrack:
+        assert np.isclose(tracks[:, 0, 4:], (1.0, *(0.0,) * 6)).all()  # unpolarised with zero reference
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("polarized", BOOL)
+def test_ScenePhotonTracer(device, polarized):
+    N, N_RUNS, N_SCATTER = 32 * 256, 5, 5
+    T0, T1, T_MAX = 10.0 * u.ns, 20.0 * u.ns, 1.0 * u.ms
+    with _device.useDevice(device):
+        water, sc, _, _ = sweepScene(device)
+        rng = random.PhiloxRNG(key=0xC01DC0FFEE)
+        source = light.SphericalLightSource(position=(-1.0, -7.0, 0.0), timeRange=(T0, T1), budget=float(N))
+        recorder = response.HitRecorder(polarized=polarized)
+        stats = trace.EventStatisticCallback()
+        tracer = trace.ScenePhotonTracer(N, source, light.UniformWavelengthSource(), recorder, rng, sc, capacity=48 * 256,
+                                         targetId=-1, nRuns=N_RUNS, nScatteringPerRun=N_SCATTER, maxTime=T_MAX, callback=stats,
+                                         polarized=polarized)
+        run(tracer)
+        hits = recorder.queue.view(0)
+        assert 0 < hits.count <= tracer.maxHits
+        hits = hits[: hits.count]
+        assert stats.created == N
+    r_hits = np.sqrt(np.square(hits["position"]).sum(-1))
+    assert np.all((r_hits <= 1.0 + 1e-6) & (r_hits >= R_SCALE - 1e-6))
+    assert np.allclose(np.square(hits["normal"]).sum(-1), 1.0)
+    assert np.max(hits["time"]) <= T_MAX
+    assert (hits["objectId"] == 0).sum() > 0 and (hits["objectId"] == 1).sum() > 0
+    if polarized:
+        checkPolarization(hits)
+
+
+@pytest.mark.parametrize("device", DEVICES)
+@pytest.mark.parametrize("polarized", BOOL)
+def test_VolumePhotonTracer(device, polarized):
+    N, N_RUNS, N_SCATTER = 32 * 256, 5, 5
+    T0, T1 = 10.0 * u.ns, 20.0 * u.ns
+    objectId, light_pos = 42, (-1.0, -7.0, 0.0)
+    target_pos, target_radius = (5.0, 2.0, -8.0), 4.0 * u.m
+    with _device.useDevice(device):
+        water = WaterTestModel().createMedium()
+        store = material.MaterialStore([], media=[water])
+        d_min = np.sqrt(np.square(np.subtract(light_pos, target_pos)).sum(-1)) - target_radius
+        t_min = d_min / np.max(water.group_velocity) + T0
+        rng = random.PhiloxRNG(key=0xC01DC0FFEE)
+        source = light.SphericalLightSource(position=light_pos, budget=1000.0, timeRange=(T0, T1))
+        recorder = response.HitRecorder(polarized=polarized)
+        stats = trace.EventStatisticCallback()
+        tracer = trace.VolumePhotonTracer(N, source, target.SphereTarget(position=target_pos, radius=target_radius),
+                                          light.UniformWavelengthSource(), recorder, rng, medium=store.media["water"],
+                                          objectId=objectId, capacity=48 * 256, nRuns=N_RUNS, nScatteringPerRun=N_SCATTER,
+                                          maxTime=float("inf"), callback=stats, polarized=polarized)
+        run(tracer)
+        hits = recorder.queue.view(0)
+        assert 0 < hits.count <= N
+        hits = hits[: hits.count]
+        assert stats.created == N
+    assert np.allclose(np.square(hits["position"]).sum(-1), 1.0)
+    assert np.allclose(np.square(hits["normal"]).sum(-1), 1.0)
+    assert np.min(hits["time"]) >= t_min
+    assert np.allclose(hits["objectId"], objectId)
+    if polarized:
+        checkPolarization(hits)

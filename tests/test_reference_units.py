@@ -508,6 +508,70 @@ def test_sphereTarget(backend):  # tests/test_target.py:166-203
     assert np.allclose(hn, r["hitNrm"][hitMask])
 
 
+def _planeTargetChecks(r, o2w, inside, area, N):
+    """shared part of tests/test_target.py:16-122 (disk / flat): sample on the plane, ray / plane hit, probabilities"""
+    w2o = o2w.inverse()
+    objObs = w2o.apply(r["observer"])
+    objDir = w2o.applyVec(r["direction"])
+    nrm = np.zeros((N, 3))
+    nrm[:, 2] = np.sign(objObs[:, 2])
+    nrm = o2w.applyVec(nrm)
+    expSampleValid = np.abs(objObs[:, 2]) > 1e-6  # should be close enough
+    assert np.all((r["sampleValid"] != 0) == expSampleValid)
+    assert np.all(r["sampleError"][expSampleValid] == 0)
+    assert np.allclose(r["sampleNrm"][expSampleValid], nrm[expSampleValid], atol=1e-6)
+    objPos = w2o.apply(r["samplePos"])
+    assert np.all(inside(objPos[expSampleValid][:, :2]))
+    assert np.abs(objPos[expSampleValid][:, 2]).max() < 2e-6
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t = -objObs[:, 2] / objDir[:, 2]
+    objHit = objObs + objDir * t[:, None]
+    hit = (t > 0) & inside(objHit[:, :2]) & expSampleValid
+    wHit = o2w.apply(objHit)
+    assert hit.sum() > 0  # otherwise the tests make no sense
+    # float32 against float64 on the rim: points within 1e-5 of the edge may fall on either side
+    rim = np.abs(np.where(hit, 0.0, 1.0) - np.where((t > 0) & inside(objHit[:, :2] * (1.0 + 1e-5)) & expSampleValid, 0.0, 1.0)) > 0
+    rim |= np.abs(np.where(hit, 0.0, 1.0) - np.where((t > 0) & inside(objHit[:, :2] * (1.0 - 1e-5)) & expSampleValid, 0.0, 1.0)) > 0
+    assert rim.sum() < 8
+    assert np.all(((r["hitValid"] != 0) == hit)[~rim])
+    hit = hit & ~rim
+    assert np.allclose(r["hitPos"][hit], wHit[hit], atol=2e-5)
+    assert np.all(r["hitError"][hit] == 0)
+    assert np.allclose(r["hitNrm"][hit], nrm[hit], atol=1e-6)
+    assert np.allclose(r["sampleProb"][expSampleValid], 1.0 / area)
+    assert np.allclose(r["hitProb"][hit], 1.0 / area)
+
+
+def test_diskTarget(backend):  # tests/test_target.py:16-67
+    from theia_b200 import random, target
+    from theia_b200.scene import Transform
+    from theia_b200.testing import TargetSampler
+    N = 32 * 256
+    radius, position, normal, up = 12.0 * u.m, (5.0, -2.0, 3.0), (-1.0, 2.0, 0.0), (1.0, 1.0, 1.0)
+    o2w = Transform.View(position=position, direction=normal, up=up)
+    with device(backend):
+        tgt = target.DiskTarget(position=position, radius=radius, normal=normal, up=up)
+        philox = random.PhiloxRNG(key=0xC0FFEE)
+        sampler = TargetSampler(N, tgt, rng=philox)
+    runSampler(backend, sampler)
+    _planeTargetChecks(sampler.getResults(0), o2w, lambda xy: np.square(xy).sum(-1) <= radius**2, np.pi * radius**2, N)
+
+
+def test_flatTarget(backend):  # tests/test_target.py:70-122
+    from theia_b200 import random, target
+    from theia_b200.scene import Transform
+    from theia_b200.testing import TargetSampler
+    N = 32 * 256
+    width, length, position, normal, up = 12.0 * u.m, 18.0 * u.m, (5.0, -2.0, 3.0), (-1.0, 2.0, 0.0), (1.0, 1.0, 1.0)
+    o2w = Transform.View(position=position, direction=normal, up=up)
+    with device(backend):
+        tgt = target.FlatTarget(width=width, length=length, position=position, direction=normal, up=up)
+        philox = random.PhiloxRNG(key=0xC0FFEE)
+        sampler = TargetSampler(N, tgt, rng=philox)
+    runSampler(backend, sampler)
+    _planeTargetChecks(sampler.getResults(0), o2w, lambda xy: (2.0 * np.abs(xy) <= (width, length)).min(-1), width * length, N)
+
+
 def intersectSphere(center, rad, pos, dir):
     """near hit, far hit, hit mask (tests/test_target_guide.py:13-26; Ray Tracing Gems ch. 7)"""
     f = pos - center
@@ -550,6 +614,71 @@ def test_sphereTargetGuide(backend):  # tests/test_target_guide.py:37-72
     assert np.all((r["evalProb"] > 0.0) == valid)
     assert np.all(r["evalDist"][valid] >= t2[valid])
     assert np.allclose(r["evalProb"][valid], prob[valid])
+
+
+def _planeGuideChecks(r, o2w, normal, inside, area, *, distSlack, rtolSample):
+    """shared part of tests/test_target_guide.py:75-185 (disk / flat guide)"""
+    w2o = o2w.inverse()
+    objObs = w2o.apply(r["observer"])
+    valid = objObs[:, 2] > 0.0
+    assert np.all((r["sampleProb"] > 0.0) == valid)
+    assert np.all((r["sampleProb"] == 0.0) != valid)
+    objDir = w2o.applyVec(r["sampleDir"])
+    with np.errstate(divide="ignore", invalid="ignore"):
+        tHit = -objObs[:, 2] / objDir[:, 2]
+    assert np.all(tHit[valid] > 0.0)
+    assert (r["sampleDist"] - tHit)[valid].min() >= -distSlack  # small error is fine
+    objHit = objObs + objDir * tHit[:, None]
+    assert np.all(inside(objHit[valid][:, :2] * (1.0 - 1e-5)))
+    nrm = np.array(normal, dtype=np.float64)
+    nrm /= np.sqrt(np.square(nrm).sum())
+    cosNrm = np.abs(np.multiply(r["sampleDir"], nrm[None, :]).sum(-1))
+    prob = 1.0 / area * (tHit**2) / cosNrm
+    assert np.allclose(r["sampleProb"][valid], prob[valid], rtol=rtolSample)
+    objDir = w2o.applyVec(r["evalDir"])
+    with np.errstate(divide="ignore", invalid="ignore"):
+        tHit = -objObs[:, 2] / objDir[:, 2]
+    objHit = objObs + objDir * tHit[:, None]
+    rim = inside(objHit[:, :2] * (1.0 + 1e-5)) != inside(objHit[:, :2] * (1.0 - 1e-5))  # float32 vs float64 on the edge
+    valid = valid & (tHit > 0.0) & inside(objHit[:, :2])
+    assert valid.sum() > 0 and rim.sum() < 8
+    assert (r["evalDist"] - tHit)[valid & ~rim].min() >= -1e-5
+    assert np.all(r["evalProb"][~valid & ~rim] == 0.0)
+    cosNrm = np.abs(np.multiply(r["evalDir"], nrm[None, :]).sum(-1))
+    prob = 1.0 / area * (tHit**2) / cosNrm
+    assert np.allclose(r["evalProb"][valid & ~rim], prob[valid & ~rim])
+
+
+def test_diskTargetGuide(backend):  # tests/test_target_guide.py:75-126
+    from theia_b200 import random, target
+    from theia_b200.scene import Transform
+    from theia_b200.testing import TargetGuideSampler
+    N = 32 * 256
+    radius, position, normal = 12.0 * u.m, (5.0, -2.0, 3.0), (-1.0, 2.0, 0.0)
+    o2w = Transform.View(position=position, direction=normal)
+    with device(backend):
+        guide = target.DiskTargetGuide(position=position, radius=radius, normal=normal)
+        philox = random.PhiloxRNG(key=0xC0FFEE)
+        sampler = TargetGuideSampler(N, guide, rng=philox)
+    runSampler(backend, sampler)
+    _planeGuideChecks(sampler.getResults(0), o2w, normal, lambda xy: np.square(xy).sum(-1) <= radius**2, np.pi * radius**2,
+                      distSlack=0.02, rtolSample=2.5e-4)
+
+
+def test_flatTargetGuide(backend):  # tests/test_target_guide.py:129-185
+    from theia_b200 import random, target
+    from theia_b200.scene import Transform
+    from theia_b200.testing import TargetGuideSampler
+    N = 32 * 256
+    width, height, position, normal, up = 18.0 * u.m, 12.0 * u.m, (5.0, -2.0, 3.0), (-1.0, 2.0, 0.0), (1.0, 1.0, 1.0)
+    o2w = Transform.View(position=position, direction=normal, up=up)
+    with device(backend):
+        guide = target.FlatTargetGuide(width=width, height=height, position=position, normal=normal, up=up)
+        philox = random.PhiloxRNG(key=0xC0FFEE)
+        sampler = TargetGuideSampler(N, guide, rng=philox)
+    runSampler(backend, sampler)
+    _planeGuideChecks(sampler.getResults(0), o2w, normal, lambda xy: (2.0 * np.abs(xy) <= (width, height)).min(-1),
+                      width * height, distSlack=0.002, rtolSample=2e-4)
 
 
 # ------------------------------------------------------------------ tests/test_light.py (forward samplers)
@@ -815,3 +944,243 @@ def test_histogramResponse(backend, rng):  # tests/test_response.py:62-99
     bin_edge = np.arange(N_BINS + 1) * BIN_SIZE + T0
     exp_hist, _ = np.histogram(samples["time"], bin_edge, weights=samples["contrib"])
     assert np.allclose(result, exp_hist * NORM, rtol=1e-4)
+
+
+@pytest.mark.parametrize("storeObjectId", [True, False])
+def test_StoreTimeHitResponse(backend, rng, storeObjectId):  # tests/test_response.py:253-288
+    from theia_b200 import random, response
+    N = 32 * 256
+    with device(backend):
+        philox = random.PhiloxRNG(key=0xC0FFEE)
+        value = response.UniformValueResponse()
+        resp = response.StoreTimeHitResponse(value, storeObjectId=storeObjectId)
+        replay = response.HitReplay(N, resp, rng=philox)
+    samples = replay.queue.view(0)
+    _fillHits(samples, rng, N, False, contrib=rng.random((N,)))
+    samples["time"] = np.arange(N)  # use integers for better checking
+    samples["objectId"] = np.arange(N, dtype=np.int32)  # use same as time stamp
+    runReplay(backend, replay)
+    result = resp.result(0)
+    assert result is not None
+    # we expect about half the photons to be accepted (binomial: sigma = 0.0055)
+    assert abs(result.count / N - 0.5) < 0.02
+    # the random numbers drawn are lost: check that the sampled time stamps can be found in the input
+    time = result["time"][: result.count]
+    assert time.min() >= 0 and time.max() < N
+    assert len(np.unique(time)) == result.count
+    # a hit is kept when its draw is below its value: over all hits the kept ones carry the larger contributions
+    kept = np.zeros(N, dtype=bool)
+    kept[time.astype(np.int64)] = True
+    assert samples["contrib"][kept].mean() > 0.6 and samples["contrib"][~kept].mean() < 0.4
+    if storeObjectId:
+        assert np.all(time == result["objectId"][: result.count])
+    else:
+        assert "objectId" not in result.fields
+
+
+@pytest.mark.parametrize("useSharedMemory", [False, True])
+def test_kernelHistogramEstimator(backend, rng, useSharedMemory):  # tests/test_response.py:133-180
+    from scipy import stats
+    from theia_b200 import response
+    N, N_BINS, BIN_SIZE, T0 = 64 * 1024, 200, 1.2 * u.ns, 20.0 * u.ns
+    T1 = T0 + N_BINS * BIN_SIZE
+    T_PEAK = T0 + 0.3 * (T1 - T0)
+    BANDWIDTH, SUPPORT, NORM = 10.0 * u.ns, 50.0 * u.ns, 5e-4
+    with device(backend):
+        value = response.UniformValueResponse()
+        resp = response.KernelHistogramHitResponse(value, nBins=N_BINS, t0=T0, binSize=BIN_SIZE, kernelBandwidth=BANDWIDTH,
+                                                   kernelSupport=SUPPORT, normalization=NORM, useSharedMemory=useSharedMemory)
+        replay = response.HitReplay(N, resp)
+    samples = replay.queue.view(0)
+    _fillHits(samples, rng, N, False, contrib=np.zeros(N))
+    samples["time"] = rng.normal(T_PEAK, 10.0 * BIN_SIZE, (N,))
+    samples["contrib"] = rng.random((N,)) + np.sqrt(samples["time"])
+    runReplay(backend, replay)
+    x = np.arange(N_BINS + 1) * BIN_SIZE + T0
+    t = samples["time"].astype(np.float64)
+    v = samples["contrib"].astype(np.float64)
+    exp_result = np.zeros_like(x)
+    for lo in range(0, N, 4096):  # (the reference loops over the hits one by one)
+        exp_result += (v[lo:lo + 4096, None] * stats.norm.cdf(x[None, :], loc=t[lo:lo + 4096, None], scale=BANDWIDTH)).sum(0)
+    exp_result = np.diff(exp_result) * NORM
+    result = resp.result(0)
+    assert np.abs(result - exp_result).max() < 6e-4
+
+
+# ------------------------------------------------------------------ tests/test_light.py: host sources, function wavelength
+@pytest.mark.parametrize("polarized", [False, True])
+def test_hostLightSource(backend, rng, polarized):  # tests/test_light.py:23-72
+    from theia_b200 import light
+    N = 32 * 256
+    with device(backend):
+        photon = light.HostWavelengthSource(N)
+        source = light.HostLightSource(N, polarized=polarized)
+        sampler = light.LightSampler(source, photon, N, polarized=polarized)
+    rays, photons = source.queue.view(0), photon.queue.view(0)
+    cos_theta = 2.0 * rng.random(N) - 1.0
+    sin_theta = np.sqrt(1.0 - cos_theta**2)
+    phi = rng.random(N) * 2.0 * np.pi
+    rays["position"] = (rng.random((N, 3)) * 10.0 - 5.0) * u.m
+    rays["direction"] = np.stack([sin_theta * np.cos(phi), sin_theta * np.sin(phi), cos_theta], axis=-1)
+    lam = (rng.random((N,)) * 600.0 + 200.0) * u.nm
+    photons["wavelength"] = lam
+    photons["contrib"] = rng.random((N,)) + 5.0
+    rays["startTime"] = rng.random((N,)) * 50.0 * u.ns
+    rays["contrib"] = rng.random((N,)) + 1.0
+    if polarized:
+        rays["stokes"] = rng.random((N, 4))  # we do not care about valid values
+        rays["polarizationRef"] = rng.random((N, 3))
+    runSampler(backend, sampler)
+    lightResult, phResult = sampler.lightQueue.view(0), sampler.wavelengthQueue.view(0)
+    assert lightResult.count == N
+    for f in ("position", "direction", "startTime", "contrib") + (("stokes", "polarizationRef") if polarized else ()):
+        assert np.allclose(lightResult[f], rays[f]), f
+    assert np.allclose(phResult["contrib"], photons["contrib"])
+    assert np.allclose(phResult["wavelength"], lam)
+
+
+def test_HostSamplerMismatch(backend):  # tests/test_light.py:144-151
+    from theia_b200 import light
+    with device(backend):
+        photon = light.ConstWavelengthSource()
+        with pytest.raises(RuntimeError):
+            light.LightSampler(light.HostLightSource(128, polarized=True), photon, 128, polarized=False)
+        with pytest.raises(RuntimeError):
+            light.LightSampler(light.HostLightSource(128, polarized=False), photon, 128, polarized=True)
+
+
+def test_functionWavelength(backend):  # tests/test_light.py:197-231
+    from theia_b200 import light
+    N, lamRange = 256 * 1024, (300.0 * u.nm, 700.0 * u.nm)
+
+    def fn(lam):  # something fancy just for testing
+        x = lam / 1000
+        return -x * np.log(x)
+
+    def Fn(lam):  # its anti-derivative
+        x = lam / 1000
+        return 250.0 * x**2 * (1.0 - 2.0 * np.log(x))
+
+    _, _, result = _lightSampler(backend, lambda: light.PencilLightSource(timeRange=(0.0, 0.0)),
+                                 lambda: light.FunctionWavelengthSource(fn, lambdaRange=lamRange), N, key=0xC0FFEE)
+    exp_contrib = Fn(lamRange[1]) - Fn(lamRange[0])
+    assert np.allclose(result["contrib"], exp_contrib)
+    assert np.abs(np.min(result["wavelength"]) - lamRange[0]) < 1.0
+    assert np.abs(np.max(result["wavelength"]) - lamRange[1]) < 1.0
+    hist, edges = np.histogram(result["wavelength"], bins=40)
+    F = Fn(edges)
+    assert np.abs(hist / N - (F[1:] - F[:-1]) / exp_contrib).max() < 9e-4
+
+
+def _cherenkovChecks(samples, photons, photon, model, trackDirs, lengthFactor, usePhotons, polarized):
+    """shared checks of tests/test_light.py:453-518 and :599-676: cone angle, Frank-Tamm contribution, polarisation"""
+    from scipy import constants as c
+    cos_theta = np.multiply(samples["direction"], trackDirs).sum(-1)
+    lam = photons["wavelength"].ravel().astype(np.float64)
+    n = model.refractive_index(lam)
+    assert np.allclose(cos_theta, 1.0 / n)
+    contrib = 1.0 - (1.0 / n**2)
+    if usePhotons:
+        contrib *= 2.0 * np.pi * c.alpha * 1e9 / (lam**2)
+    else:
+        contrib *= np.pi * c.e * c.c**2 * c.mu_0 * 1e18 / (lam**3)
+    contrib *= lengthFactor  # 1 / p(position)
+    lam0, lam1 = photon.getParam("lambdaRange")
+    assert np.allclose(contrib, samples["contrib"].ravel())
+    assert np.allclose(photons["contrib"], abs(lam1 - lam0))
+    if polarized:
+        polRef_exp = np.cross(trackDirs, samples["direction"])
+        polRef_exp /= np.sqrt(np.square(polRef_exp).sum(-1))[:, None]
+        polRef = samples["polarizationRef"]
+        assert np.allclose(samples["stokes"], (1.0, 1.0, 0.0, 0.0))
+        assert np.abs(np.abs((polRef * polRef_exp).sum(-1)) - 1.0).max() < 1e-6
+        assert np.abs(np.square(polRef).sum(-1) - 1.0).max() < 1e-6
+        assert np.abs((polRef * samples["direction"]).sum(-1)).max() < 1e-6
+
+
+def _waterMedium(store):
+    from theia_b200 import material
+    from theia_b200.testing import WaterTestModel
+
+    def medium():
+        store["s"] = material.MaterialStore([], media=[WaterTestModel().createMedium()])
+        return store["s"].media["water"]
+    return medium
+
+
+@pytest.mark.parametrize("usePhotons", [False, True])
+@pytest.mark.parametrize("polarized", [True, False])
+def test_cherenkov_fwd(backend, usePhotons, polarized):  # tests/test_light.py:453-518
+    from theia_b200 import light
+    from theia_b200.testing import WaterTestModel
+    N = 32 * 256
+    dir = np.array([0.36, 0.48, 0.8])
+    dist = 200.0 * u.m
+    startPos, startT = -dir * 0.5 * dist, -0.5 * dist / u.c
+    endPos, endT = dir * 0.5 * dist, 0.5 * dist / u.c
+    keep = {}
+    source, samples, photons = _lightSampler(
+        backend, lambda: light.CherenkovLightSource(trackStart=startPos, trackEnd=endPos, startTime=startT, endTime=endT,
+                                                    usePhotonCount=usePhotons),
+        lambda: keep.setdefault("photon", light.UniformWavelengthSource(normalize=False)), N, key=0xC0FFEE,
+        polarized=polarized, medium=_waterMedium(keep))
+    distA = np.sqrt(np.square(samples["position"] - startPos).sum(-1))
+    distB = np.sqrt(np.square(samples["position"] - endPos).sum(-1))
+    assert np.allclose(distA + distB, dist)  # on the track
+    t = samples["startTime"].ravel()
+    assert np.all((t >= startT) & (t <= endT))
+    l = distA / dist
+    # (atol: l comes from float32 positions at +- 100 m, i.e. 2e-5 ns of error, which the reference's bare allclose only
+    # tolerates for |t| > 2 ns)
+    assert np.allclose(t, (1.0 - l) * startT + l * endT, atol=1e-4)
+    _cherenkovChecks(samples, photons, keep["photon"], WaterTestModel(), dir[None, :], dist, usePhotons, polarized)
+
+
+@pytest.mark.parametrize("usePhotons", [False, True])
+@pytest.mark.parametrize("polarized", [True, False])
+def test_cherenkovTrack(backend, usePhotons, polarized):  # tests/test_light.py:599-676
+    from theia_b200 import light
+    from theia_b200.testing import WaterTestModel
+    N = 32 * 256
+    vertices = np.array([[0.0, 0.0, 0.0, 0.0], [1.0, 0.0, 0.0, 20.0], [1.0, 1.0, 0.0, 35.0], [1.0, 1.0, 1.0, 60.0]])
+    trackDir = np.eye(3)
+    dt = np.array([20.0, 15.0, 25.0])
+    keep = {}
+
+    def makeLight():
+        keep["track"] = light.ParticleTrack(4)
+        keep["track"].setVertices(vertices)
+        return light.CherenkovTrackLightSource(keep["track"], usePhotonCount=usePhotons)
+
+    source, samples, photons = _lightSampler(
+        backend, makeLight, lambda: keep.setdefault("photon", light.UniformWavelengthSource(normalize=False)), N, key=0xC0FFEE,
+        polarized=polarized, medium=_waterMedium(keep))
+    assert np.all((samples["position"] >= 0.0) & (samples["position"] <= 1.0))
+    t = samples["startTime"].ravel()
+    assert np.all((t >= 0.0) & (t <= 60.0))
+    assert np.allclose(t, np.multiply(samples["position"], dt[None, :]).sum(-1))
+    segmentId = 2 - (samples["position"] == 0.0).sum(-1)
+    # (three segments of unit length: 1 / p(position) = 3)
+    _cherenkovChecks(samples, photons, keep["photon"], WaterTestModel(), trackDir[segmentId], 3.0, usePhotons, polarized)
+
+
+@pytest.mark.parametrize("n,cos_min,cos_max,a,b,beta", [[1.33, -1.0, 1.0, 0.39, 2.61, 1.0], [1.40, -1.0, -0.5, 0.41, 2.39, 0.9],
+                                                        [1.20, 0.8, 0.9, 0.44, 2.78, 1.0], [1.35, 0.1, 0.9, 0.41, 2.78, 0.7],
+                                                        [1.35, -0.1, 0.9, 0.41, 2.78, 1.0]])
+def test_trackAngularEmission_pdf(backend, n, cos_min, cos_max, a, b, beta):  # tests/test_light.py:679-718
+    from scipy import integrate
+    if backend != "oracle":
+        pytest.skip("host side only: the pdf the emission angle tests compare against")
+
+    def pdf(x):
+        cos_chev = 1.0 / (beta * n)
+        lower = (1.0 - np.exp(-b * np.abs(cos_chev - cos_min) ** a)) * np.sign(cos_min - cos_chev)
+        upper = (1.0 - np.exp(-b * np.abs(cos_chev - cos_max) ** a)) * np.sign(cos_max - cos_chev)
+        y = np.abs(x - cos_chev)
+        return np.exp(-b * y**a) * y ** (a - 1) * a * b / np.abs(upper - lower)
+
+    cos_chev = 1.0 / (beta * n)
+    points = [cos_chev] if cos_min < cos_chev < cos_max else None
+    est = integrate.quad(pdf, cos_min, cos_max, points=points, limit=200)[0]
+    assert np.abs(est - 1.0) < 5e-4
+    assert np.all(pdf(np.linspace(cos_min, cos_max, 500)) >= 0.0)

@@ -46,6 +46,7 @@ SYMBOLS = {
     "theia_trace_forward": (c_int, [POINTER(_abi.TraceLaunch)]),
     "theia_hist_reduce": (c_int, [c_void_p, c_uint32, c_uint32, c_float, c_void_p, c_int, c_void_p]),
     "theia_hit_replay": (c_int, [c_void_p, c_uint32, c_uint32, POINTER(_abi.Response), c_uint32, c_void_p]),
+    "theia_hit_replay_rng": (c_int, [c_void_p, c_uint32, c_uint32, POINTER(_abi.Response), c_void_p, c_uint32, c_void_p]),
     "theia_math_eval": (c_int, [c_uint32, c_void_p, c_void_p, c_uint32, c_void_p, c_void_p]),
     "theia_unit_widths": (c_int, [c_uint32, c_uint32, POINTER(c_uint32), POINTER(c_uint32)]),
     "theia_unit_eval": (c_int, [POINTER(_abi.UnitArgs)]),

@@ -169,8 +169,10 @@ __global__ void histReduceKernel(float* partials, uint32_t nHist, uint32_t nBins
     out[b] = result * norm;
 }
 // sh/response.replay.glsl:35-50
+// hasRng != 0: hit k draws from stream k, starting at its first number (idx = gl_GlobalInvocationID.x, dim = 0, :37-38)
 __global__ void __launch_bounds__(128) hitReplayKernel(const uint32_t* queue, uint32_t capacity, uint32_t polarized,
-                                                       ResponseDev r) {
+                                                       ResponseDev r, const __grid_constant__ theia_philox_params_t rngParams,
+                                                       uint32_t hasRng) {
     extern __shared__ float sharedHist[];
     if (responseHasHistogram(r.kind) && r.hist_shared)
         for (uint32_t b = threadIdx.x; b < r.n_bins; b += blockDim.x) sharedHist[b] = 0.0f;
@@ -187,7 +189,12 @@ __global__ void __launch_bounds__(128) hitReplayKernel(const uint32_t* queue, ui
         item.contrib = 0.0f; item.time = 0.0f;
         if (has) item = loadHit(queue, capacity, polarized != 0, k);
         // response(hit) without the "contrib > 0" test of the tracers' call sites (sh/response.replay.glsl:46-47)
-        commitHitImpl<true, false>(r, hist, has, item, k, 0u, 2.0f);
+        float u = 2.0f;
+        if (hasRng && has && r.kind == THEIA_RESPONSE_STORE_TIME) {
+            Rng rng = makeRng(&rngParams, k);
+            u = rng.next();
+        }
+        commitHitImpl<true, false>(r, hist, has, item, k, 0u, u);
     }
     __syncthreads();
     if (responseHasHistogram(r.kind) && r.hist_shared) {
@@ -837,22 +844,29 @@ int theia_hist_reduce(float* partials_dev, uint32_t n_hist, uint32_t n_bins, flo
     return 0;
 }
 
-int theia_hit_replay(const uint32_t* queue_dev, uint32_t capacity, uint32_t polarized, const theia_response_t* response,
-                     uint32_t block_size, void* stream) {
+int theia_hit_replay_rng(const uint32_t* queue_dev, uint32_t capacity, uint32_t polarized, const theia_response_t* response,
+                         const theia_philox_params_t* rng, uint32_t block_size, void* stream) {
     (void)block_size;
     if (!queue_dev || !response) { setError("theia_hit_replay: null argument"); return -1; }
     ResponseDev r;
     if (fillResponse(*response, r)) return -1;
-    if (r.kind == THEIA_RESPONSE_STORE_TIME) { setError("theia_hit_replay: the store time response needs a random number stream, which a replay does not have"); return -1; }
+    if (r.kind == THEIA_RESPONSE_STORE_TIME && !rng) { setError("theia_hit_replay: the store time response needs a random number stream (theia_hit_replay_rng)"); return -1; }
+    theia_philox_params_t rp;
+    memset(&rp, 0, sizeof(rp));
+    if (rng) rp = *rng;
     if (capacity == 0) return 0;
     size_t smem = (responseHasHistogram(r.kind) && r.hist_shared) ? (size_t)r.n_bins * 4 : 0;
     uint32_t grid = blocksFor(capacity, 128);
     if (responseHasHistogram(r.kind) && grid > r.hist_capacity) grid = r.hist_capacity;
     if (grid > 148 * 8) grid = 148 * 8;
-    hitReplayKernel<<<grid, 128, smem, (cudaStream_t)stream>>>(queue_dev, capacity, polarized, r);
+    hitReplayKernel<<<grid, 128, smem, (cudaStream_t)stream>>>(queue_dev, capacity, polarized, r, rp, rng ? 1u : 0u);
     countLaunches(1);
     CUDA_TRY(cudaGetLastError());
     return 0;
+}
+int theia_hit_replay(const uint32_t* queue_dev, uint32_t capacity, uint32_t polarized, const theia_response_t* response,
+                     uint32_t block_size, void* stream) {
+    return theia_hit_replay_rng(queue_dev, capacity, polarized, response, nullptr, block_size, stream);
 }
 
 int theia_tlas_query(const void* tlas_dev, const float* rays_dev, uint32_t n, int32_t* out_dev, float* out_bary_dev,

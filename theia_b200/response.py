@@ -725,8 +725,9 @@ class HitReplay(PipelineStage):
                 raise RuntimeError("HitReplay needs a CUDA device (no CPU fallback)")
             nBlocks = -(self.capacity // -self.blockSize)
             r = self.response._abiResponse(i, nBlocks)
-            _lib.check(_lib.load().theia_hit_replay(
-                self.queue.tensor.data_ptr(), self.capacity, int(self.polarized), byref(r), self.blockSize,
-                _device.currentStream("cuda")))
+            rng = self.rng._abiParams(i) if self.rng is not None else None
+            _lib.check(_lib.load().theia_hit_replay_rng(
+                self.queue.tensor.data_ptr(), self.capacity, int(self.polarized), byref(r),
+                ctypes.addressof(rng) if rng is not None else None, self.blockSize, _device.currentStream("cuda")))
 
         return [*self.queue.run(i), cmd]
