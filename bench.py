@@ -359,28 +359,28 @@ def measure(name: str, args, steps: int, lib, *, detail: bool, batch: int | None
     out["segs"], out["hits"], out["shadow"], out["paths"] = (int(x) for x in counters.cpu().numpy().astype(np.int64))
 
     # ---------------- end to end through the public API, host buffers: ShardedRun (theia_b200/distributed.py), the call a
-    # user of N GPUs makes. A step = one batch per rank: parameter update and launch assembly on the host, tracer,
-    # reduce kernel, device side accumulation, one all-reduce of the light curve (N > 1), D2H of the curve, synchronise.
+    # user of N GPUs makes: ONE run of steps x N batches. Per batch on its rank: parameter update and launch assembly on
+    # the host, tracer, reduce kernel, device side accumulation, D2H of the batch's light curve handed to processFn
+    # (synchronises); at the end one all-reduce of the accumulated curve (N > 1) and its D2H.
     from theia_b200.distributed import ShardedRun, batchOffset
 
     def e2eRun(tracer, nRng, n) -> tuple[float, int]:
-        sharded = ShardedRun(tracer)
+        sharded = ShardedRun(tracer, offset0=batchOffset(0, step * world, nRng, RNG_STRIDE))  # rank r: batches = r mod N
         counters.zero_()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
+        seen = []
         t0 = time.perf_counter()
-        for k in range(n):
-            sharded.offset0 = batchOffset(0, (step + k) * world, nRng, RNG_STRIDE)  # rank r runs batch (step + k) world + r
-            curve = sharded.run(world).lightCurve  # numpy, host
-            assert curve is not None
+        res = sharded.run(n * world, processFn=lambda b, curve: seen.append(float(curve[0])))
         dt = time.perf_counter() - t0
+        assert res.lightCurve is not None and len(seen) == n
         return dt, int(counters.cpu().numpy()[0])
 
     out["e2e_sec"], out["e2e_segs"] = e2eRun(tr, nRNG, steps)
     step += steps
     out["h2d"] = ctypes.sizeof(launch0) + 512  # launch description + parameter blocks -> kernel argument space
-    out["d2h"] = resp.nBins * 8  # the float64 light curve ShardedRun hands back
+    out["d2h"] = resp.nBins * 4  # the batch's light curve (+ once per run the float64 sum over all batches)
 
     # ---------------- per kernel durations, live (CUDA events around every launch inside the library), then one
     # instrumented step for the visit counts of the ray queries

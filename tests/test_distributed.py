@@ -98,6 +98,16 @@ def test_two_ranks_reproduce_the_single_process_run(tmp_path, orc):
     assert single.counters["created"] == N_BATCHES * N_PATHS
 
 
+def test_process_function_sees_every_local_batch(orc):
+    # the per batch hook (the reference's PipelineScheduler processFn): results of each batch on the host, in order,
+    # and their mean is the reduced light curve
+    cfg, run = makeRun()
+    seen = []
+    res = run.run(N_BATCHES, processFn=lambda b, curve: seen.append((b, np.array(curve, dtype=np.float64))))
+    assert [b for b, _ in seen] == list(range(N_BATCHES))
+    assert np.allclose(np.mean([c for _, c in seen], axis=0), res.lightCurve, rtol=1e-6, atol=0.0)
+
+
 def test_two_ranks_reduce_per_object_light_curves(tmp_path, orc):
     # config C5: [module][time] histograms, one all-reduce of the whole array
     cfg, run = makeRun(perObject=True)

@@ -166,15 +166,19 @@ class ShardedRun:
             torch.cuda.current_stream().synchronize()
 
     # ------------------------------------------------------------------ run
-    def run(self, nBatches: int, *, keepHits: bool = False) -> ShardResult:
+    def run(self, nBatches: int, *, keepHits: bool = False, processFn=None) -> ShardResult:
         """``nBatches`` batches of the (first) tracer with its current parameters."""
         name = next(iter(self.tracers))
-        return self.runTasks([(name, {})] * nBatches, keepHits=keepHits)
+        return self.runTasks([(name, {})] * nBatches, keepHits=keepHits, processFn=processFn)
 
-    def runTasks(self, tasks: Iterable, *, keepHits: bool = False) -> ShardResult:
+    def runTasks(self, tasks: Iterable, *, keepHits: bool = False, processFn=None) -> ShardResult:
         """
         Tasks ``(pipeline name, {"stage__param": value, ...})`` - or plain parameter dicts with a single tracer -
         dealt to the ranks round robin (whole tasks: SURVEY.md 8e). Task ``t`` runs at the Philox offset of batch ``t``.
+
+        ``processFn(task index, result of the task's response)``, if given, is called on the rank that ran the task once
+        its result has reached the host (the per batch hook of the reference's ``PipelineScheduler``, pipeline.py:
+        ``processFn(config, batch, args)``); the light curves are still accumulated on the device and reduced once.
         """
         tasks = [t if isinstance(t, tuple) else (next(iter(self.tracers)), t) for t in tasks]
         for name, _ in tasks:
@@ -215,6 +219,9 @@ class ShardedRun:
             resp = tr.response
             if getattr(resp, "nBins", 0):
                 self._accumulate(accs[name], resp, i)
+            if processFn is not None:
+                self._sync()
+                processFn(b, resp.result(i))
             if keepHits and hasattr(resp, "queue"):
                 self._sync()
                 v = resp.queue.view(i)
