@@ -442,6 +442,16 @@ def test_sharded_run_single_rank_matches_oracle(cuda, orc):
     assert res.counters == want.counters
     assert res.counters["created"] == N * nBatches
     assert np.allclose(res.lightCurve, want.lightCurve, rtol=1e-5, atol=1e-12)
+    # per batch hook: handed over one batch behind the launches, in order, each batch's own curve
+    seenG, seenC = [], []
+    nB = 5
+    resG = distributed.ShardedRun(g["tracer"], offset0=11).run(nB, processFn=lambda b, h: seenG.append((b, np.array(h))))
+    distributed.ShardedRun(c["tracer"], offset0=11, launcher=lambda i: H.runOracle(c, i)).run(
+        nB, processFn=lambda b, h: seenC.append((b, np.array(h))))
+    assert [b for b, _ in seenG] == list(range(nB))
+    for (_, hg), (_, hc) in zip(seenG, seenC):
+        assert hc.sum() > 0 and np.allclose(hg, hc, rtol=1e-5, atol=1e-12)
+    assert np.allclose(np.mean([h for _, h in seenG], axis=0), resG.lightCurve, rtol=1e-5)
 
 
 def test_sharded_run_c4_tasks_and_gathered_hits_match_oracle(cuda, orc):

@@ -144,11 +144,12 @@ class ShardedRun:
         nBins = getattr(resp, "nBins", 0)
         return (resp.nObjects, nBins) if hasattr(resp, "nObjects") else (max(nBins, 1),)
 
-    def _launch(self, name: str, i: int) -> None:
+    def _launch(self, name: str, i: int):
+        """runs configuration i; returns the event that marks its completion (None: it has completed)"""
         if self._launchers is not None:
             self._launchers[name](i)
-        else:
-            self._pipelines[name].runAsync(i)
+            return None
+        return self._pipelines[name].runAsync(i)
 
     def _accumulate(self, acc: torch.Tensor, resp, i: int) -> None:
         """adds the light curve of the batch just launched (configuration i) to acc, stream ordered on a GPU"""
@@ -160,6 +161,13 @@ class ShardedRun:
                 acc.add_(resp._buffers[i].to(acc.device, non_blocking=True).view(acc.shape))
         else:
             acc.add_(torch.from_numpy(np.asarray(resp.result(i), dtype=np.float64)).to(acc.device).view(acc.shape))
+
+    @staticmethod
+    def _handOver(pending, processFn) -> None:
+        b, resp, i, done = pending
+        if done is not None:
+            done.synchronize()
+        processFn(b, resp.result(i))
 
     def _sync(self) -> None:
         if self.tracer._device == "cuda":
@@ -203,6 +211,7 @@ class ShardedRun:
                 if hasattr(cb, "reset"):
                     cb.reset()
         mine, n = set(batchesOf(self.rank, self.world, nTasks)), 0
+        pending = None
         for b, (name, params) in enumerate(tasks):
             # parameters persist from task to task like in a PipelineScheduler: every rank applies all of them (host
             # side only) and runs its own tasks, so the result does not depend on the number of ranks
@@ -214,19 +223,27 @@ class ShardedRun:
             i = n & 1
             n += 1
             tr.rng.setParam("offset", batchOffset(self.offset0, b, self._nRNG, self.rngStride))
-            self._launch(name, i)
+            done = self._launch(name, i)
             res.localBatches.append(b)
             resp = tr.response
             if getattr(resp, "nBins", 0):
                 self._accumulate(accs[name], resp, i)
             if processFn is not None:
-                self._sync()
-                processFn(b, resp.result(i))
+                # the batch before this one is handed over now, while this one runs (the two configurations of the
+                # pipeline keep their results apart), so the device does not wait for the host between batches
+                if pending is not None:
+                    self._handOver(pending, processFn)
+                pending = (b, resp, i, done)
+                if done is None:
+                    self._handOver(pending, processFn)
+                    pending = None
             if keepHits and hasattr(resp, "queue"):
                 self._sync()
                 v = resp.queue.view(i)
                 count = min(int(v.count), resp.capacity)
                 res.hits.append({f: np.array(v[f][:count]) for f in v.fields})
+        if pending is not None:
+            self._handOver(pending, processFn)
         self._sync()
         # the one collective of the run: light curves (+ event counters)
         self._allReduce(flat)
