@@ -366,6 +366,8 @@ def measure(name: str, args, steps: int, lib, *, detail: bool, batch: int | None
 
     def e2eRun(tracer, nRng, n) -> tuple[float, int]:
         sharded = ShardedRun(tracer, offset0=batchOffset(0, step * world, nRng, RNG_STRIDE))  # rank r: batches = r mod N
+        sharded.run(2 * world, processFn=lambda b, curve: None)  # untimed: the API path's own first-call costs
+        sharded.offset0 = batchOffset(0, (step + 2) * world, nRng, RNG_STRIDE)
         counters.zero_()
         torch.cuda.synchronize()
         if world > 1:
@@ -378,7 +380,7 @@ def measure(name: str, args, steps: int, lib, *, detail: bool, batch: int | None
         return dt, int(counters.cpu().numpy()[0])
 
     out["e2e_sec"], out["e2e_segs"] = e2eRun(tr, nRNG, steps)
-    step += steps
+    step += steps + 2
     out["h2d"] = ctypes.sizeof(launch0) + 512  # launch description + parameter blocks -> kernel argument space
     out["d2h"] = resp.nBins * 4  # the batch's light curve (+ once per run the float64 sum over all batches)
 
