@@ -3,7 +3,8 @@
 //
 // Pipeline (all on the device, caller supplied result + scratch memory):
 //   1. primitive boxes + centroid bounds          (one thread per primitive)
-//   2. 63 bit Morton codes of the centroids, radix sort (cub::DeviceRadixSort)
+//   2. 63 bit Morton codes of the centroids, own stable LSD radix sort (8 passes of 8 bits: radixCount / radixScan /
+//      radixScatter below)
 //   3. binary radix tree (Karras 2012), one thread per inner node
 //   4. bottom-up box refit with per-node arrival counters
 //      [THEIA_BVH_BUILDER=sah replaces 3 + 4 by a sweep builder: every node range of the Morton
@@ -17,7 +18,6 @@
 //      widest axis, boxes are quantised outwards to 8 bit; breadth first, deterministic
 //      (block-wide prefix sums hand out node / primitive slots)
 //   6. leaf triangles are gathered into 48 byte records in leaf order.
-#include <cub/device/device_radix_sort.cuh>
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstdlib>
@@ -51,19 +51,15 @@ struct BuildScratch {
     int4* work[2];      // [n] each: (node, first, last, -) worklists of the SAH sweep builder
     uint32_t* bounds;   // [8] ordered-int centroid bounds: lo xyz, hi xyz
     uint32_t* info;     // [8] nWide, nPrimOut, depth, overflow
-    void* cubTemp;
-    size_t cubBytes;
+    uint32_t* sortHist;  // [256][sortTiles(n)] digit counts per tile of the radix sort, then their exclusive scan
     size_t total;
 };
 
 static size_t alignUp(size_t v) { return (v + 255) & ~size_t(255); }
 
-static size_t cubTempBytes(uint32_t n) {
-    size_t bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
-                                    (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)n);
-    return bytes;
-}
+#define SORT_THREADS 256u
+#define SORT_ITEMS 16u  // keys per thread and pass: tiles of 4096 keys
+static uint32_t sortTiles(uint32_t n) { return (n + SORT_THREADS * SORT_ITEMS - 1) / (SORT_THREADS * SORT_ITEMS); }
 
 static BuildScratch layoutScratch(void* base, uint32_t n) {
     BuildScratch s;
@@ -88,8 +84,7 @@ static BuildScratch layoutScratch(void* base, uint32_t n) {
     s.work[1] = (int4*)take(sizeof(int4) * m);
     s.bounds = (uint32_t*)take(32);
     s.info = (uint32_t*)take(32);
-    s.cubBytes = cubTempBytes(m);
-    s.cubTemp = take(s.cubBytes);
+    s.sortHist = (uint32_t*)take(4 * 256 * (size_t)sortTiles(m));
     s.total = off;
     return s;
 }
@@ -610,15 +605,114 @@ static int checkCuda(cudaError_t e, const char* what) {
 static uint32_t blocksFor(uint32_t n, uint32_t bs) { return (n + bs - 1) / bs; }
 
 // steps 2-4 for n >= 1 primitives whose boxes are in s.boxLo / s.boxHi; returns the sorted order
+// ------------------------------------------------------------------ radix sort of (Morton key, primitive) pairs
+// Least significant digit first, 8 bits per pass, stable: per pass (1) every tile of 4096 keys counts its digits,
+// (2) one CTA scans the counts in (digit, tile) order, (3) every tile walks its keys again in index order and writes
+// each behind the keys of its digit that come before it: in earlier tiles (scan), earlier rounds of the tile (running
+// base), earlier warps of the round (per warp counts) and lower lanes of the warp (__match_any_sync).
+__global__ void __launch_bounds__(SORT_THREADS) radixCountKernel(const uint64_t* __restrict__ keys, uint32_t n, uint32_t shift,
+                                                                 uint32_t* __restrict__ hist, uint32_t nTiles) {
+    __shared__ uint32_t counts[256];
+    counts[threadIdx.x] = 0u;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * SORT_THREADS * SORT_ITEMS;
+    for (uint32_t r = 0; r < SORT_ITEMS; ++r) {
+        const uint32_t i = base + r * SORT_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&counts[(uint32_t)(keys[i] >> shift) & 0xFFu], 1u);
+    }
+    __syncthreads();
+    hist[threadIdx.x * nTiles + blockIdx.x] = counts[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(1024) radixScanKernel(uint32_t* __restrict__ hist, uint32_t len) {
+    __shared__ uint32_t warpSum[32];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0u;
+    __syncthreads();
+    for (uint32_t base = 0; base < len; base += 1024u) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < len ? hist[i] : 0u;
+        uint32_t incl = v;
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if ((threadIdx.x & 31u) >= (uint32_t)d) incl += o;
+        }
+        if ((threadIdx.x & 31u) == 31u) warpSum[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warpSum[threadIdx.x];
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, w, d);
+                if (threadIdx.x >= (uint32_t)d) w += o;
+            }
+            warpSum[threadIdx.x] = w;  // inclusive over the warps
+        }
+        __syncthreads();
+        const uint32_t before = carry + ((threadIdx.x >> 5) ? warpSum[(threadIdx.x >> 5) - 1] : 0u) + incl - v;
+        if (i < len) hist[i] = before;
+        __syncthreads();
+        if (threadIdx.x == 0) carry += warpSum[31];
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(SORT_THREADS) radixScatterKernel(const uint64_t* __restrict__ keysIn, const uint32_t* __restrict__ valsIn,
+                                                                   uint64_t* __restrict__ keysOut, uint32_t* __restrict__ valsOut,
+                                                                   uint32_t n, uint32_t shift, const uint32_t* __restrict__ hist,
+                                                                   uint32_t nTiles) {
+    __shared__ uint32_t digitBase[256];
+    __shared__ uint32_t warpCount[SORT_THREADS / 32][256];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    digitBase[threadIdx.x] = hist[threadIdx.x * nTiles + blockIdx.x];
+    for (uint32_t w = 0; w < SORT_THREADS / 32; ++w) warpCount[w][threadIdx.x] = 0u;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * SORT_THREADS * SORT_ITEMS;
+    for (uint32_t r = 0; r < SORT_ITEMS; ++r) {
+        const uint32_t i = base + r * SORT_THREADS + threadIdx.x;
+        const bool valid = i < n;
+        uint64_t key = 0;
+        uint32_t val = 0, digit = 0x100u + lane;  // lanes without a key match nobody
+        if (valid) { key = keysIn[i]; val = valsIn[i]; digit = (uint32_t)(key >> shift) & 0xFFu; }
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, digit);
+        const uint32_t rankInWarp = __popc(peers & ((1u << lane) - 1u));
+        if (valid && rankInWarp == 0u) warpCount[warp][digit] = __popc(peers);
+        __syncthreads();
+        if (valid) {
+            uint32_t pos = digitBase[digit] + rankInWarp;
+            for (uint32_t w = 0; w < warp; ++w) pos += warpCount[w][digit];
+            keysOut[pos] = key;
+            valsOut[pos] = val;
+        }
+        __syncthreads();
+        uint32_t sum = 0;
+        for (uint32_t w = 0; w < SORT_THREADS / 32; ++w) { sum += warpCount[w][threadIdx.x]; warpCount[w][threadIdx.x] = 0u; }
+        digitBase[threadIdx.x] += sum;
+        __syncthreads();
+    }
+}
+
+// Sorts n (key, value) pairs by the low 64 bits of the key, stable; the result is back in s.keys / s.vals.
+static int radixSortPairs(BuildScratch& s, uint32_t n, cudaStream_t st) {
+    const uint32_t nTiles = sortTiles(n);
+    uint64_t *kin = s.keys, *kout = s.keysAlt;
+    uint32_t *vin = s.vals, *vout = s.valsAlt;
+    for (uint32_t shift = 0; shift < 64; shift += 8) {
+        radixCountKernel<<<nTiles, SORT_THREADS, 0, st>>>(kin, n, shift, s.sortHist, nTiles);
+        radixScanKernel<<<1, 1024, 0, st>>>(s.sortHist, 256u * nTiles);
+        radixScatterKernel<<<nTiles, SORT_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, s.sortHist, nTiles);
+        uint64_t* tk = kin; kin = kout; kout = tk;
+        uint32_t* tv = vin; vin = vout; vout = tv;
+    }
+    CUDA_OK(cudaGetLastError());
+    return 0;  // eight passes: the sorted pairs are in s.keys / s.vals again
+}
+
 static int buildBinaryTree(BuildScratch& s, uint32_t n, cudaStream_t st, const uint32_t** order) {
     const uint32_t bs = 256;
     mortonKernel<<<blocksFor(n, bs), bs, 0, st>>>(s, n);
-    cub::DoubleBuffer<uint64_t> dk(s.keys, s.keysAlt);
-    cub::DoubleBuffer<uint32_t> dv(s.vals, s.valsAlt);
-    size_t bytes = s.cubBytes;
-    CUDA_OK(cub::DeviceRadixSort::SortPairs(s.cubTemp, bytes, dk, dv, (int)n, 0, 63, st));
-    const uint64_t* keys = dk.Current();
-    *order = dv.Current();
+    if (radixSortPairs(s, n, st)) return -1;
+    const uint64_t* keys = s.keys;
+    *order = s.vals;
     static const bool sweep = getenv("THEIA_BVH_BUILDER") && !strcmp(getenv("THEIA_BVH_BUILDER"), "sah");
     if (!sweep) {
         if (n > 1) radixTreeKernel<<<blocksFor(n - 1, bs), bs, 0, st>>>(s, keys, n);
@@ -627,7 +721,7 @@ static int buildBinaryTree(BuildScratch& s, uint32_t n, cudaStream_t st, const u
         sahTreeKernel<<<1, SWEEP_THREADS, 0, st>>>(s, *order, n);
     }
     CUDA_OK(cudaGetLastError());
-    countLaunches(n > 1 ? 4 : 3);  // morton, sort (>= 1 kernel), radix tree, refit
+    countLaunches(n > 1 ? 27 : 26);  // morton, sort (8 passes of 3 kernels), radix tree, refit
     return 0;
 }
 
