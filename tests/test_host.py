@@ -279,3 +279,71 @@ def test_host_sources_on_the_oracle():
         hits = H.hitView(cfg)
         wl = cfg["tracer"].wavelengthSource.queue.view(0)["wavelength"]
         assert hits.count > 10 and np.all(np.isin(hits["wavelength"], wl))
+
+
+# ------------------------------------------------------------------ tests/test_lookup.py of the reference (host side)
+def _sampleData1D():
+    x = np.linspace(0.0, 1.0, 100)
+    y = np.sin(4 * np.pi * x) * np.exp(-x) + (1.0 - x)
+    grad = -np.exp(-x) * (np.exp(x) + np.sin(4 * np.pi * x) - 4 * np.pi * np.cos(4 * np.pi * x))
+    return np.stack((x, y, grad), axis=-1)
+
+
+def _sampleData2D():
+    x, y = np.meshgrid(np.linspace(0.0, 1.0, 50), np.linspace(0.0, 1.0, 100))
+    x, y = x.flatten(), y.flatten()
+    z = np.sin(2 * np.pi * x) * np.cos(2 * np.pi * y) * (1.0 - y * y) * (1.0 - x * x)
+    return np.stack((x, y, z), axis=-1)
+
+
+def test_sampleTable1D():  # tests/test_lookup.py:20-36
+    from theia_b200 import lookup
+    data = np.array([[0.0, 0.0], [10.0, 10.0]])
+    sample = lookup.sampleTable1D(data, 10).data
+    assert abs(sample.min()) < 1e-5 and abs(sample.max() - 10.0) < 1e-5 and len(sample) == 10
+    sample = lookup.sampleTable1D(data, 10, boundary=(5.0, 8.0)).data
+    assert abs(sample.min() - 5.0) < 1e-5 and abs(sample.max() - 8.0) < 1e-5 and len(sample) == 10
+    sample = lookup.sampleTable1D(_sampleData1D(), 1024).data
+    x = np.linspace(0.0, 1.0, 1024)
+    y = np.sin(4 * np.pi * x) * np.exp(-x) + (1.0 - x)
+    assert np.abs(y - sample).max() < 5e-3
+
+
+def test_sampleTable2D():  # tests/test_lookup.py:117-138
+    from theia_b200 import lookup
+    data_x = np.array([0.0, 0.0, 10.0, 10.0])
+    data_y = np.array([0.0, 10.0, 0.0, 10.0])
+    data = np.stack((data_x, data_y, data_x + data_y), axis=-1)
+    sample = lookup.sampleTable2D(data, 100, 100, boundaries=(None, (3.0, 8.0))).data.flatten()
+    assert sample.size == 100 * 100
+    assert abs(sample[:100].min() - 3) < 1e-5 and abs(sample[:100].max() - 13.0) < 1e-5
+    assert abs(sample[::100].min() - 3.0) < 1e-5 and abs(sample[::100].max() - 8.0) < 1e-5
+    sample = lookup.sampleTable2D(_sampleData2D(), 250, 250, mode="cubic").data.flatten()
+    x, y = np.meshgrid(np.linspace(0.0, 1.0, 250), np.linspace(0.0, 1.0, 250))
+    z = np.sin(2 * np.pi * x) * np.cos(2 * np.pi * y) * (1.0 - y * y) * (1.0 - x * x)
+    assert np.abs(z.flatten() - sample).max() < 5e-3
+
+
+def test_getTableSize():  # tests/test_lookup.py:176-184
+    from theia_b200 import lookup
+    for column in (_sampleData1D()[:, 1], _sampleData2D()[:, 2]):
+        assert lookup.getTableSize(column) == lookup.Table(column).nbytes
+
+
+def test_uploadTables():  # tests/test_lookup.py:187-214
+    from theia_b200 import _device, lookup
+    rng = np.random.default_rng(0xC0FFEE)
+    data = [rng.random((64,)), rng.random((16,)), rng.random((32,))]
+    with _device.useDevice("cpu"):
+        tensor, ptr = lookup.uploadTables(data)
+    tables = [lookup.Table(t) for t in data]
+    expected_ptr = tensor.data_ptr()
+    for t, p in zip(tables, ptr):
+        assert p == expected_ptr
+        expected_ptr += t.nbytes
+    size = sum(t.nbytes for t in tables)
+    expected = np.empty(size, dtype=np.uint8)
+    at = expected.ctypes.data
+    for t in tables:
+        at += t.copy(at)
+    assert np.array_equal(tensor.numpy()[:size], expected)
