@@ -547,6 +547,10 @@ int theia_math_eval(uint32_t fn, const float *x_dev, const float *y_dev, uint32_
  * SIGN_BIT                  x                                   signBit(x)         (sh/math.glsl:18-20)
  * GAMMA [rng, params = alpha, lambda]   -                       sampleGamma        (sh/random.gamma.glsl:9-33)
  * EMISSION_ANGLE [params = n, a, b]     u                       cos_theta          (sh/lightsource.particles.common.glsl:52-97)
+ * MEDIUM [medium | material, params[0] = 0 inside / 1 outside]   wavelength, cos_theta, eta   ->
+ *                           n, vg, mu_s, mu_e, log_phase(cos_theta), phase_sampling(eta), m12, m22, m33, m34(cos_theta),
+ *                           flagsInwards, flagsOutwards (bits; 0 without material)
+ *                           (tests/shader/medium.test.glsl, tests/shader/material.test.glsl)
  * TARGET_SAMPLE [rng, target, params = min3, max3]   -          observer3, direction3, sample {pos3, nrm3, prob, valid, error},
  *                                                               hit {pos3, nrm3, prob, valid, error}, occluded   (29 words)
  * GUIDE_SAMPLE [rng, guide, params = min3, max3]     -          observer3, sample {dir3, dist, prob}, eval {dir3, dist, prob}
@@ -557,7 +561,7 @@ enum theia_unit {
     THEIA_UNIT_SCATTER_DIR = 1, THEIA_UNIT_REFLECTANCE, THEIA_UNIT_VOLUME_SCATTER, THEIA_UNIT_SCATTER_PROB,
     THEIA_UNIT_ROTATE_PHI, THEIA_UNIT_ALIGN_POLREF, THEIA_UNIT_ROTATE_DIR, THEIA_UNIT_PHASE_MATRIX,
     THEIA_UNIT_SURFACE, THEIA_UNIT_SIGN_BIT, THEIA_UNIT_GAMMA, THEIA_UNIT_EMISSION_ANGLE,
-    THEIA_UNIT_TARGET_SAMPLE, THEIA_UNIT_GUIDE_SAMPLE, THEIA_UNIT_LIGHT_SAMPLE, THEIA_UNIT_COUNT
+    THEIA_UNIT_TARGET_SAMPLE, THEIA_UNIT_GUIDE_SAMPLE, THEIA_UNIT_LIGHT_SAMPLE, THEIA_UNIT_MEDIUM, THEIA_UNIT_COUNT
 };
 typedef struct theia_unit_args {
     uint32_t struct_size; /* sizeof(theia_unit_args_t) */

@@ -51,6 +51,7 @@ static inline int unitWidths(uint32_t unit, uint32_t polarized, uint32_t* in, ui
     case THEIA_UNIT_TARGET_SAMPLE: *in = 0; *out = 29; return 0;
     case THEIA_UNIT_GUIDE_SAMPLE: *in = 0; *out = 13; return 0;
     case THEIA_UNIT_LIGHT_SAMPLE: *in = 0; *out = 0; return 0;
+    case THEIA_UNIT_MEDIUM: *in = 3; *out = 12; return 0;
     }
     return -1;
 }
@@ -200,6 +201,26 @@ static inline int unitEval(const theia_unit_args_t& A) {
         case THEIA_UNIT_SIGN_BIT: o[0] = signBit(q[0]); break;
         case THEIA_UNIT_GAMMA: o[0] = sampleGamma(A.params[0], rng) / A.params[1]; break;
         case THEIA_UNIT_EMISSION_ANGLE: o[0] = particle_sampleEmissionAngle(A.params[0], A.params[1], A.params[2], q[0]); break;
+        case THEIA_UNIT_MEDIUM: {  // tests/shader/medium.test.glsl, tests/shader/material.test.glsl
+            uint64_t med = A.medium;
+            o[10] = o[11] = 0.0f;
+            if (A.material != 0) {
+                const MaterialGLSL* mat = reinterpret_cast<const MaterialGLSL*>(A.material);
+                med = A.params[0] == 0.0f ? mat->inside : mat->outside;
+                o[10] = u2f(mat->flagsInwards); o[11] = u2f(mat->flagsOutwards);
+            }
+            const MediumConstants c = lookUpMedium(med, q[0]);
+            const MediumGLSL* m = med ? asMedium(med) : nullptr;
+            const float t = 0.5f * (q[1] + 1.0f);
+            o[0] = c.n; o[1] = c.vg; o[2] = c.mu_s; o[3] = c.mu_e;
+            o[4] = lookUp(m ? m->log_phase : 0, t, 0.0f);
+            o[5] = lookUp(m ? m->phase_sampling : 0, q[2], 0.0f);
+            o[6] = lookUp(m ? m->phase_m12 : 0, t, 0.0f);
+            o[7] = lookUp(m ? m->phase_m22 : 0, t, 0.0f);
+            o[8] = lookUp(m ? m->phase_m33 : 0, t, 0.0f);
+            o[9] = lookUp(m ? m->phase_m34 : 0, t, 0.0f);
+            break;
+        }
         case THEIA_UNIT_TARGET_SAMPLE: {  // sh/target.sample.glsl:62-86
             vec3 observer = sampleObserver(A.params, rng);
             vec3 direction = sampleUnitSphere(rng.next2());

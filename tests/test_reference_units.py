@@ -1184,3 +1184,84 @@ def test_trackAngularEmission_pdf(backend, n, cos_min, cos_max, a, b, beta):  # 
     est = integrate.quad(pdf, cos_min, cos_max, points=points, limit=200)[0]
     assert np.abs(est - 1.0) < 5e-4
     assert np.all(pdf(np.linspace(cos_min, cos_max, 500)) >= 0.0)
+
+
+def test_MediumShader(backend, rng):  # tests/test_material.py:132-214 (tests/shader/medium.test.glsl)
+    from theia_b200 import material
+    N = 32 * 256
+
+    class WaterModel(material.WaterBaseModel, material.HenyeyGreensteinPhaseFunction, material.MediumModel):
+        ModelName = "water"
+
+        def __init__(self) -> None:
+            material.WaterBaseModel.__init__(self, 5.0, 1000.0, 35.0)
+            material.HenyeyGreensteinPhaseFunction.__init__(self, 0.6)
+
+    model = WaterModel()
+    with device(backend):
+        water = model.createMedium()
+        store = material.MaterialStore([], media=[water])
+        dLam = water.lambda_max - water.lambda_min
+        wavelength = ((rng.random(N, np.float32) * dLam + water.lambda_min) * u.nm).astype(np.float32)
+        theta = (1.0 - 2 * rng.random(N, np.float32)).astype(np.float32)  # [-1, 1]
+        eta = rng.random(N, np.float32)  # [0, 1]
+        r = ev(backend, _abi.UNIT_MEDIUM, np.stack([wavelength, theta, eta], axis=-1), medium=store.media["water"])
+    assert np.all(r[:, 10:12].astype(np.float32).view(np.uint32) == 0)  # no material: no flags
+    mu_s = model.scattering_coef(wavelength)
+    assert np.allclose(r[:, 0], model.refractive_index(wavelength), 1e-4)
+    assert np.allclose(r[:, 1], model.group_velocity(wavelength), 1e-4)
+    assert np.allclose(r[:, 2], mu_s, 5e-3)
+    assert np.allclose(r[:, 3], model.absorption_coef(wavelength) + mu_s, 5e-3)
+    assert np.abs(r[:, 4] - model.log_phase_function(theta)).max() < 5e-5
+    assert np.allclose(r[:, 5], model.phase_sampling(eta), 1e-4, 1e-5)
+
+
+def test_MaterialShader(backend, rng):  # tests/test_material.py:217-371 (tests/shader/material.test.glsl)
+    from theia_b200 import material
+    N = 32 * 1000
+
+    class WaterModel(material.WaterBaseModel, material.HenyeyGreensteinPhaseFunction,
+                     material.KokhanovskyOceanWaterPhaseMatrix, material.MediumModel):
+        ModelName = "water"
+
+        def __init__(self) -> None:
+            material.WaterBaseModel.__init__(self, 5.0, 1000.0, 35.0)
+            material.HenyeyGreensteinPhaseFunction.__init__(self, 0.6)
+            material.KokhanovskyOceanWaterPhaseMatrix.__init__(self, p90=0.66, theta0=0.25, alpha=4.0, xi=25.6)
+
+    water_model, glass_model = WaterModel(), material.BK7Model()
+    lam = ((rng.random(N, np.float32) * 600.0 + 200.0) * u.nm).astype(np.float32)
+    theta = (1.0 - 2 * rng.random(N, np.float32)).astype(np.float32)
+    eta = rng.random(N, np.float32)
+    rows = np.stack([lam, theta, eta], axis=-1)
+    with device(backend):
+        water = water_model.createMedium()
+        glass = glass_model.createMedium(name="glass", num_lambda=4096)
+        mat_vac_glass = material.Material("vac_glass", None, glass)
+        store = material.MaterialStore([material.Material("water_glass", water, glass), mat_vac_glass])
+        h = N // 2
+        res = {(name, side): ev(backend, _abi.UNIT_MEDIUM, rows[sl], material=store.material[name], params=(side,))
+               for name, sl in (("water_glass", slice(0, h)), ("vac_glass", slice(h, N))) for side in (0, 1)}
+
+    def check(r, model, sl, vacuum=False):
+        zeros = np.zeros(h)
+        n = np.ones(h) if vacuum else model.refractive_index(lam[sl])
+        vg = np.full(h, 1.0 * u.c) if vacuum else model.group_velocity(lam[sl])
+        volume = isinstance(model, WaterModel)  # glass and vacuum do not (volume) scatter
+        mu_s = model.scattering_coef(lam[sl]) if volume else zeros
+        mu_e = mu_s + (zeros if vacuum else model.absorption_coef(lam[sl]))
+        assert np.allclose(r[:, 0], n, 1e-4) and np.allclose(r[:, 1], vg, 1e-4)
+        assert np.allclose(np.exp(-r[:, 2]), np.exp(-mu_s), 1e-5, 1e-3)
+        assert np.allclose(np.exp(-r[:, 3]), np.exp(-mu_e), 1e-5, 1e-3)
+        assert np.abs(r[:, 4] - (model.log_phase_function(theta[sl]) if volume else zeros)).max() < 5e-4
+        assert np.allclose(r[:, 5], model.phase_sampling(eta[sl]) if volume else zeros, 1e-4, 1e-5)
+        for col, fn in ((6, "phase_m12"), (7, "phase_m22"), (8, "phase_m33")):
+            assert np.abs(r[:, col] - (getattr(model, fn)(theta[sl]) if volume else zeros)).max() < 1e-3, fn
+        assert np.abs(r[:, 9]).max() < 1e-3  # no m34 for water
+
+    check(res[("water_glass", 0)], water_model, slice(0, h))
+    check(res[("water_glass", 1)], glass_model, slice(0, h))
+    check(res[("vac_glass", 0)], None, slice(h, N), vacuum=True)
+    check(res[("vac_glass", 1)], glass_model, slice(h, N))
+    flags = res[("vac_glass", 0)][0, 10:12].astype(np.float32).view(np.uint32)
+    assert flags[0] == mat_vac_glass.flagsInward and flags[1] == mat_vac_glass.flagsOutward

@@ -132,7 +132,7 @@ class InstanceDesc(Structure):
 # unit seam (theia_unit_eval)
 (UNIT_SCATTER_DIR, UNIT_REFLECTANCE, UNIT_VOLUME_SCATTER, UNIT_SCATTER_PROB, UNIT_ROTATE_PHI, UNIT_ALIGN_POLREF,
  UNIT_ROTATE_DIR, UNIT_PHASE_MATRIX, UNIT_SURFACE, UNIT_SIGN_BIT, UNIT_GAMMA, UNIT_EMISSION_ANGLE,
- UNIT_TARGET_SAMPLE, UNIT_GUIDE_SAMPLE, UNIT_LIGHT_SAMPLE) = range(1, 16)
+ UNIT_TARGET_SAMPLE, UNIT_GUIDE_SAMPLE, UNIT_LIGHT_SAMPLE, UNIT_MEDIUM) = range(1, 17)
 
 
 class UnitArgs(Structure):

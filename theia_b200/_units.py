@@ -23,6 +23,7 @@ WIDTHS = {
     _abi.UNIT_ROTATE_DIR: (12, 7), _abi.UNIT_PHASE_MATRIX: (5, 4), _abi.UNIT_SURFACE: (0, 33),
     _abi.UNIT_SIGN_BIT: (1, 1), _abi.UNIT_GAMMA: (0, 1), _abi.UNIT_EMISSION_ANGLE: (1, 1),
     _abi.UNIT_TARGET_SAMPLE: (0, 29), _abi.UNIT_GUIDE_SAMPLE: (0, 13), _abi.UNIT_LIGHT_SAMPLE: (0, 0),
+    _abi.UNIT_MEDIUM: (3, 12),
 }
 
 

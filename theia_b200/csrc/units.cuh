@@ -42,6 +42,7 @@ __host__ __device__ inline int unitWidths(uint32_t unit, uint32_t* in, uint32_t*
     case THEIA_UNIT_TARGET_SAMPLE: *in = 0; *out = 29; return 0;
     case THEIA_UNIT_GUIDE_SAMPLE: *in = 0; *out = 13; return 0;
     case THEIA_UNIT_LIGHT_SAMPLE: *in = 0; *out = 0; return 0;
+    case THEIA_UNIT_MEDIUM: *in = 3; *out = 12; return 0;
     }
     return -1;
 }
@@ -208,6 +209,25 @@ __global__ void __launch_bounds__(128) unitEvalKernel(const __grid_constant__ Un
     case THEIA_UNIT_SIGN_BIT: o[0] = signBit(q[0]); break;
     case THEIA_UNIT_GAMMA: o[0] = sampleGamma(A.params[0], rng) / A.params[1]; break;
     case THEIA_UNIT_EMISSION_ANGLE: o[0] = particle_sampleEmissionAngle(A.params[0], A.params[1], A.params[2], q[0]); break;
+    case THEIA_UNIT_MEDIUM: {  // tests/shader/medium.test.glsl, tests/shader/material.test.glsl
+        // the medium itself, or with a material its inside (params[0] == 0) / outside medium and the flag words
+        uint64_t med = A.medium;
+        o[10] = o[11] = 0.0f;
+        if (A.material != 0) {
+            med = ldp(A.material, A.params[0] == 0.0f ? MAT_INSIDE : MAT_OUTSIDE);
+            o[10] = u2f(ldu(A.material, MAT_FLAGS_IN)); o[11] = u2f(ldu(A.material, MAT_FLAGS_OUT));
+        }
+        const MediumConstants c = lookUpMedium(med, q[0]);
+        const float t = 0.5f * (q[1] + 1.0f);
+        o[0] = c.n; o[1] = c.vg; o[2] = c.mu_s; o[3] = c.mu_e;
+        o[4] = lookUp(med ? ldp(med, MED_LOG_PHASE) : 0, t, 0.0f);
+        o[5] = lookUp(med ? ldp(med, MED_PHASE_SAMPLING) : 0, q[2], 0.0f);
+        o[6] = lookUp(med ? ldp(med, MED_M12) : 0, t, 0.0f);
+        o[7] = lookUp(med ? ldp(med, MED_M22) : 0, t, 0.0f);
+        o[8] = lookUp(med ? ldp(med, MED_M33) : 0, t, 0.0f);
+        o[9] = lookUp(med ? ldp(med, MED_M34) : 0, t, 0.0f);
+        break;
+    }
     case THEIA_UNIT_TARGET_SAMPLE: {  // sh/target.sample.glsl:62-86
         vec3 observer = sampleObserver(A.params, rng);
         vec3 direction = sampleUnitSphere(rng.next2());
