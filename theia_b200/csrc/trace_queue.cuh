@@ -6,10 +6,11 @@
 // the node tests of the others. Here the two kinds of work are decoupled:
 //
 //   * a lane owns a ray and walks its stack: per round ONE node step (pop, slab test of the eight
-//     children, push). Leaves are not tested by the owner: their triangles go as items
-//     (owner lane, triangle) into a ring shared by the warp, and the lane carries on with its stack;
-//   * whenever the ring holds a full warp of items, all 32 lanes test one triangle each, whichever
-//     ray it belongs to: the owner's sheared ray (watertight test, bvh.cuh) lives in shared memory,
+//     children, push). Leaves are not tested by the owner: they go as items (owner lane, number of
+//     triangles, first triangle) into a ring shared by the warp, and the lane carries on with its stack;
+//   * whenever the ring holds a full warp of items, they are expanded into triangle slots and all 32 lanes
+//     test one triangle each, whichever ray it belongs to: the owner's sheared ray (watertight test,
+//     bvh.cuh) lives in shared memory,
 //     the result goes back with one 64 bit shared-memory atomicMin per hit on
 //     (t bits << 32 | instance * keyStride + primitive), which is exactly the closest-hit rule of
 //     the ray query (ties in t to the lower (instance, primitive)), in any order;
@@ -21,6 +22,8 @@
 // A lane may only enter the next instance once its items of the current one are done (the sheared
 // ray is per instance); such lanes, and lanes waiting for their last items, trigger a flush of a
 // partially filled ring once there are `flushWaiting` of them.
+// One warp per CTA (the queue sits at a fixed shared memory address), 28 CTAs per SM; the bottom of every lane's stack
+// lives in shared memory, too. Shadow rays are traced against the instances of the target first (targetId).
 #pragma once
 #include "traverse.cuh"
 #include "launch.cuh"
