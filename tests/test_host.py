@@ -347,3 +347,40 @@ def test_uploadTables():  # tests/test_lookup.py:187-214
     for t in tables:
         at += t.copy(at)
     assert np.array_equal(tensor.numpy()[:size], expected)
+
+
+def test_tracerReportsConfig():  # tests/test_trace.py:22-79
+    from theia_b200 import _device, light, random, response, target, trace
+    batchSize, batchSize2, capacity, polarized = 64 * 1024, 96 * 1024, 128 * 1024, True
+
+    class MockResponse(response.EmptyResponse):
+        def __init__(self) -> None:
+            super().__init__()
+            self.prepareConfig = None
+            self.updatedConfig = None
+
+        def prepare(self, config):
+            self.prepareConfig = config
+
+        def updateConfig(self, config):
+            self.updatedConfig = config
+
+    with _device.useDevice("cpu"):
+        resp = MockResponse()
+        tracer = trace.VolumeForwardTracer(batchSize, light.SphericalLightSource(), target.SphereTarget(),
+                                           light.ConstWavelengthSource(), resp, rng=random.PhiloxRNG(key=0xABBA), medium=0,
+                                           capacity=capacity, polarized=polarized)
+        c = resp.prepareConfig
+        assert c is not None
+        assert (c.batchSize, c.blockSize, c.capacity) == (batchSize, tracer.blockSize, capacity)
+        assert c.maxHitsPerThread == tracer.maxHitsPerThread
+        assert c.normalization == tracer.normalization == 1.0 / batchSize
+        assert c.polarized == polarized
+        tracer.batchSize = batchSize2
+        tracer.update(0)
+        c = resp.updatedConfig
+        assert c is not None
+        assert (c.batchSize, c.blockSize, c.capacity) == (batchSize2, tracer.blockSize, capacity)
+        assert c.maxHitsPerThread == tracer.maxHitsPerThread
+        assert c.normalization == tracer.normalization == 1.0 / batchSize2
+        assert c.polarized == polarized
