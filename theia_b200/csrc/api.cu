@@ -463,8 +463,17 @@ static int plan(const theia_trace_launch_t* L, const DeviceLaunch& D, KernelPlan
         // the lean build of the kernel serves the components of the first round (see FULL in components.cuh)
         const bool lean = D.light.kind <= THEIA_LIGHT_MUON && D.wavelength.kind <= THEIA_WAVELENGTH_UNIFORM &&
                           D.target.kind <= THEIA_TARGET_INNER_SPHERE && D.response.kind <= THEIA_RESPONSE_HISTOGRAM;
-        if (lean) K.fn = pol ? (const void*)volumeForwardKernel<true, false> : (const void*)volumeForwardKernel<false, false>;
-        else K.fn = pol ? (const void*)volumeForwardKernel<true, true> : (const void*)volumeForwardKernel<false, true>;
+        if (lean) {
+            const bool hist = D.response.kind == THEIA_RESPONSE_HISTOGRAM, nocb = D.callback.kind == THEIA_CALLBACK_EMPTY;
+            static const void* const table[2][4] = {
+                {(const void*)volumeForwardKernel<false, false, false, false>, (const void*)volumeForwardKernel<false, false, false, true>,
+                 (const void*)volumeForwardKernel<false, false, true, false>, (const void*)volumeForwardKernel<false, false, true, true>},
+                {(const void*)volumeForwardKernel<true, false, false, false>, (const void*)volumeForwardKernel<true, false, false, true>,
+                 (const void*)volumeForwardKernel<true, false, true, false>, (const void*)volumeForwardKernel<true, false, true, true>}};
+            K.fn = table[pol ? 1 : 0][(hist ? 2 : 0) | (nocb ? 1 : 0)];
+        } else {
+            K.fn = pol ? (const void*)volumeForwardKernel<true, true> : (const void*)volumeForwardKernel<false, true>;
+        }
     } else if (L->tracer == THEIA_TRACER_VOLUME_PHOTON) {
         K.fn = pol ? (const void*)volumePhotonKernel<true> : (const void*)volumePhotonKernel<false>;
     } else {

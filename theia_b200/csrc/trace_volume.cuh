@@ -41,7 +41,9 @@ TDEV bool volumeCreateResponse(const DeviceLaunch& P, Ray ray, const TargetSampl
 #ifndef THEIA_VOLUME_CTAS
 #define THEIA_VOLUME_CTAS 6
 #endif
-template <bool POL, bool FULL>
+// HIST / NOCB: the response is the plain histogram / there is no callback, known at compile time (lean launches of the
+// BASELINE configurations get those instantiations, like the shading kernels of the scene tracer: VK_* in wavefront.cuh)
+template <bool POL, bool FULL, bool HIST = false, bool NOCB = false>
 __global__ void __launch_bounds__(128, THEIA_VOLUME_CTAS) volumeForwardKernel(const __grid_constant__ DeviceLaunch P) {
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
@@ -104,10 +106,10 @@ __global__ void __launch_bounds__(128, THEIA_VOLUME_CTAS) volumeForwardKernel(co
         } else if (alive) {
             scatterRay<POL>(ray, rng.next2());
         }
-        onEvent<POL>(P.callback, &sh, created, ray, THEIA_RESULT_RAY_CREATED, k, 0);
-        onEvent<POL>(P.callback, &sh, aborted, ray, THEIA_ERROR_TRACE_ABORT, k, 0);
+        onEvent<POL, NOCB>(P.callback, &sh, created, ray, THEIA_RESULT_RAY_CREATED, k, 0);
+        onEvent<POL, NOCB>(P.callback, &sh, aborted, ray, THEIA_ERROR_TRACE_ABORT, k, 0);
         if (aborted) alive = false;
-        has = commitHit<FULL>(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
+        has = commitHit<FULL, HIST>(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
 
         // ---- stage 2: trace (:153-208)
@@ -155,15 +157,15 @@ __global__ void __launch_bounds__(128, THEIA_VOLUME_CTAS) volumeForwardKernel(co
             float wPhase = pPP * pPP / (pPP * pPP + pTP * pTP);
             has = volumeCreateResponse<POL, FULL>(P, ray, phaseHit, dirPhase, wPhase, true, item);
         }
-        has = commitHit<FULL>(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
+        has = commitHit<FULL, HIST>(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
         hitSeq += has ? 1u : 0u;
         // ---- stage 4: MIS, target sample
         has = false;
         if (wantMIS) has = volumeCreateResponse<POL, FULL>(P, ray, targetHit, dirTarget, wTarget, true, item);
-        has = commitHit<FULL>(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
+        has = commitHit<FULL, HIST>(P.response, hist, has, item, idx, seg | (hitSeq << 16), nResponses, responseDraw<FULL>(P.response, rng, has, item));
 
         // ---- events and path bookkeeping (:254-275)
-        onEvent<POL>(P.callback, &sh, alive, ray, result, k, seg + 1);
+        onEvent<POL, NOCB>(P.callback, &sh, alive, ray, result, k, seg + 1);
         bool maxIter = false;
         if (alive) {
             if (result < 0) {
@@ -175,7 +177,7 @@ __global__ void __launch_bounds__(128, THEIA_VOLUME_CTAS) volumeForwardKernel(co
                 seg++;
             }
         }
-        onEvent<POL>(P.callback, &sh, maxIter, ray, THEIA_RESULT_MAX_ITER, k, lastSeg + 2);
+        onEvent<POL, NOCB>(P.callback, &sh, maxIter, ray, THEIA_RESULT_MAX_ITER, k, lastSeg + 2);
     }
     sinkFinish(P, &sh, sharedHist, nSegments, nResponses, 0, nPaths);
 }
