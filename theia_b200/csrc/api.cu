@@ -471,6 +471,14 @@ static int plan(const theia_trace_launch_t* L, const DeviceLaunch& D, KernelPlan
                 {(const void*)volumeForwardKernel<true, false, false, false>, (const void*)volumeForwardKernel<true, false, false, true>,
                  (const void*)volumeForwardKernel<true, false, true, false>, (const void*)volumeForwardKernel<true, false, true, true>}};
             K.fn = table[pol ? 1 : 0][(hist ? 2 : 0) | (nocb ? 1 : 0)];
+            if (hist && nocb) {  // and the light source, too, for the shape of the BASELINE configurations
+                if (D.light.kind == THEIA_LIGHT_SPHERICAL)
+                    K.fn = pol ? (const void*)volumeForwardKernel<true, false, true, true, THEIA_LIGHT_SPHERICAL>
+                               : (const void*)volumeForwardKernel<false, false, true, true, THEIA_LIGHT_SPHERICAL>;
+                else if (D.light.kind == THEIA_LIGHT_CONE)
+                    K.fn = pol ? (const void*)volumeForwardKernel<true, false, true, true, THEIA_LIGHT_CONE>
+                               : (const void*)volumeForwardKernel<false, false, true, true, THEIA_LIGHT_CONE>;
+            }
         } else {
             K.fn = pol ? (const void*)volumeForwardKernel<true, true> : (const void*)volumeForwardKernel<false, true>;
         }
@@ -521,7 +529,13 @@ static WavefrontKernels wavefrontKernelsOf(const DeviceLaunch& D) {
     static const void* const shadow[4] = {
         shadowFn<POL, VK_GUIDE>(), shadowFn<POL, VK_GUIDE | VK_NOCB>(), shadowFn<POL, VK_GUIDE | VK_HIST>(),
         shadowFn<POL, VK_GUIDE | VK_HIST | VK_NOCB>()};
-    return {(const void*)wfGenerateKernel<POL, false>, shade[key], shadow[key & 3u]};
+    const void* gen = nocb ? (const void*)wfGenerateKernel<POL, false, true> : (const void*)wfGenerateKernel<POL, false>;
+    if (nocb) {
+        if (D.light.kind == THEIA_LIGHT_SPHERICAL) gen = (const void*)wfGenerateKernel<POL, false, true, THEIA_LIGHT_SPHERICAL>;
+        else if (D.light.kind == THEIA_LIGHT_CONE) gen = (const void*)wfGenerateKernel<POL, false, true, THEIA_LIGHT_CONE>;
+        else if (D.light.kind == THEIA_LIGHT_CASCADE) gen = (const void*)wfGenerateKernel<POL, false, true, THEIA_LIGHT_CASCADE>;
+    }
+    return {gen, shade[key], shadow[key & 3u]};
 }
 static WavefrontKernels wavefrontKernels(bool pol, const DeviceLaunch& D) {
     return pol ? wavefrontKernelsOf<true>(D) : wavefrontKernelsOf<false>(D);

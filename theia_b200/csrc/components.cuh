@@ -190,10 +190,12 @@ static __device__ __noinline__ SourceRay cherenkovSample(const LightSel& c, floa
 }
 
 // ------------------------------------------------------------------ light sources (forward)
-template <bool POL, bool FULL = true>
+// KIND >= 0: the kind of the light source is known at compile time (the kernels of the BASELINE configurations are
+// instantiated per light source; the others decide at run time)
+template <bool POL, bool FULL = true, int KIND = -1>
 TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants medium, Rng& rng,
                            PreGamma pre = PreGamma{false, 0.0f, 0u}) {
-    switch (c.kind) {
+    switch (KIND >= 0 ? (uint32_t)KIND : (uint32_t)c.kind) {
     case THEIA_LIGHT_SPHERICAL: {  // sh/lightsource.spherical.glsl:16-34
         const theia_light_spherical_t& p = c.p.spherical;
         vec3 rayDir = sampleUnitSphere(rng.next2());
@@ -283,12 +285,12 @@ TDEV SourceRay sampleLight(const LightSel& c, float wavelength, MediumConstants 
 }
 
 // sh/tracer.volume.forward.glsl:223-229, sh/tracer.scene.forward.glsl:50-56
-template <bool POL, bool FULL = true>
+template <bool POL, bool FULL = true, int KIND = -1>
 TDEV Ray sampleRay(const WavelengthSel& wl, const LightSel& light, uint64_t medium, Rng& rng,
                    PreGamma pre = PreGamma{false, 0.0f, 0u}) {
     WavelengthSample photon = sampleWavelength<FULL>(wl, rng);
     MediumConstants constants = lookUpMedium(medium, photon.wavelength);
-    SourceRay lightRay = sampleLight<POL, FULL>(light, photon.wavelength, constants, rng, pre);
+    SourceRay lightRay = sampleLight<POL, FULL, KIND>(light, photon.wavelength, constants, rng, pre);
     return createRay(lightRay, medium, constants, photon);
 }
 

@@ -43,7 +43,7 @@ TDEV bool volumeCreateResponse(const DeviceLaunch& P, Ray ray, const TargetSampl
 #endif
 // HIST / NOCB: the response is the plain histogram / there is no callback, known at compile time (lean launches of the
 // BASELINE configurations get those instantiations, like the shading kernels of the scene tracer: VK_* in wavefront.cuh)
-template <bool POL, bool FULL, bool HIST = false, bool NOCB = false>
+template <bool POL, bool FULL, bool HIST = false, bool NOCB = false, int LIGHT = -1>
 __global__ void __launch_bounds__(128, THEIA_VOLUME_CTAS) volumeForwardKernel(const __grid_constant__ DeviceLaunch P) {
     extern __shared__ float sharedHist[];
     __shared__ SinkShared sh;
@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(128, THEIA_VOLUME_CTAS) volumeForwardKernel(co
         bool aborted = false;
         if (created) {
             rng = makeRng(&P.rng, idx);
-            ray = sampleRay<POL, FULL>(P.wavelength, P.light, P.medium, rng);
+            ray = sampleRay<POL, FULL, LIGHT>(P.wavelength, P.light, P.medium, rng);
             nPaths++;
             aborted = isOccludedByTarget<FULL>(P.target, ray.position);
             if (!aborted && MIS && DIRECT) {

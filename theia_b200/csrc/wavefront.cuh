@@ -595,12 +595,13 @@ TDEV void pregenerateGamma(const DeviceLaunch& P, const Workspace& ws, uint32_t 
 }
 
 // generate: sh/tracer.scene.forward.glsl:50-66. Each warp owns a contiguous range of paths.
-template <bool POL, bool FULL>
+// NOCB: no callback; LIGHT >= 0: kind of the light source, both known at compile time (lean launches only)
+template <bool POL, bool FULL, bool NOCB = false, int LIGHT = -1>
 __global__ void __launch_bounds__(128, THEIA_GEN_CTAS) wfGenerateKernel(const __grid_constant__ DeviceLaunch P, const Workspace ws) {
     __shared__ SinkShared sh;
     sinkInit(P, &sh, nullptr);
     const bool GUIDE = P.guide.kind != THEIA_GUIDE_NONE;
-    const bool PREGAMMA = P.light.kind == THEIA_LIGHT_CASCADE;
+    const bool PREGAMMA = LIGHT >= 0 ? LIGHT == (int)THEIA_LIGHT_CASCADE : P.light.kind == THEIA_LIGHT_CASCADE;
     const uint32_t warpsPerCta = blockDim.x >> 5, nWarps = gridDim.x * warpsPerCta;
     const uint32_t warp = blockIdx.x * warpsPerCta + (threadIdx.x >> 5);
     const uint32_t perWarp = ((P.batch_size + nWarps - 1) / nWarps + 31u) & ~31u;
@@ -619,14 +620,14 @@ __global__ void __launch_bounds__(128, THEIA_GEN_CTAS) wfGenerateKernel(const __
         if (active) {
             PreGamma pre = {false, 0.0f, 0u};
             if (PREGAMMA) pre = {true, u2f(ws.state[1][WF_PX * (size_t)ws.capacity + k]), ws.state[1][WF_DIM * (size_t)ws.capacity + k]};
-            ray = sampleRay<POL, FULL>(P.wavelength, P.light, P.medium, rng, pre);
+            ray = sampleRay<POL, FULL, LIGHT>(P.wavelength, P.light, P.medium, rng, pre);
             if (FULL && P.photon) { ray.lin_contrib = 1.0f; ray.log_contrib = 0.0f; }  // sh/tracer.scene.photon.init.glsl:50-54
             nPaths++;
             nSegments++;
         }
-        onEvent<POL>(P.callback, &sh, active, ray, THEIA_RESULT_RAY_CREATED, k, 0);
+        onEvent<POL, NOCB>(P.callback, &sh, active, ray, THEIA_RESULT_RAY_CREATED, k, 0);
         const bool ok = active && !isRayBad(ray);
-        onEvent<POL>(P.callback, &sh, active && !ok, ray, THEIA_ERROR_RAY_BAD, k, 1);
+        onEvent<POL, NOCB>(P.callback, &sh, active && !ok, ray, THEIA_ERROR_RAY_BAD, k, 1);
         const uint32_t j = denseAlloc(ws.cntOut, ok);
         if (ok) {
             bool mis;
