@@ -58,6 +58,23 @@ def test_philox_stream_bit_exact(cuda, orc, key, offset):
     assert got.min() >= 0.0 and got.max() < 1.0
 
 
+@pytest.mark.parametrize("sampleDim", [1, 2])
+def test_rngSink(cuda, orc, sampleDim):
+    # tests/test_random.py:36-64 of the reference: 250 streams x 800 samples from stream 12 / draw 316 on
+    from theia_b200 import pipeline as pl
+    from theia_b200.random import PhiloxRNG, RNGBufferSink
+    with _device.useDevice("cuda"):
+        rng = PhiloxRNG(key=0xC0FFEE, offset=77)
+        sink = RNGBufferSink(rng, 250, 800, baseStream=12, baseCount=316, sampleDim=sampleDim)
+        pl.runPipeline([rng, sink])
+        torch.cuda.synchronize()
+        got = sink.tensor.cpu().numpy().reshape(sink.shape)
+    want = orc.philoxFill(0xC0FFEE, 77, 250, 800, baseStream=12, baseCount=316, dim=sampleDim).reshape(sink.shape)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    if sampleDim == 2:  # random2D_s(stream, i) = (draw i, draw i + 1)
+        assert np.array_equal(got[:, 1:, 0], got[:, :-1, 1])
+
+
 def test_philox_uniformity(cuda):
     # the reference's own pin (tests/test_random.py:67-81): 20 bins, max deviation < 0.5 %
     lib = _lib.load()

@@ -88,6 +88,34 @@ def test_rng_sink_layout(orc):
     assert np.array_equal(b[2][:, 0], d[:8]) and np.array_equal(b[2][:, 1], d[1:])
 
 
+def test_rng_sink_bases(orc):
+    # tests/test_random.py:36-64 of the reference (sizes and bases of test_rngSink / test_rngSink_2D): element [s, c] is
+    # draw baseCount + c of stream baseStream + s. The reference checks this with a debug generator that returns
+    # 10000 stream + i; generators are kinds here, so the pin is the Philox stream mapping restated with Python integers.
+    a = orc.philoxFill(0xC0FFEE, 77, 250, 800, baseStream=12, baseCount=316)
+    assert a.shape == (250, 800)
+    for s in (0, 17, 249):
+        assert np.array_equal(a[s], theiaDraws(0xC0FFEE, 77, 12 + s, 316, 800))
+    b = orc.philoxFill(0xC0FFEE, 77, 250, 800, baseStream=12, baseCount=316, dim=2)
+    assert b.shape == (250, 800, 2)
+    for s in (0, 249):
+        d = theiaDraws(0xC0FFEE, 77, 12 + s, 316, 801)
+        assert np.array_equal(b[s][:, 0], d[:800]) and np.array_equal(b[s][:, 1], d[1:])
+
+
+def test_counter_and_key_words_round_trip():
+    # tests/test_random.py:125-127 (uvec4 <-> int): the 128 bit offset and the 64 bit key as little endian words
+    from theia_b200.random import Counter, Key
+    c = Counter()
+    c.value = 0xC0110FFC0FFEE
+    assert c.value == 0xC0110FFC0FFEE and list(c.word) == [0xFFC0FFEE, 0xC0110, 0, 0]
+    c.value = (1 << 128) - 3
+    assert c.value == (1 << 128) - 3 and list(c.word) == [0xFFFFFFFD, 0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF]
+    k = Key()
+    k.value = 0x0123456789ABCDEF
+    assert (k.lo, k.hi, k.value) == (0x89ABCDEF, 0x01234567, 0x0123456789ABCDEF)
+
+
 def test_uniformity_reference_pin(orc):
     # tests/test_random.py:67-81 of the reference: 20 bins, max deviation < 0.5 %
     u = orc.philoxFill(0xC0FFEE, 0, 4096, 2048).reshape(-1)
